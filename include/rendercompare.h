@@ -1,0 +1,215 @@
+/*
+ * rendercompare.h -- C ABI of librendercompare.so (sm_100a).
+ *
+ * Drop-in boundary for the render-and-compare data path of DeepIM
+ * (reference: wangg12/mx-DeepIM).  Every entry point is `extern "C"`, takes
+ * plain pointers and sizes, and (except the host-pointer drop-in `_flow`)
+ * returns an int status.  "dev" entry points take DEVICE pointers plus a
+ * CUDA stream handle (cudaStream_t passed as void*; NULL = legacy default
+ * stream); they never allocate, never synchronise and never touch the host.
+ *
+ * Each declaration cites the reference interface it replaces (paths relative
+ * to the reference root).
+ */
+#ifndef RENDERCOMPARE_H_
+#define RENDERCOMPARE_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ------------------------------------------------------------------ status */
+#define RC_OK 0
+#define RC_ERR_INVALID_ARG 1  /* null pointer, negative size, bad enum        */
+#define RC_ERR_CUDA 2         /* a CUDA runtime call failed; see rc_last_cuda_error */
+#define RC_ERR_UNALIGNED 3    /* pointer/width not aligned as the entry point requires */
+#define RC_ERR_CAPACITY 4     /* a caller-sized workspace or handle table is too small */
+
+int rc_version(void);                      /* ABI version, currently 1                */
+const char *rc_status_string(int status);  /* static string for an RC_* code          */
+const char *rc_last_cuda_error(void);      /* cudaGetErrorString of the last failure  */
+int rc_device_sm_count(int device_id, int *sm_count);
+
+/* ---------------------------------------------------------------- GT flow
+ * Replaces lib/flow_c/gpu_flow_kernel.cu:32-69 (flow_kernel) and :82-148
+ * (_flow); bound by lib/flow_c/gpu_flow.pyx:12-16,24-41.
+ *
+ * Layouts (all float32, C-contiguous):
+ *   depth_src [B,1,H,W]  rendered depth (metres, 0 = background)
+ *   depth_tgt [B,1,H,W]  observed depth
+ *   KT        [B,3,4]    K * [R_rel | t_rel]
+ *   Kinv      [3,3]
+ *   flow      [B,2,H,W]  channel 0 = delta-row, channel 1 = delta-col
+ *   valid     [B,1,H,W]  1.0 where the z-test passed, else 0.0
+ */
+
+/* Same signature and HOST-pointer contract as the reference's `_flow`
+ * (lib/flow_c/gpu_flow.hpp:1-3): blocking, selects `device_id`, outputs are
+ * fully overwritten.  Like the reference it has no return value; unlike the
+ * reference a CUDA failure is recorded (rc_last_status) instead of printed. */
+void _flow(float *flow, float *valid, float *depth_src, float *depth_tgt,
+           float *KT, float *Kinv, int batch_size, int height, int width,
+           int device_id);
+int rc_last_status(void);
+
+/* Same work, status-returning.  Uses an internal per-device staging arena
+ * that grows monotonically (no per-call cudaMalloc/cudaFree). */
+int rc_flow_host(float *flow, float *valid, const float *depth_src,
+                 const float *depth_tgt, const float *KT, const float *Kinv,
+                 int batch_size, int height, int width, int device_id);
+
+/* Device-pointer fast path.  Requires W % 4 == 0 and 16-byte aligned planes. */
+int rc_flow_dev(const float *depth_src, const float *depth_tgt, const float *KT,
+                const float *Kinv, float *flow, float *valid, int batch_size,
+                int height, int width, void *stream);
+
+/* --------------------------------------------------------------- zoom ops
+ * Replace the MXNet CustomOps in deepim/operator_py (zoom_mask.py,
+ * zoom_image.py, zoom_image_with_factor.py, zoom_depth.py, zoom_flow.py,
+ * zoom_mask_with_factor.py, zoom_trans.py) together with the MXNet built-ins
+ * they call (GridGenerator(affine) + BilinearSampler).
+ */
+
+/* Crop box + zoom factor.  Replaces the per-sample host block
+ * deepim/operator_py/zoom_mask.py:36-119 (mode RC_ZF_MASK) and
+ * deepim/operator_py/zoom_image.py:30-118 (mode RC_ZF_IMAGE).
+ *
+ *   obs, rend   [B,C,H,W] the two inputs the bbox is taken from
+ *               RC_ZF_MASK : obs = mask_gt_observed, rend = mask_rendered;
+ *                            pixel valid iff sum_c obs > 0.3, resp.
+ *                            sum_c (rend > 0.2 ? 1 : 0) > 0.3
+ *               RC_ZF_IMAGE: pixel valid iff sum_c (img + pixel_means[c]) > 0.01
+ *   src_pose    [B,3,4]
+ *   K           [3,3] (device)
+ *   pixel_means [C] (device; RC_ZF_IMAGE only, may be NULL for RC_ZF_MASK)
+ *   zoom_factor [B,4]  (wx, wy, tx, ty) float32
+ *   bbox        [B,8]  int32: obs x0,x1,y0,y1 then rend x0,x1,y0,y1
+ *               (x0 > x1 marks an empty set; rend empty -> reference fallback,
+ *               obs empty -> zoom_factor row is NaN, the reference raises)
+ *   workspace   [B,RC_ZF_WS_INTS] int32 scratch (caller-owned; initialised by the call)
+ */
+#define RC_ZF_WS_INTS 10
+#define RC_ZF_MASK 0
+#define RC_ZF_IMAGE 1
+int rc_zoom_factor_dev(const float *obs, const float *rend, const float *src_pose,
+                       const float *K, const float *pixel_means, float *zoom_factor,
+                       int32_t *bbox, int32_t *workspace, int batch_size,
+                       int channels, int height, int width, int mode, void *stream);
+
+/* One resampled plane family.  `src`/`dst` point at [B,channels,H,W] tensors;
+ * every channel of the family gets the same pre/post operation.            */
+typedef struct rc_zoom_group {
+  const float *src;
+  float *dst;
+  int32_t channels;
+  int32_t pre_op;   /* RC_PRE_*  applied to each source tap before blending  */
+  int32_t post_op;  /* RC_POST_* applied to the blended value                */
+  int32_t accumulate; /* 0: dst = value (req "write"), 1: dst += value ("add") */
+  float mean[4];    /* per-channel constant for RC_PRE_ADD_MEAN / RC_POST_*_SUB_MEAN */
+} rc_zoom_group;
+
+#define RC_PRE_NONE 0
+#define RC_PRE_THRESH02 1   /* tap = tap > 0.2 ? 1 : 0   (zoom_mask.py:40-45)          */
+#define RC_PRE_ADD_MEAN 2   /* tap = tap + mean[c]       (zoom_image_with_factor.py:46) */
+
+#define RC_POST_NONE 0
+#define RC_POST_ROUND 1          /* mx.nd.round, half away from zero (zoom_mask.py:121) */
+#define RC_POST_ROUND_M045 2     /* round(v - 0.45)           (zoom_flow.py:74-76)      */
+#define RC_POST_DIV_WX 3         /* v / wx_in                 (zoom_flow.py:66)         */
+#define RC_POST_MUL_WX 4         /* v * wx_in                 (zoom_flow.py:64)         */
+#define RC_POST_SUB_MEAN 5       /* v - mean[c]               (zoom_image_with_factor.py:71-72) */
+#define RC_POST_SPOT_SUB_MEAN 6  /* max(v, centre spot) - mean[c]  (:36-45,:67-70)      */
+
+#define RC_ZOOM_MAX_GROUPS 8
+#define RC_ZOOM_MAX_PLANES 16
+
+/* Bilinear resampling of up to RC_ZOOM_MAX_PLANES planes that share one
+ * sampling grid per sample.  Replaces the GridGenerator loops and the
+ * BilinearSampler calls at zoom_mask.py:107-129, zoom_image.py:95-115,
+ * zoom_image_with_factor.py:52-72, zoom_depth.py:30-48, zoom_flow.py:33-76,
+ * zoom_mask_with_factor.py:41-66.
+ *   zoom_factor [B,4] device
+ *   inverse     0: grid from (wx,wy,tx,ty) as given
+ *               1: inverse zoom (zoom_flow.py:35-44): wx' = 1/wx ...
+ *   groups      HOST array of n_groups descriptors (copied into kernel params)
+ * Requires W % 4 == 0 and 16-byte aligned planes. */
+int rc_zoom_sample_dev(const float *zoom_factor, int inverse,
+                       const rc_zoom_group *groups, int n_groups, int batch_size,
+                       int height, int width, void *stream);
+
+/* ZoomTrans forward and backward (deepim/operator_py/zoom_trans.py:22-76).
+ *   trans_in/out [B,3]; x,y are divided by wx (inverse=0) or multiplied
+ *   (inverse=1); z passes through.  float32 scalar arithmetic (np.float32 op
+ *   np.float32 in the reference).  Forward: scale_xy = 1.  Backward: pass the
+ *   incoming gradient as trans_in and scale_xy = b_zoom_grad (:59-70).     */
+int rc_zoom_trans_dev(const float *zoom_factor, const float *trans_in,
+                      float *trans_out, int batch_size, int inverse, int scale_xy,
+                      int accumulate, void *stream);
+
+/* Zero-fill (every zoom backward: zoom_mask.py:136-140, zoom_flow.py:79-82 ...). */
+int rc_fill_zero_dev(float *dst, int64_t count, void *stream);
+
+/* ------------------------------------------------ point-matching loss path
+ * Replaces deepim/operator_py/transform3d.py:42-118 (forward), :120-327
+ * (backward) and the loss graph deepim/symbols/deepIM_flownet.py:460-499.
+ *
+ *   points    [B,3,N]  model points (zero padded)
+ *   rotation  [B,4]    quaternion w,x,y,z (already L2-normalised upstream)
+ *   trans     [B,3]    translation delta (un-zoomed)
+ *   pose_src  [B,3,4]
+ *   T_means, T_stds  [3] HOST floats (CustomOp kwargs in the reference)
+ *   rot_coord  RC_ROT_MODEL / RC_ROT_CAMERA / RC_ROT_CAMERA_NEW / RC_ROT_NAIVE
+ */
+#define RC_ROT_MODEL 0
+#define RC_ROT_CAMERA 1
+#define RC_ROT_CAMERA_NEW 2
+#define RC_ROT_NAIVE 3
+
+/* Transform3D forward: out[B,3,N] = (R_delta (x) R_src) * points + T_tgt. */
+int rc_transform3d_fwd_dev(const float *points, const float *rotation,
+                           const float *trans, const float *pose_src,
+                           const float *T_means, const float *T_stds, int rot_coord,
+                           float *out, int batch_size, int num_points,
+                           int accumulate, void *stream);
+
+/* Transform3D backward: grad_rot[B,4], grad_trans[B,3] from out_grad[B,3,N]. */
+int rc_transform3d_bwd_dev(const float *out_grad, const float *points,
+                           const float *rotation, const float *trans,
+                           const float *pose_src, const float *T_means,
+                           const float *T_stds, int rot_coord, float *grad_rot,
+                           float *grad_trans, int batch_size, int num_points,
+                           int accumulate, void *stream);
+
+#define RC_PM_L1 0
+#define RC_PM_L2 1
+#define RC_PM_SMOOTH_L1 2
+
+/* Fused Transform3D + point-matching loss forward.
+ *   points_obs [B,3,N], weights [B,3,N]
+ *   loss_map   [B,3,N]  w * f((est-obs)/norm_term)  (may be NULL)
+ *   loss_sum   [B]      per-sample sum of loss_map  (may be NULL)
+ *   est        [B,3,N]  transformed points          (may be NULL)          */
+int rc_pm_loss_fwd_dev(const float *points, const float *points_obs,
+                       const float *weights, const float *rotation,
+                       const float *trans, const float *pose_src,
+                       const float *T_means, const float *T_stds, int rot_coord,
+                       int loss_type, float norm_term, float sl1_scalar,
+                       float *est, float *loss_map, float *loss_sum,
+                       int batch_size, int num_points, void *stream);
+
+/* Fused loss-gradient + Transform3D backward: MakeLoss(grad_scale) head
+ * gradient, d f / d est, then transform3d.py:120-191 in one pass.          */
+int rc_pm_loss_bwd_dev(const float *points, const float *points_obs,
+                       const float *weights, const float *rotation,
+                       const float *trans, const float *pose_src,
+                       const float *T_means, const float *T_stds, int rot_coord,
+                       int loss_type, float norm_term, float sl1_scalar,
+                       float grad_scale, float *grad_rot, float *grad_trans,
+                       int batch_size, int num_points, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RENDERCOMPARE_H_ */

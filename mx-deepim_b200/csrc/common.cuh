@@ -1,0 +1,88 @@
+// common.cuh -- shared helpers for librendercompare (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "rendercompare.h"
+
+#if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
+#error "librendercompare is written for sm_100a (B200) only"
+#endif
+
+namespace rc {
+
+// Recorded by every failing CUDA call so that rc_last_cuda_error() can report it.
+void set_cuda_error(cudaError_t e);
+int note_status(int status);
+
+#define RC_CUDA_TRY(expr)                         \
+  do {                                            \
+    cudaError_t _e = (expr);                      \
+    if (_e != cudaSuccess) {                      \
+      ::rc::set_cuda_error(_e);                   \
+      return ::rc::note_status(RC_ERR_CUDA);      \
+    }                                             \
+  } while (0)
+
+#define RC_REQUIRE(cond, code)                    \
+  do {                                            \
+    if (!(cond)) return ::rc::note_status(code);  \
+  } while (0)
+
+static inline bool aligned16(const void *p) {
+  return (reinterpret_cast<uintptr_t>(p) & 15u) == 0;
+}
+
+static inline int check_launch() {
+  cudaError_t e = cudaPeekAtLastError();
+  if (e != cudaSuccess) {
+    (void)cudaGetLastError();
+    set_cuda_error(e);
+    return note_status(RC_ERR_CUDA);
+  }
+  return RC_OK;
+}
+
+// ---------------------------------------------------------------- device side
+#ifdef __CUDACC__
+
+// 128-bit read-only load that does not allocate in L1 (streamed once).
+__device__ __forceinline__ float4 ld_stream_f4(const float4 *p) {
+  float4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+               : "l"(p));
+  return r;
+}
+
+// 128-bit store; default L2 policy so that a consumer kernel can still hit L2.
+__device__ __forceinline__ void st_f4(float4 *p, const float4 &v) {
+  asm volatile("st.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y),
+               "f"(v.z), "f"(v.w)
+               : "memory");
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ int warp_min(int v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = min(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ int warp_max(int v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = max(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+#endif  // __CUDACC__
+
+}  // namespace rc

@@ -1,0 +1,220 @@
+// flow.cu -- ground-truth optical flow with visibility z-test.
+//
+// Replaces /root/reference/lib/flow_c/gpu_flow_kernel.cu:32-69 (flow_kernel)
+// and its host wrapper :82-148 (_flow).
+//
+// B200 design: the pass is a pure HBM stream (8 B/px read, 12 B/px written,
+// one L2-resident gather).  One thread owns four horizontally adjacent pixels:
+// one 128-bit no-allocate load of depth_src, three 128-bit stores, and up to
+// four scalar gathers of depth_tgt through the read-only path (the target
+// pixel is spatially coherent with the source pixel, so the gather hits lines
+// that neighbouring threads stream anyway).  A block never straddles samples,
+// so the 12 KT coefficients are block-uniform and live in registers.
+//
+// Bit-exactness: every floating-point operation is written with an explicit
+// rounding intrinsic in the association nvcc gives the reference source
+// (FMUL/FFMA/FADD sequence read from its sm_100a SASS), so the
+// result does not depend on this file's optimisation flags.
+#include "common.cuh"
+
+namespace rc {
+
+struct FlowCoef {
+  float kt[12];
+  float ki[6];
+};
+
+__device__ __forceinline__ void flow_pixel(float d, float fw, float fh, const FlowCoef &c,
+                                           const float *__restrict__ tgt_plane, int H,
+                                           int W, float &f0, float &f1, float &v) {
+  f0 = 0.f;
+  f1 = 0.f;
+  v = 0.f;
+  if ((double)d > 1E-3) {  // gpu_flow_kernel.cu:45 (double compare)
+    const float ax = __fadd_rn(__fmaf_rn(fw, c.ki[0], __fmul_rn(fh, c.ki[1])), c.ki[2]);
+    const float ay = __fadd_rn(__fmaf_rn(fw, c.ki[3], __fmul_rn(fh, c.ki[4])), c.ki[5]);
+    const float x = __fmul_rn(ax, d);  // :42
+    const float y = __fmul_rn(ay, d);  // :43
+    const float z = d;                 // :44
+    const float xp = __fadd_rn(
+        __fmaf_rn(z, c.kt[2], __fmaf_rn(x, c.kt[0], __fmul_rn(y, c.kt[1]))), c.kt[3]);
+    const float yp = __fadd_rn(
+        __fmaf_rn(z, c.kt[6], __fmaf_rn(x, c.kt[4], __fmul_rn(y, c.kt[5]))), c.kt[7]);
+    const float zs = __fadd_rn(
+        __fmaf_rn(z, c.kt[10], __fmaf_rn(x, c.kt[8], __fmul_rn(y, c.kt[9]))), c.kt[11]);
+    const float zp = (float)((double)zs + 1E-15);  // :49
+    const float wp = __fdiv_rn(xp, zp);            // :50
+    const float hp = __fdiv_rn(yp, zp);            // :51
+    if (wp >= 0.f && wp <= (float)(W - 1) && hp >= 0.f && hp <= (float)(H - 1)) {  // :54
+      const int wi = (int)roundf(wp);  // :52
+      const int hi = (int)roundf(hp);  // :53
+      const float dt = __ldg(tgt_plane + hi * W + wi);  // :55
+      if ((double)fabsf(__fsub_rn(zp, dt)) < 3E-3) {    // :56
+        f0 = __fsub_rn(hp, fh);  // :57  channel 0 = delta row
+        f1 = __fsub_rn(wp, fw);  // :58  channel 1 = delta col
+        v = 1.f;                 // :59
+      }
+    }
+  }
+}
+
+__device__ __forceinline__ void load_coef(FlowCoef &c, const float *__restrict__ KT,
+                                          const float *__restrict__ Kinv, int b) {
+#pragma unroll
+  for (int i = 0; i < 12; ++i) c.kt[i] = __ldg(KT + b * 12 + i);
+#pragma unroll
+  for (int i = 0; i < 6; ++i) c.ki[i] = __ldg(Kinv + i);
+}
+
+// grid = (ceil(H*W/4 / 256), B); block = 256.
+__global__ void __launch_bounds__(256)
+flow_kernel_v4(const float *__restrict__ depth_src, const float *__restrict__ depth_tgt,
+               const float *__restrict__ KT, const float *__restrict__ Kinv,
+               float *__restrict__ flow, float *__restrict__ valid, int H, int W) {
+  const int b = blockIdx.y;
+  const int quads = (H * W) >> 2;
+  const int q = blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= quads) return;
+  FlowCoef c;
+  load_coef(c, KT, Kinv, b);
+  const size_t plane = (size_t)H * W;
+  const int p = q << 2;
+  const int h = p / W;
+  const int w = p - h * W;
+  const float4 d = ld_stream_f4(reinterpret_cast<const float4 *>(depth_src + b * plane) + q);
+  const float *tgt = depth_tgt + b * plane;
+  const float fh = (float)h;
+  float4 o0, o1, ov;
+  flow_pixel(d.x, (float)(w + 0), fh, c, tgt, H, W, o0.x, o1.x, ov.x);
+  flow_pixel(d.y, (float)(w + 1), fh, c, tgt, H, W, o0.y, o1.y, ov.y);
+  flow_pixel(d.z, (float)(w + 2), fh, c, tgt, H, W, o0.z, o1.z, ov.z);
+  flow_pixel(d.w, (float)(w + 3), fh, c, tgt, H, W, o0.w, o1.w, ov.w);
+  float *f = flow + (size_t)b * 2 * plane;
+  st_f4(reinterpret_cast<float4 *>(f) + q, o0);
+  st_f4(reinterpret_cast<float4 *>(f + plane) + q, o1);
+  st_f4(reinterpret_cast<float4 *>(valid + b * plane) + q, ov);
+}
+
+// Scalar variant for widths that are not a multiple of four (host entry only).
+__global__ void __launch_bounds__(256)
+flow_kernel_v1(const float *__restrict__ depth_src, const float *__restrict__ depth_tgt,
+               const float *__restrict__ KT, const float *__restrict__ Kinv,
+               float *__restrict__ flow, float *__restrict__ valid, int H, int W) {
+  const int b = blockIdx.y;
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= H * W) return;
+  FlowCoef c;
+  load_coef(c, KT, Kinv, b);
+  const size_t plane = (size_t)H * W;
+  const int h = p / W;
+  const int w = p - h * W;
+  float f0, f1, v;
+  flow_pixel(__ldg(depth_src + b * plane + p), (float)w, (float)h, c, depth_tgt + b * plane,
+             H, W, f0, f1, v);
+  flow[(size_t)b * 2 * plane + p] = f0;
+  flow[(size_t)b * 2 * plane + plane + p] = f1;
+  valid[b * plane + p] = v;
+}
+
+static int launch_flow(const float *depth_src, const float *depth_tgt, const float *KT,
+                       const float *Kinv, float *flow, float *valid, int B, int H, int W,
+                       cudaStream_t stream, bool vec) {
+  if (B == 0) return RC_OK;
+  if (vec) {
+    const int quads = (H * W) / 4;
+    dim3 grid((quads + 255) / 256, B);
+    flow_kernel_v4<<<grid, 256, 0, stream>>>(depth_src, depth_tgt, KT, Kinv, flow, valid, H, W);
+  } else {
+    dim3 grid((H * W + 255) / 256, B);
+    flow_kernel_v1<<<grid, 256, 0, stream>>>(depth_src, depth_tgt, KT, Kinv, flow, valid, H, W);
+  }
+  return check_launch();
+}
+
+// Grow-only staging arena for the host-pointer entry point (one per device).
+struct Arena {
+  void *ptr = nullptr;
+  size_t bytes = 0;
+};
+static Arena g_arena[64];
+
+static int arena_reserve(int dev, size_t bytes, void **out) {
+  Arena &a = g_arena[dev];
+  if (a.bytes < bytes) {
+    if (a.ptr) RC_CUDA_TRY(cudaFree(a.ptr));
+    a.ptr = nullptr;
+    a.bytes = 0;
+    RC_CUDA_TRY(cudaMalloc(&a.ptr, bytes));
+    a.bytes = bytes;
+  }
+  *out = a.ptr;
+  return RC_OK;
+}
+
+}  // namespace rc
+
+extern "C" {
+
+int rc_flow_dev(const float *depth_src, const float *depth_tgt, const float *KT,
+                const float *Kinv, float *flow, float *valid, int batch_size, int height,
+                int width, void *stream) {
+  RC_REQUIRE(batch_size >= 0 && height > 0 && width > 0, RC_ERR_INVALID_ARG);
+  if (batch_size == 0) return rc::note_status(RC_OK);  // gpu_flow.pyx:36
+  RC_REQUIRE(depth_src && depth_tgt && KT && Kinv && flow && valid, RC_ERR_INVALID_ARG);
+  RC_REQUIRE((int64_t)batch_size * height * width * 2 < (int64_t)INT32_MAX, RC_ERR_INVALID_ARG);
+  RC_REQUIRE(width % 4 == 0 && rc::aligned16(depth_src) && rc::aligned16(flow) &&
+                 rc::aligned16(valid),
+             RC_ERR_UNALIGNED);
+  return rc::note_status(rc::launch_flow(depth_src, depth_tgt, KT, Kinv, flow, valid,
+                                         batch_size, height, width,
+                                         static_cast<cudaStream_t>(stream), true));
+}
+
+int rc_flow_host(float *flow, float *valid, const float *depth_src, const float *depth_tgt,
+                 const float *KT, const float *Kinv, int batch_size, int height, int width,
+                 int device_id) {
+  RC_REQUIRE(batch_size >= 0 && height > 0 && width > 0, RC_ERR_INVALID_ARG);
+  RC_REQUIRE(device_id >= 0 && device_id < 64, RC_ERR_INVALID_ARG);
+  if (batch_size == 0) return rc::note_status(RC_OK);
+  RC_REQUIRE(depth_src && depth_tgt && KT && Kinv && flow && valid, RC_ERR_INVALID_ARG);
+  int cur = -1;
+  RC_CUDA_TRY(cudaGetDevice(&cur));  // gpu_flow_kernel.cu:71-80
+  if (cur != device_id) RC_CUDA_TRY(cudaSetDevice(device_id));
+  const size_t plane = (size_t)batch_size * height * width * sizeof(float);
+  const size_t kt_bytes = (size_t)batch_size * 12 * sizeof(float);
+  const size_t kt_pad = (kt_bytes + 255) & ~(size_t)255;
+  // layout: src | tgt | flow(2) | valid | KT | Kinv ; planes are 16-byte multiples
+  // only when H*W % 4 == 0, so pad each region to 256 bytes.
+  const size_t plane_pad = (plane + 255) & ~(size_t)255;
+  const size_t total = plane_pad * 5 + kt_pad + 256;
+  void *base = nullptr;
+  int st = rc::arena_reserve(device_id, total, &base);
+  if (st != RC_OK) return st;
+  char *p = static_cast<char *>(base);
+  float *d_src = reinterpret_cast<float *>(p);
+  float *d_tgt = reinterpret_cast<float *>(p + plane_pad);
+  float *d_flow = reinterpret_cast<float *>(p + 2 * plane_pad);  // 2 planes contiguous
+  float *d_valid = reinterpret_cast<float *>(p + 4 * plane_pad);
+  float *d_kt = reinterpret_cast<float *>(p + 5 * plane_pad);
+  float *d_ki = reinterpret_cast<float *>(p + 5 * plane_pad + kt_pad);
+  cudaStream_t s = cudaStreamPerThread;
+  RC_CUDA_TRY(cudaMemcpyAsync(d_src, depth_src, plane, cudaMemcpyHostToDevice, s));
+  RC_CUDA_TRY(cudaMemcpyAsync(d_tgt, depth_tgt, plane, cudaMemcpyHostToDevice, s));
+  RC_CUDA_TRY(cudaMemcpyAsync(d_kt, KT, kt_bytes, cudaMemcpyHostToDevice, s));
+  RC_CUDA_TRY(cudaMemcpyAsync(d_ki, Kinv, 9 * sizeof(float), cudaMemcpyHostToDevice, s));
+  st = rc::launch_flow(d_src, d_tgt, d_kt, d_ki, d_flow, d_valid, batch_size, height, width, s,
+                       width % 4 == 0);
+  if (st != RC_OK) return rc::note_status(st);
+  RC_CUDA_TRY(cudaMemcpyAsync(flow, d_flow, 2 * plane, cudaMemcpyDeviceToHost, s));
+  RC_CUDA_TRY(cudaMemcpyAsync(valid, d_valid, plane, cudaMemcpyDeviceToHost, s));
+  RC_CUDA_TRY(cudaStreamSynchronize(s));
+  return rc::note_status(RC_OK);
+}
+
+void _flow(float *flow, float *valid, float *depth_src, float *depth_tgt, float *KT,
+           float *Kinv, int batch_size, int height, int width, int device_id) {
+  (void)rc_flow_host(flow, valid, depth_src, depth_tgt, KT, Kinv, batch_size, height, width,
+                     device_id);
+}
+
+}  // extern "C"

@@ -1,0 +1,468 @@
+// zoom.cu -- crop-box / zoom-factor reduction and the fused bilinear resampler.
+//
+// Replaces the host-side numpy blocks and the MXNet GridGenerator(affine) +
+// BilinearSampler calls of
+//   /root/reference/deepim/operator_py/zoom_mask.py:29-134
+//   /root/reference/deepim/operator_py/zoom_image.py:26-119
+//   /root/reference/deepim/operator_py/zoom_image_with_factor.py:31-75
+//   /root/reference/deepim/operator_py/zoom_depth.py:24-50
+//   /root/reference/deepim/operator_py/zoom_flow.py:28-77
+//   /root/reference/deepim/operator_py/zoom_mask_with_factor.py:29-68
+//   /root/reference/deepim/operator_py/zoom_trans.py:22-76
+//
+// B200 design.  (1) bbox: one streaming pass with 128-bit loads, per-thread
+// min/max, warp-shuffle + shared-memory block reduction, eight integer atomics
+// per block; the last block of a sample (ticket counter) computes the zoom
+// factor in float64 exactly as the numpy scalars do, so there is no second
+// launch and no host round trip.  (2) sampler: all planes that share a grid
+// (3 masks + 6 image channels + 2 flow + 2 weight planes in the default
+// configuration) are resampled by ONE launch; a thread owns four adjacent
+// output pixels of a row, computes the source coordinates once, and for each
+// plane gathers the taps through the read-only path (zoom-in means the source
+// window is smaller than the output tile, so the taps are L1/L2 hits) and
+// issues one 128-bit store.  Write traffic dominates: 52 B/px out of 60.
+#include <limits.h>
+
+#include "common.cuh"
+
+namespace rc {
+
+// ------------------------------------------------------------------- bbox
+struct BBoxAcc {
+  int x0, x1, y0, y1;
+  __device__ __forceinline__ void init() {
+    x0 = INT_MAX;
+    y0 = INT_MAX;
+    x1 = -1;
+    y1 = -1;
+  }
+  __device__ __forceinline__ void add(int x, int y) {
+    x0 = min(x0, x);
+    x1 = max(x1, x);
+    y0 = min(y0, y);
+    y1 = max(y1, y);
+  }
+};
+
+__device__ __forceinline__ float comp(const float4 &v, int k) {
+  return k == 0 ? v.x : (k == 1 ? v.y : (k == 2 ? v.z : v.w));
+}
+
+// workspace layout per sample (int32 x 10):
+//   [0..3] obs x0,x1,y0,y1   [4..7] rend x0,x1,y0,y1   [8] ticket  [9] unused
+#define RC_ZF_WS_STRIDE RC_ZF_WS_INTS
+
+__global__ void zoom_bbox_init_kernel(int32_t *ws, int B) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B * RC_ZF_WS_STRIDE) return;
+  const int k = i % RC_ZF_WS_STRIDE;
+  int v = 0;
+  if (k == 0 || k == 2 || k == 4 || k == 6) v = INT_MAX;
+  if (k == 1 || k == 3 || k == 5 || k == 7) v = -1;
+  ws[i] = v;
+}
+
+// Zoom factor from the two boxes; float64 scalar arithmetic as numpy 1.x
+// evaluates zoom_mask.py:63-105 (np.float32 scalar op Python/int64 scalar ->
+// float64), stored as float32 (:116-119).
+__device__ void zoom_factor_finalize(const int32_t *w, const float *__restrict__ src_pose,
+                                     const float *__restrict__ K, float *__restrict__ zf,
+                                     int32_t *__restrict__ bbox, int H, int W) {
+  const int ox0 = w[0], ox1 = w[1], oy0 = w[2], oy1 = w[3];
+  int rx0 = w[4], rx1 = w[5], ry0 = w[6], ry1 = w[7];
+  if (bbox) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) bbox[k] = w[k];
+  }
+  if (ox1 < 0) {  // observed set empty: the reference raises (np.min of empty), zoom_mask.py:59
+    const float nanv = __int_as_float(0x7fc00000);
+    zf[0] = zf[1] = zf[2] = zf[3] = nanv;
+    return;
+  }
+  // np.dot(K, src_pose[:, 3]) in float32 (zoom_mask.py:72)
+  const float t0 = src_pose[3], t1 = src_pose[7], t2 = src_pose[11];
+  const float c0 = __fadd_rn(__fadd_rn(__fmul_rn(K[0], t0), __fmul_rn(K[1], t1)), __fmul_rn(K[2], t2));
+  const float c1 = __fadd_rn(__fadd_rn(__fmul_rn(K[3], t0), __fmul_rn(K[4], t1)), __fmul_rn(K[5], t2));
+  const float c2 = __fadd_rn(__fadd_rn(__fmul_rn(K[6], t0), __fmul_rn(K[7], t1)), __fmul_rn(K[8], t2));
+  double zcx, zcy;
+  if (rx1 < 0) {  // "NO POINT VALID IN MASK rendered" fallback, zoom_mask.py:74-81
+    rx0 = ox0;
+    rx1 = ox1;
+    ry0 = oy0;
+    ry1 = oy1;
+    zcx = (double)(ox0 + ox1) * 0.5;
+    zcy = (double)(oy0 + oy1) * 0.5;
+  } else {
+    zcx = (double)__fdiv_rn(c0, c2);  // :73
+    zcy = (double)__fdiv_rn(c1, c2);
+  }
+  const double left = fmax(zcx - rx0, zcx - ox0);
+  const double right = fmax(rx1 - zcx, ox1 - zcx);
+  const double up = fmax(zcy - ry0, zcy - oy0);
+  const double down = fmax(oy1 - zcy, ry1 - zcy);
+  const double m = fmax(fmax(__dmul_rn(0.75, right), __dmul_rn(0.75, left)), fmax(up, down));
+  const double crop_h = __dmul_rn(__dmul_rn(m, 1.4), 2.0);  // :96-100
+  const double wx = crop_h / (double)H;                     // :102-103 (both / height)
+  const double tx = __dadd_rn(__dmul_rn(zcx / (double)W, 2.0), -1.0);  // :104
+  const double ty = __dadd_rn(__dmul_rn(zcy / (double)H, 2.0), -1.0);  // :105
+  zf[0] = (float)wx;
+  zf[1] = (float)wx;
+  zf[2] = (float)tx;
+  zf[3] = (float)ty;
+}
+
+// grid = (blocks_per_sample, B), block = 256.
+template <int MODE>
+__global__ void __launch_bounds__(256)
+zoom_bbox_kernel(const float *__restrict__ obs, const float *__restrict__ rend,
+                 const float *__restrict__ src_pose, const float *__restrict__ K,
+                 const float *__restrict__ pixel_means, float *__restrict__ zoom_factor,
+                 int32_t *__restrict__ bbox, int32_t *__restrict__ ws, int C, int H, int W) {
+  const int b = blockIdx.y;
+  const int quads = (H * W) >> 2;
+  const size_t plane = (size_t)H * W;
+  const float *o = obs + (size_t)b * C * plane;
+  const float *r = rend + (size_t)b * C * plane;
+  BBoxAcc ao, ar;
+  ao.init();
+  ar.init();
+  for (int q = blockIdx.x * blockDim.x + threadIdx.x; q < quads; q += gridDim.x * blockDim.x) {
+    const int p = q << 2;
+    const int y = p / W;
+    const int x = p - y * W;
+    float so[4] = {0.f, 0.f, 0.f, 0.f}, sr[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int c = 0; c < C; ++c) {
+      const float4 vo = ld_stream_f4(reinterpret_cast<const float4 *>(o + c * plane) + q);
+      const float4 vr = ld_stream_f4(reinterpret_cast<const float4 *>(r + c * plane) + q);
+      const float mean = (MODE == RC_ZF_IMAGE) ? __ldg(pixel_means + c) : 0.f;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        float eo = comp(vo, k), er = comp(vr, k);
+        if (MODE == RC_ZF_IMAGE) {
+          eo = __fadd_rn(eo, mean);  // zoom_image.py:31-32
+          er = __fadd_rn(er, mean);
+        } else {
+          er = er > 0.2f ? 1.f : 0.f;  // zoom_mask.py:40-45
+        }
+        so[k] = c == 0 ? eo : __fadd_rn(so[k], eo);  // np.sum(axis=1), sequential
+        sr[k] = c == 0 ? er : __fadd_rn(sr[k], er);
+      }
+    }
+    const float thr = (MODE == RC_ZF_IMAGE) ? 0.01f : 0.3f;  // zoom_image.py:35 / zoom_mask.py:37
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      if (so[k] > thr) ao.add(x + k, y);
+      if (sr[k] > thr) ar.add(x + k, y);
+    }
+  }
+  // block reduction: warp shuffles, then 8 warps through shared memory
+  int v[8] = {ao.x0, ao.x1, ao.y0, ao.y1, ar.x0, ar.x1, ar.y0, ar.y1};
+  __shared__ int sm[8][8];
+  __shared__ int s_last;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    v[k] = (k & 1) ? warp_max(v[k]) : warp_min(v[k]);
+    if (lane == 0) sm[warp][k] = v[k];
+  }
+  __syncthreads();
+  int32_t *w = ws + b * RC_ZF_WS_STRIDE;
+  if (threadIdx.x < 8) {
+    const int k = threadIdx.x;
+    int acc = sm[0][k];
+    for (int i = 1; i < (int)(blockDim.x >> 5); ++i)
+      acc = (k & 1) ? max(acc, sm[i][k]) : min(acc, sm[i][k]);
+    if (k & 1) {
+      if (acc >= 0) atomicMax(w + k, acc);
+    } else {
+      if (acc != INT_MAX) atomicMin(w + k, acc);
+    }
+  }
+  // last block of this sample finalises (ticket counter; fence orders the atomics)
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const int t = atomicAdd(w + 8, 1);
+    s_last = (t == (int)gridDim.x - 1);
+  }
+  __syncthreads();
+  if (s_last && threadIdx.x == 0) {
+    __threadfence();
+    int32_t fin[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) fin[k] = atomicAdd(w + k, 0);  // coherent read at L2
+    zoom_factor_finalize(fin, src_pose + b * 12, K, zoom_factor + b * 4,
+                         bbox ? bbox + b * 8 : nullptr, H, W);
+  }
+}
+
+// ---------------------------------------------------------------- sampler
+struct ZoomPlane {
+  const float *src;
+  float *dst;
+  long long src_bstride;  // floats between samples
+  long long dst_bstride;
+  int pre_op;
+  int post_op;
+  int accumulate;
+  int channel;  // channel index inside its group (for the centre spot)
+  float mean;
+};
+
+struct ZoomParams {
+  ZoomPlane planes[RC_ZOOM_MAX_PLANES];
+  const float *zoom_factor;
+  int n_planes;
+  int inverse;
+  int H, W;
+  int spot_x0, spot_x1, spot_y0, spot_y1;  // zoom_image_with_factor.py:36-45
+};
+
+// Affine parameters of one sample: (wx, wy, tx, ty) as float32, forward or
+// inverse (zoom_flow.py:35-44 evaluated in float64 like numpy 1.x scalars).
+__device__ __forceinline__ void zoom_affine(const float *__restrict__ zf, int inverse, int H,
+                                            int W, float &wx, float &wy, float &tx, float &ty,
+                                            float &wx_in) {
+  const float a = __ldg(zf + 0), bq = __ldg(zf + 1), c = __ldg(zf + 2), d = __ldg(zf + 3);
+  wx_in = a;
+  if (!inverse) {
+    wx = a;
+    wy = bq;
+    tx = c;
+    ty = d;
+  } else {
+    const double wxi = a, wyi = bq, txi = c, tyi = d;
+    const double crop_w = wxi * W, crop_h = wyi * H;
+    const double cx = __dadd_rn(__dmul_rn(__dmul_rn(txi, 0.5), (double)W), 0.5 * W);
+    const double cy = __dadd_rn(__dmul_rn(__dmul_rn(tyi, 0.5), (double)H), 0.5 * H);
+    wx = (float)(1.0 / wxi);
+    wy = (float)(1.0 / wyi);
+    tx = (float)__dmul_rn((W * 0.5 - cx) / crop_w, 2.0);
+    ty = (float)__dmul_rn((H * 0.5 - cy) / crop_h, 2.0);
+  }
+}
+
+// Source coordinate of output index i along an axis of length n:
+//   GridGenerator: g = w * (-1 + i * 2/(n-1)) + t      (float32)
+//   BilinearSampler: real = (g + 1) * (n - 1) / 2      (float32)
+__device__ __forceinline__ float src_coord(int i, float step, float w, float t, float nm1) {
+  const float n = __fmaf_rn((float)i, step, -1.0f);
+  const float g = __fadd_rn(__fmul_rn(w, n), t);
+  return __fmul_rn(__fmul_rn(__fadd_rn(g, 1.0f), nm1), 0.5f);
+}
+
+__device__ __forceinline__ float pre(float v, int pre_op, float mean) {
+  if (pre_op == RC_PRE_THRESH02) return v > 0.2f ? 1.f : 0.f;
+  if (pre_op == RC_PRE_ADD_MEAN) return __fadd_rn(v, mean);
+  return v;
+}
+
+// grid = (ceil(H*W/4 / 256), B); block = 256.
+__global__ void __launch_bounds__(256)
+zoom_sample_kernel(const __grid_constant__ ZoomParams P) {
+  const int H = P.H, W = P.W;
+  const int b = blockIdx.y;
+  const int q = blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= ((H * W) >> 2)) return;
+  const int p = q << 2;
+  const int j = p / W;
+  const int i0 = p - j * W;
+
+  float wx, wy, tx, ty, wx_in;
+  zoom_affine(P.zoom_factor + b * 4, P.inverse, H, W, wx, wy, tx, ty, wx_in);
+  const float stepx = (float)(2.0 / (W - 1)), stepy = (float)(2.0 / (H - 1));
+
+  const float yr = src_coord(j, stepy, wy, ty, (float)(H - 1));
+  const float yf = floorf(yr);
+  const int y0 = (int)yf;
+  const float wyt = __fsub_rn(1.0f, __fsub_rn(yr, yf));  // top weight
+  const float wyb = __fsub_rn(1.0f, wyt);
+  const bool yin0 = (y0 >= 0) && (y0 <= H - 1);
+  const bool yin1 = (y0 + 1 >= 0) && (y0 + 1 <= H - 1);
+
+  int x0[4];
+  float wxl[4], wxr[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const float xr = src_coord(i0 + k, stepx, wx, tx, (float)(W - 1));
+    const float xf = floorf(xr);
+    x0[k] = (int)xf;
+    wxl[k] = __fsub_rn(1.0f, __fsub_rn(xr, xf));
+    wxr[k] = __fsub_rn(1.0f, wxl[k]);
+  }
+
+  for (int pl = 0; pl < P.n_planes; ++pl) {
+    const ZoomPlane &zp = P.planes[pl];
+    const float *__restrict__ s = zp.src + (long long)b * zp.src_bstride;
+    const float *__restrict__ r0 = s + (long long)y0 * W;
+    const float *__restrict__ r1 = r0 + W;
+    float out[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int xa = x0[k], xb = x0[k] + 1;
+      const bool xin0 = (xa >= 0) && (xa <= W - 1);
+      const bool xin1 = (xb >= 0) && (xb <= W - 1);
+      const float tl = (yin0 && xin0) ? pre(__ldg(r0 + xa), zp.pre_op, zp.mean) : 0.f;
+      const float tr = (yin0 && xin1) ? pre(__ldg(r0 + xb), zp.pre_op, zp.mean) : 0.f;
+      const float bl = (yin1 && xin0) ? pre(__ldg(r1 + xa), zp.pre_op, zp.mean) : 0.f;
+      const float br = (yin1 && xin1) ? pre(__ldg(r1 + xb), zp.pre_op, zp.mean) : 0.f;
+      float v = __fmul_rn(__fmul_rn(tl, wyt), wxl[k]);
+      v = __fmaf_rn(__fmul_rn(tr, wyt), wxr[k], v);
+      v = __fmaf_rn(__fmul_rn(bl, wyb), wxl[k], v);
+      v = __fmaf_rn(__fmul_rn(br, wyb), wxr[k], v);
+      switch (zp.post_op) {
+        case RC_POST_ROUND: v = roundf(v); break;
+        case RC_POST_ROUND_M045: v = roundf(__fsub_rn(v, 0.45f)); break;
+        case RC_POST_DIV_WX: v = __fdiv_rn(v, wx_in); break;
+        case RC_POST_MUL_WX: v = __fmul_rn(v, wx_in); break;
+        case RC_POST_SUB_MEAN: v = __fsub_rn(v, zp.mean); break;
+        case RC_POST_SPOT_SUB_MEAN: {
+          const int x = i0 + k;
+          const float spot = (zp.channel == 0 && x >= P.spot_x0 && x < P.spot_x1 &&
+                              j >= P.spot_y0 && j < P.spot_y1) ? 255.f : 0.f;
+          v = __fsub_rn(fmaxf(v, spot), zp.mean);
+        } break;
+        default: break;
+      }
+      out[k] = v;
+    }
+    float4 *d = reinterpret_cast<float4 *>(zp.dst + (long long)b * zp.dst_bstride) + q;
+    float4 o = make_float4(out[0], out[1], out[2], out[3]);
+    if (zp.accumulate) {
+      const float4 old = *d;
+      o.x += old.x;
+      o.y += old.y;
+      o.z += old.z;
+      o.w += old.w;
+    }
+    st_f4(d, o);
+  }
+}
+
+// ------------------------------------------------------------- ZoomTrans
+// zoom_trans.py:30-44 (forward) and :57-73 (backward); float32 scalar ops.
+__global__ void zoom_trans_kernel(const float *__restrict__ zf, const float *__restrict__ in,
+                                  float *__restrict__ out, int B, int inverse, int scale_xy,
+                                  int accumulate) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  const float wx = zf[b * 4 + 0];  // wy = zoom_factor[b][0] as well (:32-33)
+  float x = in[b * 3 + 0], y = in[b * 3 + 1];
+  const float z = in[b * 3 + 2];
+  if (scale_xy) {
+    if (inverse) {
+      x = __fmul_rn(x, wx);
+      y = __fmul_rn(y, wx);
+    } else {
+      x = __fdiv_rn(x, wx);
+      y = __fdiv_rn(y, wx);
+    }
+  }
+  if (accumulate) {
+    out[b * 3 + 0] += x;
+    out[b * 3 + 1] += y;
+    out[b * 3 + 2] += z;
+  } else {
+    out[b * 3 + 0] = x;
+    out[b * 3 + 1] = y;
+    out[b * 3 + 2] = z;
+  }
+}
+
+}  // namespace rc
+
+extern "C" {
+
+int rc_zoom_factor_dev(const float *obs, const float *rend, const float *src_pose,
+                       const float *K, const float *pixel_means, float *zoom_factor,
+                       int32_t *bbox, int32_t *workspace, int batch_size, int channels,
+                       int height, int width, int mode, void *stream) {
+  RC_REQUIRE(batch_size >= 0 && channels > 0 && height > 0 && width > 0, RC_ERR_INVALID_ARG);
+  RC_REQUIRE(mode == RC_ZF_MASK || mode == RC_ZF_IMAGE, RC_ERR_INVALID_ARG);
+  if (batch_size == 0) return rc::note_status(RC_OK);
+  RC_REQUIRE(obs && rend && src_pose && K && zoom_factor && workspace, RC_ERR_INVALID_ARG);
+  RC_REQUIRE(mode == RC_ZF_MASK || pixel_means != nullptr, RC_ERR_INVALID_ARG);
+  RC_REQUIRE(width % 4 == 0 && rc::aligned16(obs) && rc::aligned16(rend), RC_ERR_UNALIGNED);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int n = batch_size * RC_ZF_WS_STRIDE;
+  rc::zoom_bbox_init_kernel<<<(n + 255) / 256, 256, 0, s>>>(workspace, batch_size);
+  const int quads = height * width / 4;
+  int bps = (quads + 256 * 4 - 1) / (256 * 4);  // four quads per thread
+  if (bps < 1) bps = 1;
+  dim3 grid(bps, batch_size);
+  if (mode == RC_ZF_MASK)
+    rc::zoom_bbox_kernel<RC_ZF_MASK><<<grid, 256, 0, s>>>(obs, rend, src_pose, K, pixel_means,
+                                                          zoom_factor, bbox, workspace,
+                                                          channels, height, width);
+  else
+    rc::zoom_bbox_kernel<RC_ZF_IMAGE><<<grid, 256, 0, s>>>(obs, rend, src_pose, K, pixel_means,
+                                                           zoom_factor, bbox, workspace,
+                                                           channels, height, width);
+  return rc::note_status(rc::check_launch());
+}
+
+int rc_zoom_sample_dev(const float *zoom_factor, int inverse, const rc_zoom_group *groups,
+                       int n_groups, int batch_size, int height, int width, void *stream) {
+  RC_REQUIRE(batch_size >= 0 && height > 1 && width > 1, RC_ERR_INVALID_ARG);
+  RC_REQUIRE(n_groups >= 0 && n_groups <= RC_ZOOM_MAX_GROUPS, RC_ERR_INVALID_ARG);
+  if (batch_size == 0 || n_groups == 0) return rc::note_status(RC_OK);
+  RC_REQUIRE(zoom_factor && groups, RC_ERR_INVALID_ARG);
+  RC_REQUIRE(width % 4 == 0, RC_ERR_UNALIGNED);
+  rc::ZoomParams P;
+  P.n_planes = 0;
+  const long long plane = (long long)height * width;
+  for (int g = 0; g < n_groups; ++g) {
+    const rc_zoom_group &G = groups[g];
+    RC_REQUIRE(G.src && G.dst && G.channels > 0 && G.channels <= 4, RC_ERR_INVALID_ARG);
+    RC_REQUIRE(G.pre_op >= 0 && G.pre_op <= RC_PRE_ADD_MEAN, RC_ERR_INVALID_ARG);
+    RC_REQUIRE(G.post_op >= 0 && G.post_op <= RC_POST_SPOT_SUB_MEAN, RC_ERR_INVALID_ARG);
+    RC_REQUIRE(rc::aligned16(G.dst), RC_ERR_UNALIGNED);
+    for (int c = 0; c < G.channels; ++c) {
+      RC_REQUIRE(P.n_planes < RC_ZOOM_MAX_PLANES, RC_ERR_CAPACITY);
+      rc::ZoomPlane &z = P.planes[P.n_planes++];
+      z.src = G.src + c * plane;
+      z.dst = G.dst + c * plane;
+      z.src_bstride = G.channels * plane;
+      z.dst_bstride = G.channels * plane;
+      z.pre_op = G.pre_op;
+      z.post_op = G.post_op;
+      z.accumulate = G.accumulate;
+      z.channel = c;
+      z.mean = G.mean[c];
+    }
+  }
+  P.zoom_factor = zoom_factor;
+  P.inverse = inverse ? 1 : 0;
+  P.H = height;
+  P.W = width;
+  // floor(W/2 - 5) .. ceil(W/2 + 5) (zoom_image_with_factor.py:38-41, spot_radius = 5)
+  P.spot_x0 = (int)floor((double)width / 2 - 5);
+  P.spot_x1 = (int)ceil((double)width / 2 + 5);
+  P.spot_y0 = (int)floor((double)height / 2 - 5);
+  P.spot_y1 = (int)ceil((double)height / 2 + 5);
+  const int quads = height * width / 4;
+  dim3 grid((quads + 255) / 256, batch_size);
+  rc::zoom_sample_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(P);
+  return rc::note_status(rc::check_launch());
+}
+
+int rc_zoom_trans_dev(const float *zoom_factor, const float *trans_in, float *trans_out,
+                      int batch_size, int inverse, int scale_xy, int accumulate, void *stream) {
+  RC_REQUIRE(batch_size >= 0, RC_ERR_INVALID_ARG);
+  if (batch_size == 0) return rc::note_status(RC_OK);
+  RC_REQUIRE(zoom_factor && trans_in && trans_out, RC_ERR_INVALID_ARG);
+  rc::zoom_trans_kernel<<<(batch_size + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(
+      zoom_factor, trans_in, trans_out, batch_size, inverse, scale_xy, accumulate);
+  return rc::note_status(rc::check_launch());
+}
+
+int rc_fill_zero_dev(float *dst, int64_t count, void *stream) {
+  RC_REQUIRE(count >= 0, RC_ERR_INVALID_ARG);
+  if (count == 0) return rc::note_status(RC_OK);
+  RC_REQUIRE(dst != nullptr, RC_ERR_INVALID_ARG);
+  RC_CUDA_TRY(cudaMemsetAsync(dst, 0, (size_t)count * sizeof(float),
+                              static_cast<cudaStream_t>(stream)));
+  return rc::note_status(RC_OK);
+}
+
+}  // extern "C"
