@@ -1,0 +1,363 @@
+#!/usr/bin/env python
+"""bench.py -- render-compare pairs/s at 640x480 (BASELINE.json metric).
+
+    python bench.py --gpus N --steps K --warmup W            # this framework
+    python bench.py --impl reference --steps K --warmup W    # CPU reference arm (oracle port)
+
+Workload (N = 1): BASELINE.json configs[1] -- "batch 16 LINEMOD-ape-shaped pairs: zoom-in +
+GT flow + point-matching loss on 1 B200".  A step is one pass of that path over one batch
+of 16 synthetic pairs per GPU (weak scaling: every rank owns its own 16 pairs, no
+collective on the data path).  Three input sets rotate so that the bytes touched between
+two uses of the same buffer exceed the 126 MB L2.
+
+Printed JSON (one line, rank 0): value = pairs/s with inputs resident in HBM; e2e = the
+same through the public API with pinned HOST inputs (H2D of every input + D2H of the loss
+and zoom factors inside the timed region); roofline = the dominant kernel (the fused
+bilinear resampler) timed with CUDA events on its own stream inside the timed region;
+cpu_baseline = the oracle port of the reference's CPU path on the host cores.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "render-compare pairs/s @640x480"
+UNIT = "pairs/s"
+WORKLOAD = "cfg2: batch 16 LINEMOD-shaped pairs per GPU: GT flow + zoom-in (13 planes) + PM loss"
+BATCH = 16
+NSETS = 3
+SEED = 20181804 + 2  # default_rng(20181804 + cfg_id), + rank per GPU
+
+
+def _peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        try:
+            return float(json.load(open(path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler(object):
+    """nvidia-smi clocks / throttle reasons sampled every 100 ms while the GPU is under load."""
+
+    FIELDS = ("clocks.sm,clocks.max.sm,utilization.gpu,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.FIELDS,
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, smax, reasons = [], [], set()
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for line in self.lines:
+            parts = [p.strip() for p in line.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                clk, mx, util = float(parts[0]), float(parts[1]), float(parts[2])
+            except ValueError:
+                continue
+            smax.append(mx)
+            if util > 0:
+                sm.append(clk)
+                for n, v in zip(names, parts[3:7]):
+                    if v.lower().startswith("active"):
+                        reasons.add(n)
+        return {"sm_mhz": statistics.median(sm) if sm else None,
+                "sm_max_mhz": max(smax) if smax else None, "reasons": sorted(reasons),
+                "samples_under_load": len(sm), "samples": len(self.lines)}
+
+
+# ------------------------------------------------------------------ CPU reference arm
+_CPU_HOST = None
+
+def _cpu_pair(args):
+    """The reference's CPU path for ONE pair (oracle port): flow_kernel in C, numpy zoom
+    plugins, numpy Transform3D + loss."""
+    b = args
+    host = _CPU_HOST  # inherited through fork: no per-task pickling of the images
+    import numpy as np
+
+    from oracle import flow_np, transform3d_np, zoom_np
+
+    s = slice(b, b + 1)
+    flow, valid = flow_np.flow_kernel_cpu(host["depth_rendered"][s], host["depth_gt_observed"][s],
+                                          host["KT"][s], host["Kinv"], num_threads=1)
+    K = np.array([[572.4114, 0.0, 325.2611], [0.0, 573.57043, 242.04899], [0.0, 0.0, 1.0]], np.float32)
+    pm = np.array([123.68, 116.779, 103.939], np.float32)[::-1]
+    zm = zoom_np.zoom_mask_forward(host["mask_observed"][s], host["mask_gt_observed"][s],
+                                   host["depth_rendered"][s], host["src_pose"][s], K)
+    zi = zoom_np.zoom_image_with_factor_forward(zm[3], host["image_observed"][s],
+                                                host["image_rendered"][s], pm)
+    zf = zoom_np.zoom_flow_forward(zm[3], flow, np.tile(valid, [1, 2, 1, 1]))
+    zt = zoom_np.zoom_trans_forward(zm[3], host["trans_gt"][s])
+    _, _, sums = transform3d_np.pm_loss_forward(
+        host["point_cloud_model"][s], host["point_cloud_observed"][s], host["point_cloud_weights"][s],
+        host["rot_est"][s], host["trans_est"][s], host["src_pose"][s], np.zeros(3, np.float32),
+        np.ones(3, np.float32))
+    return float(sums[0]) + float(zi[0][0, 0, 0, 0]) + float(zf[0][0, 0, 0, 0]) + float(zt[0, 0])
+
+
+class CpuReference(object):
+    """Times the oracle port on the host cores: `pairs` pairs per step, one process per core."""
+
+    def __init__(self, pairs=None):
+        import multiprocessing as mp
+
+        from mx_deepim_b200 import synth
+        from oracle import build as obuild
+
+        obuild.build_oracle()
+        self.cores = os.cpu_count() or 1
+        self.pairs = pairs or min(BATCH, self.cores)
+        global _CPU_HOST
+        self.host = synth.make_compare_batch(self.pairs, SEED)
+        _CPU_HOST = self.host
+        self.pool = mp.get_context("fork").Pool(min(self.cores, self.pairs))
+        self.work = list(range(self.pairs))
+
+    def step(self):
+        t0 = time.perf_counter()
+        self.pool.map(_cpu_pair, self.work, chunksize=1)
+        return time.perf_counter() - t0
+
+    def close(self):
+        self.pool.close()
+        self.pool.join()
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return
+    ref = CpuReference()
+    for _ in range(max(args.warmup, 1)):
+        ref.step()
+    times = [ref.step() for _ in range(args.steps)]
+    ref.close()
+    total = sum(times)
+    value = ref.pairs * args.steps / total
+    sample = "%d pairs per step (1 per process, %d processes), oracle port: C flow_kernel + numpy zoom + numpy loss" % (
+        ref.pairs, min(ref.cores, ref.pairs))
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT,
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "batch_per_step": ref.pairs},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": min(ref.cores, ref.pairs),
+                         "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+# ------------------------------------------------------------------------ GPU arm
+def run_ours(args, rank, world, local_rank):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    from mx_deepim_b200 import _lib, pipeline, synth
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+
+    B, K, Wm = BATCH, args.steps, args.warmup
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    hosts = [synth.make_compare_batch(B, SEED + 1000 * rank + s) for s in range(NSETS)]
+    step = pipeline.CompareStep(B, dev)
+    dsets = [step.to_device(h, non_blocking=False) for h in hosts]
+    bound = [step.bind(x) for x in dsets]
+    torch.cuda.synchronize()
+
+    # ---------------------------------------------------- device-resident arm (`value`)
+    for i in range(max(Wm, 3)):
+        step.run(None, args=bound[i % NSETS])
+    torch.cuda.synchronize()
+    marks = [[None, None, _lib.Event(), _lib.Event(), None, None] for _ in range(K)]
+    e0, e1 = _lib.Event(), _lib.Event()
+    barrier()
+    torch.cuda.synchronize()
+    e0.record()
+    for i in range(K):
+        step.run(None, args=bound[i % NSETS], marks=marks[i])
+    e1.record()
+    torch.cuda.synchronize()
+    barrier()
+    ms = e0.elapsed_ms(e1)
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_max = float(t.item())
+    value = world * B * K / (ms_max * 1e-3)
+    k_ms = [m[2].elapsed_ms(m[3]) for m in marks]
+    kernel_ms = sum(k_ms) / len(k_ms)
+
+    # -------------------------------------- per-kernel breakdown (all marks; extra info)
+    full = [[_lib.Event() for _ in range(_lib.RC_STEP_MARKS)] for _ in range(min(K, 20))]
+    for i, m in enumerate(full):
+        step.run(None, args=bound[i % NSETS], marks=m)
+    torch.cuda.synchronize()
+    names = ["flow", "zoom_bbox_factor", "zoom_sample", "zoom_trans", "pm_loss"]
+    breakdown = {n: sum(m[j].elapsed_ms(m[j + 1]) for m in full) / len(full) * 1e3
+                 for j, n in enumerate(names)}
+
+    # ------------------------------------------------ end-to-end arm (host buffers, `e2e`)
+    pinned = [{k: torch.from_numpy(np.ascontiguousarray(h[k])).pin_memory()
+               for k in pipeline.INPUT_KEYS} for h in hosts]
+    stage = {k: torch.empty_like(v, device=dev) for k, v in pinned[0].items()}
+    stage_args = step.bind(stage)
+    out_loss = torch.empty((B,), dtype=torch.float32).pin_memory()
+    out_zf = torch.empty((B, 4), dtype=torch.float32).pin_memory()
+    h2d = sum(v.numel() * v.element_size() for v in pinned[0].values())
+    d2h = out_loss.numel() * 4 + out_zf.numel() * 4
+
+    def e2e_step(i):
+        src = pinned[i % NSETS]
+        for k in pipeline.INPUT_KEYS:
+            stage[k].copy_(src[k], non_blocking=True)
+        step.run(None, args=stage_args)
+        out_loss.copy_(step.loss_sum, non_blocking=True)
+        out_zf.copy_(step.zoom_factor, non_blocking=True)
+
+    Ke = max(3, min(K, 30))
+    for i in range(3):
+        e2e_step(i)
+    torch.cuda.synchronize()
+    barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    e0.record()
+    for i in range(Ke):
+        e2e_step(i)
+    e1.record()
+    torch.cuda.synchronize()
+    wall = time.perf_counter() - t0
+    barrier()
+    ms_e = max(e0.elapsed_ms(e1), wall * 1e3)  # host wall clock includes the final sync
+    t = torch.tensor([ms_e], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_value = world * B * Ke / (float(t.item()) * 1e-3)
+    loss_host = float(out_loss.sum())
+
+    clocks = sampler.stop() if rank == 0 else None
+
+    # ------------------------------------------------------------- CPU baseline (rank 0)
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        ref = CpuReference()
+        ref.step()
+        reps, total = 0, 0.0
+        while total < 10.0 and reps < 20:
+            total += ref.step()
+            reps += 1
+        ref.close()
+        cpu = {"value": ref.pairs * reps / total, "unit": UNIT,
+               "cores": min(ref.cores, ref.pairs), "kind": "port",
+               "sample": "%d steps of %d pairs (1 pair per process); oracle port: C flow_kernel + "
+                         "numpy zoom plugins + numpy Transform3D/loss; host has %d cores"
+                         % (reps, ref.pairs, ref.cores)}
+
+    if rank == 0:
+        peak, peak_src = _peaks()
+        px = synth.H * synth.W
+        kbytes = pipeline.BYTES_PER_PX_ZOOM_SAMPLE * px * B
+        achieved = kbytes / (kernel_ms * 1e-3) / 1e9
+        step_bytes = pipeline.algorithmic_bytes_per_pair(synth.H, synth.W, synth.NUM_3D_SAMPLE) * B
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K,
+            "warmup": Wm, "ms_per_step": ms_max / K, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "batch_per_gpu": B, "height": synth.H,
+                       "width": synth.W, "num_3d_sample": synth.NUM_3D_SAMPLE,
+                       "parallelism": "dp%d (pairs sharded, no collective on the path)" % world,
+                       "l2": "%d rotating input sets; %.0f MB touched per step > 126 MB L2"
+                             % (NSETS, step_bytes / 1e6)},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": d2h, "steps": Ke, "loss_checksum": loss_host},
+            "gpu_launches": step.launches_per_step * K,
+            "roofline": {"bound": "hbm", "kernel": "zoom_sample_kernel", "achieved": achieved,
+                         "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "peak_source": peak_src,
+                         "kernel_us": kernel_ms * 1e3,
+                         "algorithmic_bytes_per_launch": kbytes,
+                         "step_achieved_gbs": step_bytes * K / (ms_max * 1e-3) / 1e9},
+            "kernel_us": breakdown,
+            "clocks": clocks,
+            "cpu_baseline": cpu,
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        if args.steps > 50:
+            args.steps = 50  # bounded: each step is ~0.5 s of CPU work per core
+        run_reference(args, rank)
+        return
+    run_ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

@@ -106,9 +106,15 @@ typedef struct rc_zoom_group {
   int32_t channels;
   int32_t pre_op;   /* RC_PRE_*  applied to each source tap before blending  */
   int32_t post_op;  /* RC_POST_* applied to the blended value                */
-  int32_t accumulate; /* 0: dst = value (req "write"), 1: dst += value ("add") */
+  int32_t flags;    /* RC_ZOOM_ACCUMULATE: dst += value (req "add") instead of dst = value;
+                       RC_ZOOM_SRC_BROADCAST: src is [B,1,H,W] and feeds every dst channel
+                       (np.tile(valid, [1,2,1,1]) of batch_updater_py_multi.py:352 without
+                       materialising the tiled tensor) */
   float mean[4];    /* per-channel constant for RC_PRE_ADD_MEAN / RC_POST_*_SUB_MEAN */
 } rc_zoom_group;
+
+#define RC_ZOOM_ACCUMULATE 1
+#define RC_ZOOM_SRC_BROADCAST 2
 
 #define RC_PRE_NONE 0
 #define RC_PRE_THRESH02 1   /* tap = tap > 0.2 ? 1 : 0   (zoom_mask.py:40-45)          */
@@ -208,6 +214,77 @@ int rc_pm_loss_bwd_dev(const float *points, const float *points_obs,
                        int loss_type, float norm_term, float sl1_scalar,
                        float grad_scale, float *grad_rot, float *grad_trans,
                        int batch_size, int num_points, void *stream);
+
+/* ------------------------------------------------------ fused compare step
+ * One call = one pass of the path between two network evaluations for B
+ * pairs: gpu_flow (lib/pair_matching/batch_updater_py_multi.py:331-352), then
+ * ZoomMask / ZoomImageWithFactor / ZoomFlow / ZoomTrans
+ * (deepim/symbols/deepIM_flownet.py:595-698) and Transform3D + point-matching
+ * loss (:446-499).  Replaces six Python-level CustomOp invocations and their
+ * device<->host syncs by six kernel launches issued from C on one stream.
+ * All pointers are device pointers unless marked host.  Optional outputs may
+ * be NULL.  `marks` (host array of cudaEvent_t, or NULL) receives up to
+ * RC_STEP_MARKS event records: [0] before flow, [1] after flow, [2] after
+ * zoom factor, [3] after the resampler, [4] after ZoomTrans, [5] after the
+ * loss; NULL entries are skipped.
+ */
+#define RC_STEP_MARKS 6
+typedef struct rc_compare_step_args {
+  /* inputs */
+  const float *image_observed;     /* [B,3,H,W] mean-subtracted */
+  const float *image_rendered;     /* [B,3,H,W] */
+  const float *depth_gt_observed;  /* [B,1,H,W] */
+  const float *depth_rendered;     /* [B,1,H,W] (also the rendered "mask", zoom_mask.py:40-45) */
+  const float *mask_observed;      /* [B,1,H,W] */
+  const float *mask_gt_observed;   /* [B,1,H,W] */
+  const float *src_pose;           /* [B,3,4] */
+  const float *KT;                 /* [B,3,4] */
+  const float *Kinv;               /* [3,3] */
+  const float *K;                  /* [3,3] */
+  const float *point_cloud_model;    /* [B,3,N] */
+  const float *point_cloud_weights;  /* [B,3,N] */
+  const float *point_cloud_observed; /* [B,3,N] */
+  const float *rot_est;            /* [B,4] */
+  const float *trans_est;          /* [B,3] */
+  const float *trans_gt;           /* [B,3] */
+  /* outputs */
+  float *flow;                     /* [B,2,H,W] */
+  float *valid;                    /* [B,1,H,W] */
+  float *zoom_factor;              /* [B,4] */
+  int32_t *bbox;                   /* [B,8] or NULL */
+  int32_t *workspace;              /* [B,RC_ZF_WS_INTS] */
+  float *zoom_mask_observed;       /* [B,1,H,W] */
+  float *zoom_mask_gt_observed;    /* [B,1,H,W] */
+  float *zoom_mask_rendered;       /* [B,1,H,W] */
+  float *zoom_image_observed;      /* [B,3,H,W] */
+  float *zoom_image_rendered;      /* [B,3,H,W] */
+  float *zoom_flow;                /* [B,2,H,W] */
+  float *zoom_flow_weights;        /* [B,2,H,W] */
+  float *zoom_trans_gt;            /* [B,3] */
+  float *loss_map;                 /* [B,3,N] or NULL */
+  float *loss_sum;                 /* [B] */
+  /* constants (host values) */
+  float pixel_means[4];            /* per image channel, already in channel order */
+  float T_means[3];
+  float T_stds[3];
+  float norm_term;
+  float sl1_scalar;
+  int32_t rot_coord;
+  int32_t loss_type;
+  int32_t batch_size, height, width, num_points;
+  void *stream;                    /* cudaStream_t */
+  void **marks;                    /* host array of RC_STEP_MARKS cudaEvent_t, or NULL */
+} rc_compare_step_args;
+
+int rc_compare_step_dev(const rc_compare_step_args *args);
+
+/* CUDA-event helpers so that a host language without a CUDA binding can time
+ * kernels on the stream they were launched on. */
+int rc_event_create(void **event);
+int rc_event_destroy(void *event);
+int rc_event_record(void *event, void *stream);
+int rc_event_synchronize(void *event);
+int rc_event_elapsed_ms(void *start, void *end, float *ms);
 
 #ifdef __cplusplus
 }

@@ -22,6 +22,7 @@ RC_PRE_NONE, RC_PRE_THRESH02, RC_PRE_ADD_MEAN = 0, 1, 2
  RC_POST_SUB_MEAN, RC_POST_SPOT_SUB_MEAN) = range(7)
 RC_ROT_MODEL, RC_ROT_CAMERA, RC_ROT_CAMERA_NEW, RC_ROT_NAIVE = range(4)
 RC_PM_L1, RC_PM_L2, RC_PM_SMOOTH_L1 = range(3)
+RC_ZOOM_ACCUMULATE, RC_ZOOM_SRC_BROADCAST = 1, 2
 RC_ZOOM_MAX_GROUPS = 8
 RC_ZOOM_MAX_PLANES = 16
 RC_ZF_WS_INTS = 10
@@ -42,9 +43,39 @@ class rc_zoom_group(ctypes.Structure):
         ("channels", c_int32),
         ("pre_op", c_int32),
         ("post_op", c_int32),
-        ("accumulate", c_int32),
+        ("flags", c_int32),
         ("mean", c_float * 4),
     ]
+
+
+RC_STEP_MARKS = 6
+_STEP_IN = ("image_observed", "image_rendered", "depth_gt_observed", "depth_rendered",
+            "mask_observed", "mask_gt_observed", "src_pose", "KT", "Kinv", "K",
+            "point_cloud_model", "point_cloud_weights", "point_cloud_observed", "rot_est",
+            "trans_est", "trans_gt")
+_STEP_OUT = ("flow", "valid", "zoom_factor", "bbox", "workspace", "zoom_mask_observed",
+             "zoom_mask_gt_observed", "zoom_mask_rendered", "zoom_image_observed",
+             "zoom_image_rendered", "zoom_flow", "zoom_flow_weights", "zoom_trans_gt", "loss_map",
+             "loss_sum")
+
+
+class rc_compare_step_args(ctypes.Structure):
+    """Mirror of `rc_compare_step_args` in include/rendercompare.h (field order matters)."""
+    _fields_ = ([(n, c_void_p) for n in _STEP_IN] + [(n, c_void_p) for n in _STEP_OUT] + [
+        ("pixel_means", c_float * 4),
+        ("T_means", c_float * 3),
+        ("T_stds", c_float * 3),
+        ("norm_term", c_float),
+        ("sl1_scalar", c_float),
+        ("rot_coord", c_int32),
+        ("loss_type", c_int32),
+        ("batch_size", c_int32),
+        ("height", c_int32),
+        ("width", c_int32),
+        ("num_points", c_int32),
+        ("stream", c_void_p),
+        ("marks", POINTER(c_void_p)),
+    ])
 
 
 # name -> (restype, argtypes); every symbol include/rendercompare.h declares.
@@ -70,6 +101,12 @@ SIGNATURES = {
                                        c_int, _P, _P, c_int, c_int, c_int, _P]),
     "rc_pm_loss_fwd_dev": (c_int, [_P, _P, _P, _P, _P, _P, POINTER(c_float), POINTER(c_float),
                                    c_int, c_int, c_float, c_float, _P, _P, _P, c_int, c_int, _P]),
+    "rc_compare_step_dev": (c_int, [POINTER(rc_compare_step_args)]),
+    "rc_event_create": (c_int, [POINTER(c_void_p)]),
+    "rc_event_destroy": (c_int, [c_void_p]),
+    "rc_event_record": (c_int, [c_void_p, c_void_p]),
+    "rc_event_synchronize": (c_int, [c_void_p]),
+    "rc_event_elapsed_ms": (c_int, [c_void_p, c_void_p, POINTER(c_float)]),
     "rc_pm_loss_bwd_dev": (c_int, [_P, _P, _P, _P, _P, _P, POINTER(c_float), POINTER(c_float),
                                    c_int, c_int, c_float, c_float, c_float, _P, _P, c_int, c_int,
                                    _P]),
@@ -121,3 +158,30 @@ def stream_ptr(stream=None) -> int:
 
     s = torch.cuda.current_stream() if stream is None else stream
     return int(s.cuda_stream)
+
+
+class Event(object):
+    """cudaEvent_t created through the C ABI (rc_event_*)."""
+
+    def __init__(self):
+        self.handle = c_void_p()
+        check(load().rc_event_create(ctypes.byref(self.handle)), "rc_event_create")
+
+    def record(self, stream=None):
+        check(load().rc_event_record(self.handle, stream_ptr(stream)), "rc_event_record")
+
+    def synchronize(self):
+        check(load().rc_event_synchronize(self.handle), "rc_event_synchronize")
+
+    def elapsed_ms(self, end) -> float:
+        ms = c_float()
+        check(load().rc_event_elapsed_ms(self.handle, end.handle, ctypes.byref(ms)),
+              "rc_event_elapsed_ms")
+        return float(ms.value)
+
+    def __del__(self):
+        try:
+            if self.handle:
+                load().rc_event_destroy(self.handle)
+        except Exception:
+            pass

@@ -1,0 +1,124 @@
+// step.cu -- the fused compare step: every launch of one pass of the path
+// between two network evaluations, issued from C on one stream.
+//
+// Stands in for the host driver
+//   /root/reference/lib/pair_matching/batch_updater_py_multi.py:331-352 (gpu_flow + tile)
+// and the CustomOp invocations the MXNet executor makes per pass
+//   /root/reference/deepim/symbols/deepIM_flownet.py:595-698, :446-499.
+//
+// B200 design: at batch 16 a step is ~100 us of HBM time; issuing its six
+// launches from Python (ctypes + tensor bookkeeping per call) would leave the
+// GPU idle between kernels.  One C call enqueues everything in a few
+// microseconds, so the host runs ahead of the device and the stream stays full
+// without needing a CUDA graph; optional event marks bracket each kernel for
+// roofline timing on the launching stream.
+#include "common.cuh"
+
+namespace rc {
+static inline int mark(void **marks, int i, cudaStream_t s) {
+  if (marks && marks[i]) RC_CUDA_TRY(cudaEventRecord(static_cast<cudaEvent_t>(marks[i]), s));
+  return RC_OK;
+}
+}  // namespace rc
+
+extern "C" {
+
+int rc_compare_step_dev(const rc_compare_step_args *a) {
+  RC_REQUIRE(a != nullptr, RC_ERR_INVALID_ARG);
+  const int B = a->batch_size, H = a->height, W = a->width, N = a->num_points;
+  RC_REQUIRE(B >= 0 && H > 1 && W > 1 && N >= 0, RC_ERR_INVALID_ARG);
+  if (B == 0) return rc::note_status(RC_OK);
+  cudaStream_t s = static_cast<cudaStream_t>(a->stream);
+  int st;
+  if ((st = rc::mark(a->marks, 0, s)) != RC_OK) return st;
+  // (1) GT flow
+  st = rc_flow_dev(a->depth_rendered, a->depth_gt_observed, a->KT, a->Kinv, a->flow, a->valid, B,
+                   H, W, a->stream);
+  if (st != RC_OK) return st;
+  if ((st = rc::mark(a->marks, 1, s)) != RC_OK) return st;
+  // (2) crop boxes + zoom factor (ZoomMask, first half)
+  st = rc_zoom_factor_dev(a->mask_gt_observed, a->depth_rendered, a->src_pose, a->K, nullptr,
+                          a->zoom_factor, a->bbox, a->workspace, B, 1, H, W, RC_ZF_MASK,
+                          a->stream);
+  if (st != RC_OK) return st;
+  if ((st = rc::mark(a->marks, 2, s)) != RC_OK) return st;
+  // (3) one resampler launch: 3 masks + 6 image channels + 2 flow + 2 flow-weight planes
+  rc_zoom_group g[7];
+  auto set = [&](int i, const float *src, float *dst, int ch, int pre, int post, int flags) {
+    g[i].src = src;
+    g[i].dst = dst;
+    g[i].channels = ch;
+    g[i].pre_op = pre;
+    g[i].post_op = post;
+    g[i].flags = flags;
+    for (int c = 0; c < 4; ++c) g[i].mean[c] = a->pixel_means[c];
+  };
+  int n = 0;
+  if (a->zoom_mask_observed)
+    set(n++, a->mask_observed, a->zoom_mask_observed, 1, RC_PRE_NONE, RC_POST_ROUND, 0);
+  if (a->zoom_mask_gt_observed)
+    set(n++, a->mask_gt_observed, a->zoom_mask_gt_observed, 1, RC_PRE_NONE, RC_POST_ROUND, 0);
+  if (a->zoom_mask_rendered)
+    set(n++, a->depth_rendered, a->zoom_mask_rendered, 1, RC_PRE_THRESH02, RC_POST_ROUND, 0);
+  if (a->zoom_image_observed)
+    set(n++, a->image_observed, a->zoom_image_observed, 3, RC_PRE_ADD_MEAN, RC_POST_SUB_MEAN, 0);
+  if (a->zoom_image_rendered)
+    set(n++, a->image_rendered, a->zoom_image_rendered, 3, RC_PRE_ADD_MEAN, RC_POST_SUB_MEAN, 0);
+  if (a->zoom_flow) set(n++, a->flow, a->zoom_flow, 2, RC_PRE_NONE, RC_POST_DIV_WX, 0);
+  if (a->zoom_flow_weights)
+    set(n++, a->valid, a->zoom_flow_weights, 2, RC_PRE_NONE, RC_POST_ROUND_M045,
+        RC_ZOOM_SRC_BROADCAST);
+  st = rc_zoom_sample_dev(a->zoom_factor, 0, g, n, B, H, W, a->stream);
+  if (st != RC_OK) return st;
+  if ((st = rc::mark(a->marks, 3, s)) != RC_OK) return st;
+  // (4) ZoomTrans of the GT translation label
+  if (a->zoom_trans_gt && a->trans_gt) {
+    st = rc_zoom_trans_dev(a->zoom_factor, a->trans_gt, a->zoom_trans_gt, B, 0, 1, 0, a->stream);
+    if (st != RC_OK) return st;
+  }
+  if ((st = rc::mark(a->marks, 4, s)) != RC_OK) return st;
+  // (5) Transform3D + point-matching loss
+  if (N > 0 && a->loss_sum) {
+    st = rc_pm_loss_fwd_dev(a->point_cloud_model, a->point_cloud_observed, a->point_cloud_weights,
+                            a->rot_est, a->trans_est, a->src_pose, a->T_means, a->T_stds,
+                            a->rot_coord, a->loss_type, a->norm_term, a->sl1_scalar, nullptr,
+                            a->loss_map, a->loss_sum, B, N, a->stream);
+    if (st != RC_OK) return st;
+  }
+  if ((st = rc::mark(a->marks, 5, s)) != RC_OK) return st;
+  return rc::note_status(RC_OK);
+}
+
+int rc_event_create(void **event) {
+  RC_REQUIRE(event != nullptr, RC_ERR_INVALID_ARG);
+  cudaEvent_t e;
+  RC_CUDA_TRY(cudaEventCreate(&e));
+  *event = e;
+  return rc::note_status(RC_OK);
+}
+
+int rc_event_destroy(void *event) {
+  if (event) RC_CUDA_TRY(cudaEventDestroy(static_cast<cudaEvent_t>(event)));
+  return rc::note_status(RC_OK);
+}
+
+int rc_event_record(void *event, void *stream) {
+  RC_REQUIRE(event != nullptr, RC_ERR_INVALID_ARG);
+  RC_CUDA_TRY(cudaEventRecord(static_cast<cudaEvent_t>(event), static_cast<cudaStream_t>(stream)));
+  return rc::note_status(RC_OK);
+}
+
+int rc_event_synchronize(void *event) {
+  RC_REQUIRE(event != nullptr, RC_ERR_INVALID_ARG);
+  RC_CUDA_TRY(cudaEventSynchronize(static_cast<cudaEvent_t>(event)));
+  return rc::note_status(RC_OK);
+}
+
+int rc_event_elapsed_ms(void *start, void *end, float *ms) {
+  RC_REQUIRE(start && end && ms, RC_ERR_INVALID_ARG);
+  RC_CUDA_TRY(cudaEventElapsedTime(ms, static_cast<cudaEvent_t>(start),
+                                   static_cast<cudaEvent_t>(end)));
+  return rc::note_status(RC_OK);
+}
+
+}  // extern "C"

@@ -420,13 +420,14 @@ int rc_zoom_sample_dev(const float *zoom_factor, int inverse, const rc_zoom_grou
     for (int c = 0; c < G.channels; ++c) {
       RC_REQUIRE(P.n_planes < RC_ZOOM_MAX_PLANES, RC_ERR_CAPACITY);
       rc::ZoomPlane &z = P.planes[P.n_planes++];
-      z.src = G.src + c * plane;
+      const bool bcast = (G.flags & RC_ZOOM_SRC_BROADCAST) != 0;
+      z.src = bcast ? G.src : G.src + c * plane;
       z.dst = G.dst + c * plane;
-      z.src_bstride = G.channels * plane;
+      z.src_bstride = bcast ? plane : G.channels * plane;
       z.dst_bstride = G.channels * plane;
       z.pre_op = G.pre_op;
       z.post_op = G.post_op;
-      z.accumulate = G.accumulate;
+      z.accumulate = (G.flags & RC_ZOOM_ACCUMULATE) ? 1 : 0;
       z.channel = c;
       z.mean = G.mean[c];
     }

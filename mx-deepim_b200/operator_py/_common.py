@@ -35,9 +35,10 @@ class Group(object):
     """One rc_zoom_group: a [B,C,H,W] source resampled into a [B,C,H,W] destination."""
 
     def __init__(self, src, dst, pre_op=_lib.RC_PRE_NONE, post_op=_lib.RC_POST_NONE, req="write",
-                 mean=None):
+                 mean=None, broadcast_src=False):
         self.src, self.dst, self.pre_op, self.post_op, self.req, self.mean = (
             src, dst, pre_op, post_op, req, mean)
+        self.broadcast_src = broadcast_src
 
 
 def zoom_sample(zoom_factor, groups, height, width, inverse=False, stream=None):
@@ -52,7 +53,10 @@ def zoom_sample(zoom_factor, groups, height, width, inverse=False, stream=None):
             continue
         check_tensor("zoom source", g.src, 4)
         check_tensor("zoom destination", g.dst, 4)
-        if tuple(g.src.shape) != tuple(g.dst.shape) or g.src.shape[0] != B or \
+        src_shape = tuple(g.src.shape)
+        if g.broadcast_src and src_shape[1] == 1:
+            src_shape = (src_shape[0], g.dst.shape[1]) + src_shape[2:]
+        if src_shape != tuple(g.dst.shape) or g.src.shape[0] != B or \
                 g.src.shape[2] != height or g.src.shape[3] != width:
             raise ValueError("zoom group shape mismatch: src %s dst %s expected [%d,C,%d,%d]"
                              % (tuple(g.src.shape), tuple(g.dst.shape), B, height, width))
@@ -61,10 +65,11 @@ def zoom_sample(zoom_factor, groups, height, width, inverse=False, stream=None):
         e = arr[n]
         e.src = g.src.data_ptr()
         e.dst = g.dst.data_ptr()
-        e.channels = g.src.shape[1]
+        e.channels = g.dst.shape[1]
         e.pre_op = g.pre_op
         e.post_op = g.post_op
-        e.accumulate = acc
+        e.flags = (_lib.RC_ZOOM_ACCUMULATE if acc else 0) | (
+            _lib.RC_ZOOM_SRC_BROADCAST if g.broadcast_src else 0)
         mean = [0.0] * 4 if g.mean is None else [float(v) for v in g.mean] + [0.0] * (4 - len(g.mean))
         for i in range(4):
             e.mean[i] = mean[i]

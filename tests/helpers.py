@@ -1,0 +1,159 @@
+"""Seeded synthetic inputs shared by the tests (LINEMOD-shaped, no dataset needed)."""
+from __future__ import annotations
+
+import numpy as np
+
+H, W = 480, 640
+# LINEMOD intrinsics, /root/reference/experiments/deepim/cfgs/*LM*.yaml:36-45
+K_LM = np.array([[572.4114, 0.0, 325.2611], [0.0, 573.57043, 242.04899], [0.0, 0.0, 1.0]],
+                dtype=np.float32)
+PIXEL_MEANS = np.array([123.68, 116.779, 103.939], dtype=np.float32)  # cfgs/*.yaml:56-59
+
+
+def random_rotation(rng):
+    q = rng.normal(size=4)
+    q /= np.linalg.norm(q)
+    w, x, y, z = q
+    return np.array([
+        [1 - 2 * (y * y + z * z), 2 * (x * y - w * z), 2 * (x * z + w * y)],
+        [2 * (x * y + w * z), 1 - 2 * (x * x + z * z), 2 * (y * z - w * x)],
+        [2 * (x * z - w * y), 2 * (y * z + w * x), 1 - 2 * (x * x + y * y)],
+    ])
+
+
+def small_rotation(rng, sigma_deg=15.0, max_deg=45.0):
+    """Pose noise like toolkit/LM6d_1_gen_rendered_pose.py:59,115-117."""
+    while True:
+        ang = np.deg2rad(rng.normal(0, sigma_deg, size=3))
+        if np.all(np.abs(ang) < np.deg2rad(max_deg)):
+            break
+    cx, cy, cz = np.cos(ang)
+    sx, sy, sz = np.sin(ang)
+    Rx = np.array([[1, 0, 0], [0, cx, -sx], [0, sx, cx]])
+    Ry = np.array([[cy, 0, sy], [0, 1, 0], [-sy, 0, cy]])
+    Rz = np.array([[cz, -sz, 0], [sz, cz, 0], [0, 0, 1]])
+    return Rz @ Ry @ Rx
+
+
+def random_pose_pair(rng, K=K_LM, margin=60):
+    """(pose_src, pose_tgt) float32 [3,4]; projected centre at least `margin` px inside."""
+    z = rng.uniform(0.6, 1.2)
+    u = rng.uniform(margin, W - margin)
+    v = rng.uniform(margin, H - margin)
+    t = np.array([(u - K[0, 2]) / K[0, 0] * z, (v - K[1, 2]) / K[1, 1] * z, z])
+    R = random_rotation(rng)
+    pose_tgt = np.concatenate([R, t[:, None]], axis=1)
+    dR = small_rotation(rng)
+    dt = rng.normal(0, [0.01, 0.01, 0.05])
+    pose_src = np.concatenate([dR @ R, (t + dt)[:, None]], axis=1)
+    return pose_src.astype(np.float32), pose_tgt.astype(np.float32)
+
+
+def ellipsoid_depth(pose, radii, K=K_LM, height=H, width=W):
+    """Analytic depth map (metres, 0 = background) of an ellipsoid with semi-axes `radii`
+    (object frame) at pose [R|t]: nearest intersection of each pixel ray with the surface."""
+    R = pose[:, :3].astype(np.float64)
+    t = pose[:, 3].astype(np.float64)
+    Kinv = np.linalg.inv(K.astype(np.float64))
+    u, v = np.meshgrid(np.arange(width, dtype=np.float64), np.arange(height, dtype=np.float64))
+    rays = np.stack([u, v, np.ones_like(u)], axis=-1) @ Kinv.T  # camera-frame direction, z = 1
+    S = np.diag(1.0 / np.asarray(radii, dtype=np.float64))
+    d = rays @ (S @ R.T).T  # direction in the scaled object frame
+    o = -(S @ R.T @ t)      # camera origin in the scaled object frame
+    a = np.sum(d * d, axis=-1)
+    b = 2 * np.sum(d * o, axis=-1)
+    c = np.dot(o, o) - 1.0
+    disc = b * b - 4 * a * c
+    hit = disc > 0
+    s = np.where(hit, (-b - np.sqrt(np.where(hit, disc, 0))) / (2 * a), 0.0)
+    depth = np.where(hit & (s > 0), s, 0.0)  # ray has z = 1, so the parameter is the depth
+    return depth.astype(np.float32)
+
+
+def make_flow_inputs(batch, seed, occlude=False, K=K_LM):
+    """depth_src (rendered at src pose), depth_tgt (observed at tgt pose, 1 mm quantised),
+    KT, Kinv as the batch updater builds them (batch_updater_py_multi.py:306-345)."""
+    from oracle import pose_np
+
+    rng = np.random.default_rng(seed)
+    depth_src = np.zeros((batch, 1, H, W), np.float32)
+    depth_tgt = np.zeros((batch, 1, H, W), np.float32)
+    KT = np.zeros((batch, 3, 4), np.float64)
+    poses_src = np.zeros((batch, 3, 4), np.float32)
+    poses_tgt = np.zeros((batch, 3, 4), np.float32)
+    for b in range(batch):
+        ps, pt = random_pose_pair(rng, K)
+        radii = rng.uniform(0.04, 0.12, size=3)
+        depth_src[b, 0] = ellipsoid_depth(ps, radii, K)
+        d = ellipsoid_depth(pt, radii, K)
+        d = np.round(d * 1000.0) / 1000.0  # u16 PNG depth in mm (lib/utils/image.py:200-205)
+        if occlude:
+            x0, y0 = rng.integers(0, W - 80), rng.integers(0, H - 80)
+            d[y0:y0 + 80, x0:x0 + 80] = 0.4
+        depth_tgt[b, 0] = d.astype(np.float32)
+        KT[b] = pose_np.make_KT(K, ps, pt)
+        poses_src[b], poses_tgt[b] = ps, pt
+    Kinv = np.array(np.linalg.inv(np.matrix(K)))  # batch_updater_py_multi.py:70
+    return dict(depth_src=depth_src, depth_tgt=depth_tgt, KT=KT.astype(np.float32),
+                Kinv=Kinv.astype(np.float32), pose_src=poses_src, pose_tgt=poses_tgt)
+
+
+def make_zoom_inputs(batch, seed, K=K_LM, empty_rendered=()):
+    """Everything the zoom plugins consume for `batch` pairs: masks, mean-subtracted images,
+    depths, flow + weights (from the flow oracle) and src poses."""
+    from oracle import flow_np
+
+    rng = np.random.default_rng(seed)
+    f = make_flow_inputs(batch, seed, K=K)
+    depth_r, depth_o = f["depth_src"], f["depth_tgt"]
+    for b in empty_rendered:
+        depth_r[b] = 0
+    mask_rendered = depth_r.copy()  # the graph feeds rendered depth as the mask (zoom_mask.py:40)
+    mask_gt_observed = (depth_o > 0).astype(np.float32)
+    mask_observed = mask_gt_observed.copy()
+    for b in range(batch):  # the estimated observed mask is a perturbed GT mask
+        y0, x0 = rng.integers(0, H - 40), rng.integers(0, W - 40)
+        mask_observed[b, 0, y0:y0 + 40, x0:x0 + 40] = 0
+    pm = PIXEL_MEANS[[2, 1, 0]].reshape(1, 3, 1, 1)  # batch_updater_py_multi.py:24-25
+    tex = rng.uniform(0, 255, size=(batch, 3, H, W)).astype(np.float32)
+    image_rendered = (tex * (depth_r > 0) - pm).astype(np.float32)
+    bg = rng.uniform(1, 255, size=(batch, 3, H, W)).astype(np.float32)
+    image_observed = (np.where(depth_o > 0, tex[:, ::-1], bg) - pm).astype(np.float32)
+    flow, valid = flow_np.flow_kernel_cpu(depth_r, depth_o, f["KT"], f["Kinv"])
+    flow_weights = np.tile(valid, [1, 2, 1, 1])  # batch_updater_py_multi.py:352
+    return dict(mask_observed=mask_observed, mask_gt_observed=mask_gt_observed,
+                mask_rendered=mask_rendered, image_observed=image_observed,
+                image_rendered=image_rendered, depth_observed=depth_o, depth_rendered=depth_r,
+                flow=flow, flow_weights=flow_weights, src_pose=f["pose_src"],
+                tgt_pose=f["pose_tgt"], KT=f["KT"], Kinv=f["Kinv"])
+
+
+def make_points_inputs(batch, seed, num_points=3000, num_keep=None):
+    """point_cloud_model / weights / observed as lib/utils/image.py:559-596 builds them, random
+    unit quaternion + translation deltas near the GT update, src/tgt poses."""
+    from oracle import pose_np
+
+    rng = np.random.default_rng(seed)
+    num_keep = num_points if num_keep is None else num_keep
+    pts = np.zeros((batch, 3, num_points), np.float32)
+    wts = np.zeros((batch, 3, num_points), np.float32)
+    obs = np.zeros((batch, 3, num_points), np.float32)
+    rot = np.zeros((batch, 4), np.float32)
+    trans = np.zeros((batch, 3), np.float32)
+    poses_src = np.zeros((batch, 3, 4), np.float32)
+    poses_tgt = np.zeros((batch, 3, 4), np.float32)
+    for b in range(batch):
+        ps, pt = random_pose_pair(rng)
+        model = rng.uniform(-0.1, 0.1, size=(num_keep, 3))
+        pts[b, :, :num_keep] = model.T
+        wts[b, :, :num_keep] = 1
+        obs[b] = (pt[:, :3].astype(np.float64) @ pts[b].astype(np.float64) +
+                  pt[:, 3:].astype(np.float64))
+        q, t = pose_np.calc_RT_delta(ps, pt, np.zeros(3), np.ones(3), "CAMERA", "QUAT")
+        q = q + rng.normal(0, 0.02, size=4)
+        q /= np.linalg.norm(q)
+        rot[b] = q
+        trans[b] = t + rng.normal(0, 0.01, size=3)
+        poses_src[b], poses_tgt[b] = ps, pt
+    return dict(points=pts, weights=wts, points_obs=obs, rotation=rot, translation=trans,
+                pose_src=poses_src, pose_tgt=poses_tgt)
