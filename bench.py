@@ -246,9 +246,9 @@ def run_ours(args, rank, world, local_rank):
     for i, m in enumerate(full):
         step.run(None, args=bound[i % NSETS], marks=m)
     torch.cuda.synchronize()
-    names = ["flow", "zoom_bbox_factor", "zoom_sample", "zoom_trans", "pm_loss"]
-    breakdown = {n: sum(m[j].elapsed_ms(m[j + 1]) for m in full) / len(full) * 1e3
-                 for j, n in enumerate(names)}
+    names = {"flow": (0, 1), "zoom_bbox_factor_trans": (1, 2), "zoom_sample": (2, 3), "pm_loss": (4, 5)}
+    breakdown = {n: sum(m[a].elapsed_ms(m[b]) for m in full) / len(full) * 1e3
+                 for n, (a, b) in names.items()}
 
     # ------------------------------------------------ end-to-end arm (host buffers, `e2e`)
     pinned = [{k: torch.from_numpy(np.ascontiguousarray(h[k])).pin_memory()

@@ -88,7 +88,8 @@ int rc_flow_dev(const float *depth_src, const float *depth_tgt, const float *KT,
  *   bbox        [B,8]  int32: obs x0,x1,y0,y1 then rend x0,x1,y0,y1
  *               (x0 > x1 marks an empty set; rend empty -> reference fallback,
  *               obs empty -> zoom_factor row is NaN, the reference raises)
- *   workspace   [B,RC_ZF_WS_INTS] int32 scratch (caller-owned; initialised by the call)
+ *   workspace   [B,RC_ZF_WS_INTS] int32 scratch, caller-owned.  Must be ZERO before the first
+ *               call; every call leaves it zeroed again (no init launch, no memset).
  */
 #define RC_ZF_WS_INTS 10
 #define RC_ZF_MASK 0
@@ -221,12 +222,12 @@ int rc_pm_loss_bwd_dev(const float *points, const float *points_obs,
  * ZoomMask / ZoomImageWithFactor / ZoomFlow / ZoomTrans
  * (deepim/symbols/deepIM_flownet.py:595-698) and Transform3D + point-matching
  * loss (:446-499).  Replaces six Python-level CustomOp invocations and their
- * device<->host syncs by six kernel launches issued from C on one stream.
+ * device<->host syncs by four kernel launches issued from C on one stream.
  * All pointers are device pointers unless marked host.  Optional outputs may
  * be NULL.  `marks` (host array of cudaEvent_t, or NULL) receives up to
  * RC_STEP_MARKS event records: [0] before flow, [1] after flow, [2] after
- * zoom factor, [3] after the resampler, [4] after ZoomTrans, [5] after the
- * loss; NULL entries are skipped.
+ * zoom factor (+ fused ZoomTrans), [3] after the resampler, [4] = [3], [5] after
+ * the loss; NULL entries are skipped.
  */
 #define RC_STEP_MARKS 6
 typedef struct rc_compare_step_args {
@@ -252,7 +253,7 @@ typedef struct rc_compare_step_args {
   float *valid;                    /* [B,1,H,W] */
   float *zoom_factor;              /* [B,4] */
   int32_t *bbox;                   /* [B,8] or NULL */
-  int32_t *workspace;              /* [B,RC_ZF_WS_INTS] */
+  int32_t *workspace;              /* [B,RC_ZF_WS_INTS], zero before first use */
   float *zoom_mask_observed;       /* [B,1,H,W] */
   float *zoom_mask_gt_observed;    /* [B,1,H,W] */
   float *zoom_mask_rendered;       /* [B,1,H,W] */

@@ -29,6 +29,14 @@ int note_status(int status);
     if (!(cond)) return ::rc::note_status(code);  \
   } while (0)
 
+// zoom.cu: bbox + zoom factor, optionally with ZoomTrans forward fused into the finalising
+// block (trans_in/trans_out both NULL or both set).
+int launch_zoom_factor(const float *obs, const float *rend, const float *src_pose,
+                       const float *K, const float *pixel_means, float *zoom_factor,
+                       int32_t *bbox, int32_t *workspace, const float *trans_in,
+                       float *trans_out, int batch_size, int channels, int height, int width,
+                       int mode, void *stream);
+
 static inline bool aligned16(const void *p) {
   return (reinterpret_cast<uintptr_t>(p) & 15u) == 0;
 }

@@ -8,15 +8,22 @@
 //
 // B200 design: the reference runs three per-sample Python loops with a
 // device->host sync each plus two cuBLAS batched GEMMs with a 3-wide inner
-// dimension.  Here one block owns one sample: thread 0 evaluates the pose
-// algebra (a few dozen scalar operations, float64 where numpy promotes to
-// float64) into shared memory, then all threads stream the [3,N] point arrays
-// with coalesced loads, and the 1 (loss), 3 (sum G) and 9 (G X^T) sums are
-// reduced with warp shuffles and one shared-memory stage -- deterministic, no
-// atomics.  The path moves 0.144 MB (fwd) / 0.108 MB (bwd) per pair, so it is
-// launch/latency bound; fusing loss and Transform3D removes four launches and
-// the [B,3,N] intermediate.
+// dimension.  Here one thread-block CLUSTER of eight CTAs owns one sample
+// (2048 threads for N = 3000 points, so every thread has at most two points
+// and all its loads are in flight at once): thread 0 of each CTA evaluates the
+// pose algebra (a few dozen scalar operations, float64 where numpy promotes to
+// float64) into shared memory, all threads stream the [3,N] point arrays with
+// coalesced loads, and the 1 (loss), 3 (sum G) and 9 (G X^T) sums are reduced
+// with warp shuffles, one shared-memory stage per CTA and one distributed-
+// shared-memory stage across the cluster (rank order) -- deterministic, no
+// atomics, no global workspace.  The path moves 0.144 MB (fwd) / 0.108 MB
+// (bwd) per pair, so it is latency bound; the cluster spreads a batch of 16
+// pairs over 128 SMs instead of 16.
+#include <cooperative_groups.h>
+
 #include "common.cuh"
+
+namespace cg = cooperative_groups;
 
 namespace rc {
 
@@ -138,19 +145,48 @@ __device__ __forceinline__ double block_sum(double v, double *sm) {
 }
 
 constexpr int PM_THREADS = 256;
+constexpr int PM_CLUSTER = 8;  // CTAs per sample (portable cluster size limit)
 
-// One block per sample.  est / loss_map / loss_sum are optional outputs;
-// obs == nullptr turns the kernel into plain Transform3D forward.
-__global__ void __launch_bounds__(PM_THREADS)
+// Sum `n` per-CTA partials across the cluster through distributed shared memory:
+// every CTA writes its values into rank 0's table, rank 0 adds them in rank order.
+// Returns true in (rank 0, thread 0), where out[0..n) holds the totals.
+template <int NV>
+__device__ __forceinline__ bool cluster_sum(const double (&mine)[NV], double *table /* smem [PM_CLUSTER][NV] */,
+                                            double (&out)[NV]) {
+  cg::cluster_group cluster = cg::this_cluster();
+  const unsigned rank = cluster.block_rank();
+  if (threadIdx.x == 0) {
+    double *dst = cluster.map_shared_rank(table, 0);
+#pragma unroll
+    for (int i = 0; i < NV; ++i) dst[rank * NV + i] = mine[i];
+  }
+  cluster.sync();
+  if (rank == 0 && threadIdx.x == 0) {
+#pragma unroll
+    for (int i = 0; i < NV; ++i) {
+      double a = 0.0;
+      for (int r = 0; r < PM_CLUSTER; ++r) a += table[r * NV + i];
+      out[i] = a;
+    }
+    return true;
+  }
+  return false;
+}
+
+// One cluster of PM_CLUSTER blocks per sample.  est / loss_map / loss_sum are optional
+// outputs; obs == nullptr turns the kernel into plain Transform3D forward.
+__global__ void __cluster_dims__(PM_CLUSTER, 1, 1) __launch_bounds__(PM_THREADS)
 pm_fwd_kernel(const float *__restrict__ points, const float *__restrict__ obs,
               const float *__restrict__ weights, const float *__restrict__ rotation,
               const float *__restrict__ trans, const float *__restrict__ pose_src,
               PoseParams pp, int loss_type, float norm_term, float sigma, float *est,
               float *__restrict__ loss_map, float *__restrict__ loss_sum, int N,
               int accumulate) {
-  const int b = blockIdx.x;
+  const int b = blockIdx.x / PM_CLUSTER;
+  const int crank = blockIdx.x % PM_CLUSTER;
   __shared__ PoseOut po;
   __shared__ double red[PM_THREADS / 32];
+  __shared__ double table[PM_CLUSTER];
   if (threadIdx.x == 0) compose_pose(rotation + b * 4, trans + b * 3, pose_src + b * 12, pp, po);
   __syncthreads();
   float R[9], T[3];
@@ -161,7 +197,7 @@ pm_fwd_kernel(const float *__restrict__ points, const float *__restrict__ obs,
   const float sigma2 = sigma * sigma, inv_sigma2 = 1.f / (sigma * sigma);
   const size_t base = (size_t)b * 3 * N;
   double acc = 0.0;
-  for (int n = threadIdx.x; n < N; n += PM_THREADS) {
+  for (int n = crank * PM_THREADS + threadIdx.x; n < N; n += PM_THREADS * PM_CLUSTER) {
     const float p0 = __ldg(points + base + n);
     const float p1 = __ldg(points + base + N + n);
     const float p2 = __ldg(points + base + 2 * N + n);
@@ -181,10 +217,10 @@ pm_fwd_kernel(const float *__restrict__ points, const float *__restrict__ obs,
       }
     }
   }
-  if (loss_sum) {
-    const double s = block_sum<PM_THREADS>(acc, red);
-    if (threadIdx.x == 0) loss_sum[b] = (float)s;
-  }
+  // every CTA of the cluster takes part in the reduction (cluster.sync inside)
+  double mine[1], tot[1];
+  mine[0] = block_sum<PM_THREADS>(acc, red);
+  if (cluster_sum<1>(mine, table, tot) && loss_sum) loss_sum[b] = (float)tot[0];
 }
 
 // quat2mat_backward, transform3d.py:256-327 (float64 tail, float32 result).
@@ -222,17 +258,18 @@ __device__ void quat2mat_bwd(const double *D, const float *q, float *gq, int acc
 // loss definition (MakeLoss grad_scale, weights, d|x|/dx, 1/norm); otherwise
 // it is read from out_grad (plain Transform3D backward).
 template <bool FROM_LOSS>
-__global__ void __launch_bounds__(PM_THREADS)
+__global__ void __cluster_dims__(PM_CLUSTER, 1, 1) __launch_bounds__(PM_THREADS)
 pm_bwd_kernel(const float *__restrict__ out_grad, const float *__restrict__ points,
               const float *__restrict__ obs, const float *__restrict__ weights,
               const float *__restrict__ rotation, const float *__restrict__ trans,
               const float *__restrict__ pose_src, PoseParams pp, int loss_type,
               float norm_term, float sigma, float grad_scale, float *__restrict__ grad_rot,
               float *__restrict__ grad_trans, int N, int accumulate) {
-  const int b = blockIdx.x;
+  const int b = blockIdx.x / PM_CLUSTER;
+  const int crank = blockIdx.x % PM_CLUSTER;
   __shared__ PoseOut po;
   __shared__ double red[PM_THREADS / 32];
-  __shared__ double sums[12];
+  __shared__ double table[PM_CLUSTER * 12];
   if (threadIdx.x == 0) compose_pose(rotation + b * 4, trans + b * 3, pose_src + b * 12, pp, po);
   __syncthreads();
   float R[9], T[3], Rs[9], Ts[3];
@@ -250,7 +287,7 @@ pm_bwd_kernel(const float *__restrict__ out_grad, const float *__restrict__ poin
   const size_t base = (size_t)b * 3 * N;
   double gt[3] = {0, 0, 0};  // sum_n G            (transform3d.py:138)
   double gr[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};  // G X^T (:154-157)
-  for (int n = threadIdx.x; n < N; n += PM_THREADS) {
+  for (int n = crank * PM_THREADS + threadIdx.x; n < N; n += PM_THREADS * PM_CLUSTER) {
     float p[3];
     p[0] = __ldg(points + base + n);
     p[1] = __ldg(points + base + N + n);
@@ -286,17 +323,12 @@ pm_bwd_kernel(const float *__restrict__ out_grad, const float *__restrict__ poin
       gr[k * 3 + 2] += (double)g * xr[2];
     }
   }
+  double mine[12], sums[12];
 #pragma unroll
-  for (int k = 0; k < 3; ++k) {
-    const double s = block_sum<PM_THREADS>(gt[k], red);
-    if (threadIdx.x == 0) sums[k] = s;
-  }
+  for (int k = 0; k < 3; ++k) mine[k] = block_sum<PM_THREADS>(gt[k], red);
 #pragma unroll
-  for (int k = 0; k < 9; ++k) {
-    const double s = block_sum<PM_THREADS>(gr[k], red);
-    if (threadIdx.x == 0) sums[3 + k] = s;
-  }
-  if (threadIdx.x != 0) return;
+  for (int k = 0; k < 9; ++k) mine[3 + k] = block_sum<PM_THREADS>(gr[k], red);
+  if (!cluster_sum<12>(mine, table, sums)) return;
   // values the reference holds as float32 NDArrays
   float Df[3], Gf[9];
 #pragma unroll
@@ -367,7 +399,7 @@ int rc_transform3d_fwd_dev(const float *points, const float *rotation, const flo
   RC_REQUIRE(rc::fill_pose_params(pp, T_means, T_stds, rot_coord) == RC_OK, RC_ERR_INVALID_ARG);
   if (batch_size == 0 || num_points == 0) return rc::note_status(RC_OK);
   RC_REQUIRE(points && rotation && trans && pose_src && out, RC_ERR_INVALID_ARG);
-  rc::pm_fwd_kernel<<<batch_size, rc::PM_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
+  rc::pm_fwd_kernel<<<batch_size * rc::PM_CLUSTER, rc::PM_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
       points, nullptr, nullptr, rotation, trans, pose_src, pp, RC_PM_L1, 1.f, 1.f, out, nullptr,
       nullptr, num_points, accumulate);
   return rc::note_status(rc::check_launch());
@@ -384,7 +416,7 @@ int rc_transform3d_bwd_dev(const float *out_grad, const float *points, const flo
   if (batch_size == 0) return rc::note_status(RC_OK);
   RC_REQUIRE(out_grad && points && rotation && trans && pose_src && grad_rot && grad_trans,
              RC_ERR_INVALID_ARG);
-  rc::pm_bwd_kernel<false><<<batch_size, rc::PM_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
+  rc::pm_bwd_kernel<false><<<batch_size * rc::PM_CLUSTER, rc::PM_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
       out_grad, points, nullptr, nullptr, rotation, trans, pose_src, pp, RC_PM_L1, 1.f, 1.f, 1.f,
       grad_rot, grad_trans, num_points, accumulate);
   return rc::note_status(rc::check_launch());
@@ -402,7 +434,7 @@ int rc_pm_loss_fwd_dev(const float *points, const float *points_obs, const float
   RC_REQUIRE(rc::fill_pose_params(pp, T_means, T_stds, rot_coord) == RC_OK, RC_ERR_INVALID_ARG);
   if (batch_size == 0) return rc::note_status(RC_OK);
   RC_REQUIRE(points && points_obs && weights && rotation && trans && pose_src, RC_ERR_INVALID_ARG);
-  rc::pm_fwd_kernel<<<batch_size, rc::PM_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
+  rc::pm_fwd_kernel<<<batch_size * rc::PM_CLUSTER, rc::PM_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
       points, points_obs, weights, rotation, trans, pose_src, pp, loss_type, norm_term,
       sl1_scalar, est, loss_map, loss_sum, num_points, 0);
   return rc::note_status(rc::check_launch());
@@ -422,7 +454,7 @@ int rc_pm_loss_bwd_dev(const float *points, const float *points_obs, const float
   RC_REQUIRE(points && points_obs && weights && rotation && trans && pose_src && grad_rot &&
                  grad_trans,
              RC_ERR_INVALID_ARG);
-  rc::pm_bwd_kernel<true><<<batch_size, rc::PM_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
+  rc::pm_bwd_kernel<true><<<batch_size * rc::PM_CLUSTER, rc::PM_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
       nullptr, points, points_obs, weights, rotation, trans, pose_src, pp, loss_type, norm_term,
       sl1_scalar, grad_scale, grad_rot, grad_trans, num_points, 0);
   return rc::note_status(rc::check_launch());

@@ -6,9 +6,10 @@
 // and the CustomOp invocations the MXNet executor makes per pass
 //   /root/reference/deepim/symbols/deepIM_flownet.py:595-698, :446-499.
 //
-// B200 design: at batch 16 a step is ~100 us of HBM time; issuing its six
+// B200 design: at batch 16 a step is ~100 us of HBM time; issuing its
 // launches from Python (ctypes + tensor bookkeeping per call) would leave the
-// GPU idle between kernels.  One C call enqueues everything in a few
+// GPU idle between kernels.  One C call enqueues all four kernels (flow; bbox + zoom
+// factor + ZoomTrans; resampler; point-matching loss) in a few
 // microseconds, so the host runs ahead of the device and the stream stays full
 // without needing a CUDA graph; optional event marks bracket each kernel for
 // roofline timing on the launching stream.
@@ -37,9 +38,11 @@ int rc_compare_step_dev(const rc_compare_step_args *a) {
   if (st != RC_OK) return st;
   if ((st = rc::mark(a->marks, 1, s)) != RC_OK) return st;
   // (2) crop boxes + zoom factor (ZoomMask, first half)
-  st = rc_zoom_factor_dev(a->mask_gt_observed, a->depth_rendered, a->src_pose, a->K, nullptr,
-                          a->zoom_factor, a->bbox, a->workspace, B, 1, H, W, RC_ZF_MASK,
-                          a->stream);
+  // ZoomTrans of the GT translation label rides in the finalising block of the same kernel
+  const bool zt = a->zoom_trans_gt && a->trans_gt;
+  st = rc::launch_zoom_factor(a->mask_gt_observed, a->depth_rendered, a->src_pose, a->K, nullptr,
+                              a->zoom_factor, a->bbox, a->workspace, zt ? a->trans_gt : nullptr,
+                              zt ? a->zoom_trans_gt : nullptr, B, 1, H, W, RC_ZF_MASK, a->stream);
   if (st != RC_OK) return st;
   if ((st = rc::mark(a->marks, 2, s)) != RC_OK) return st;
   // (3) one resampler launch: 3 masks + 6 image channels + 2 flow + 2 flow-weight planes
@@ -71,13 +74,8 @@ int rc_compare_step_dev(const rc_compare_step_args *a) {
   st = rc_zoom_sample_dev(a->zoom_factor, 0, g, n, B, H, W, a->stream);
   if (st != RC_OK) return st;
   if ((st = rc::mark(a->marks, 3, s)) != RC_OK) return st;
-  // (4) ZoomTrans of the GT translation label
-  if (a->zoom_trans_gt && a->trans_gt) {
-    st = rc_zoom_trans_dev(a->zoom_factor, a->trans_gt, a->zoom_trans_gt, B, 0, 1, 0, a->stream);
-    if (st != RC_OK) return st;
-  }
   if ((st = rc::mark(a->marks, 4, s)) != RC_OK) return st;
-  // (5) Transform3D + point-matching loss
+  // (4) Transform3D + point-matching loss
   if (N > 0 && a->loss_sum) {
     st = rc_pm_loss_fwd_dev(a->point_cloud_model, a->point_cloud_observed, a->point_cloud_weights,
                             a->rot_est, a->trans_est, a->src_pose, a->T_means, a->T_stds,

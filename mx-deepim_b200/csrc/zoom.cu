@@ -50,17 +50,11 @@ __device__ __forceinline__ float comp(const float4 &v, int k) {
 
 // workspace layout per sample (int32 x 10):
 //   [0..3] obs x0,x1,y0,y1   [4..7] rend x0,x1,y0,y1   [8] ticket  [9] unused
+// Entries are kept in an all-zero-when-idle encoding so that no init launch is needed:
+// minima are stored as INT_MAX - x and maxima as x + 1, both merged with atomicMax
+// (0 = empty set); the finalising block reads them with atomicExch(.., 0), which leaves
+// the workspace zeroed for the next call.
 #define RC_ZF_WS_STRIDE RC_ZF_WS_INTS
-
-__global__ void zoom_bbox_init_kernel(int32_t *ws, int B) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= B * RC_ZF_WS_STRIDE) return;
-  const int k = i % RC_ZF_WS_STRIDE;
-  int v = 0;
-  if (k == 0 || k == 2 || k == 4 || k == 6) v = INT_MAX;
-  if (k == 1 || k == 3 || k == 5 || k == 7) v = -1;
-  ws[i] = v;
-}
 
 // Zoom factor from the two boxes; float64 scalar arithmetic as numpy 1.x
 // evaluates zoom_mask.py:63-105 (np.float32 scalar op Python/int64 scalar ->
@@ -117,7 +111,9 @@ __global__ void __launch_bounds__(256)
 zoom_bbox_kernel(const float *__restrict__ obs, const float *__restrict__ rend,
                  const float *__restrict__ src_pose, const float *__restrict__ K,
                  const float *__restrict__ pixel_means, float *__restrict__ zoom_factor,
-                 int32_t *__restrict__ bbox, int32_t *__restrict__ ws, int C, int H, int W) {
+                 int32_t *__restrict__ bbox, int32_t *__restrict__ ws,
+                 const float *__restrict__ trans_in, float *__restrict__ trans_out, int C, int H,
+                 int W) {
   const int b = blockIdx.y;
   const int quads = (H * W) >> 2;
   const size_t plane = (size_t)H * W;
@@ -173,9 +169,9 @@ zoom_bbox_kernel(const float *__restrict__ obs, const float *__restrict__ rend,
     for (int i = 1; i < (int)(blockDim.x >> 5); ++i)
       acc = (k & 1) ? max(acc, sm[i][k]) : min(acc, sm[i][k]);
     if (k & 1) {
-      if (acc >= 0) atomicMax(w + k, acc);
+      if (acc >= 0) atomicMax(w + k, acc + 1);
     } else {
-      if (acc != INT_MAX) atomicMin(w + k, acc);
+      if (acc != INT_MAX) atomicMax(w + k, INT_MAX - acc);
     }
   }
   // last block of this sample finalises (ticket counter; fence orders the atomics)
@@ -190,9 +186,19 @@ zoom_bbox_kernel(const float *__restrict__ obs, const float *__restrict__ rend,
     __threadfence();
     int32_t fin[8];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) fin[k] = atomicAdd(w + k, 0);  // coherent read at L2
+    for (int k = 0; k < 8; ++k) {
+      const int e = atomicExch(w + k, 0);  // coherent read at L2, and reset for the next call
+      fin[k] = (k & 1) ? e - 1 : INT_MAX - e;
+    }
+    atomicExch(w + 8, 0);
     zoom_factor_finalize(fin, src_pose + b * 12, K, zoom_factor + b * 4,
                          bbox ? bbox + b * 8 : nullptr, H, W);
+    if (trans_out) {  // fused ZoomTrans forward (zoom_trans.py:30-44) of this sample
+      const float wx = zoom_factor[b * 4];
+      trans_out[b * 3 + 0] = __fdiv_rn(trans_in[b * 3 + 0], wx);
+      trans_out[b * 3 + 1] = __fdiv_rn(trans_in[b * 3 + 1], wx);
+      trans_out[b * 3 + 2] = trans_in[b * 3 + 2];
+    }
   }
 }
 
@@ -257,40 +263,169 @@ __device__ __forceinline__ float pre(float v, int pre_op, float mean) {
   return v;
 }
 
-// grid = (ceil(H*W/4 / 256), B); block = 256.
-__global__ void __launch_bounds__(256)
-zoom_sample_kernel(const __grid_constant__ ZoomParams P) {
+__device__ __forceinline__ void post4(float (&v)[4], const ZoomPlane &zp, const ZoomParams &P,
+                                      float wx_in, int i0, int j) {
+  switch (zp.post_op) {
+    case RC_POST_ROUND:
+#pragma unroll
+      for (int k = 0; k < 4; ++k) v[k] = roundf(v[k]);
+      break;
+    case RC_POST_ROUND_M045:
+#pragma unroll
+      for (int k = 0; k < 4; ++k) v[k] = roundf(__fsub_rn(v[k], 0.45f));
+      break;
+    case RC_POST_DIV_WX:
+#pragma unroll
+      for (int k = 0; k < 4; ++k) v[k] = __fdiv_rn(v[k], wx_in);
+      break;
+    case RC_POST_MUL_WX:
+#pragma unroll
+      for (int k = 0; k < 4; ++k) v[k] = __fmul_rn(v[k], wx_in);
+      break;
+    case RC_POST_SUB_MEAN:
+#pragma unroll
+      for (int k = 0; k < 4; ++k) v[k] = __fsub_rn(v[k], zp.mean);
+      break;
+    case RC_POST_SPOT_SUB_MEAN:
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int x = i0 + k;
+        const float spot = (zp.channel == 0 && x >= P.spot_x0 && x < P.spot_x1 &&
+                            j >= P.spot_y0 && j < P.spot_y1) ? 255.f : 0.f;
+        v[k] = __fsub_rn(fmaxf(v[k], spot), zp.mean);
+      }
+      break;
+    default:
+      break;
+  }
+}
+
+__device__ __forceinline__ void store4(const ZoomPlane &zp, int b, int q, const float (&v)[4]) {
+  float4 *d = reinterpret_cast<float4 *>(zp.dst + (long long)b * zp.dst_bstride) + q;
+  float4 o = make_float4(v[0], v[1], v[2], v[3]);
+  if (zp.accumulate) {
+    const float4 old = *d;
+    o.x += old.x;
+    o.y += old.y;
+    o.z += old.z;
+    o.w += old.w;
+  }
+  st_f4(d, o);
+}
+
+// The four-tap blend of MXNet's BilinearSampler (bilinear_sampler.cu forward kernel),
+// evaluated in float32 in the operator's left-to-right association.
+__device__ __forceinline__ float blend(float tl, float tr, float bl, float br, float wyt,
+                                       float wyb, float wxl, float wxr) {
+  float v = __fmul_rn(__fmul_rn(tl, wyt), wxl);
+  v = __fmaf_rn(__fmul_rn(tr, wyt), wxr, v);
+  v = __fmaf_rn(__fmul_rn(bl, wyb), wxl, v);
+  v = __fmaf_rn(__fmul_rn(br, wyb), wxr, v);
+  return v;
+}
+
+// Output tile of one block: ZT_W x ZT_H pixels, 256 threads, four adjacent pixels each.
+constexpr int ZT_W = 64;
+constexpr int ZT_H = 16;
+constexpr int ZT_THREADS = 256;
+
+// grid = (ceil(W/ZT_W), ceil(H/ZT_H), B); block = 256; dynamic smem = smem_floats * 4.
+//
+// The source window of a tile -- [x_lo, x_hi] x [y_lo, y_hi], every tap any of its
+// 1024 outputs can touch -- is staged into shared memory once per plane with the
+// pre-operation applied and out-of-image taps set to zero, so the per-output work is
+// four conflict-free LDS, seven FP32 operations and a quarter of a 128-bit store.
+// As many planes as fit are staged per barrier pair.  Tiles whose window does not fit
+// (strong zoom-out / inverse zoom) fall back to gathering through the read-only path.
+__global__ void __launch_bounds__(ZT_THREADS)
+zoom_sample_kernel(const __grid_constant__ ZoomParams P, int smem_floats) {
+  extern __shared__ float win[];
   const int H = P.H, W = P.W;
-  const int b = blockIdx.y;
-  const int q = blockIdx.x * blockDim.x + threadIdx.x;
-  if (q >= ((H * W) >> 2)) return;
-  const int p = q << 2;
-  const int j = p / W;
-  const int i0 = p - j * W;
+  const int b = blockIdx.z;
+  const int tx4 = threadIdx.x & 15, trow = threadIdx.x >> 4;
+  const int i_first = blockIdx.x * ZT_W, j_first = blockIdx.y * ZT_H;
+  const int i_last = min(i_first + ZT_W, W) - 1, j_last = min(j_first + ZT_H, H) - 1;
+  const int i0 = i_first + tx4 * 4, j = j_first + trow;
+  const bool active = (i0 < W) && (j < H);
 
   float wx, wy, tx, ty, wx_in;
   zoom_affine(P.zoom_factor + b * 4, P.inverse, H, W, wx, wy, tx, ty, wx_in);
   const float stepx = (float)(2.0 / (W - 1)), stepy = (float)(2.0 / (H - 1));
+  const float nxm1 = (float)(W - 1), nym1 = (float)(H - 1);
 
-  const float yr = src_coord(j, stepy, wy, ty, (float)(H - 1));
+  // per-thread coordinates (clamped indices keep inactive threads harmless)
+  const int jc = min(j, H - 1);
+  const float yr = src_coord(jc, stepy, wy, ty, nym1);
   const float yf = floorf(yr);
   const int y0 = (int)yf;
-  const float wyt = __fsub_rn(1.0f, __fsub_rn(yr, yf));  // top weight
+  const float wyt = __fsub_rn(1.0f, __fsub_rn(yr, yf));
   const float wyb = __fsub_rn(1.0f, wyt);
-  const bool yin0 = (y0 >= 0) && (y0 <= H - 1);
-  const bool yin1 = (y0 + 1 >= 0) && (y0 + 1 <= H - 1);
-
   int x0[4];
   float wxl[4], wxr[4];
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
-    const float xr = src_coord(i0 + k, stepx, wx, tx, (float)(W - 1));
+    const float xr = src_coord(min(i0 + k, W - 1), stepx, wx, tx, nxm1);
     const float xf = floorf(xr);
     x0[k] = (int)xf;
     wxl[k] = __fsub_rn(1.0f, __fsub_rn(xr, xf));
     wxr[k] = __fsub_rn(1.0f, wxl[k]);
   }
+  const int q = (j * W + i0) >> 2;
 
+  // tile window (block-uniform); src_coord is monotone in the index when the scale is > 0
+  const float fx_lo = floorf(src_coord(i_first, stepx, wx, tx, nxm1));
+  const float fx_hi = floorf(src_coord(i_last, stepx, wx, tx, nxm1));
+  const float fy_lo = floorf(src_coord(j_first, stepy, wy, ty, nym1));
+  const float fy_hi = floorf(src_coord(j_last, stepy, wy, ty, nym1));
+  const float wwf = fx_hi - fx_lo + 2.0f, whf = fy_hi - fy_lo + 2.0f;
+  bool staged = (wx > 0.f) && (wy > 0.f) && (wwf >= 2.0f) && (whf >= 2.0f) &&
+                (wwf * whf <= (float)smem_floats) && (fabsf(fx_lo) < 1e6f) && (fabsf(fy_lo) < 1e6f);
+  if (staged) {
+    const int x_lo = (int)fx_lo, y_lo = (int)fy_lo;
+    const int ww = (int)wwf, wh = (int)whf;
+    const int win_floats = ww * wh;
+    const int pps = max(1, min(P.n_planes, smem_floats / win_floats));  // planes per stage
+    int off[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) off[k] = (y0 - y_lo) * ww + (x0[k] - x_lo);
+    for (int p0 = 0; p0 < P.n_planes; p0 += pps) {
+      const int np = min(pps, P.n_planes - p0);
+      if (p0 > 0) __syncthreads();  // consumers of the previous stage are done
+      for (int idx = threadIdx.x; idx < win_floats; idx += ZT_THREADS) {
+        const int r = idx / ww, c = idx - r * ww;
+        const int ys = y_lo + r, xs = x_lo + c;
+        const bool inb = (xs >= 0) && (xs <= W - 1) && (ys >= 0) && (ys <= H - 1);
+        const long long goff = (long long)ys * W + xs;
+        for (int pl = 0; pl < np; ++pl) {
+          const ZoomPlane &zp = P.planes[p0 + pl];
+          float v = 0.f;
+          if (inb) v = pre(__ldg(zp.src + (long long)b * zp.src_bstride + goff), zp.pre_op, zp.mean);
+          win[pl * win_floats + idx] = v;
+        }
+      }
+      __syncthreads();
+      if (active) {
+        for (int pl = 0; pl < np; ++pl) {
+          const ZoomPlane &zp = P.planes[p0 + pl];
+          const float *wp = win + pl * win_floats;
+          float out[4];
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const float *t = wp + off[k];
+            out[k] = blend(t[0], t[1], t[ww], t[ww + 1], wyt, wyb, wxl[k], wxr[k]);
+          }
+          post4(out, zp, P, wx_in, i0, j);
+          store4(zp, b, q, out);
+        }
+      }
+    }
+    return;
+  }
+
+  // ---- fallback: gather every tap through the read-only path, bounds-checked
+  if (!active) return;
+  const bool yin0 = (y0 >= 0) && (y0 <= H - 1);
+  const bool yin1 = (y0 + 1 >= 0) && (y0 + 1 <= H - 1);
   for (int pl = 0; pl < P.n_planes; ++pl) {
     const ZoomPlane &zp = P.planes[pl];
     const float *__restrict__ s = zp.src + (long long)b * zp.src_bstride;
@@ -306,36 +441,10 @@ zoom_sample_kernel(const __grid_constant__ ZoomParams P) {
       const float tr = (yin0 && xin1) ? pre(__ldg(r0 + xb), zp.pre_op, zp.mean) : 0.f;
       const float bl = (yin1 && xin0) ? pre(__ldg(r1 + xa), zp.pre_op, zp.mean) : 0.f;
       const float br = (yin1 && xin1) ? pre(__ldg(r1 + xb), zp.pre_op, zp.mean) : 0.f;
-      float v = __fmul_rn(__fmul_rn(tl, wyt), wxl[k]);
-      v = __fmaf_rn(__fmul_rn(tr, wyt), wxr[k], v);
-      v = __fmaf_rn(__fmul_rn(bl, wyb), wxl[k], v);
-      v = __fmaf_rn(__fmul_rn(br, wyb), wxr[k], v);
-      switch (zp.post_op) {
-        case RC_POST_ROUND: v = roundf(v); break;
-        case RC_POST_ROUND_M045: v = roundf(__fsub_rn(v, 0.45f)); break;
-        case RC_POST_DIV_WX: v = __fdiv_rn(v, wx_in); break;
-        case RC_POST_MUL_WX: v = __fmul_rn(v, wx_in); break;
-        case RC_POST_SUB_MEAN: v = __fsub_rn(v, zp.mean); break;
-        case RC_POST_SPOT_SUB_MEAN: {
-          const int x = i0 + k;
-          const float spot = (zp.channel == 0 && x >= P.spot_x0 && x < P.spot_x1 &&
-                              j >= P.spot_y0 && j < P.spot_y1) ? 255.f : 0.f;
-          v = __fsub_rn(fmaxf(v, spot), zp.mean);
-        } break;
-        default: break;
-      }
-      out[k] = v;
+      out[k] = blend(tl, tr, bl, br, wyt, wyb, wxl[k], wxr[k]);
     }
-    float4 *d = reinterpret_cast<float4 *>(zp.dst + (long long)b * zp.dst_bstride) + q;
-    float4 o = make_float4(out[0], out[1], out[2], out[3]);
-    if (zp.accumulate) {
-      const float4 old = *d;
-      o.x += old.x;
-      o.y += old.y;
-      o.z += old.z;
-      o.w += old.w;
-    }
-    st_f4(d, o);
+    post4(out, zp, P, wx_in, i0, j);
+    store4(zp, b, q, out);
   }
 }
 
@@ -369,6 +478,34 @@ __global__ void zoom_trans_kernel(const float *__restrict__ zf, const float *__r
   }
 }
 
+int launch_zoom_factor(const float *obs, const float *rend, const float *src_pose,
+                       const float *K, const float *pixel_means, float *zoom_factor,
+                       int32_t *bbox, int32_t *workspace, const float *trans_in,
+                       float *trans_out, int batch_size, int channels, int height, int width,
+                       int mode, void *stream) {
+  RC_REQUIRE(batch_size >= 0 && channels > 0 && height > 0 && width > 0, RC_ERR_INVALID_ARG);
+  RC_REQUIRE(mode == RC_ZF_MASK || mode == RC_ZF_IMAGE, RC_ERR_INVALID_ARG);
+  if (batch_size == 0) return note_status(RC_OK);
+  RC_REQUIRE(obs && rend && src_pose && K && zoom_factor && workspace, RC_ERR_INVALID_ARG);
+  RC_REQUIRE(mode == RC_ZF_MASK || pixel_means != nullptr, RC_ERR_INVALID_ARG);
+  RC_REQUIRE((trans_in == nullptr) == (trans_out == nullptr), RC_ERR_INVALID_ARG);
+  RC_REQUIRE(width % 4 == 0 && aligned16(obs) && aligned16(rend), RC_ERR_UNALIGNED);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int quads = height * width / 4;
+  int bps = (quads + 256 * 4 - 1) / (256 * 4);  // four quads per thread
+  if (bps < 1) bps = 1;
+  dim3 grid(bps, batch_size);
+  if (mode == RC_ZF_MASK)
+    zoom_bbox_kernel<RC_ZF_MASK><<<grid, 256, 0, s>>>(obs, rend, src_pose, K, pixel_means,
+                                                      zoom_factor, bbox, workspace, trans_in,
+                                                      trans_out, channels, height, width);
+  else
+    zoom_bbox_kernel<RC_ZF_IMAGE><<<grid, 256, 0, s>>>(obs, rend, src_pose, K, pixel_means,
+                                                       zoom_factor, bbox, workspace, trans_in,
+                                                       trans_out, channels, height, width);
+  return note_status(check_launch());
+}
+
 }  // namespace rc
 
 extern "C" {
@@ -377,28 +514,9 @@ int rc_zoom_factor_dev(const float *obs, const float *rend, const float *src_pos
                        const float *K, const float *pixel_means, float *zoom_factor,
                        int32_t *bbox, int32_t *workspace, int batch_size, int channels,
                        int height, int width, int mode, void *stream) {
-  RC_REQUIRE(batch_size >= 0 && channels > 0 && height > 0 && width > 0, RC_ERR_INVALID_ARG);
-  RC_REQUIRE(mode == RC_ZF_MASK || mode == RC_ZF_IMAGE, RC_ERR_INVALID_ARG);
-  if (batch_size == 0) return rc::note_status(RC_OK);
-  RC_REQUIRE(obs && rend && src_pose && K && zoom_factor && workspace, RC_ERR_INVALID_ARG);
-  RC_REQUIRE(mode == RC_ZF_MASK || pixel_means != nullptr, RC_ERR_INVALID_ARG);
-  RC_REQUIRE(width % 4 == 0 && rc::aligned16(obs) && rc::aligned16(rend), RC_ERR_UNALIGNED);
-  cudaStream_t s = static_cast<cudaStream_t>(stream);
-  const int n = batch_size * RC_ZF_WS_STRIDE;
-  rc::zoom_bbox_init_kernel<<<(n + 255) / 256, 256, 0, s>>>(workspace, batch_size);
-  const int quads = height * width / 4;
-  int bps = (quads + 256 * 4 - 1) / (256 * 4);  // four quads per thread
-  if (bps < 1) bps = 1;
-  dim3 grid(bps, batch_size);
-  if (mode == RC_ZF_MASK)
-    rc::zoom_bbox_kernel<RC_ZF_MASK><<<grid, 256, 0, s>>>(obs, rend, src_pose, K, pixel_means,
-                                                          zoom_factor, bbox, workspace,
-                                                          channels, height, width);
-  else
-    rc::zoom_bbox_kernel<RC_ZF_IMAGE><<<grid, 256, 0, s>>>(obs, rend, src_pose, K, pixel_means,
-                                                           zoom_factor, bbox, workspace,
-                                                           channels, height, width);
-  return rc::note_status(rc::check_launch());
+  return rc::launch_zoom_factor(obs, rend, src_pose, K, pixel_means, zoom_factor, bbox, workspace,
+                                nullptr, nullptr, batch_size, channels, height, width, mode,
+                                stream);
 }
 
 int rc_zoom_sample_dev(const float *zoom_factor, int inverse, const rc_zoom_group *groups,
@@ -441,9 +559,21 @@ int rc_zoom_sample_dev(const float *zoom_factor, int inverse, const rc_zoom_grou
   P.spot_x1 = (int)ceil((double)width / 2 + 5);
   P.spot_y0 = (int)floor((double)height / 2 - 5);
   P.spot_y1 = (int)ceil((double)height / 2 + 5);
-  const int quads = height * width / 4;
-  dim3 grid((quads + 255) / 256, batch_size);
-  rc::zoom_sample_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(P);
+  // 48 KB of staging per block: all 13 planes of the default configuration fit for
+  // zoom factors up to ~0.9 (window (64*0.9+2) x (16*0.9+2) floats per plane); four blocks
+  // per SM stay resident.
+  constexpr int kSmemFloats = 12288;
+  static bool attr_set = false;
+  if (!attr_set) {
+    RC_CUDA_TRY(cudaFuncSetAttribute(rc::zoom_sample_kernel,
+                                     cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     kSmemFloats * (int)sizeof(float)));
+    attr_set = true;
+  }
+  dim3 grid((width + rc::ZT_W - 1) / rc::ZT_W, (height + rc::ZT_H - 1) / rc::ZT_H, batch_size);
+  RC_REQUIRE(batch_size <= 65535, RC_ERR_INVALID_ARG);
+  rc::zoom_sample_kernel<<<grid, rc::ZT_THREADS, kSmemFloats * sizeof(float),
+                           static_cast<cudaStream_t>(stream)>>>(P, kSmemFloats);
   return rc::note_status(rc::check_launch());
 }
 

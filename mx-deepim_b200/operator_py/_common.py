@@ -97,6 +97,19 @@ def device_const(values, device):
     return t
 
 
+_WS_CACHE = {}
+
+
+def _workspace(batch, device):
+    """Zeroed bbox workspace; the kernel leaves it zeroed, so one buffer per (device, B)."""
+    key = (str(device), int(batch))
+    ws = _WS_CACHE.get(key)
+    if ws is None:
+        ws = torch.zeros((batch, _lib.RC_ZF_WS_INTS), dtype=torch.int32, device=device)
+        _WS_CACHE[key] = ws
+    return ws
+
+
 def zoom_factor(obs, rend, src_pose, K, pixel_means, zoom_factor_out, mode, bbox=None,
                 stream=None):
     """Crop box + zoom factor on device (rc_zoom_factor_dev)."""
@@ -108,7 +121,7 @@ def zoom_factor(obs, rend, src_pose, K, pixel_means, zoom_factor_out, mode, bbox
     dev = obs.device
     Kd = device_const(K, dev)
     pm = device_const(pixel_means, dev) if pixel_means is not None else None
-    ws = torch.empty((B, _lib.RC_ZF_WS_INTS), dtype=torch.int32, device=dev)
+    ws = _workspace(B, dev)
     lib = _lib.load()
     with torch.cuda.device(dev):
         st = lib.rc_zoom_factor_dev(obs.data_ptr(), rend.data_ptr(), src_pose.data_ptr(),

@@ -15,8 +15,9 @@ network evaluations:
 ZoomMask's three masks, the six image channels, the two flow planes and the
 two flow-weight planes share one sampling grid per pair, so they are ONE
 launch of the resampler (13 planes); `np.tile(valid, [1,2,1,1])` is never
-materialised (RC_ZOOM_SRC_BROADCAST).  Six launches per step in total; the
-step can be captured into a CUDA graph (`capture()` / `replay()`).
+materialised (RC_ZOOM_SRC_BROADCAST).  ZoomTrans rides in the finalising block of the
+bbox kernel.  Four launches per step in total, all issued by ONE C call
+(rc_compare_step_dev).
 """
 from __future__ import annotations
 
@@ -79,7 +80,7 @@ class CompareStep(object):
         self.valid = torch.empty((B, 1, Hh, Ww), **f)
         self.zoom_factor = torch.empty((B, 4), **f)
         self.bbox = torch.empty((B, 8), dtype=torch.int32, device=self.device)
-        self.ws = torch.empty((B, _lib.RC_ZF_WS_INTS), dtype=torch.int32, device=self.device)
+        self.ws = torch.zeros((B, _lib.RC_ZF_WS_INTS), dtype=torch.int32, device=self.device)
         self.zoom_mask_observed = torch.empty((B, 1, Hh, Ww), **f)
         self.zoom_mask_gt_observed = torch.empty((B, 1, Hh, Ww), **f)
         self.zoom_mask_rendered = torch.empty((B, 1, Hh, Ww), **f)
@@ -92,7 +93,7 @@ class CompareStep(object):
         self.loss_sum = torch.empty((B,), **f)
         self.Kd = C.device_const(self.K, self.device)
         self.graph = None
-        self.launches_per_step = 6  # flow, bbox init, bbox+factor, resampler, zoom_trans, pm loss
+        self.launches_per_step = 4  # flow, bbox+zoom factor(+ZoomTrans), resampler, pm loss
         self._lib = _lib.load()
 
     # ------------------------------------------------------------------ inputs
@@ -148,7 +149,7 @@ class CompareStep(object):
         return a
 
     def run(self, x, stream=None, marks=None, args=None):
-        """One step: a single C call that enqueues the six kernels on the current stream.
+        """One step: a single C call that enqueues the four kernels on the current stream.
         `marks`: optional list of RC_STEP_MARKS _lib.Event (or None entries) recorded around
         the kernels.  `args`: a struct from bind(x) to skip re-binding."""
         a = self.bind(x) if args is None else args
