@@ -122,33 +122,70 @@ zoom_bbox_kernel(const float *__restrict__ obs, const float *__restrict__ rend,
   BBoxAcc ao, ar;
   ao.init();
   ar.init();
-  for (int q = blockIdx.x * blockDim.x + threadIdx.x; q < quads; q += gridDim.x * blockDim.x) {
-    const int p = q << 2;
-    const int y = p / W;
-    const int x = p - y * W;
-    float so[4] = {0.f, 0.f, 0.f, 0.f}, sr[4] = {0.f, 0.f, 0.f, 0.f};
+  const float thr = (MODE == RC_ZF_IMAGE) ? 0.01f : 0.3f;  // zoom_image.py:35 / zoom_mask.py:37
+  const int stride = gridDim.x * blockDim.x;
+  constexpr int UNROLL = 4;  // the launch gives every thread at most UNROLL quads: all loads in flight
+  for (int q0 = blockIdx.x * blockDim.x + threadIdx.x; q0 < quads; q0 += UNROLL * stride) {
+    float4 so[UNROLL], sr[UNROLL];
     for (int c = 0; c < C; ++c) {
-      const float4 vo = ld_stream_f4(reinterpret_cast<const float4 *>(o + c * plane) + q);
-      const float4 vr = ld_stream_f4(reinterpret_cast<const float4 *>(r + c * plane) + q);
       const float mean = (MODE == RC_ZF_IMAGE) ? __ldg(pixel_means + c) : 0.f;
+      float4 vo[UNROLL], vr[UNROLL];
 #pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        float eo = comp(vo, k), er = comp(vr, k);
-        if (MODE == RC_ZF_IMAGE) {
-          eo = __fadd_rn(eo, mean);  // zoom_image.py:31-32
-          er = __fadd_rn(er, mean);
+      for (int u = 0; u < UNROLL; ++u) {
+        const int q = q0 + u * stride;
+        if (q < quads) {
+          vo[u] = ld_stream_f4(reinterpret_cast<const float4 *>(o + c * plane) + q);
+          vr[u] = ld_stream_f4(reinterpret_cast<const float4 *>(r + c * plane) + q);
         } else {
-          er = er > 0.2f ? 1.f : 0.f;  // zoom_mask.py:40-45
+          vo[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+          vr[u] = (MODE == RC_ZF_IMAGE) ? make_float4(-mean, -mean, -mean, -mean)
+                                        : make_float4(0.f, 0.f, 0.f, 0.f);
+          if (MODE == RC_ZF_IMAGE) vo[u] = vr[u];
         }
-        so[k] = c == 0 ? eo : __fadd_rn(so[k], eo);  // np.sum(axis=1), sequential
-        sr[k] = c == 0 ? er : __fadd_rn(sr[k], er);
+      }
+#pragma unroll
+      for (int u = 0; u < UNROLL; ++u) {
+        float eo[4] = {vo[u].x, vo[u].y, vo[u].z, vo[u].w};
+        float er[4] = {vr[u].x, vr[u].y, vr[u].z, vr[u].w};
+        float ao_[4], ar_[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          if (MODE == RC_ZF_IMAGE) {
+            eo[k] = __fadd_rn(eo[k], mean);  // zoom_image.py:31-32
+            er[k] = __fadd_rn(er[k], mean);
+          } else {
+            er[k] = er[k] > 0.2f ? 1.f : 0.f;  // zoom_mask.py:40-45
+          }
+          const float po = (k == 0) ? so[u].x : (k == 1) ? so[u].y : (k == 2) ? so[u].z : so[u].w;
+          const float pr = (k == 0) ? sr[u].x : (k == 1) ? sr[u].y : (k == 2) ? sr[u].z : sr[u].w;
+          ao_[k] = c == 0 ? eo[k] : __fadd_rn(po, eo[k]);  // np.sum(axis=1), sequential
+          ar_[k] = c == 0 ? er[k] : __fadd_rn(pr, er[k]);
+        }
+        so[u] = make_float4(ao_[0], ao_[1], ao_[2], ao_[3]);
+        sr[u] = make_float4(ar_[0], ar_[1], ar_[2], ar_[3]);
       }
     }
-    const float thr = (MODE == RC_ZF_IMAGE) ? 0.01f : 0.3f;  // zoom_image.py:35 / zoom_mask.py:37
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      if (so[k] > thr) ao.add(x + k, y);
-      if (sr[k] > thr) ar.add(x + k, y);
+    for (int u = 0; u < UNROLL; ++u) {
+      const int q = q0 + u * stride;
+      // 4-bit validity masks of the quad; background quads (the common case) skip the update
+      const unsigned mo = (so[u].x > thr ? 1u : 0u) | (so[u].y > thr ? 2u : 0u) |
+                          (so[u].z > thr ? 4u : 0u) | (so[u].w > thr ? 8u : 0u);
+      const unsigned mr = (sr[u].x > thr ? 1u : 0u) | (sr[u].y > thr ? 2u : 0u) |
+                          (sr[u].z > thr ? 4u : 0u) | (sr[u].w > thr ? 8u : 0u);
+      if ((mo | mr) && q < quads) {
+        const int p = q << 2;
+        const int y = p / W;
+        const int x = p - y * W;
+        if (mo) {
+          ao.add(x + __ffs(mo) - 1, y);
+          ao.add(x + 31 - __clz(mo), y);
+        }
+        if (mr) {
+          ar.add(x + __ffs(mr) - 1, y);
+          ar.add(x + 31 - __clz(mr), y);
+        }
+      }
     }
   }
   // block reduction: warp shuffles, then 8 warps through shared memory
@@ -268,11 +305,14 @@ __device__ __forceinline__ void post4(float (&v)[4], const ZoomPlane &zp, const 
   switch (zp.post_op) {
     case RC_POST_ROUND:
 #pragma unroll
-      for (int k = 0; k < 4; ++k) v[k] = roundf(v[k]);
+      for (int k = 0; k < 4; ++k) v[k] = truncf(__fadd_rz(v[k], copysignf(0.5f, v[k])));
       break;
     case RC_POST_ROUND_M045:
 #pragma unroll
-      for (int k = 0; k < 4; ++k) v[k] = roundf(__fsub_rn(v[k], 0.45f));
+      for (int k = 0; k < 4; ++k) {
+        const float t = __fsub_rn(v[k], 0.45f);
+        v[k] = truncf(__fadd_rz(t, copysignf(0.5f, t)));
+      }
       break;
     case RC_POST_DIV_WX:
 #pragma unroll
@@ -328,18 +368,37 @@ __device__ __forceinline__ float blend(float tl, float tr, float bl, float br, f
 constexpr int ZT_W = 64;
 constexpr int ZT_H = 16;
 constexpr int ZT_THREADS = 256;
+constexpr int ZT_BATCH = 8;  // planes whose window loads are in flight together
+
+// Per-plane, per-sample constants resolved once per block (shared memory).
+struct PlaneCtx {
+  const float *src;  // plane of this sample
+  float *dst;
+  int pre_op, post_op, accumulate, channel;
+  float mean;
+  int pad_[3];
+};
+
+// round half away from zero, the FADD.RZ + FRND.TRUNC sequence CUDA's roundf reduces to
+// for |v| < 2^23 (exact for every float: v + 0.5 rounded toward zero never crosses an integer).
+__device__ __forceinline__ float round_away(float v) {
+  return truncf(__fadd_rz(v, copysignf(0.5f, v)));
+}
 
 // grid = (ceil(W/ZT_W), ceil(H/ZT_H), B); block = 256; dynamic smem = smem_floats * 4.
 //
 // The source window of a tile -- [x_lo, x_hi] x [y_lo, y_hi], every tap any of its
 // 1024 outputs can touch -- is staged into shared memory once per plane with the
-// pre-operation applied and out-of-image taps set to zero, so the per-output work is
-// four conflict-free LDS, seven FP32 operations and a quarter of a 128-bit store.
-// As many planes as fit are staged per barrier pair.  Tiles whose window does not fit
-// (strong zoom-out / inverse zoom) fall back to gathering through the read-only path.
+// pre-operation applied and out-of-image taps set to zero.  Window element (r, c) is
+// stored as the float2 {v(r, c), v(r+1, c)}, so an output fetches its four taps with two
+// 64-bit LDS at a constant 8-byte distance; per output that leaves 2 LDS + 8 FP32
+// operations and a quarter of a 128-bit store.  As many planes as fit are staged per
+// barrier pair.  Tiles whose window does not fit (strong zoom-out / inverse zoom) fall
+// back to gathering through the read-only path.
 __global__ void __launch_bounds__(ZT_THREADS)
 zoom_sample_kernel(const __grid_constant__ ZoomParams P, int smem_floats) {
-  extern __shared__ float win[];
+  extern __shared__ float2 win[];
+  __shared__ PlaneCtx ctx[RC_ZOOM_MAX_PLANES];
   const int H = P.H, W = P.W;
   const int b = blockIdx.z;
   const int tx4 = threadIdx.x & 15, trow = threadIdx.x >> 4;
@@ -347,6 +406,19 @@ zoom_sample_kernel(const __grid_constant__ ZoomParams P, int smem_floats) {
   const int i_last = min(i_first + ZT_W, W) - 1, j_last = min(j_first + ZT_H, H) - 1;
   const int i0 = i_first + tx4 * 4, j = j_first + trow;
   const bool active = (i0 < W) && (j < H);
+
+  if (threadIdx.x < P.n_planes) {
+    const ZoomPlane &zp = P.planes[threadIdx.x];
+    PlaneCtx c;
+    c.src = zp.src + (long long)b * zp.src_bstride;
+    c.dst = zp.dst + (long long)b * zp.dst_bstride;
+    c.pre_op = zp.pre_op;
+    c.post_op = zp.post_op;
+    c.accumulate = zp.accumulate;
+    c.channel = zp.channel;
+    c.mean = zp.mean;
+    ctx[threadIdx.x] = c;
+  }
 
   float wx, wy, tx, ty, wx_in;
   zoom_affine(P.zoom_factor + b * 4, P.inverse, H, W, wx, wy, tx, ty, wx_in);
@@ -377,45 +449,109 @@ zoom_sample_kernel(const __grid_constant__ ZoomParams P, int smem_floats) {
   const float fx_hi = floorf(src_coord(i_last, stepx, wx, tx, nxm1));
   const float fy_lo = floorf(src_coord(j_first, stepy, wy, ty, nym1));
   const float fy_hi = floorf(src_coord(j_last, stepy, wy, ty, nym1));
-  const float wwf = fx_hi - fx_lo + 2.0f, whf = fy_hi - fy_lo + 2.0f;
-  bool staged = (wx > 0.f) && (wy > 0.f) && (wwf >= 2.0f) && (whf >= 2.0f) &&
-                (wwf * whf <= (float)smem_floats) && (fabsf(fx_lo) < 1e6f) && (fabsf(fy_lo) < 1e6f);
+  // window elements: columns x_lo .. x_hi+1, row pairs y_lo .. y_hi
+  const float wwf = fx_hi - fx_lo + 2.0f, whf = fy_hi - fy_lo + 1.0f;
+  const bool staged = (wx > 0.f) && (wy > 0.f) && (wwf >= 2.0f) && (whf >= 1.0f) &&
+                      (2.0f * wwf * whf <= (float)smem_floats) && (fabsf(fx_lo) < 1e6f) &&
+                      (fabsf(fy_lo) < 1e6f);
+  __syncthreads();  // ctx[] visible
   if (staged) {
     const int x_lo = (int)fx_lo, y_lo = (int)fy_lo;
     const int ww = (int)wwf, wh = (int)whf;
-    const int win_floats = ww * wh;
-    const int pps = max(1, min(P.n_planes, smem_floats / win_floats));  // planes per stage
+    const int win_elems = ww * wh;
+    const int pps = max(1, min(P.n_planes, (smem_floats >> 1) / win_elems));  // planes per stage
     int off[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) off[k] = (y0 - y_lo) * ww + (x0[k] - x_lo);
     for (int p0 = 0; p0 < P.n_planes; p0 += pps) {
       const int np = min(pps, P.n_planes - p0);
       if (p0 > 0) __syncthreads();  // consumers of the previous stage are done
-      for (int idx = threadIdx.x; idx < win_floats; idx += ZT_THREADS) {
+      // Source rows y_lo .. y_lo + wh (one more than the row pairs); every global element is
+      // loaded once and written to the .x slot of its own row pair and the .y slot of the
+      // pair above.  Loads of up to ZT_BATCH planes are issued before any is consumed.
+      float *winf = reinterpret_cast<float *>(win);
+      const int src_elems = ww * (wh + 1);
+      for (int idx = threadIdx.x; idx < src_elems; idx += ZT_THREADS) {
         const int r = idx / ww, c = idx - r * ww;
         const int ys = y_lo + r, xs = x_lo + c;
         const bool inb = (xs >= 0) && (xs <= W - 1) && (ys >= 0) && (ys <= H - 1);
         const long long goff = (long long)ys * W + xs;
-        for (int pl = 0; pl < np; ++pl) {
-          const ZoomPlane &zp = P.planes[p0 + pl];
-          float v = 0.f;
-          if (inb) v = pre(__ldg(zp.src + (long long)b * zp.src_bstride + goff), zp.pre_op, zp.mean);
-          win[pl * win_floats + idx] = v;
+        const int slot_x = (r < wh) ? 2 * idx : -1;              // {v(r,c), .}
+        const int slot_y = (r >= 1) ? 2 * (idx - ww) + 1 : -1;   // {., v(r,c)} of the pair above
+        for (int pb = 0; pb < np; pb += ZT_BATCH) {
+          float v[ZT_BATCH];
+#pragma unroll
+          for (int u = 0; u < ZT_BATCH; ++u) {
+            v[u] = 0.f;
+            if (inb && pb + u < np) v[u] = __ldg(ctx[p0 + pb + u].src + goff);
+          }
+#pragma unroll
+          for (int u = 0; u < ZT_BATCH; ++u) {
+            if (pb + u < np) {
+              const PlaneCtx &c_ = ctx[p0 + pb + u];
+              const float t = inb ? pre(v[u], c_.pre_op, c_.mean) : 0.f;
+              float *wpl = winf + 2 * (pb + u) * win_elems;
+              if (slot_x >= 0) wpl[slot_x] = t;
+              if (slot_y >= 0) wpl[slot_y] = t;
+            }
+          }
         }
       }
       __syncthreads();
       if (active) {
         for (int pl = 0; pl < np; ++pl) {
-          const ZoomPlane &zp = P.planes[p0 + pl];
-          const float *wp = win + pl * win_floats;
+          const PlaneCtx &c_ = ctx[p0 + pl];
+          const float2 *wp = win + pl * win_elems;
           float out[4];
 #pragma unroll
           for (int k = 0; k < 4; ++k) {
-            const float *t = wp + off[k];
-            out[k] = blend(t[0], t[1], t[ww], t[ww + 1], wyt, wyb, wxl[k], wxr[k]);
+            const float2 l = wp[off[k]];      // {top-left, bottom-left}
+            const float2 r = wp[off[k] + 1];  // {top-right, bottom-right}
+            out[k] = blend(l.x, r.x, l.y, r.y, wyt, wyb, wxl[k], wxr[k]);
           }
-          post4(out, zp, P, wx_in, i0, j);
-          store4(zp, b, q, out);
+          switch (c_.post_op) {
+            case RC_POST_ROUND:
+#pragma unroll
+              for (int k = 0; k < 4; ++k) out[k] = round_away(out[k]);
+              break;
+            case RC_POST_ROUND_M045:
+#pragma unroll
+              for (int k = 0; k < 4; ++k) out[k] = round_away(__fsub_rn(out[k], 0.45f));
+              break;
+            case RC_POST_DIV_WX:
+#pragma unroll
+              for (int k = 0; k < 4; ++k) out[k] = __fdiv_rn(out[k], wx_in);
+              break;
+            case RC_POST_MUL_WX:
+#pragma unroll
+              for (int k = 0; k < 4; ++k) out[k] = __fmul_rn(out[k], wx_in);
+              break;
+            case RC_POST_SUB_MEAN:
+#pragma unroll
+              for (int k = 0; k < 4; ++k) out[k] = __fsub_rn(out[k], c_.mean);
+              break;
+            case RC_POST_SPOT_SUB_MEAN:
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                const int x = i0 + k;
+                const float spot = (c_.channel == 0 && x >= P.spot_x0 && x < P.spot_x1 &&
+                                    j >= P.spot_y0 && j < P.spot_y1) ? 255.f : 0.f;
+                out[k] = __fsub_rn(fmaxf(out[k], spot), c_.mean);
+              }
+              break;
+            default:
+              break;
+          }
+          float4 *d = reinterpret_cast<float4 *>(c_.dst) + q;
+          float4 o = make_float4(out[0], out[1], out[2], out[3]);
+          if (c_.accumulate) {
+            const float4 old = *d;
+            o.x += old.x;
+            o.y += old.y;
+            o.z += old.z;
+            o.w += old.w;
+          }
+          st_f4(d, o);
         }
       }
     }
@@ -492,7 +628,18 @@ int launch_zoom_factor(const float *obs, const float *rend, const float *src_pos
   RC_REQUIRE(width % 4 == 0 && aligned16(obs) && aligned16(rend), RC_ERR_UNALIGNED);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const int quads = height * width / 4;
-  int bps = (quads + 256 * 4 - 1) / (256 * 4);  // four quads per thread
+  // One resident wave: about four 256-thread blocks per SM in total, never more blocks per
+  // sample than it takes to give every thread four quads (the loop batches 4 loads per plane).
+  static int sm_count = 0;
+  if (sm_count == 0) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess ||
+        cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
+      sm_count = 148;
+  }
+  const int max_bps = (quads + 256 * 4 - 1) / (256 * 4);
+  int bps = (sm_count * 4 + batch_size - 1) / batch_size;
+  if (bps > max_bps) bps = max_bps;
   if (bps < 1) bps = 1;
   dim3 grid(bps, batch_size);
   if (mode == RC_ZF_MASK)
