@@ -287,6 +287,64 @@ int rc_event_record(void *event, void *stream);
 int rc_event_synchronize(void *event);
 int rc_event_elapsed_ms(void *start, void *end, float *ms);
 
+/* -------------------------------------------------------------- rasteriser
+ * Replaces the OpenGL renderers of lib/render_glumpy:
+ *   Render_Py.__init__ / render        render_py_multi.py:49-147 (GLSL :17-47)
+ *   Render_Py_Light_ModelNet_Multi     render_py_light_modelnet_multi.py:83-231 (GLSL :14-79)
+ * and the post-render block lib/pair_matching/batch_updater_py_multi.py:279-320
+ * (BGR->RGB, HWC->CHW, - pixel_means, mask = depth > 0.2), fused into the resolve pass.
+ *
+ * Geometry convention (derived from my_compute_calib_proj / _get_view_mtx,
+ * render_py_multi.py:152-178): pixel (x, y) is covered iff the
+ * pinhole projection (fx X/Z + cx, fy Y/Z + cy) of the triangle contains the
+ * integer point (x, y); nearest fragment wins (GL_LESS), ties go to the lower
+ * triangle index; no face culling; near/far planes at zNear/zFar.
+ */
+typedef struct rc_mesh_desc {      /* HOST pointers, copied at create time */
+  const float *vertices;           /* [V,3] object frame, metres            */
+  const float *uv;                 /* [V,2] or NULL                         */
+  const float *normals;            /* [V,3] or NULL (needed for RC_RENDER_LAMBERT) */
+  const int32_t *triangles;        /* [T,3] vertex indices                  */
+  const uint8_t *texture;          /* [tex_h,tex_w,3] RGB, row 0 = top of the image file */
+  int32_t n_vertices, n_triangles, tex_h, tex_w;
+} rc_mesh_desc;
+
+/* Uploads all meshes and allocates every workspace for up to `max_batch`
+ * renders per call on `device_id`.  No allocation happens in rc_render_dev. */
+int rc_renderer_create(const rc_mesh_desc *meshes, int n_meshes, int height, int width,
+                       int max_batch, int device_id, void **handle);
+int rc_renderer_destroy(void *handle);
+
+#define RC_RENDER_TEXTURED 0  /* gl_FragColor = texture2D(u_texture, v_texcoord)          */
+#define RC_RENDER_LAMBERT 1   /* ... * ((1-r) + r*brightness) * light_intensity (ModelNet) */
+
+typedef struct rc_render_args {
+  const int32_t *cls_idx;     /* dev [B] mesh index per render                         */
+  const float *poses;         /* dev [B,3,4] object-to-camera [R|t]                    */
+  const float *light_pos;     /* dev [B,3] (LAMBERT; GL eye coordinates) or NULL       */
+  const float *light_int;     /* dev [B,3] (LAMBERT) or NULL                           */
+  float *depth;               /* dev [B,1,H,W] metres, 0 = background                  */
+  float *image_chw;           /* dev [B,3,H,W] RGB - pixel_means, or NULL (batch_updater :279-284) */
+  float *bgr_hwc;             /* dev [B,H,W,3] BGR 0..255 as render() returns it, or NULL */
+  float *mask;                /* dev [B,1,H,W] depth > mask_thresh ? 1 : 0, or NULL (:316-319) */
+  int32_t *tri_id;            /* dev [B,H,W] winning triangle, -1 = background, or NULL */
+  int32_t *status;            /* dev [1] set non-zero on tile-list overflow, or NULL   */
+  float K[9];                 /* intrinsics (host values)                              */
+  float pixel_means[3];       /* subtracted from image_chw channels R,G,B              */
+  float znear, zfar, mask_thresh, brightness_ratio;
+  int32_t mode;               /* RC_RENDER_*                                           */
+  int32_t batch_size;
+  void *stream;               /* cudaStream_t                                          */
+  void **marks;               /* host array of 5 cudaEvent_t (before setup, after setup, after
+                                 scan, after fill, after raster) or NULL               */
+} rc_render_args;
+
+int rc_render_dev(void *handle, const rc_render_args *args);
+
+/* Counters of the last rc_render_dev call on this handle's workspaces (debug / bench):
+ * out[0] = triangle records emitted, out[1] = tile-list entries.  Synchronises the stream. */
+int rc_render_stats(void *handle, int batch_size, void *stream, int64_t *out);
+
 #ifdef __cplusplus
 }
 #endif

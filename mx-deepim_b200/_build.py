@@ -30,6 +30,11 @@ NVCC_FLAGS = [
 ]
 
 
+# raster.cu keeps geometry in float64 and must evaluate it exactly like the C oracle: no
+# compiler-chosen FMA contraction (explicit fma() calls stay fused).
+PER_FILE_FLAGS = {"raster.cu": ["-fmad=false"]}
+
+
 def _nvcc() -> str:
     for cand in (os.environ.get("NVCC"), shutil.which("nvcc"), "/usr/local/cuda/bin/nvcc"):
         if cand and os.path.exists(cand):
@@ -50,6 +55,7 @@ def _digest() -> str:
         with open(f, "rb") as fh:
             h.update(fh.read())
     h.update(" ".join(NVCC_FLAGS).encode())
+    h.update(repr(sorted(PER_FILE_FLAGS.items())).encode())
     return h.hexdigest()
 
 
@@ -71,7 +77,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
     procs = []
     for src in _sources():
         obj = os.path.join(obj_dir, os.path.basename(src)[:-3] + ".o")
-        cmd = [nvcc, *NVCC_FLAGS, "-I", INCLUDE, "-I", CSRC, "-c", src, "-o", obj]
+        extra = PER_FILE_FLAGS.get(os.path.basename(src), [])
+        cmd = [nvcc, *NVCC_FLAGS, *extra, "-I", INCLUDE, "-I", CSRC, "-c", src, "-o", obj]
         procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE,
                                             stderr=subprocess.STDOUT, text=True)))
         objs.append(obj)

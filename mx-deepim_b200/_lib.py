@@ -78,6 +78,26 @@ class rc_compare_step_args(ctypes.Structure):
     ])
 
 
+RC_RENDER_TEXTURED, RC_RENDER_LAMBERT = 0, 1
+RC_RENDER_MARKS = 5
+
+
+class rc_mesh_desc(ctypes.Structure):
+    _fields_ = [("vertices", c_void_p), ("uv", c_void_p), ("normals", c_void_p),
+                ("triangles", c_void_p), ("texture", c_void_p), ("n_vertices", c_int32),
+                ("n_triangles", c_int32), ("tex_h", c_int32), ("tex_w", c_int32)]
+
+
+class rc_render_args(ctypes.Structure):
+    _fields_ = [("cls_idx", c_void_p), ("poses", c_void_p), ("light_pos", c_void_p),
+                ("light_int", c_void_p), ("depth", c_void_p), ("image_chw", c_void_p),
+                ("bgr_hwc", c_void_p), ("mask", c_void_p), ("tri_id", c_void_p),
+                ("status", c_void_p), ("K", c_float * 9), ("pixel_means", c_float * 3),
+                ("znear", c_float), ("zfar", c_float), ("mask_thresh", c_float),
+                ("brightness_ratio", c_float), ("mode", c_int32), ("batch_size", c_int32),
+                ("stream", c_void_p), ("marks", POINTER(c_void_p))]
+
+
 # name -> (restype, argtypes); every symbol include/rendercompare.h declares.
 _P = c_void_p
 SIGNATURES = {
@@ -107,6 +127,11 @@ SIGNATURES = {
     "rc_event_record": (c_int, [c_void_p, c_void_p]),
     "rc_event_synchronize": (c_int, [c_void_p]),
     "rc_event_elapsed_ms": (c_int, [c_void_p, c_void_p, POINTER(c_float)]),
+    "rc_renderer_create": (c_int, [POINTER(rc_mesh_desc), c_int, c_int, c_int, c_int, c_int,
+                                   POINTER(c_void_p)]),
+    "rc_renderer_destroy": (c_int, [c_void_p]),
+    "rc_render_dev": (c_int, [c_void_p, POINTER(rc_render_args)]),
+    "rc_render_stats": (c_int, [c_void_p, c_int, c_void_p, POINTER(c_int64)]),
     "rc_pm_loss_bwd_dev": (c_int, [_P, _P, _P, _P, _P, _P, POINTER(c_float), POINTER(c_float),
                                    c_int, c_int, c_float, c_float, c_float, _P, _P, c_int, c_int,
                                    _P]),

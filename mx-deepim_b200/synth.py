@@ -149,3 +149,94 @@ def make_compare_batch(batch, seed, K=K_LINEMOD, num_points=NUM_3D_SAMPLE, occlu
     bg = rng.uniform(1, 255, size=(batch, 3, H, W)).astype(np.float32)
     out["image_observed"] = (np.where(do > 0, tex[:, ::-1], bg) - pm).astype(np.float32)
     return out
+
+
+# ----------------------------------------------------------------- procedural meshes
+def icosphere(level):
+    """Unit icosphere: 20 * 4**level triangles (level 4 -> 5120 tris, level 5 -> 20480)."""
+    t = (1.0 + 5.0 ** 0.5) / 2.0
+    v = [(-1, t, 0), (1, t, 0), (-1, -t, 0), (1, -t, 0), (0, -1, t), (0, 1, t), (0, -1, -t),
+         (0, 1, -t), (t, 0, -1), (t, 0, 1), (-t, 0, -1), (-t, 0, 1)]
+    verts = [np.array(p, dtype=np.float64) / np.linalg.norm(p) for p in v]
+    faces = [(0, 11, 5), (0, 5, 1), (0, 1, 7), (0, 7, 10), (0, 10, 11), (1, 5, 9), (5, 11, 4),
+             (11, 10, 2), (10, 7, 6), (7, 1, 8), (3, 9, 4), (3, 4, 2), (3, 2, 6), (3, 6, 8),
+             (3, 8, 9), (4, 9, 5), (2, 4, 11), (6, 2, 10), (8, 6, 7), (9, 8, 1)]
+    for _ in range(level):
+        cache = {}
+
+        def mid(a, b):
+            key = (a, b) if a < b else (b, a)
+            if key not in cache:
+                m = verts[a] + verts[b]
+                verts.append(m / np.linalg.norm(m))
+                cache[key] = len(verts) - 1
+            return cache[key]
+
+        nf = []
+        for a, b, c in faces:
+            ab, bc, ca = mid(a, b), mid(b, c), mid(c, a)
+            nf += [(a, ab, ca), (b, bc, ab), (c, ca, bc), (ab, bc, ca)]
+        faces = nf
+    return np.array(verts), np.array(faces, dtype=np.int32)
+
+
+def vertex_normals(vertices, triangles):
+    """Area-weighted per-vertex normals."""
+    v = np.asarray(vertices, np.float64)
+    f = np.asarray(triangles)
+    fn = np.cross(v[f[:, 1]] - v[f[:, 0]], v[f[:, 2]] - v[f[:, 0]])
+    n = np.zeros_like(v)
+    for k in range(3):
+        np.add.at(n, f[:, k], fn)
+    ln = np.linalg.norm(n, axis=1, keepdims=True)
+    return n / np.where(ln > 0, ln, 1.0)
+
+
+def procedural_texture(rng, size=512):
+    """[size,size,3] uint8 RGB: smooth colour field + checker so texel errors are visible."""
+    y, x = np.mgrid[0:size, 0:size].astype(np.float64) / size
+    ph = rng.uniform(0, 2 * np.pi, size=6)
+    img = np.stack([0.5 + 0.35 * np.sin(2 * np.pi * (3 * x + 2 * y) + ph[0]),
+                    0.5 + 0.35 * np.sin(2 * np.pi * (1 * x - 4 * y) + ph[1]),
+                    0.5 + 0.35 * np.sin(2 * np.pi * (5 * x + 1 * y) + ph[2])], axis=-1)
+    checker = (((x * 16).astype(int) + (y * 16).astype(int)) % 2)[..., None] * 0.12
+    return np.clip((img + checker) * 255, 1, 255).astype(np.uint8)
+
+
+def make_mesh(rng, level=4, diameter=None, kind=None, texture_size=512):
+    """Closed procedural mesh (displaced icosphere / superquadric / squashed blob) with
+    spherical UVs, vertex normals and an RGB texture.  Diameter 0.1-0.3 m (LINEMOD-like)."""
+    sphere, tris = icosphere(level)
+    kind = kind if kind is not None else int(rng.integers(0, 3))
+    x, y, z = sphere.T
+    if kind == 0:    # low-frequency displacement noise
+        a = rng.uniform(1.5, 4.0, size=3)
+        p = rng.uniform(0, 2 * np.pi, size=3)
+        r = 1 + 0.18 * np.sin(a[0] * x + p[0]) * np.sin(a[1] * y + p[1]) + 0.1 * np.sin(a[2] * z + p[2])
+        verts = sphere * r[:, None]
+    elif kind == 1:  # superquadric
+        e = rng.uniform(0.5, 1.6, size=2)
+        verts = np.sign(sphere) * np.abs(sphere) ** e[0]
+        verts[:, 2] = np.sign(z) * np.abs(z) ** e[1]
+    else:            # anisotropic blob
+        verts = sphere * rng.uniform(0.45, 1.0, size=3)
+    diameter = diameter if diameter is not None else rng.uniform(0.1, 0.3)
+    extent = np.linalg.norm(verts.max(0) - verts.min(0))
+    verts = (verts - verts.mean(0)) * (diameter / extent)
+    u = 0.5 + np.arctan2(sphere[:, 1], sphere[:, 0]) / (2 * np.pi)
+    v = 0.5 + np.arcsin(np.clip(sphere[:, 2], -1, 1)) / np.pi
+    return {"vertices": verts.astype(np.float32), "uv": np.stack([u, v], 1).astype(np.float32),
+            "normals": vertex_normals(verts, tris).astype(np.float32),
+            "triangles": tris.astype(np.int32), "texture": procedural_texture(rng, texture_size)}
+
+
+def mesh_points(mesh, rng, num_points=NUM_3D_SAMPLE):
+    """point_cloud_model / weights from mesh vertices (lib/utils/image.py:559-589)."""
+    v = np.asarray(mesh["vertices"], np.float64)
+    keep = min(len(v), num_points)
+    idx = rng.permutation(len(v))[:keep]
+    pts = np.zeros((3, num_points), np.float32)
+    wts = np.zeros((3, num_points), np.float32)
+    pts[:, :keep] = v[idx].T
+    wts[:, :keep] = 1
+    return pts, wts
