@@ -1,0 +1,271 @@
+"""CPU tests (no GPU): the oracle restatements against the reference's golden vectors,
+its docstring known answers and its own self-test recipe."""
+import os
+
+import numpy as np
+import pytest
+
+import helpers
+from oracle import flow_np, pose_np, raster_np, transform3d_np as t3d, zoom_np
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+# ------------------------------------------------------------------- flow
+@pytest.mark.parametrize("seed", [0, 4])
+def test_calc_flow_restatement_matches_reference_golden(seed):
+    """oracle.flow_np.calc_flow == the reference's calc_flow (outputs stored by make_golden.py)."""
+    g = np.load(os.path.join(GOLD, "flow_calc_flow_seed%d.npz" % seed))
+    inp = helpers.make_flow_inputs(1, seed, occlude=(seed == 4))
+    f, vis, X = flow_np.calc_flow(inp["depth_src"][0, 0].astype(np.float64), inp["pose_src"][0],
+                                  inp["pose_tgt"][0], helpers.K_LM,
+                                  inp["depth_tgt"][0, 0].astype(np.float64))
+    idx = np.flatnonzero(vis.reshape(-1))
+    assert np.array_equal(idx, g["visible_idx"])
+    assert np.array_equal(f.reshape(-1, 2)[idx], g["flow_at_visible"])
+    assert X.shape[1] == int(g["n_X_valid"])
+
+
+@pytest.mark.parametrize("seed", [0, 4])
+def test_flow_kernel_oracle_vs_reference_calc_flow(seed):
+    """The flow_kernel restatement against the reference's numpy twin: the two rules differ only
+    in rounding mode / bound test / float width, so they agree on all but a handful of pixels
+    and the flow values agree to float32 accuracy where both are valid."""
+    g = np.load(os.path.join(GOLD, "flow_calc_flow_seed%d.npz" % seed))
+    inp = helpers.make_flow_inputs(1, seed, occlude=(seed == 4))
+    flow, valid = flow_np.flow_kernel_cpu(inp["depth_src"], inp["depth_tgt"], inp["KT"], inp["Kinv"])
+    vis = np.zeros(helpers.H * helpers.W, bool)
+    vis[g["visible_idx"]] = True
+    v = valid[0, 0].reshape(-1) > 0
+    assert (vis != v).sum() <= 0.002 * vis.sum()
+    both = v[g["visible_idx"]]
+    f_ref = g["flow_at_visible"][both]
+    idx = g["visible_idx"][both]
+    f = np.stack([flow[0, 0].reshape(-1)[idx], flow[0, 1].reshape(-1)[idx]], axis=1)
+    # float32 kernel vs float64 numpy twin: coordinates near 600 px carry ~3e-5 px per float32 op
+    assert np.abs(f - f_ref).max() < 5e-4
+    # structural: zero outside valid, valid in {0,1}
+    assert set(np.unique(valid)) <= {0.0, 1.0}
+    assert not flow[0, :, valid[0, 0] == 0].any()
+
+
+def test_flow_oracle_threads_and_empty():
+    inp = helpers.make_flow_inputs(3, 8)
+    a = flow_np.flow_kernel_cpu(inp["depth_src"], inp["depth_tgt"], inp["KT"], inp["Kinv"], 1)
+    b = flow_np.flow_kernel_cpu(inp["depth_src"], inp["depth_tgt"], inp["KT"], inp["Kinv"], 0)
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+    e = np.zeros((0, 1, 480, 640), np.float32)
+    f, v = flow_np.flow_kernel_cpu(e, e, np.zeros((0, 3, 4), np.float32), inp["Kinv"])
+    assert f.shape == (0, 2, 480, 640) and v.shape == (0, 1, 480, 640)
+
+
+# ------------------------------------------------------------------- pose
+def test_pose_restatement_matches_reference_golden():
+    g = np.load(os.path.join(GOLD, "pose_reference.npz"))
+    for i in range(len(g["pose_src"])):
+        ps, pt = g["pose_src"][i].astype(np.float64), g["pose_tgt"][i].astype(np.float64)
+        q, t = pose_np.calc_RT_delta(ps, pt, np.zeros(3), np.ones(3), "CAMERA", "QUAT")
+        assert np.allclose(q, g["q"][i], atol=1e-12) and np.allclose(t, g["t"][i], atol=1e-12)
+        est = pose_np.RT_transform(ps, g["rt_q"][i], g["rt_t"][i], np.zeros(3), np.ones(3), "CAMERA")
+        assert np.allclose(est, g["pose_est"][i], atol=1e-12)
+        R, tt = pose_np.calc_se3(g["pose_src"][i], g["pose_tgt"][i])
+        assert np.array_equal(R, g["se3_R"][i]) and np.array_equal(tt, g["se3_t"][i])
+        qn = g["rt_q"][i] / np.linalg.norm(g["rt_q"][i])
+        assert np.allclose(pose_np.quat2mat(qn), g["quat2mat"][i], atol=1e-14)
+        assert np.allclose(pose_np.mat2quat(pt[:, :3]), g["mat2quat"][i], atol=1e-12)
+
+
+def test_pose_docstring_known_answers():
+    """RT_transform.py:409-414 and :478-483."""
+    assert np.allclose(pose_np.quat2mat([1, 0, 0, 0]), np.eye(3))
+    assert np.allclose(pose_np.quat2mat([0, 1, 0, 0]), np.diag([1, -1, -1]))
+    assert np.allclose(pose_np.mat2quat(np.eye(3)), [1, 0, 0, 0])
+    assert np.allclose(pose_np.mat2quat(np.diag([1, -1, -1])), [0, 1, 0, 0])
+
+
+def test_product_pose_module_matches_oracle():
+    from mx_deepim_b200 import pose as P
+
+    rng = np.random.default_rng(3)
+    for _ in range(8):
+        ps, pt = helpers.random_pose_pair(rng)
+        assert np.array_equal(P.make_KT(helpers.K_LM, ps, pt),
+                              pose_np.make_KT(helpers.K_LM, ps, pt).astype(np.float32))
+        q, t = P.calc_RT_delta(ps, pt, np.zeros(3), np.ones(3))
+        q2, t2 = pose_np.calc_RT_delta(ps.astype(np.float64), pt.astype(np.float64), np.zeros(3),
+                                       np.ones(3), "CAMERA", "QUAT")
+        assert np.allclose(q, q2) and np.allclose(t, t2)
+        est = P.RT_transform(ps, q, t, np.zeros(3), np.ones(3))
+        assert np.allclose(est, pt, atol=1e-6)  # applying the GT delta recovers the target pose
+
+
+# ------------------------------------------------------------------- zoom
+def test_sampler_restatement_vs_grid_sample():
+    """GridGenerator(affine) + BilinearSampler restatement == torch grid_sample
+    (align_corners=True, zeros padding) up to coordinate rounding."""
+    import torch
+    import torch.nn.functional as F
+
+    d = helpers.make_zoom_inputs(2, 5)
+    zf = zoom_np.zoom_mask_forward(d["mask_observed"], d["mask_gt_observed"], d["mask_rendered"],
+                                   d["src_pose"], helpers.K_LM)[3]
+    zf[1] = [1.7, 1.7, 0.3, -0.2]  # zoom-out: exercises the zero padding
+    theta = torch.tensor([[[z[0], 0, z[2]], [0, z[1], z[3]]] for z in zf])
+    grid = F.affine_grid(theta, (2, 1, 480, 640), align_corners=True)
+    smooth = np.fromfunction(lambda b, c, y, x: np.sin(x / 37.0) + np.cos(y / 23.0) + b,
+                             (2, 1, 480, 640)).astype(np.float32)
+    ref = F.grid_sample(torch.from_numpy(smooth), grid, mode="bilinear", padding_mode="zeros",
+                        align_corners=True).numpy()
+    mine = zoom_np.sample_batch(smooth, zf)
+    assert np.abs(ref - mine).max() < 2e-4
+    assert (mine[1, 0, 0, :5] == 0).all()  # outside the source image
+
+
+def test_zoom_factor_cases():
+    d = helpers.make_zoom_inputs(3, 6, empty_rendered=(1,))
+    out = zoom_np.zoom_mask_forward(d["mask_observed"], d["mask_gt_observed"], d["mask_rendered"],
+                                    d["src_pose"], helpers.K_LM)
+    zf, bbox = out[3], out[4]
+    assert zf.dtype == np.float32 and (zf[:, 0] == zf[:, 1]).all() and (zf[:, 0] > 0).all()
+    # rendered mask empty -> observed box and its mid-point (zoom_mask.py:74-81)
+    x0, x1, y0, y1 = bbox[1, :4]
+    assert bbox[1, 5] == -1
+    assert np.isclose(zf[1, 2], (x0 + x1) * 0.5 / 640 * 2 - 1)
+    # observed mask empty -> the reference raises
+    d["mask_gt_observed"][0] = 0
+    with pytest.raises(ValueError):
+        zoom_np.zoom_mask_forward(d["mask_observed"], d["mask_gt_observed"], d["mask_rendered"],
+                                  d["src_pose"], helpers.K_LM)
+    # masks stay binary after bilinear + round
+    assert set(np.unique(out[0])) <= {0.0, 1.0}
+
+
+def test_zoom_round_trip_and_rounding():
+    assert np.array_equal(zoom_np.mx_round(np.array([0.5, 1.5, 2.5, -0.5, 0.49999997], np.float32)),
+                          np.array([1, 2, 3, -1, 0], np.float32))
+    zf = np.array([[0.5, 0.5, 0.1, -0.1]], np.float32)
+    yy, xx = np.meshgrid(np.arange(480, dtype=np.float32), np.arange(640, dtype=np.float32), indexing="ij")
+    flow = np.stack([0.01 * yy, 0.02 * xx])[None].astype(np.float32)
+    z, w = zoom_np.zoom_flow_forward(zf, flow, np.ones_like(flow))
+    back = zoom_np.zoom_flow_forward(zf, z, b_inv_zoom=True)
+    assert np.abs(back[:, :, 120:300, 220:480] - flow[:, :, 120:300, 220:480]).max() < 2e-2
+    td = np.array([[0.3, -0.2, 0.1]], np.float32)
+    fwd = zoom_np.zoom_trans_forward(zf, td)
+    assert np.allclose(zoom_np.zoom_trans_forward(zf, fwd, b_inv_zoom=True), td, atol=1e-7)
+
+
+# ----------------------------------------------------------- transform3d
+def test_transform3d_reference_self_test_recipe():
+    """Re-hosts transform3d.py:365-638 on synthetic points: seed 1, B = 8, N = 3000, forward
+    < 1e-4 against RT_transform + matmul, central differences (step 1e-2) within 5e-3."""
+    np.random.seed(1)
+    B, N = 8, 3000
+    pts = np.random.uniform(-0.1, 0.1, size=(B, 3, N)).astype(np.float32)
+    q = np.random.normal(size=(B, 4))
+    q = (q / np.linalg.norm(q, axis=1, keepdims=True)).astype(np.float32)
+    t = np.random.normal(0, 0.1, size=(B, 3)).astype(np.float32)
+    pose_src = np.tile(np.array([[0, 1, 0, 0], [1, 0, 0, 0], [0, 0, 1, 1]], np.float32), (B, 1, 1))
+    means, stds = np.zeros(3, np.float32), np.ones(3, np.float32)
+    out = t3d.forward(pts, q, t, pose_src, means, stds, "CAMERA")
+    for b in range(B):
+        est = pose_np.RT_transform(pose_src[b].astype(np.float64), q[b], t[b], means, stds, "CAMERA")
+        ref = est[:, :3] @ pts[b].astype(np.float64) + est[:, 3:]
+        assert np.abs(out[b] - ref).max() < 1e-4
+    # gradient check of sum(out * G)
+    G = np.random.normal(size=out.shape).astype(np.float32)
+    g_rot, g_tr = t3d.backward(G, pts, q, t, pose_src, means, stds, "CAMERA")
+
+    def f(qq, tt):
+        return float((t3d.forward(pts, qq, tt, pose_src, means, stds, "CAMERA").astype(np.float64) * G).sum())
+
+    step = 1e-2
+    for b in (0, 5):
+        for k in range(3):
+            tp, tm = t.copy(), t.copy()
+            tp[b, k] += step
+            tm[b, k] -= step
+            num = (f(q, tp) - f(q, tm)) / (2 * step)
+            assert abs(num - g_tr[b, k]) <= 5e-3 * max(1.0, abs(num))
+        for k in range(4):
+            qp, qm = q.astype(np.float64), q.astype(np.float64)
+            qp[b, k] += 1e-4
+            qm[b, k] -= 1e-4
+            # the operator's quaternion gradient includes the re-normalisation Jacobian (:316-322)
+            qp[b] /= np.linalg.norm(qp[b])
+            qm[b] /= np.linalg.norm(qm[b])
+            num = (f(qp.astype(np.float32), t) - f(qm.astype(np.float32), t)) / 2e-4
+            assert abs(num - g_rot[b, k]) <= 5e-3 * max(1.0, abs(num)) + 2e-2
+
+
+def test_pm_loss_types_and_metric():
+    d = helpers.make_points_inputs(4, 2, num_points=500, num_keep=400)
+    args = [d[k] for k in ("points", "points_obs", "weights", "rotation", "translation", "pose_src")]
+    means, stds = np.zeros(3, np.float32), np.ones(3, np.float32)
+    l1, est, s1 = t3d.pm_loss_forward(*args, means, stds, "CAMERA", "L1")
+    l2, _, _ = t3d.pm_loss_forward(*args, means, stds, "CAMERA", "L2")
+    sl, _, _ = t3d.pm_loss_forward(*args, means, stds, "CAMERA", "smooth_L1", sl1_scalar=1.0)
+    x = (est - d["points_obs"]) / 0.1
+    assert np.allclose(l1, d["weights"] * np.abs(x), atol=1e-5)
+    assert np.allclose(l2, d["weights"] * x * x, rtol=1e-4, atol=1e-5)
+    assert np.allclose(sl, d["weights"] * np.where(np.abs(x) < 1, 0.5 * x * x, np.abs(x) - 0.5),
+                       rtol=1e-4, atol=1e-5)
+    assert not l1[:, :, 400:].any()
+    assert np.isclose(t3d.pm_metric(l1, 500), l1.sum() / 500)
+    assert np.allclose(s1, l1.reshape(4, -1).sum(1), rtol=1e-5)
+
+
+# ----------------------------------------------------------------- raster
+def test_raster_oracle_cross_checks():
+    """Cross-oracle pin (north_star): flow of the mesh rendered at pose A into pose B lands on
+    the mesh rendered at B; identical poses -> every foreground pixel valid with zero flow."""
+    from mx_deepim_b200 import synth
+
+    rng = np.random.default_rng(0)
+    mesh = synth.make_mesh(rng, level=3)
+    ps, pt = synth.random_pose_pair(rng)
+    bgr, d_tgt, tri = raster_np.render_py(mesh, pt[:, :3], pt[:, 3], helpers.K_LM, r_type="mat", want_tri=True)
+    _, d_src = raster_np.render_py(mesh, ps[:, :3], ps[:, 3], helpers.K_LM, r_type="mat")
+    assert bgr.shape == (480, 640, 3) and (d_tgt > 0).sum() > 2000
+    assert np.array_equal(d_tgt > 0, tri >= 0) and not bgr[d_tgt == 0].any()
+    Kinv = np.linalg.inv(helpers.K_LM.astype(np.float64)).astype(np.float32)
+    KT = pose_np.make_KT(helpers.K_LM, ps, pt).astype(np.float32)[None]
+    f, v = flow_np.flow_kernel_cpu(d_src[None, None], d_tgt[None, None], KT, Kinv)
+    assert v.sum() > 0.8 * (d_src > 0).sum()
+    KT0 = pose_np.make_KT(helpers.K_LM, pt, pt).astype(np.float32)[None]
+    f0, v0 = flow_np.flow_kernel_cpu(d_tgt[None, None], d_tgt[None, None], KT0, Kinv)
+    inner = (slice(None), slice(None), slice(1, -1), slice(1, -1))
+    assert np.array_equal((v0 > 0)[inner], (d_tgt > 0)[None, None][inner])
+    assert np.abs(f0).max() < 1e-3
+    # depth of the rendered surface stays within the object's extent around t.z
+    fg = d_tgt[d_tgt > 0]
+    rad = np.linalg.norm(mesh["vertices"], axis=1).max()
+    assert fg.min() > pt[2, 3] - rad - 1e-3 and fg.max() < pt[2, 3] + rad + 1e-3
+
+
+def test_raster_oracle_plane_and_clip():
+    quad = {"vertices": np.array([[-0.1, -0.1, 0], [0.1, -0.1, 0], [0.1, 0.1, 0], [-0.1, 0.1, 0]], np.float32),
+            "uv": np.array([[0, 0], [1, 0], [1, 1], [0, 1]], np.float32), "normals": None,
+            "triangles": np.array([[0, 1, 2], [0, 2, 3]], np.int32),
+            "texture": np.arange(4 * 4 * 3, dtype=np.uint8).reshape(4, 4, 3)}
+    bgr, depth = raster_np.render_py(quad, np.eye(3), np.array([0, 0, 0.8]), helpers.K_LM, r_type="mat")
+    fg = depth > 0
+    assert np.abs(depth[fg] - 0.8).max() < 1e-6
+    # pixel (x, y) is covered iff the pinhole projection contains the integer point (SURVEY 5.10 ii)
+    u0, u1 = helpers.K_LM[0, 0] * -0.1 / 0.8 + helpers.K_LM[0, 2], helpers.K_LM[0, 0] * 0.1 / 0.8 + helpers.K_LM[0, 2]
+    cols = np.flatnonzero(fg.any(axis=0))
+    assert cols.min() == int(np.ceil(u0)) and cols.max() == int(np.floor(u1))
+    # texture orientation: image top row of the quad (smallest y = object -y ... v = 0 side)
+    # tilted quad crossing the near plane is clipped at z = 0.25
+    R = np.array([[1, 0, 0], [0, 0.2, -0.98], [0, 0.98, 0.2]], np.float64)
+    _, d2 = raster_np.render_py(quad, R, np.array([0, 0, 0.3]), helpers.K_LM, r_type="mat")
+    assert d2[d2 > 0].min() >= 0.25 - 1e-6 and (d2 > 0).sum() > 100
+
+
+def test_synth_batch_shapes():
+    from mx_deepim_b200 import pipeline, synth
+
+    h = synth.make_compare_batch(2, 7)
+    for k in pipeline.INPUT_KEYS:
+        assert h[k].dtype == np.float32, k
+    assert h["image_observed"].shape == (2, 3, 480, 640) and h["KT"].shape == (2, 3, 4)
+    assert pipeline.algorithmic_bytes_per_pair(480, 640, 3000) == (20 + 112) * 307200 + 144000
