@@ -345,6 +345,19 @@ int rc_render_dev(void *handle, const rc_render_args *args);
  * out[0] = triangle records emitted, out[1] = tile-list entries.  Synchronises the stream. */
 int rc_render_stats(void *handle, int batch_size, void *stream, int64_t *out);
 
+/* ------------------------------------------------------ pose update (host driver math)
+ * The per-pair block of lib/pair_matching/batch_updater_py_multi.py:211-312, batched:
+ *   refined_pose = RT_transform(src_pose, rot_est, trans_est)     (RT_transform.py:135-161)
+ *   rot_res, trans_res = calc_RT_delta(refined_pose, tgt_pose, rot_type="QUAT")   (:16-48)
+ *   KT = K . calc_se3(refined_pose, tgt_pose)                     (:186-197, updater :306-312)
+ * All arrays device float32: src_pose, tgt_pose, refined_pose, KT [B,3,4]; rot_est, rot_res
+ * [B,4] (w,x,y,z); trans_est, trans_res [B,3]; K [3,3].  T_means/T_stds host [3].
+ * refined_pose must not alias src_pose.  rot_coord: MODEL / CAMERA / CAMERA_NEW. */
+int rc_pose_update_dev(const float *src_pose, const float *rot_est, const float *trans_est,
+                       const float *tgt_pose, const float *K, const float *T_means,
+                       const float *T_stds, int rot_coord, float *refined_pose, float *rot_res,
+                       float *trans_res, float *KT, int batch_size, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

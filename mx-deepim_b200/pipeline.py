@@ -187,3 +187,173 @@ class CompareStep(object):
             "zoom_flow_weights": self.zoom_flow_weights, "zoom_trans_gt": self.zoom_trans_gt,
             "point_matching_loss": self.loss_map, "point_matching_loss_sum": self.loss_sum,
         }
+
+
+def pose_update(src_pose, rot_est, trans_est, tgt_pose, K, T_means=(0, 0, 0), T_stds=(1, 1, 1),
+                rot_coord="CAMERA", out=None, stream=None):
+    """Batched pose block of the batch updater (batch_updater_py_multi.py:211-312) on device.
+    Returns (refined_pose [B,3,4], rot_res [B,4], trans_res [B,3], KT [B,3,4])."""
+    for n, t in (("src_pose", src_pose), ("rot_est", rot_est), ("trans_est", trans_est),
+                 ("tgt_pose", tgt_pose)):
+        C.check_tensor(n, t)
+    B = src_pose.shape[0]
+    dev = src_pose.device
+    if out is None:
+        f = dict(dtype=torch.float32, device=dev)
+        out = (torch.empty((B, 3, 4), **f), torch.empty((B, 4), **f), torch.empty((B, 3), **f),
+               torch.empty((B, 3, 4), **f))
+    if out[0].data_ptr() == src_pose.data_ptr():
+        raise ValueError("refined_pose must not alias src_pose")
+    Kd = C.device_const(K, dev)
+    with torch.cuda.device(dev):
+        st = _lib.load().rc_pose_update_dev(
+            src_pose.data_ptr(), rot_est.data_ptr(), trans_est.data_ptr(), tgt_pose.data_ptr(),
+            Kd.data_ptr(), _lib.f3(T_means), _lib.f3(T_stds), _lib.ROT_COORD[rot_coord.lower()],
+            out[0].data_ptr(), out[1].data_ptr(), out[2].data_ptr(), out[3].data_ptr(), B,
+            _lib.stream_ptr(stream))
+    _lib.check(st, "rc_pose_update_dev")
+    return out
+
+
+class RefineLoop(object):
+    """On-device replacement of the refine loop's data path
+    (/root/reference/deepim/core/module.py:1205-1213 calling
+    /root/reference/lib/pair_matching/batch_updater_py_multi.py:100-387 between network passes):
+
+        per iteration:  network stand-in -> pose update -> rasterise at the refined pose
+                        (+ fused image post / mask) -> GT flow -> zoom (13 planes) -> PM loss
+
+    Everything stays on the device; one iteration is 1 (pose) + 1 memset + 4 (render) +
+    4 (compare step) launches plus the stand-in's few elementwise torch kernels, and no host
+    synchronisation.  The CNN is out of scope (north_star): `predict` is a pluggable callback
+    (labels -> predictions); the default is the damped ground-truth update of SURVEY.md 8(d).
+    """
+
+    def __init__(self, meshes, batch, device, K=synth.K_LINEMOD, pixel_means=synth.PIXEL_MEANS,
+                 num_points=synth.NUM_3D_SAMPLE, damping=0.5, predict=None, seed=0):
+        from .render import DeviceRenderer
+
+        self.B = batch
+        self.device = torch.device(device)
+        self.K = np.asarray(K, np.float32)
+        self.renderer = DeviceRenderer(meshes, self.K, synth.W, synth.H, synth.ZNEAR, synth.ZFAR,
+                                       max_batch=batch, device=self.device)
+        self.step = CompareStep(batch, self.device, K=self.K, pixel_means=pixel_means,
+                                num_points=num_points)
+        # the updater subtracts PIXEL_MEANS[[2,1,0]] from the RGB image (:24-25, :279-284)
+        self.render_means = np.asarray(pixel_means, np.float32)[[2, 1, 0]].copy()
+        f = dict(dtype=torch.float32, device=self.device)
+        B = batch
+        self.pose = [torch.empty((B, 3, 4), **f), torch.empty((B, 3, 4), **f)]
+        self.rot_gt = torch.empty((B, 4), **f)
+        self.trans_gt = torch.empty((B, 3), **f)
+        self.KT = torch.empty((B, 3, 4), **f)
+        self.depth_rendered = torch.empty((B, 1, synth.H, synth.W), **f)
+        self.image_rendered = torch.empty((B, 3, synth.H, synth.W), **f)
+        self.mask_rendered = torch.empty((B, 1, synth.H, synth.W), **f)
+        self.rot_est = torch.empty((B, 4), **f)
+        self.trans_est = torch.empty((B, 3), **f)
+        self.damping = float(damping)
+        self.predict = predict if predict is not None else self._damped_gt
+        g = torch.Generator(device="cpu").manual_seed(int(seed))
+        self.noise_q = (0.01 * torch.randn((8, B, 4), generator=g)).to(self.device)
+        self.noise_t = (0.005 * torch.randn((8, B, 3), generator=g)).to(self.device)
+        self.identity_q = torch.tensor([1.0, 0.0, 0.0, 0.0], **f)
+        self.cur = 0
+        self.bound = [None, None]
+        self.obs = None
+        self.launches_per_iteration = 1 + 1 + 4 + 4
+
+    def _damped_gt(self, it, rot_gt, trans_gt):
+        """Stand-in for the FlowNet heads: move `damping` of the way to the target, plus noise."""
+        a = self.damping
+        q = (1.0 - a) * self.identity_q + a * rot_gt + self.noise_q[it % 8]
+        torch.div(q, q.norm(dim=1, keepdim=True), out=self.rot_est)  # L2Normalization upstream
+        torch.add(a * trans_gt, self.noise_t[it % 8], out=self.trans_est)
+
+    def set_batch(self, host):
+        """Observed side of the batch + initial poses.  `host`: numpy dict with image_observed,
+        depth_gt_observed, mask_observed, mask_gt_observed, src_pose, tgt_pose, class_index,
+        point_cloud_model / weights / observed, Kinv."""
+        t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(self.device)
+        self.obs = {k: t(host[k]) for k in ("image_observed", "depth_gt_observed", "mask_observed",
+                                            "mask_gt_observed", "tgt_pose", "point_cloud_model",
+                                            "point_cloud_weights", "point_cloud_observed", "Kinv")}
+        self.cls = t(np.asarray(host["class_index"], np.int32))
+        self.pose[0].copy_(t(host["src_pose"]))
+        self.cur = 0
+        from . import pose as P
+
+        q0 = np.zeros((self.B, 4), np.float32)
+        t0 = np.zeros((self.B, 3), np.float32)
+        for b in range(self.B):
+            q0[b], t0[b] = P.calc_RT_delta(host["src_pose"][b], host["tgt_pose"][b], np.zeros(3),
+                                           np.ones(3), "CAMERA")
+        self.rot_gt.copy_(t(q0))
+        self.trans_gt.copy_(t(t0))
+        for par in (0, 1):
+            x = dict(self.obs)
+            x.update(image_rendered=self.image_rendered, depth_rendered=self.depth_rendered,
+                     src_pose=self.pose[par], KT=self.KT, rot_est=self.rot_est,
+                     trans_est=self.trans_est, trans_gt=self.trans_gt)
+            self.bound[par] = self.step.bind(x)
+
+    def iterate(self, it, marks=None, render_marks=None):
+        """One refinement iteration on the current stream (no synchronisation)."""
+        self.predict(it, self.rot_gt, self.trans_gt)
+        nxt = 1 - self.cur
+        pose_update(self.pose[self.cur], self.rot_est, self.trans_est, self.obs["tgt_pose"], self.K,
+                    out=(self.pose[nxt], self.rot_gt, self.trans_gt, self.KT))
+        self.renderer.render_batch(self.cls, self.pose[nxt], pixel_means=self.render_means,
+                                   want=("depth", "image", "mask"),
+                                   out={"depth": self.depth_rendered, "image": self.image_rendered,
+                                        "mask": self.mask_rendered}, marks=render_marks)
+        self.cur = nxt
+        self.step.run(None, args=self.bound[nxt], marks=marks)
+
+    def run(self, iterations=4):
+        for it in range(iterations):
+            self.iterate(it)
+
+
+def make_refine_batch(meshes, batch, seed, K=synth.K_LINEMOD, num_points=synth.NUM_3D_SAMPLE,
+                      renderer=None, occlusion=False):
+    """Synthetic observed side for RefineLoop: target renders come from `renderer`
+    (a DeviceRenderer; the product's own rasteriser) so that no oracle is involved."""
+    rng = np.random.default_rng(seed)
+    B = batch
+    cls = rng.integers(0, len(meshes), size=B).astype(np.int32)
+    src = np.zeros((B, 3, 4), np.float32)
+    tgt = np.zeros((B, 3, 4), np.float32)
+    pts = np.zeros((B, 3, num_points), np.float32)
+    wts = np.zeros((B, 3, num_points), np.float32)
+    obs = np.zeros((B, 3, num_points), np.float32)
+    for b in range(B):
+        src[b], tgt[b] = synth.random_pose_pair(rng, K)
+        pts[b], wts[b] = synth.mesh_points(meshes[cls[b]], rng, num_points)
+        obs[b] = tgt[b, :, :3].astype(np.float64) @ pts[b].astype(np.float64) + tgt[b, :, 3:].astype(np.float64)
+    dev = renderer.device
+    pm = synth.PIXEL_MEANS[[2, 1, 0]]
+    out = renderer.render_batch(torch.from_numpy(cls).to(dev), torch.from_numpy(tgt).to(dev),
+                                pixel_means=pm, want=("depth", "image"))
+    torch.cuda.synchronize(dev)
+    depth = out["depth"].cpu().numpy()
+    image = out["image"].cpu().numpy()
+    depth = (np.round(depth.astype(np.float64) * 1000.0) / 1000.0).astype(np.float32)  # 1 mm PNG
+    if occlusion:
+        for b in range(B):
+            x0, y0 = rng.integers(0, synth.W - 80), rng.integers(0, synth.H - 80)
+            depth[b, 0, y0:y0 + 80, x0:x0 + 80] = 0.4
+    bg = rng.uniform(1, 255, size=image.shape).astype(np.float32) - pm.reshape(1, 3, 1, 1)
+    image = np.where(depth > 0, image, bg).astype(np.float32)
+    mask_gt = (depth > 0).astype(np.float32)
+    mask_obs = mask_gt.copy()
+    for b in range(B):
+        y0, x0 = rng.integers(0, synth.H - 40), rng.integers(0, synth.W - 40)
+        mask_obs[b, 0, y0:y0 + 40, x0:x0 + 40] = 0
+    from . import pose as P
+
+    return {"class_index": cls, "src_pose": src, "tgt_pose": tgt, "image_observed": image,
+            "depth_gt_observed": depth, "mask_gt_observed": mask_gt, "mask_observed": mask_obs,
+            "point_cloud_model": pts, "point_cloud_weights": wts, "point_cloud_observed": obs,
+            "Kinv": P.make_Kinv(K)}

@@ -1,0 +1,67 @@
+"""On-device refine loop vs the numpy restatement of batchUpdaterPyMulti.forward."""
+import numpy as np
+import pytest
+
+import helpers
+from oracle import transform3d_np, updater_np, zoom_np
+
+pytestmark = pytest.mark.gpu
+
+
+def test_refine_loop_matches_updater_oracle(cuda_device):
+    import torch
+
+    from mx_deepim_b200 import pipeline, synth
+
+    rng = np.random.default_rng(11)
+    meshes = [synth.make_mesh(rng, level=3, kind=0), synth.make_mesh(rng, level=3, kind=2)]
+    B = 3
+    loop = pipeline.RefineLoop(meshes, B, cuda_device, seed=5)
+    host = pipeline.make_refine_batch(meshes, B, 123, renderer=loop.renderer, occlusion=True)
+    loop.set_batch(host)
+    pm = synth.PIXEL_MEANS[[2, 1, 0]]
+    means, stds = np.zeros(3, np.float32), np.ones(3, np.float32)
+    prev_pose = host["src_pose"].copy()
+    losses = []
+    for it in range(3):
+        loop.iterate(it)
+        torch.cuda.synchronize()
+        rot_est = loop.rot_est.cpu().numpy()
+        trans_est = loop.trans_est.cpu().numpy()
+        ref = updater_np.updater_forward(meshes, host["class_index"], prev_pose, host["tgt_pose"],
+                                         rot_est, trans_est, host["depth_gt_observed"], synth.K_LINEMOD,
+                                         pm, means, stds)
+        pose = loop.pose[loop.cur].cpu().numpy()
+        np.testing.assert_allclose(pose, ref["src_pose"], rtol=2e-6, atol=2e-7)
+        np.testing.assert_allclose(loop.rot_gt.cpu().numpy(), ref["rot"], atol=3e-6)
+        np.testing.assert_allclose(loop.trans_gt.cpu().numpy(), ref["trans"], rtol=1e-5, atol=2e-6)
+        depth = loop.depth_rendered.cpu().numpy()
+        fg, rfg = depth > 0, ref["depth_rendered"] > 0
+        assert (fg == rfg).mean() >= 0.999
+        both = fg & rfg
+        rel = np.abs(depth[both] - ref["depth_rendered"][both]) / ref["depth_rendered"][both]
+        assert (rel <= 1e-5).mean() >= 0.999
+        assert np.array_equal(loop.mask_rendered.cpu().numpy(), (depth > 0.2).astype(np.float32))
+        img = loop.image_rendered.cpu().numpy()
+        b3 = np.broadcast_to(both, img.shape)
+        assert (np.abs(img[b3] - ref["image_rendered"][b3]) < 1e-3).mean() >= 0.995
+        valid = loop.step.valid.cpu().numpy()
+        assert (valid == ref["flow_weights"][:, :1]).mean() >= 0.999
+        v2 = (valid > 0) & (ref["flow_weights"][:, :1] > 0)
+        fl = loop.step.flow.cpu().numpy()
+        for c in range(2):
+            assert np.abs(fl[:, c:c + 1][v2] - ref["flow"][:, c:c + 1][v2]).max() < 2e-3
+        # zoom + loss consistent with the oracles fed with the device's own intermediates
+        zm = zoom_np.zoom_mask_forward(host["mask_observed"], host["mask_gt_observed"], depth, pose,
+                                       synth.K_LINEMOD)
+        assert np.array_equal(loop.step.zoom_factor.cpu().numpy(), zm[3])
+        _, _, sums = transform3d_np.pm_loss_forward(
+            host["point_cloud_model"], host["point_cloud_observed"], host["point_cloud_weights"],
+            rot_est, trans_est, pose, means, stds)
+        np.testing.assert_allclose(loop.step.loss_sum.cpu().numpy(), sums, rtol=1e-4)
+        losses.append(float(sums.sum()))
+        prev_pose = pose
+    # the damped ground-truth update converges: the poses approach the targets
+    err0 = np.abs(host["src_pose"] - host["tgt_pose"]).max()
+    err3 = np.abs(prev_pose - host["tgt_pose"]).max()
+    assert err3 < 0.5 * err0
