@@ -55,6 +55,8 @@ struct Renderer {
   TriRec *recs;                              // [max_batch][2*max_tris]
   int32_t *tile_count, *tile_start, *tile_fill;  // [max_batch][n_tiles (+1)]
   int32_t *tile_list;                        // [max_batch][list_cap]
+  int32_t *work_count;                       // [1] number of non-empty (tile, pair) items
+  int32_t *work_list;                        // [max_batch * n_tiles] b * n_tiles + tile
 };
 
 struct Cam {
@@ -262,8 +264,10 @@ raster_scan_kernel(Renderer R, int n_tiles, int32_t *__restrict__ status) {
   int acc = part[threadIdx.x];
   for (int i = lo; i < hi; ++i) {
     start[i] = acc;
-    acc += count[i];
+    const int c = count[i];
+    acc += c;
     fill[i] = 0;
+    if (c > 0) R.work_list[atomicAdd(R.work_count, 1)] = b * n_tiles + i;  // non-empty tiles only
   }
 }
 
@@ -428,14 +432,49 @@ __device__ Shaded shade_pixel(const Renderer &R, const RasterOut &O, const Cam &
   return s;
 }
 
-// grid = (tiles_x * tiles_y, B); block = 256; static smem 8 KB z-buffer.
+// ------------------------------------------------------------------ 4a. clear
+// Streams the background of every output: depth 0, mask 0, image = 0 - mean, bgr 0, tri -1.
+// Plain 128-bit stores, grid-stride; ~20 B/px at HBM write speed.
+__global__ void __launch_bounds__(256)
+raster_clear_kernel(RasterOut O, long long plane_quads, int n_batch) {
+  const long long total = plane_quads * n_batch;  // float4 per single-channel output
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < total; q += stride) {
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    st_f4(reinterpret_cast<float4 *>(O.depth) + q, z);
+    if (O.mask) st_f4(reinterpret_cast<float4 *>(O.mask) + q, z);
+    if (O.tri_id) reinterpret_cast<int4 *>(O.tri_id)[q] = make_int4(-1, -1, -1, -1);
+    if (O.image_chw) {
+      const long long b = q / plane_quads, r = q - b * plane_quads;
+      float4 *img = reinterpret_cast<float4 *>(O.image_chw) + b * 3 * plane_quads + r;
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const float m = 0.f - O.mean[c];
+        st_f4(img + c * plane_quads, make_float4(m, m, m, m));
+      }
+    }
+    if (O.bgr_hwc) {
+      float4 *o = reinterpret_cast<float4 *>(O.bgr_hwc) + q * 3;
+      st_f4(o, z);
+      st_f4(o + 1, z);
+      st_f4(o + 2, z);
+    }
+  }
+}
+
+// grid = a few CTAs per SM (persistent over the non-empty tiles); block = 256; 8 KB z-buffer.
 __global__ void __launch_bounds__(RT_THREADS)
 raster_tile_kernel(Renderer R, const int32_t *__restrict__ cls_idx,
-                   const float *__restrict__ poses, Cam cam, RasterOut O, int n_tiles) {
+                   const float *__restrict__ poses, Cam cam, RasterOut O, int n_tiles, int n_batch) {
   __shared__ unsigned long long zbuf[RT_TILE * RT_TILE];
-  const int b = blockIdx.y, tile = blockIdx.x;
-  const int tx0 = (tile % R.tiles_x) * RT_TILE, ty0 = (tile / R.tiles_x) * RT_TILE;
   const int W = R.W, H = R.H;
+  // persistent CTAs walk the compacted list of NON-EMPTY (tile, pair) items; the background of
+  // the frame is written by raster_clear_kernel at streaming speed.
+  const int n_work = *R.work_count;
+  for (int wi = blockIdx.x; wi < n_work; wi += gridDim.x) {
+  const int work = R.work_list[wi];
+  const int b = work / n_tiles, tile = work - b * n_tiles;
+  const int tx0 = (tile % R.tiles_x) * RT_TILE, ty0 = (tile / R.tiles_x) * RT_TILE;
   const int32_t *start = R.tile_start + (size_t)b * (n_tiles + 1);
   const int first = start[tile];
   const int n = min(start[tile + 1], R.list_cap) - first;
@@ -484,7 +523,7 @@ raster_tile_kernel(Renderer R, const int32_t *__restrict__ cls_idx,
   // resolve: four adjacent pixels per thread
   const int row = threadIdx.x >> 3, xq = (threadIdx.x & 7) * 4;
   const int y = ty0 + row, x = tx0 + xq;
-  if (y >= H || x >= W) return;
+  if (y < H && x < W) {
   const int mesh = __ldg(cls_idx + b);
   const float *pose = poses + b * 12;
   float dz[4], cr[4], cg[4], cb[4];
@@ -537,6 +576,9 @@ raster_tile_kernel(Renderer R, const int32_t *__restrict__ cls_idx,
   }
   if (O.tri_id)
     *reinterpret_cast<int4 *>(O.tri_id + b * plane + pix) = make_int4(tid4[0], tid4[1], tid4[2], tid4[3]);
+  }
+  if (n > 0) __syncthreads();  // z-buffer is re-initialised by the next work item
+  }
 }
 
 }  // namespace rc
@@ -554,8 +596,8 @@ static int dev_alloc(T **p, size_t n) {
 static void renderer_free(Renderer *r) {
   if (!r) return;
   void *ptrs[] = {r->verts, r->uv, r->normals, r->tris, r->mesh_tri_off, r->mesh_has, r->tex,
-                  r->tex_off, r->tex_hw, r->recs, r->tile_count, r->tile_start, r->tile_fill,
-                  r->tile_list};
+                  r->tex_off, r->tex_hw, r->recs, r->work_count, r->tile_start, r->tile_fill,
+                  r->tile_list, r->work_list};
   for (void *p : ptrs)
     if (p) cudaFree(p);
   delete r;
@@ -646,7 +688,9 @@ int rc_renderer_create(const rc_mesh_desc *meshes, int n_meshes, int height, int
   RC_TRY(rc::dev_alloc(&r->tex_off, (size_t)n_meshes));
   RC_TRY(rc::dev_alloc(&r->tex_hw, (size_t)n_meshes * 2));
   RC_TRY(rc::dev_alloc(&r->recs, (size_t)max_batch * 2 * max_tris));
-  RC_TRY(rc::dev_alloc(&r->tile_count, (size_t)max_batch * n_tiles));
+  RC_TRY(rc::dev_alloc(&r->work_count, (size_t)max_batch * n_tiles + 4));  // [4 | tile counts]
+  r->tile_count = r->work_count + 4;
+  RC_TRY(rc::dev_alloc(&r->work_list, (size_t)max_batch * n_tiles));
   RC_TRY(rc::dev_alloc(&r->tile_start, (size_t)max_batch * (n_tiles + 1)));
   RC_TRY(rc::dev_alloc(&r->tile_fill, (size_t)max_batch * n_tiles));
   RC_TRY(rc::dev_alloc(&r->tile_list, (size_t)max_batch * r->list_cap));
@@ -714,7 +758,7 @@ int rc_render_dev(void *handle, const rc_render_args *a) {
   };
   int st;
   if ((st = mark(0)) != RC_OK) return st;
-  RC_CUDA_TRY(cudaMemsetAsync(R.tile_count, 0, sizeof(int32_t) * (size_t)B * n_tiles, s));
+  RC_CUDA_TRY(cudaMemsetAsync(R.work_count, 0, sizeof(int32_t) * ((size_t)B * n_tiles + 4), s));
   dim3 gs((R.max_tris + 255) / 256, B);
   rc::raster_setup_kernel<<<gs, 256, 0, s>>>(R, a->cls_idx, a->poses, cam, n_tiles);
   if ((st = mark(1)) != RC_OK) return st;
@@ -723,8 +767,19 @@ int rc_render_dev(void *handle, const rc_render_args *a) {
   dim3 gf((2 * R.max_tris + 255) / 256, B);
   rc::raster_fill_kernel<<<gf, 256, 0, s>>>(R, a->cls_idx, n_tiles);
   if ((st = mark(3)) != RC_OK) return st;
-  dim3 gr(n_tiles, B);
-  rc::raster_tile_kernel<<<gr, rc::RT_THREADS, 0, s>>>(R, a->cls_idx, a->poses, cam, O, n_tiles);
+  static int sm_count = 0;
+  if (sm_count == 0 &&
+      cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, R.device) != cudaSuccess)
+    sm_count = 148;
+  {
+    const long long plane_quads = (long long)R.H * R.W / 4;
+    long long blocks = (plane_quads * B + 255) / 256;
+    if (blocks > sm_count * 16) blocks = sm_count * 16;
+    rc::raster_clear_kernel<<<(int)blocks, 256, 0, s>>>(O, plane_quads, B);
+  }
+  int gr = sm_count * 4;
+  if (gr > n_tiles * B) gr = n_tiles * B;
+  rc::raster_tile_kernel<<<gr, rc::RT_THREADS, 0, s>>>(R, a->cls_idx, a->poses, cam, O, n_tiles, B);
   if ((st = mark(4)) != RC_OK) return st;
   return rc::note_status(rc::check_launch());
 }

@@ -291,12 +291,25 @@ class RefineLoop(object):
                                            np.ones(3), "CAMERA")
         self.rot_gt.copy_(t(q0))
         self.trans_gt.copy_(t(t0))
+        self._pose0 = None
         for par in (0, 1):
             x = dict(self.obs)
             x.update(image_rendered=self.image_rendered, depth_rendered=self.depth_rendered,
                      src_pose=self.pose[par], KT=self.KT, rot_est=self.rot_est,
                      trans_est=self.trans_est, trans_gt=self.trans_gt)
             self.bound[par] = self.step.bind(x)
+
+    def set_batch_poses(self, host):
+        """Restart the loop from the batch's initial source poses (same observed side)."""
+        if getattr(self, "_pose0", None) is None:
+            t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(self.device)
+            self._pose0 = t(host["src_pose"])
+            self._rot0 = self.rot_gt.clone()
+            self._trans0 = self.trans_gt.clone()
+        self.pose[0].copy_(self._pose0)
+        self.rot_gt.copy_(self._rot0)
+        self.trans_gt.copy_(self._trans0)
+        self.cur = 0
 
     def iterate(self, it, marks=None, render_marks=None):
         """One refinement iteration on the current stream (no synchronisation)."""
