@@ -300,59 +300,6 @@ __device__ __forceinline__ float pre(float v, int pre_op, float mean) {
   return v;
 }
 
-__device__ __forceinline__ void post4(float (&v)[4], const ZoomPlane &zp, const ZoomParams &P,
-                                      float wx_in, int i0, int j) {
-  switch (zp.post_op) {
-    case RC_POST_ROUND:
-#pragma unroll
-      for (int k = 0; k < 4; ++k) v[k] = truncf(__fadd_rz(v[k], copysignf(0.5f, v[k])));
-      break;
-    case RC_POST_ROUND_M045:
-#pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        const float t = __fsub_rn(v[k], 0.45f);
-        v[k] = truncf(__fadd_rz(t, copysignf(0.5f, t)));
-      }
-      break;
-    case RC_POST_DIV_WX:
-#pragma unroll
-      for (int k = 0; k < 4; ++k) v[k] = __fdiv_rn(v[k], wx_in);
-      break;
-    case RC_POST_MUL_WX:
-#pragma unroll
-      for (int k = 0; k < 4; ++k) v[k] = __fmul_rn(v[k], wx_in);
-      break;
-    case RC_POST_SUB_MEAN:
-#pragma unroll
-      for (int k = 0; k < 4; ++k) v[k] = __fsub_rn(v[k], zp.mean);
-      break;
-    case RC_POST_SPOT_SUB_MEAN:
-#pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        const int x = i0 + k;
-        const float spot = (zp.channel == 0 && x >= P.spot_x0 && x < P.spot_x1 &&
-                            j >= P.spot_y0 && j < P.spot_y1) ? 255.f : 0.f;
-        v[k] = __fsub_rn(fmaxf(v[k], spot), zp.mean);
-      }
-      break;
-    default:
-      break;
-  }
-}
-
-__device__ __forceinline__ void store4(const ZoomPlane &zp, int b, int q, const float (&v)[4]) {
-  float4 *d = reinterpret_cast<float4 *>(zp.dst + (long long)b * zp.dst_bstride) + q;
-  float4 o = make_float4(v[0], v[1], v[2], v[3]);
-  if (zp.accumulate) {
-    const float4 old = *d;
-    o.x += old.x;
-    o.y += old.y;
-    o.z += old.z;
-    o.w += old.w;
-  }
-  st_f4(d, o);
-}
-
 // The four-tap blend of MXNet's BilinearSampler (bilinear_sampler.cu forward kernel),
 // evaluated in float32 in the operator's left-to-right association.
 __device__ __forceinline__ float blend(float tl, float tr, float bl, float br, float wyt,
@@ -364,10 +311,11 @@ __device__ __forceinline__ float blend(float tl, float tr, float bl, float br, f
   return v;
 }
 
-// Output tile of one block: ZT_W x ZT_H pixels, 256 threads, four adjacent pixels each.
-constexpr int ZT_W = 64;
-constexpr int ZT_H = 16;
-constexpr int ZT_THREADS = 256;
+// Output tile of one block: ZT_W x ZT_H pixels, 128 threads; a thread owns one column of
+// the tile (eight vertically adjacent outputs).
+constexpr int ZT_W = 128;
+constexpr int ZT_H = 8;
+constexpr int ZT_THREADS = 128;
 constexpr int ZT_BATCH = 8;  // planes whose window loads are in flight together
 
 // Per-plane, per-sample constants resolved once per block (shared memory).
@@ -379,33 +327,138 @@ struct PlaneCtx {
   int pad_[3];
 };
 
+// What the staging loop needs per plane, 24 bytes (see the kernel for the encoding).
+struct StageCtx {
+  const float *src;
+  float thr, keep, add;
+  int pad_;
+};
+
+__device__ __forceinline__ void sts_f1(uint32_t addr, float v) {
+  asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+}
+
 // round half away from zero, the FADD.RZ + FRND.TRUNC sequence CUDA's roundf reduces to
 // for |v| < 2^23 (exact for every float: v + 0.5 rounded toward zero never crosses an integer).
 __device__ __forceinline__ float round_away(float v) {
   return truncf(__fadd_rz(v, copysignf(0.5f, v)));
 }
 
-// grid = (ceil(W/ZT_W), ceil(H/ZT_H), B); block = 256; dynamic smem = smem_floats * 4.
+// 64-bit shared-memory load from a 32-bit shared-window address (keeps the address
+// arithmetic in 32-bit registers instead of re-deriving the generic pointer per plane).
+__device__ __forceinline__ float2 lds_f2(uint32_t addr) {
+  float2 v;
+  asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(addr));
+  return v;
+}
+
+// IEEE-754 round-to-nearest a / b without the library's slow path.  `rb` = RN(1/b).  For
+// operands inside the guarded exponent range the two FMA refinements below deliver the
+// correctly rounded quotient (Markstein; checked exhaustively-at-random on 4e8 operand pairs
+// including all-ones / all-zeros significands against the host's IEEE division); zero
+// numerators -- the background of a flow field, i.e. most pixels -- would otherwise take
+// __fdiv_rn's ~60-instruction special-case subroutine.
+__device__ __forceinline__ float div_rn_guarded(float a, float b, float rb, bool b_ok) {
+  const float aa = fabsf(a);
+  if (aa == 0.f) return __fmul_rn(a, b);  // +-0 with the sign of a / b
+  if (b_ok && aa > 1e-15f && aa < 1e15f) {
+    float q = __fmul_rn(a, rb);
+    float r = __fmaf_rn(-b, q, a);
+    q = __fmaf_rn(r, rb, q);
+    r = __fmaf_rn(-b, q, a);
+    return __fmaf_rn(r, rb, q);
+  }
+  return __fdiv_rn(a, b);
+}
+
+// Post-operation on the ZT_H outputs of one column (x = i, rows j0 .. j0 + ZT_H - 1).
+__device__ __forceinline__ void post_col(float (&out)[ZT_H], int post_op, float mean, int channel,
+                                         const ZoomParams &P, float wx_in, float rwx, bool wx_ok,
+                                         int i, int j0) {
+  switch (post_op) {
+    case RC_POST_ROUND:
+#pragma unroll
+      for (int k = 0; k < ZT_H; ++k) out[k] = round_away(out[k]);
+      break;
+    case RC_POST_ROUND_M045:
+#pragma unroll
+      for (int k = 0; k < ZT_H; ++k) out[k] = round_away(__fsub_rn(out[k], 0.45f));
+      break;
+    case RC_POST_DIV_WX:
+#pragma unroll
+      for (int k = 0; k < ZT_H; ++k) out[k] = div_rn_guarded(out[k], wx_in, rwx, wx_ok);
+      break;
+    case RC_POST_MUL_WX:
+#pragma unroll
+      for (int k = 0; k < ZT_H; ++k) out[k] = __fmul_rn(out[k], wx_in);
+      break;
+    case RC_POST_SUB_MEAN:
+#pragma unroll
+      for (int k = 0; k < ZT_H; ++k) out[k] = __fsub_rn(out[k], mean);
+      break;
+    case RC_POST_SPOT_SUB_MEAN: {
+      const bool xin = (channel == 0) && (i >= P.spot_x0) && (i < P.spot_x1);
+#pragma unroll
+      for (int k = 0; k < ZT_H; ++k) {
+        const int j = j0 + k;
+        const float spot = (xin && j >= P.spot_y0 && j < P.spot_y1) ? 255.f : 0.f;
+        out[k] = __fsub_rn(fmaxf(out[k], spot), mean);
+      }
+      break;
+    }
+    default:
+      break;
+  }
+}
+
+// Row coordinate of one output row: source row index and the two row weights.
+struct RowCoord {
+  int y0;
+  float wt, wb;
+};
+__device__ __forceinline__ RowCoord row_coord(int j, float stepy, float wy, float ty, float nym1) {
+  const float yr = src_coord(j, stepy, wy, ty, nym1);
+  const float yf = floorf(yr);
+  RowCoord r;
+  r.y0 = (int)yf;
+  r.wt = __fsub_rn(1.0f, __fsub_rn(yr, yf));
+  r.wb = __fsub_rn(1.0f, r.wt);
+  return r;
+}
+
+// grid = (ceil(W/ZT_W), ceil(H/ZT_H), B); block = 128; dynamic smem = smem_floats * 4.
 //
-// The source window of a tile -- [x_lo, x_hi] x [y_lo, y_hi], every tap any of its
-// 1024 outputs can touch -- is staged into shared memory once per plane with the
-// pre-operation applied and out-of-image taps set to zero.  Window element (r, c) is
-// stored as the float2 {v(r, c), v(r+1, c)}, so an output fetches its four taps with two
-// 64-bit LDS at a constant 8-byte distance; per output that leaves 2 LDS + 8 FP32
-// operations and a quarter of a 128-bit store.  As many planes as fit are staged per
-// barrier pair.  Tiles whose window does not fit (strong zoom-out / inverse zoom) fall
-// back to gathering through the read-only path.
-__global__ void __launch_bounds__(ZT_THREADS)
+// One thread owns ONE output column of the 128 x 8 tile and walks its eight rows; the lanes
+// of a warp are 32 adjacent columns.  Consequences, in order of weight:
+//  * everything that depends on the row (source row, row weights, which window rows to read)
+//    depends on blockIdx only, so the compiler keeps it in uniform registers and the
+//    row-to-row reuse below is decided by uniform branches;
+//  * the source window of the tile is staged in shared memory once per plane (pre-operation
+//    applied, out-of-image taps zero) as HORIZONTAL pairs {v(r,c), v(r,c+1)}: one 64-bit LDS
+//    fetches the left and right tap of a row.  Zooming in, consecutive output rows share
+//    source rows, so a column of eight outputs needs only ~8*wy+2 such loads instead of 16,
+//    and the 16 lanes one shared-memory wavefront serves read 16*wx+1 <= 16 consecutive
+//    pairs of one row: conflict-free by construction;
+//  * every store instruction writes 128 contiguous bytes per warp.
+// As many planes as fit are staged per barrier pair.  Tiles whose window does not fit
+// (strong zoom-out / inverse zoom) fall back to gathering through the read-only path.
+//
+// WC: compile-time image width (0 = use P.W); with the width known the eight row stores of a
+// column use immediate offsets from one address.
+template <int WC>
+__global__ void __launch_bounds__(ZT_THREADS, 8)
 zoom_sample_kernel(const __grid_constant__ ZoomParams P, int smem_floats) {
   extern __shared__ float2 win[];
   __shared__ PlaneCtx ctx[RC_ZOOM_MAX_PLANES];
-  const int H = P.H, W = P.W;
+  __shared__ StageCtx sctx[RC_ZOOM_MAX_PLANES];
+  const int H = P.H, W = WC ? WC : P.W;
   const int b = blockIdx.z;
-  const int tx4 = threadIdx.x & 15, trow = threadIdx.x >> 4;
   const int i_first = blockIdx.x * ZT_W, j_first = blockIdx.y * ZT_H;
   const int i_last = min(i_first + ZT_W, W) - 1, j_last = min(j_first + ZT_H, H) - 1;
-  const int i0 = i_first + tx4 * 4, j = j_first + trow;
-  const bool active = (i0 < W) && (j < H);
+  const int i = i_first + threadIdx.x;
+  const bool act = i < W;
+  const bool full_rows = j_first + ZT_H <= H;
+  const size_t col_off = (size_t)j_first * W + i;
 
   if (threadIdx.x < P.n_planes) {
     const ZoomPlane &zp = P.planes[threadIdx.x];
@@ -418,40 +471,49 @@ zoom_sample_kernel(const __grid_constant__ ZoomParams P, int smem_floats) {
     c.channel = zp.channel;
     c.mean = zp.mean;
     ctx[threadIdx.x] = c;
+    // staging constants: tap = v > thr ? 1 : fma(v, keep, add)
+    //   NONE      thr = +inf, keep = 1, add = -0  (v + -0 == v bit for bit)
+    //   THRESH02  thr = 0.2,  keep = 0, add = 0   (zoom_mask.py:40-45)
+    //   ADD_MEAN  thr = +inf, keep = 1, add = mean (zoom_image_with_factor.py:46)
+    StageCtx s;
+    s.src = c.src;
+    s.thr = (zp.pre_op == RC_PRE_THRESH02) ? 0.2f : __int_as_float(0x7f800000);
+    s.keep = (zp.pre_op == RC_PRE_THRESH02) ? 0.f : 1.f;
+    s.add = (zp.pre_op == RC_PRE_ADD_MEAN) ? zp.mean : ((zp.pre_op == RC_PRE_THRESH02) ? 0.f : -0.f);
+    s.pad_ = 0;
+    sctx[threadIdx.x] = s;
   }
 
   float wx, wy, tx, ty, wx_in;
   zoom_affine(P.zoom_factor + b * 4, P.inverse, H, W, wx, wy, tx, ty, wx_in);
   const float stepx = (float)(2.0 / (W - 1)), stepy = (float)(2.0 / (H - 1));
   const float nxm1 = (float)(W - 1), nym1 = (float)(H - 1);
+  // division by wx_in (ZoomFlow): reciprocal once per thread; the FMA refinement is exact
+  // unless wx_in is tiny/huge or its significand is all ones (then __fdiv_rn is used).
+  const float rwx = __frcp_rn(wx_in);
+  const float awx = fabsf(wx_in);
+  const bool wx_ok = (awx > 1e-15f) && (awx < 1e15f) &&
+                     ((__float_as_uint(wx_in) & 0x7fffffu) != 0x7fffffu);
 
-  // per-thread coordinates (clamped indices keep inactive threads harmless)
-  const int jc = min(j, H - 1);
-  const float yr = src_coord(jc, stepy, wy, ty, nym1);
-  const float yf = floorf(yr);
-  const int y0 = (int)yf;
-  const float wyt = __fsub_rn(1.0f, __fsub_rn(yr, yf));
-  const float wyb = __fsub_rn(1.0f, wyt);
-  int x0[4];
-  float wxl[4], wxr[4];
+  // column coordinate of this thread (clamped index keeps inactive threads harmless)
+  const float xr = src_coord(min(i, W - 1), stepx, wx, tx, nxm1);
+  const float xf = floorf(xr);
+  const int x0 = (int)xf;
+  const float wl = __fsub_rn(1.0f, __fsub_rn(xr, xf));
+  const float wr = __fsub_rn(1.0f, wl);
+  // row coordinates of the tile (block-uniform)
+  RowCoord rows[ZT_H];
 #pragma unroll
-  for (int k = 0; k < 4; ++k) {
-    const float xr = src_coord(min(i0 + k, W - 1), stepx, wx, tx, nxm1);
-    const float xf = floorf(xr);
-    x0[k] = (int)xf;
-    wxl[k] = __fsub_rn(1.0f, __fsub_rn(xr, xf));
-    wxr[k] = __fsub_rn(1.0f, wxl[k]);
-  }
-  const int q = (j * W + i0) >> 2;
+  for (int m = 0; m < ZT_H; ++m) rows[m] = row_coord(min(j_first + m, H - 1), stepy, wy, ty, nym1);
 
   // tile window (block-uniform); src_coord is monotone in the index when the scale is > 0
   const float fx_lo = floorf(src_coord(i_first, stepx, wx, tx, nxm1));
   const float fx_hi = floorf(src_coord(i_last, stepx, wx, tx, nxm1));
   const float fy_lo = floorf(src_coord(j_first, stepy, wy, ty, nym1));
   const float fy_hi = floorf(src_coord(j_last, stepy, wy, ty, nym1));
-  // window elements: columns x_lo .. x_hi+1, row pairs y_lo .. y_hi
-  const float wwf = fx_hi - fx_lo + 2.0f, whf = fy_hi - fy_lo + 1.0f;
-  const bool staged = (wx > 0.f) && (wy > 0.f) && (wwf >= 2.0f) && (whf >= 1.0f) &&
+  // window pairs: columns x_lo .. x_hi (each with its right neighbour), rows y_lo .. y_hi+1
+  const float wwf = fx_hi - fx_lo + 1.0f, whf = fy_hi - fy_lo + 2.0f;
+  const bool staged = (wx > 0.f) && (wy > 0.f) && (wwf >= 1.0f) && (whf >= 2.0f) &&
                       (2.0f * wwf * whf <= (float)smem_floats) && (fabsf(fx_lo) < 1e6f) &&
                       (fabsf(fy_lo) < 1e6f);
   __syncthreads();  // ctx[] visible
@@ -460,98 +522,99 @@ zoom_sample_kernel(const __grid_constant__ ZoomParams P, int smem_floats) {
     const int ww = (int)wwf, wh = (int)whf;
     const int win_elems = ww * wh;
     const int pps = max(1, min(P.n_planes, (smem_floats >> 1) / win_elems));  // planes per stage
-    int off[4];
-#pragma unroll
-    for (int k = 0; k < 4; ++k) off[k] = (y0 - y_lo) * ww + (x0[k] - x_lo);
+    const uint32_t win_s = (uint32_t)__cvta_generic_to_shared(win);
+    const uint32_t a_col = win_s + 8u * (uint32_t)(x0 - x_lo);
+    const uint32_t pitch = 8u * (uint32_t)ww;
+    const uint32_t plane_bytes = 8u * (uint32_t)win_elems;
     for (int p0 = 0; p0 < P.n_planes; p0 += pps) {
       const int np = min(pps, P.n_planes - p0);
       if (p0 > 0) __syncthreads();  // consumers of the previous stage are done
-      // Source rows y_lo .. y_lo + wh (one more than the row pairs); every global element is
-      // loaded once and written to the .x slot of its own row pair and the .y slot of the
-      // pair above.  Loads of up to ZT_BATCH planes are issued before any is consumed.
-      float *winf = reinterpret_cast<float *>(win);
-      const int src_elems = ww * (wh + 1);
+      // Source columns x_lo .. x_lo + ww (one more than the pairs); every global element is
+      // loaded once and written to the .x slot of its own pair and the .y slot of the pair
+      // to its left.  Loads of up to ZT_BATCH planes are issued before any is consumed.
+      const int sw = ww + 1;
+      const int src_elems = sw * wh;
+      const float inv_sw = __frcp_rn((float)sw);
+      const uint32_t win_f = win_s;  // float-granular shared address of plane 0
       for (int idx = threadIdx.x; idx < src_elems; idx += ZT_THREADS) {
-        const int r = idx / ww, c = idx - r * ww;
+        int r = __float2int_rz(__fmul_rn((float)idx + 0.5f, inv_sw));
+        int c = idx - r * sw;
+        if (c < 0) {
+          c += sw;
+          --r;
+        } else if (c >= sw) {
+          c -= sw;
+          ++r;
+        }
         const int ys = y_lo + r, xs = x_lo + c;
         const bool inb = (xs >= 0) && (xs <= W - 1) && (ys >= 0) && (ys <= H - 1);
-        const long long goff = (long long)ys * W + xs;
-        const int slot_x = (r < wh) ? 2 * idx : -1;              // {v(r,c), .}
-        const int slot_y = (r >= 1) ? 2 * (idx - ww) + 1 : -1;   // {., v(r,c)} of the pair above
-        for (int pb = 0; pb < np; pb += ZT_BATCH) {
-          float v[ZT_BATCH];
+        const int goff = inb ? ys * W + xs : 0;
+        const int e = r * ww + c;
+        const bool has_x = c < ww, has_y = c >= 1;
+        uint32_t ax = win_f + 8u * (uint32_t)e;  // .x of pair (r, c); .y of pair (r, c-1) is ax - 4
+        if (inb) {
+#pragma unroll 1
+          for (int pb = 0; pb < np; pb += ZT_BATCH) {
+            float v[ZT_BATCH];
 #pragma unroll
-          for (int u = 0; u < ZT_BATCH; ++u) {
-            v[u] = 0.f;
-            if (inb && pb + u < np) v[u] = __ldg(ctx[p0 + pb + u].src + goff);
-          }
+            for (int u = 0; u < ZT_BATCH; ++u)
+              if (pb + u < np) v[u] = __ldg(sctx[p0 + pb + u].src + goff);
 #pragma unroll
-          for (int u = 0; u < ZT_BATCH; ++u) {
-            if (pb + u < np) {
-              const PlaneCtx &c_ = ctx[p0 + pb + u];
-              const float t = inb ? pre(v[u], c_.pre_op, c_.mean) : 0.f;
-              float *wpl = winf + 2 * (pb + u) * win_elems;
-              if (slot_x >= 0) wpl[slot_x] = t;
-              if (slot_y >= 0) wpl[slot_y] = t;
+            for (int u = 0; u < ZT_BATCH; ++u) {
+              if (pb + u < np) {
+                const StageCtx &s_ = sctx[p0 + pb + u];
+                const float t = v[u] > s_.thr ? 1.0f : __fmaf_rn(v[u], s_.keep, s_.add);
+                if (has_x) sts_f1(ax, t);
+                if (has_y) sts_f1(ax - 4u, t);
+                ax += plane_bytes;
+              }
             }
+          }
+        } else {
+          for (int pl = 0; pl < np; ++pl, ax += plane_bytes) {
+            if (has_x) sts_f1(ax, 0.f);
+            if (has_y) sts_f1(ax - 4u, 0.f);
           }
         }
       }
       __syncthreads();
-      if (active) {
-        for (int pl = 0; pl < np; ++pl) {
-          const PlaneCtx &c_ = ctx[p0 + pl];
-          const float2 *wp = win + pl * win_elems;
-          float out[4];
+      uint32_t a_pl = a_col;
+      for (int pl = 0; pl < np; ++pl, a_pl += plane_bytes) {
+        const PlaneCtx &c_ = ctx[p0 + pl];
+        float out[ZT_H];
+        float2 top = make_float2(0.f, 0.f), bot = top;  // {left, right} taps of the two rows
+        int cur = -2;                                    // window row held in `top`
 #pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            const float2 l = wp[off[k]];      // {top-left, bottom-left}
-            const float2 r = wp[off[k] + 1];  // {top-right, bottom-right}
-            out[k] = blend(l.x, r.x, l.y, r.y, wyt, wyb, wxl[k], wxr[k]);
+        for (int m = 0; m < ZT_H; ++m) {
+          const int ry = rows[m].y0 - y_lo;  // block-uniform
+          if (ry != cur) {
+            if (ry == cur + 1) {
+              top = bot;
+            } else {
+              top = lds_f2(a_pl + (uint32_t)ry * pitch);
+            }
+            bot = lds_f2(a_pl + (uint32_t)(ry + 1) * pitch);
+            cur = ry;
           }
-          switch (c_.post_op) {
-            case RC_POST_ROUND:
+          out[m] = blend(top.x, top.y, bot.x, bot.y, rows[m].wt, rows[m].wb, wl, wr);
+        }
+        const int post_op = c_.post_op, channel = c_.channel, acc = c_.accumulate;
+        const float mean = c_.mean;
+        float *dst = c_.dst + col_off;
+        post_col(out, post_op, mean, channel, P, wx_in, rwx, wx_ok, i, j_first);
+        if (act) {
+          if (!acc && full_rows) {
 #pragma unroll
-              for (int k = 0; k < 4; ++k) out[k] = round_away(out[k]);
-              break;
-            case RC_POST_ROUND_M045:
+            for (int m = 0; m < ZT_H; ++m) dst[m * W] = out[m];
+          } else {
 #pragma unroll
-              for (int k = 0; k < 4; ++k) out[k] = round_away(__fsub_rn(out[k], 0.45f));
-              break;
-            case RC_POST_DIV_WX:
-#pragma unroll
-              for (int k = 0; k < 4; ++k) out[k] = __fdiv_rn(out[k], wx_in);
-              break;
-            case RC_POST_MUL_WX:
-#pragma unroll
-              for (int k = 0; k < 4; ++k) out[k] = __fmul_rn(out[k], wx_in);
-              break;
-            case RC_POST_SUB_MEAN:
-#pragma unroll
-              for (int k = 0; k < 4; ++k) out[k] = __fsub_rn(out[k], c_.mean);
-              break;
-            case RC_POST_SPOT_SUB_MEAN:
-#pragma unroll
-              for (int k = 0; k < 4; ++k) {
-                const int x = i0 + k;
-                const float spot = (c_.channel == 0 && x >= P.spot_x0 && x < P.spot_x1 &&
-                                    j >= P.spot_y0 && j < P.spot_y1) ? 255.f : 0.f;
-                out[k] = __fsub_rn(fmaxf(out[k], spot), c_.mean);
+            for (int m = 0; m < ZT_H; ++m) {
+              if (j_first + m < H) {
+                float *d = dst + (size_t)m * W;
+                *d = acc ? __fadd_rn(*d, out[m]) : out[m];
               }
-              break;
-            default:
-              break;
+            }
           }
-          float4 *d = reinterpret_cast<float4 *>(c_.dst) + q;
-          float4 o = make_float4(out[0], out[1], out[2], out[3]);
-          if (c_.accumulate) {
-            const float4 old = *d;
-            o.x += old.x;
-            o.y += old.y;
-            o.z += old.z;
-            o.w += old.w;
-          }
-          st_f4(d, o);
         }
       }
     }
@@ -559,28 +622,35 @@ zoom_sample_kernel(const __grid_constant__ ZoomParams P, int smem_floats) {
   }
 
   // ---- fallback: gather every tap through the read-only path, bounds-checked
-  if (!active) return;
-  const bool yin0 = (y0 >= 0) && (y0 <= H - 1);
-  const bool yin1 = (y0 + 1 >= 0) && (y0 + 1 <= H - 1);
+  if (!act) return;
+  const bool xin0 = (x0 >= 0) && (x0 <= W - 1);
+  const bool xin1 = (x0 + 1 >= 0) && (x0 + 1 <= W - 1);
   for (int pl = 0; pl < P.n_planes; ++pl) {
     const ZoomPlane &zp = P.planes[pl];
     const float *__restrict__ s = zp.src + (long long)b * zp.src_bstride;
-    const float *__restrict__ r0 = s + (long long)y0 * W;
-    const float *__restrict__ r1 = r0 + W;
-    float out[4];
+    float out[ZT_H];
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const int xa = x0[k], xb = x0[k] + 1;
-      const bool xin0 = (xa >= 0) && (xa <= W - 1);
-      const bool xin1 = (xb >= 0) && (xb <= W - 1);
-      const float tl = (yin0 && xin0) ? pre(__ldg(r0 + xa), zp.pre_op, zp.mean) : 0.f;
-      const float tr = (yin0 && xin1) ? pre(__ldg(r0 + xb), zp.pre_op, zp.mean) : 0.f;
-      const float bl = (yin1 && xin0) ? pre(__ldg(r1 + xa), zp.pre_op, zp.mean) : 0.f;
-      const float br = (yin1 && xin1) ? pre(__ldg(r1 + xb), zp.pre_op, zp.mean) : 0.f;
-      out[k] = blend(tl, tr, bl, br, wyt, wyb, wxl[k], wxr[k]);
+    for (int m = 0; m < ZT_H; ++m) {
+      const int y0 = rows[m].y0;
+      const bool yin0 = (y0 >= 0) && (y0 <= H - 1);
+      const bool yin1 = (y0 + 1 >= 0) && (y0 + 1 <= H - 1);
+      const float *__restrict__ r0 = s + (long long)y0 * W;
+      const float *__restrict__ r1 = r0 + W;
+      const float tl = (yin0 && xin0) ? pre(__ldg(r0 + x0), zp.pre_op, zp.mean) : 0.f;
+      const float tr = (yin0 && xin1) ? pre(__ldg(r0 + x0 + 1), zp.pre_op, zp.mean) : 0.f;
+      const float bl = (yin1 && xin0) ? pre(__ldg(r1 + x0), zp.pre_op, zp.mean) : 0.f;
+      const float br = (yin1 && xin1) ? pre(__ldg(r1 + x0 + 1), zp.pre_op, zp.mean) : 0.f;
+      out[m] = blend(tl, tr, bl, br, rows[m].wt, rows[m].wb, wl, wr);
     }
-    post4(out, zp, P, wx_in, i0, j);
-    store4(zp, b, q, out);
+    post_col(out, zp.post_op, zp.mean, zp.channel, P, wx_in, rwx, wx_ok, i, j_first);
+    float *dst = zp.dst + (long long)b * zp.dst_bstride + (size_t)j_first * W + i;
+#pragma unroll
+    for (int m = 0; m < ZT_H; ++m) {
+      if (j_first + m < H) {
+        float *d = dst + (size_t)m * W;
+        *d = zp.accumulate ? __fadd_rn(*d, out[m]) : out[m];
+      }
+    }
   }
 }
 
@@ -706,21 +776,28 @@ int rc_zoom_sample_dev(const float *zoom_factor, int inverse, const rc_zoom_grou
   P.spot_x1 = (int)ceil((double)width / 2 + 5);
   P.spot_y0 = (int)floor((double)height / 2 - 5);
   P.spot_y1 = (int)ceil((double)height / 2 + 5);
-  // 48 KB of staging per block: all 13 planes of the default configuration fit for
-  // zoom factors up to ~0.9 (window (64*0.9+2) x (16*0.9+2) floats per plane); four blocks
-  // per SM stay resident.
-  constexpr int kSmemFloats = 12288;
+  // 26 KB of staging per block (+ the 1 KB plane context): eight 128-thread blocks stay
+  // resident per SM; all 13 planes of the default configuration fit in one stage for zoom
+  // factors up to ~0.45 (window (128*wx+1) x (8*wy+3) float2 per plane).
+  constexpr int kSmemFloats = 6656;
   static bool attr_set = false;
   if (!attr_set) {
-    RC_CUDA_TRY(cudaFuncSetAttribute(rc::zoom_sample_kernel,
+    RC_CUDA_TRY(cudaFuncSetAttribute(rc::zoom_sample_kernel<640>,
+                                     cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     kSmemFloats * (int)sizeof(float)));
+    RC_CUDA_TRY(cudaFuncSetAttribute(rc::zoom_sample_kernel<0>,
                                      cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      kSmemFloats * (int)sizeof(float)));
     attr_set = true;
   }
   dim3 grid((width + rc::ZT_W - 1) / rc::ZT_W, (height + rc::ZT_H - 1) / rc::ZT_H, batch_size);
   RC_REQUIRE(batch_size <= 65535, RC_ERR_INVALID_ARG);
-  rc::zoom_sample_kernel<<<grid, rc::ZT_THREADS, kSmemFloats * sizeof(float),
-                           static_cast<cudaStream_t>(stream)>>>(P, kSmemFloats);
+  if (width == 640)
+    rc::zoom_sample_kernel<640><<<grid, rc::ZT_THREADS, kSmemFloats * sizeof(float),
+                                  static_cast<cudaStream_t>(stream)>>>(P, kSmemFloats);
+  else
+    rc::zoom_sample_kernel<0><<<grid, rc::ZT_THREADS, kSmemFloats * sizeof(float),
+                                static_cast<cudaStream_t>(stream)>>>(P, kSmemFloats);
   return rc::note_status(rc::check_launch());
 }
 
