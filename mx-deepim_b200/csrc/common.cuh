@@ -70,6 +70,10 @@ __device__ __forceinline__ void st_f4(float4 *p, const float4 &v) {
                : "memory");
 }
 
+__device__ __forceinline__ void st_f1(float *p, float v) {
+  asm volatile("st.global.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -526,6 +526,21 @@ zoom_sample_kernel(const __grid_constant__ ZoomParams P, int smem_floats) {
     const uint32_t a_col = win_s + 8u * (uint32_t)(x0 - x_lo);
     const uint32_t pitch = 8u * (uint32_t)ww;
     const uint32_t plane_bytes = 8u * (uint32_t)win_elems;
+    // Row stepping pattern of the tile: bit m of step_mask = row m reads one source row
+    // further down than row m-1; jump_mask = any other change (zoom-out).  Block-uniform by
+    // construction; the warp reduction makes that visible to the compiler, which then keeps
+    // the masks in uniform registers and branches uniformly.
+    unsigned sm_ = 0u, jm_ = 0u;
+#pragma unroll
+    for (int m = 1; m < ZT_H; ++m) {
+      const int d = rows[m].y0 - rows[m - 1].y0;
+      if (d == 1) sm_ |= 1u << m;
+      else if (d != 0) jm_ |= 1u << m;
+    }
+    const unsigned step_mask = __reduce_or_sync(0xffffffffu, sm_);
+    const unsigned jump_mask = __reduce_or_sync(0xffffffffu, jm_);
+    uint32_t a_row0 = a_col + (uint32_t)(rows[0].y0 - y_lo) * pitch;
+    asm volatile("" : "+r"(a_row0));  // keep the shared-window address in a register
     for (int p0 = 0; p0 < P.n_planes; p0 += pps) {
       const int np = min(pps, P.n_planes - p0);
       if (p0 > 0) __syncthreads();  // consumers of the previous stage are done
@@ -578,25 +593,33 @@ zoom_sample_kernel(const __grid_constant__ ZoomParams P, int smem_floats) {
         }
       }
       __syncthreads();
-      uint32_t a_pl = a_col;
+      uint32_t a_pl = a_row0;
       for (int pl = 0; pl < np; ++pl, a_pl += plane_bytes) {
         const PlaneCtx &c_ = ctx[p0 + pl];
         float out[ZT_H];
-        float2 top = make_float2(0.f, 0.f), bot = top;  // {left, right} taps of the two rows
-        int cur = -2;                                    // window row held in `top`
+        if (jump_mask == 0u) {
+          // zoom-in: a row either shares both source rows with the row above or advances by one
+          uint32_t ab = a_pl;
+          float2 top = lds_f2(ab);  // {left, right} taps of the upper source row
+          ab += pitch;
+          float2 bot = lds_f2(ab);
+          out[0] = blend(top.x, top.y, bot.x, bot.y, rows[0].wt, rows[0].wb, wl, wr);
 #pragma unroll
-        for (int m = 0; m < ZT_H; ++m) {
-          const int ry = rows[m].y0 - y_lo;  // block-uniform
-          if (ry != cur) {
-            if (ry == cur + 1) {
+          for (int m = 1; m < ZT_H; ++m) {
+            if (step_mask & (1u << m)) {  // warp-uniform
               top = bot;
-            } else {
-              top = lds_f2(a_pl + (uint32_t)ry * pitch);
+              ab += pitch;
+              bot = lds_f2(ab);
             }
-            bot = lds_f2(a_pl + (uint32_t)(ry + 1) * pitch);
-            cur = ry;
+            out[m] = blend(top.x, top.y, bot.x, bot.y, rows[m].wt, rows[m].wb, wl, wr);
           }
-          out[m] = blend(top.x, top.y, bot.x, bot.y, rows[m].wt, rows[m].wb, wl, wr);
+        } else {
+#pragma unroll
+          for (int m = 0; m < ZT_H; ++m) {
+            const uint32_t at = a_pl + (uint32_t)(rows[m].y0 - rows[0].y0) * pitch;
+            const float2 top = lds_f2(at), bot = lds_f2(at + pitch);
+            out[m] = blend(top.x, top.y, bot.x, bot.y, rows[m].wt, rows[m].wb, wl, wr);
+          }
         }
         const int post_op = c_.post_op, channel = c_.channel, acc = c_.accumulate;
         const float mean = c_.mean;
@@ -605,7 +628,7 @@ zoom_sample_kernel(const __grid_constant__ ZoomParams P, int smem_floats) {
         if (act) {
           if (!acc && full_rows) {
 #pragma unroll
-            for (int m = 0; m < ZT_H; ++m) dst[m * W] = out[m];
+            for (int m = 0; m < ZT_H; ++m) st_f1(dst + m * W, out[m]);
           } else {
 #pragma unroll
             for (int m = 0; m < ZT_H; ++m) {
