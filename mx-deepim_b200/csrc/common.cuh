@@ -37,6 +37,30 @@ int launch_zoom_factor(const float *obs, const float *rend, const float *src_pos
                        float *trans_out, int batch_size, int channels, int height, int width,
                        int mode, void *stream);
 
+// Set by rc_compare_step_dev around launches that may overlap their predecessor in the stream
+// (programmatic dependent launch: the kernel does not consume the predecessor's output).
+inline thread_local bool tl_pdl = false;
+
+#ifdef __CUDACC__
+template <typename... KArgs, typename... Args>
+static inline cudaError_t launch_maybe_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block,
+                                           size_t smem, cudaStream_t s, bool pdl, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute at[1];
+  if (pdl) {
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+  }
+  return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+#endif
+
 static inline bool aligned16(const void *p) {
   return (reinterpret_cast<uintptr_t>(p) & 15u) == 0;
 }
@@ -68,6 +92,12 @@ __device__ __forceinline__ void st_f4(float4 *p, const float4 &v) {
   asm volatile("st.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y),
                "f"(v.z), "f"(v.w)
                : "memory");
+}
+
+// Lets the next kernel in the stream start (if it was launched with programmatic stream
+// serialization); a no-op otherwise.
+__device__ __forceinline__ void pdl_launch_dependents() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 }
 
 __device__ __forceinline__ void st_f1(float *p, float v) {

@@ -123,6 +123,11 @@ static int launch_flow(const float *depth_src, const float *depth_tgt, const flo
   if (vec) {
     const int quads = (H * W) / 4;
     dim3 grid((quads + 255) / 256, B);
+    if (tl_pdl) {
+      RC_CUDA_TRY(launch_maybe_pdl(flow_kernel_v4, grid, dim3(256), 0, stream, true, depth_src,
+                                   depth_tgt, KT, Kinv, flow, valid, H, W));
+      return RC_OK;
+    }
     flow_kernel_v4<<<grid, 256, 0, stream>>>(depth_src, depth_tgt, KT, Kinv, flow, valid, H, W);
   } else {
     dim3 grid((H * W + 255) / 256, B);

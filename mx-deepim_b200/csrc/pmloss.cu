@@ -182,6 +182,7 @@ pm_fwd_kernel(const float *__restrict__ points, const float *__restrict__ obs,
               PoseParams pp, int loss_type, float norm_term, float sigma, float *est,
               float *__restrict__ loss_map, float *__restrict__ loss_sum, int N,
               int accumulate) {
+  pdl_launch_dependents();
   const int b = blockIdx.x / PM_CLUSTER;
   const int crank = blockIdx.x % PM_CLUSTER;
   __shared__ PoseOut po;

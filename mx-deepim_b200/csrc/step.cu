@@ -11,43 +11,15 @@
 // GPU idle between kernels.  One C call enqueues all four kernels (flow; bbox + zoom
 // factor + ZoomTrans; resampler; point-matching loss) in a few microseconds, so the host
 // runs ahead of the device.  Flow, the bbox reduction and the loss are independent of each
-// other and each is too small to fill 148 SMs (latency-bound, 15-25 us), so the step forks:
-// the bbox and the loss run on two internal side streams concurrently with flow, and the
-// resampler joins flow + bbox.  Optional event marks bracket each kernel for roofline timing
+// other and each is too small to fill 148 SMs (latency-bound, 15-25 us), so they are issued
+// back to back with programmatic stream serialisation (loss -> bbox -> flow; the first two
+// call griddepcontrol.launch_dependents at once) and run concurrently; the resampler is a
+// normal launch and waits for all three.  Optional event marks bracket each kernel for roofline timing
 // on the launching stream; asking for the flow/bbox/loss marks serialises the step so that
 // the per-kernel times are clean.
 #include "common.cuh"
 
-#include <mutex>
-
 namespace rc {
-// Two side streams + fork/join events per device, created on first use.
-struct StepSide {
-  cudaStream_t s_bbox = nullptr, s_loss = nullptr;
-  cudaEvent_t fork = nullptr, bbox_done = nullptr, loss_done = nullptr;
-  bool ready = false;
-};
-static StepSide g_side[64];
-static std::mutex g_side_mu;
-
-static int side_for_current_device(StepSide **out) {
-  int dev = 0;
-  RC_CUDA_TRY(cudaGetDevice(&dev));
-  RC_REQUIRE(dev >= 0 && dev < 64, RC_ERR_CAPACITY);
-  std::lock_guard<std::mutex> lock(g_side_mu);
-  StepSide &S = g_side[dev];
-  if (!S.ready) {
-    RC_CUDA_TRY(cudaStreamCreateWithFlags(&S.s_bbox, cudaStreamNonBlocking));
-    RC_CUDA_TRY(cudaStreamCreateWithFlags(&S.s_loss, cudaStreamNonBlocking));
-    RC_CUDA_TRY(cudaEventCreateWithFlags(&S.fork, cudaEventDisableTiming));
-    RC_CUDA_TRY(cudaEventCreateWithFlags(&S.bbox_done, cudaEventDisableTiming));
-    RC_CUDA_TRY(cudaEventCreateWithFlags(&S.loss_done, cudaEventDisableTiming));
-    S.ready = true;
-  }
-  *out = &S;
-  return RC_OK;
-}
-
 static inline int mark(void **marks, int i, cudaStream_t s) {
   if (marks && marks[i]) RC_CUDA_TRY(cudaEventRecord(static_cast<cudaEvent_t>(marks[i]), s));
   return RC_OK;
@@ -64,52 +36,49 @@ int rc_compare_step_dev(const rc_compare_step_args *a) {
   cudaStream_t s = static_cast<cudaStream_t>(a->stream);
   int st;
   const bool do_loss = N > 0 && a->loss_sum;
-  // fork unless the caller wants per-kernel marks of the overlapped kernels
+  // overlap unless the caller wants per-kernel marks of the overlapped kernels
   const bool serial = a->marks && (a->marks[0] || a->marks[1] || a->marks[4] || a->marks[5]);
-  rc::StepSide *side = nullptr;
-  cudaStream_t s_bbox = s, s_loss = s;
-  if (!serial) {
-    if ((st = rc::side_for_current_device(&side)) != RC_OK) return rc::note_status(st);
-    s_bbox = side->s_bbox;
-    s_loss = side->s_loss;
-    RC_CUDA_TRY(cudaEventRecord(side->fork, s));
-    RC_CUDA_TRY(cudaStreamWaitEvent(s_bbox, side->fork, 0));
-    if (do_loss) RC_CUDA_TRY(cudaStreamWaitEvent(s_loss, side->fork, 0));
-  }
-  auto loss = [&](cudaStream_t ls) -> int {
+  auto loss = [&]() -> int {
     return rc_pm_loss_fwd_dev(a->point_cloud_model, a->point_cloud_observed,
                               a->point_cloud_weights, a->rot_est, a->trans_est, a->src_pose,
                               a->T_means, a->T_stds, a->rot_coord, a->loss_type, a->norm_term,
-                              a->sl1_scalar, nullptr, a->loss_map, a->loss_sum, B, N, ls);
+                              a->sl1_scalar, nullptr, a->loss_map, a->loss_sum, B, N, a->stream);
   };
-  // (2) crop boxes + zoom factor (ZoomMask, first half); ZoomTrans of the GT translation
-  // label rides in the finalising block of the same kernel.  Issued first when forked: it
-  // gates the resampler.
+  // crop boxes + zoom factor (ZoomMask, first half); ZoomTrans of the GT translation label
+  // rides in the finalising block of the same kernel.
   const bool zt = a->zoom_trans_gt && a->trans_gt;
-  auto bbox = [&](cudaStream_t bs) -> int {
+  auto bbox = [&]() -> int {
     return rc::launch_zoom_factor(a->mask_gt_observed, a->depth_rendered, a->src_pose, a->K,
                                   nullptr, a->zoom_factor, a->bbox, a->workspace,
                                   zt ? a->trans_gt : nullptr, zt ? a->zoom_trans_gt : nullptr, B,
-                                  1, H, W, RC_ZF_MASK, bs);
+                                  1, H, W, RC_ZF_MASK, a->stream);
+  };
+  struct PdlScope {  // launches inside the scope may start before their predecessor ends
+    explicit PdlScope(bool on) { rc::tl_pdl = on; }
+    ~PdlScope() { rc::tl_pdl = false; }
   };
   if (!serial) {
-    if ((st = bbox(s_bbox)) != RC_OK) return st;
-    RC_CUDA_TRY(cudaEventRecord(side->bbox_done, s_bbox));
-    if (do_loss) {
-      if ((st = loss(s_loss)) != RC_OK) return st;
-      RC_CUDA_TRY(cudaEventRecord(side->loss_done, s_loss));
+    // loss (normal launch: waits for everything before it) -> bbox -> flow, the last two
+    // programmatically serialised, so all three are resident together; the resampler is a
+    // normal launch again and therefore waits for all of them.
+    if (do_loss && (st = loss()) != RC_OK) return st;
+    {
+      PdlScope scope(do_loss);
+      if ((st = bbox()) != RC_OK) return st;
     }
-  }
-  if ((st = rc::mark(a->marks, 0, s)) != RC_OK) return st;
-  // (1) GT flow
-  st = rc_flow_dev(a->depth_rendered, a->depth_gt_observed, a->KT, a->Kinv, a->flow, a->valid, B,
-                   H, W, a->stream);
-  if (st != RC_OK) return st;
-  if ((st = rc::mark(a->marks, 1, s)) != RC_OK) return st;
-  if (serial) {
-    if ((st = bbox(s)) != RC_OK) return st;
+    {
+      PdlScope scope(true);
+      st = rc_flow_dev(a->depth_rendered, a->depth_gt_observed, a->KT, a->Kinv, a->flow, a->valid,
+                       B, H, W, a->stream);
+      if (st != RC_OK) return st;
+    }
   } else {
-    RC_CUDA_TRY(cudaStreamWaitEvent(s, side->bbox_done, 0));
+    if ((st = rc::mark(a->marks, 0, s)) != RC_OK) return st;
+    st = rc_flow_dev(a->depth_rendered, a->depth_gt_observed, a->KT, a->Kinv, a->flow, a->valid,
+                     B, H, W, a->stream);
+    if (st != RC_OK) return st;
+    if ((st = rc::mark(a->marks, 1, s)) != RC_OK) return st;
+    if ((st = bbox()) != RC_OK) return st;
   }
   if ((st = rc::mark(a->marks, 2, s)) != RC_OK) return st;
   // (3) one resampler launch: 3 masks + 6 image channels + 2 flow + 2 flow-weight planes
@@ -142,14 +111,8 @@ int rc_compare_step_dev(const rc_compare_step_args *a) {
   if (st != RC_OK) return st;
   if ((st = rc::mark(a->marks, 3, s)) != RC_OK) return st;
   if ((st = rc::mark(a->marks, 4, s)) != RC_OK) return st;
-  // (4) Transform3D + point-matching loss
-  if (do_loss) {
-    if (serial) {
-      if ((st = loss(s)) != RC_OK) return st;
-    } else {
-      RC_CUDA_TRY(cudaStreamWaitEvent(s, side->loss_done, 0));
-    }
-  }
+  // Transform3D + point-matching loss (already issued when overlapped)
+  if (serial && do_loss && (st = loss()) != RC_OK) return st;
   if ((st = rc::mark(a->marks, 5, s)) != RC_OK) return st;
   return rc::note_status(RC_OK);
 }

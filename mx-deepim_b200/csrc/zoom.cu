@@ -106,14 +106,16 @@ __device__ void zoom_factor_finalize(const int32_t *w, const float *__restrict__
 }
 
 // grid = (blocks_per_sample, B), block = 256.
-template <int MODE>
-__global__ void __launch_bounds__(256)
+// ONE: single-channel inputs (the mask configuration): no per-pixel channel sums to carry.
+template <int MODE, bool ONE>
+__global__ void __launch_bounds__(256, ONE ? 4 : 2)
 zoom_bbox_kernel(const float *__restrict__ obs, const float *__restrict__ rend,
                  const float *__restrict__ src_pose, const float *__restrict__ K,
                  const float *__restrict__ pixel_means, float *__restrict__ zoom_factor,
                  int32_t *__restrict__ bbox, int32_t *__restrict__ ws,
                  const float *__restrict__ trans_in, float *__restrict__ trans_out, int C, int H,
                  int W) {
+  pdl_launch_dependents();
   const int b = blockIdx.y;
   const int quads = (H * W) >> 2;
   const size_t plane = (size_t)H * W;
@@ -127,7 +129,8 @@ zoom_bbox_kernel(const float *__restrict__ obs, const float *__restrict__ rend,
   constexpr int UNROLL = 4;  // the launch gives every thread at most UNROLL quads: all loads in flight
   for (int q0 = blockIdx.x * blockDim.x + threadIdx.x; q0 < quads; q0 += UNROLL * stride) {
     float4 so[UNROLL], sr[UNROLL];
-    for (int c = 0; c < C; ++c) {
+    const int nc = ONE ? 1 : C;
+    for (int c = 0; c < nc; ++c) {
       const float mean = (MODE == RC_ZF_IMAGE) ? __ldg(pixel_means + c) : 0.f;
       float4 vo[UNROLL], vr[UNROLL];
 #pragma unroll
@@ -158,8 +161,8 @@ zoom_bbox_kernel(const float *__restrict__ obs, const float *__restrict__ rend,
           }
           const float po = (k == 0) ? so[u].x : (k == 1) ? so[u].y : (k == 2) ? so[u].z : so[u].w;
           const float pr = (k == 0) ? sr[u].x : (k == 1) ? sr[u].y : (k == 2) ? sr[u].z : sr[u].w;
-          ao_[k] = c == 0 ? eo[k] : __fadd_rn(po, eo[k]);  // np.sum(axis=1), sequential
-          ar_[k] = c == 0 ? er[k] : __fadd_rn(pr, er[k]);
+          ao_[k] = (ONE || c == 0) ? eo[k] : __fadd_rn(po, eo[k]);  // np.sum(axis=1), sequential
+          ar_[k] = (ONE || c == 0) ? er[k] : __fadd_rn(pr, er[k]);
         }
         so[u] = make_float4(ao_[0], ao_[1], ao_[2], ao_[3]);
         sr[u] = make_float4(ar_[0], ar_[1], ar_[2], ar_[3]);
@@ -721,8 +724,11 @@ int launch_zoom_factor(const float *obs, const float *rend, const float *src_pos
   RC_REQUIRE(width % 4 == 0 && aligned16(obs) && aligned16(rend), RC_ERR_UNALIGNED);
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const int quads = height * width / 4;
-  // One resident wave: about four 256-thread blocks per SM in total, never more blocks per
-  // sample than it takes to give every thread four quads (the loop batches 4 loads per plane).
+  // One resident wave of at most two 256-thread blocks per SM (the kernel is compiled for four
+  // per SM, so half of every SM stays free for the flow kernel that overlaps it), never more
+  // blocks per sample than it takes to give every thread four quads (the loop batches 4 loads
+  // per plane).  All blocks being resident at once also means griddepcontrol.launch_dependents
+  // releases the next kernel immediately.
   static int sm_count = 0;
   if (sm_count == 0) {
     int dev = 0;
@@ -731,18 +737,23 @@ int launch_zoom_factor(const float *obs, const float *rend, const float *src_pos
       sm_count = 148;
   }
   const int max_bps = (quads + 256 * 4 - 1) / (256 * 4);
-  int bps = (sm_count * 4 + batch_size - 1) / batch_size;
+  int bps = (sm_count * (channels == 1 ? 2 : 1)) / batch_size;
   if (bps > max_bps) bps = max_bps;
   if (bps < 1) bps = 1;
   dim3 grid(bps, batch_size);
-  if (mode == RC_ZF_MASK)
-    zoom_bbox_kernel<RC_ZF_MASK><<<grid, 256, 0, s>>>(obs, rend, src_pose, K, pixel_means,
-                                                      zoom_factor, bbox, workspace, trans_in,
-                                                      trans_out, channels, height, width);
-  else
-    zoom_bbox_kernel<RC_ZF_IMAGE><<<grid, 256, 0, s>>>(obs, rend, src_pose, K, pixel_means,
-                                                       zoom_factor, bbox, workspace, trans_in,
-                                                       trans_out, channels, height, width);
+  const bool pdl = tl_pdl;
+#define RC_BBOX_LAUNCH(MODE_, ONE_)                                                              \
+  RC_CUDA_TRY(launch_maybe_pdl(zoom_bbox_kernel<MODE_, ONE_>, grid, dim3(256), 0, s, pdl, obs, rend, \
+                               src_pose, K, pixel_means, zoom_factor, bbox, workspace, trans_in,     \
+                               trans_out, channels, height, width))
+  if (mode == RC_ZF_MASK) {
+    if (channels == 1) RC_BBOX_LAUNCH(RC_ZF_MASK, true);
+    else RC_BBOX_LAUNCH(RC_ZF_MASK, false);
+  } else {
+    if (channels == 1) RC_BBOX_LAUNCH(RC_ZF_IMAGE, true);
+    else RC_BBOX_LAUNCH(RC_ZF_IMAGE, false);
+  }
+#undef RC_BBOX_LAUNCH
   return note_status(check_launch());
 }
 
