@@ -262,6 +262,7 @@ struct ZoomParams {
   int inverse;
   int H, W;
   int spot_x0, spot_x1, spot_y0, spot_y1;  // zoom_image_with_factor.py:36-45
+  int src_aligned;                          // every source plane 16-byte aligned (cp.async staging)
 };
 
 // Affine parameters of one sample: (wx, wy, tx, ty) as float32, forward or
@@ -319,7 +320,6 @@ __device__ __forceinline__ float blend(float tl, float tr, float bl, float br, f
 constexpr int ZT_W = 128;
 constexpr int ZT_H = 8;
 constexpr int ZT_THREADS = 128;
-constexpr int ZT_BATCH = 8;  // planes whose window loads are in flight together
 
 // Per-plane, per-sample constants resolved once per block (shared memory).
 struct PlaneCtx {
@@ -330,37 +330,36 @@ struct PlaneCtx {
   int pad_[3];
 };
 
-// What the staging loop needs per plane, 24 bytes (see the kernel for the encoding).
-struct StageCtx {
-  const float *src;
-  float thr, keep, add;
-  int pad_;
-};
-
-__device__ __forceinline__ void sts_f1(uint32_t addr, float v) {
-  asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
-}
-
 // round half away from zero, the FADD.RZ + FRND.TRUNC sequence CUDA's roundf reduces to
 // for |v| < 2^23 (exact for every float: v + 0.5 rounded toward zero never crosses an integer).
 __device__ __forceinline__ float round_away(float v) {
   return truncf(__fadd_rz(v, copysignf(0.5f, v)));
 }
 
-// 64-bit shared-memory load from a 32-bit shared-window address (keeps the address
+// Shared-memory accesses through 32-bit shared-window addresses (keeps the address
 // arithmetic in 32-bit registers instead of re-deriving the generic pointer per plane).
-__device__ __forceinline__ float2 lds_f2(uint32_t addr) {
-  float2 v;
-  asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(addr));
+__device__ __forceinline__ float lds_f1(uint32_t addr) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
   return v;
+}
+
+// 16-byte asynchronous global -> shared copy that bypasses registers and L1; `bytes` = 16
+// copies, `bytes` = 0 zero-fills the destination (out-of-image chunk).
+__device__ __forceinline__ void cp_async_16(uint32_t dst, const void *src, int bytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+  asm volatile("cp.async.commit_group;\n\tcp.async.wait_group 0;" ::: "memory");
 }
 
 // IEEE-754 round-to-nearest a / b without the library's slow path.  `rb` = RN(1/b).  For
 // operands inside the guarded exponent range the two FMA refinements below deliver the
-// correctly rounded quotient (Markstein; checked exhaustively-at-random on 4e8 operand pairs
-// including all-ones / all-zeros significands against the host's IEEE division); zero
-// numerators -- the background of a flow field, i.e. most pixels -- would otherwise take
-// __fdiv_rn's ~60-instruction special-case subroutine.
+// correctly rounded quotient (Markstein; checked at random on 4e8 operand pairs including
+// all-ones / all-zeros significands against the host's IEEE division); zero numerators --
+// the background of a flow field, i.e. most pixels -- would otherwise take __fdiv_rn's
+// ~60-instruction special-case subroutine.
 __device__ __forceinline__ float div_rn_guarded(float a, float b, float rb, bool b_ok) {
   const float aa = fabsf(a);
   if (aa == 0.f) return __fmul_rn(a, b);  // +-0 with the sign of a / b
@@ -429,31 +428,101 @@ __device__ __forceinline__ RowCoord row_coord(int j, float stepy, float wy, floa
   return r;
 }
 
+// The {left, right} taps of one window row for this thread's column, with the plane's
+// pre-operation applied.  EDGE: the window reaches outside the image, where taps are zero
+// AFTER the pre-operation (the sampler zero-pads the pre-processed image), so the additive
+// pre-operation must not touch them; `ok` = this row is inside the image, okl/okr = the
+// columns are.  (The threshold maps the zero fill to zero by itself.)
+template <int PRE, bool EDGE>
+__device__ __forceinline__ float2 load_taps(uint32_t addr, float mean, bool ok, bool okl, bool okr) {
+  float2 t;
+  t.x = lds_f1(addr);
+  t.y = lds_f1(addr + 4u);
+  if (PRE == RC_PRE_THRESH02) {
+    t.x = t.x > 0.2f ? 1.f : 0.f;
+    t.y = t.y > 0.2f ? 1.f : 0.f;
+  } else if (PRE == RC_PRE_ADD_MEAN) {
+    if (EDGE) {
+      t.x = (ok && okl) ? __fadd_rn(t.x, mean) : 0.f;
+      t.y = (ok && okr) ? __fadd_rn(t.y, mean) : 0.f;
+    } else {
+      t.x = __fadd_rn(t.x, mean);
+      t.y = __fadd_rn(t.y, mean);
+    }
+  }
+  return t;
+}
+
+// Eight outputs of one column of one plane from the staged window.
+//   a_row0      shared address of the left tap of output row 0's upper source row
+//   pitch       bytes between window rows
+//   step_mask   bit m: row m reads one source row further down than row m-1 (zoom-in)
+//   jump_mask   any other row change (zoom-out): every row loads both of its source rows
+//   rowok_mask  bit r: window row (first row of output row 0) + r is inside the image (EDGE)
+template <int PRE, bool EDGE>
+__device__ __forceinline__ void blend_col(float (&out)[ZT_H], const RowCoord (&rows)[ZT_H],
+                                          uint32_t a_row0, uint32_t pitch, unsigned step_mask,
+                                          unsigned jump_mask, unsigned rowok_mask, float mean,
+                                          bool okl, bool okr, float wl, float wr) {
+  if (jump_mask == 0u) {
+    uint32_t ab = a_row0;
+    unsigned rk = rowok_mask;
+    float2 top = load_taps<PRE, EDGE>(ab, mean, rk & 1u, okl, okr);
+    ab += pitch;
+    rk >>= 1;
+    float2 bot = load_taps<PRE, EDGE>(ab, mean, rk & 1u, okl, okr);
+    out[0] = blend(top.x, top.y, bot.x, bot.y, rows[0].wt, rows[0].wb, wl, wr);
+#pragma unroll
+    for (int m = 1; m < ZT_H; ++m) {
+      if (step_mask & (1u << m)) {  // warp-uniform
+        top = bot;
+        ab += pitch;
+        rk >>= 1;
+        bot = load_taps<PRE, EDGE>(ab, mean, rk & 1u, okl, okr);
+      }
+      out[m] = blend(top.x, top.y, bot.x, bot.y, rows[m].wt, rows[m].wb, wl, wr);
+    }
+  } else {
+#pragma unroll
+    for (int m = 0; m < ZT_H; ++m) {
+      const int dr = rows[m].y0 - rows[0].y0;
+      const uint32_t at = a_row0 + (uint32_t)dr * pitch;
+      const bool ok0 = dr >= 0 && dr < 32 && ((rowok_mask >> dr) & 1u);
+      const bool ok1 = dr + 1 >= 0 && dr + 1 < 32 && ((rowok_mask >> (dr + 1)) & 1u);
+      const float2 top = load_taps<PRE, EDGE>(at, mean, ok0, okl, okr);
+      const float2 bot = load_taps<PRE, EDGE>(at + pitch, mean, ok1, okl, okr);
+      out[m] = blend(top.x, top.y, bot.x, bot.y, rows[m].wt, rows[m].wb, wl, wr);
+    }
+  }
+}
+
 // grid = (ceil(W/ZT_W), ceil(H/ZT_H), B); block = 128; dynamic smem = smem_floats * 4.
 //
 // One thread owns ONE output column of the 128 x 8 tile and walks its eight rows; the lanes
 // of a warp are 32 adjacent columns.  Consequences, in order of weight:
+//  * the source window of the tile (every tap any of its 1024 outputs can touch, widened to
+//    16-byte chunks) is staged in shared memory once per plane by cp.async: ~9 asynchronous
+//    16-byte copies per thread for all 13 planes, no registers, out-of-image chunks
+//    zero-filled by the copy itself.  The planes' pre-operations are applied to the taps as
+//    they are read;
 //  * everything that depends on the row (source row, row weights, which window rows to read)
-//    depends on blockIdx only, so the compiler keeps it in uniform registers and the
-//    row-to-row reuse below is decided by uniform branches;
-//  * the source window of the tile is staged in shared memory once per plane (pre-operation
-//    applied, out-of-image taps zero) as HORIZONTAL pairs {v(r,c), v(r,c+1)}: one 64-bit LDS
-//    fetches the left and right tap of a row.  Zooming in, consecutive output rows share
-//    source rows, so a column of eight outputs needs only ~8*wy+2 such loads instead of 16,
-//    and the 16 lanes one shared-memory wavefront serves read 16*wx+1 <= 16 consecutive
-//    pairs of one row: conflict-free by construction;
-//  * every store instruction writes 128 contiguous bytes per warp.
+//    depends on blockIdx only.  Zooming in, consecutive output rows share source rows, so a
+//    column of eight outputs reads only ~8*wy+2 window rows instead of 16; the stepping
+//    pattern is a warp-uniform bit mask (made visible to the compiler by a warp reduction);
+//  * the 32 lanes of a warp read 32*wx+1 consecutive floats of one window row: one
+//    conflict-free shared-memory wavefront per load, and every store instruction writes 128
+//    contiguous bytes per warp.
 // As many planes as fit are staged per barrier pair.  Tiles whose window does not fit
-// (strong zoom-out / inverse zoom) fall back to gathering through the read-only path.
+// (strong zoom-out / inverse zoom) or whose sources are not 16-byte aligned fall back to
+// gathering through the read-only path.
 //
 // WC: compile-time image width (0 = use P.W); with the width known the eight row stores of a
 // column use immediate offsets from one address.
 template <int WC>
 __global__ void __launch_bounds__(ZT_THREADS, 8)
 zoom_sample_kernel(const __grid_constant__ ZoomParams P, int smem_floats) {
-  extern __shared__ float2 win[];
+  extern __shared__ float4 win4[];
   __shared__ PlaneCtx ctx[RC_ZOOM_MAX_PLANES];
-  __shared__ StageCtx sctx[RC_ZOOM_MAX_PLANES];
   const int H = P.H, W = WC ? WC : P.W;
   const int b = blockIdx.z;
   const int i_first = blockIdx.x * ZT_W, j_first = blockIdx.y * ZT_H;
@@ -474,17 +543,6 @@ zoom_sample_kernel(const __grid_constant__ ZoomParams P, int smem_floats) {
     c.channel = zp.channel;
     c.mean = zp.mean;
     ctx[threadIdx.x] = c;
-    // staging constants: tap = v > thr ? 1 : fma(v, keep, add)
-    //   NONE      thr = +inf, keep = 1, add = -0  (v + -0 == v bit for bit)
-    //   THRESH02  thr = 0.2,  keep = 0, add = 0   (zoom_mask.py:40-45)
-    //   ADD_MEAN  thr = +inf, keep = 1, add = mean (zoom_image_with_factor.py:46)
-    StageCtx s;
-    s.src = c.src;
-    s.thr = (zp.pre_op == RC_PRE_THRESH02) ? 0.2f : __int_as_float(0x7f800000);
-    s.keep = (zp.pre_op == RC_PRE_THRESH02) ? 0.f : 1.f;
-    s.add = (zp.pre_op == RC_PRE_ADD_MEAN) ? zp.mean : ((zp.pre_op == RC_PRE_THRESH02) ? 0.f : -0.f);
-    s.pad_ = 0;
-    sctx[threadIdx.x] = s;
   }
 
   float wx, wy, tx, ty, wx_in;
@@ -514,21 +572,28 @@ zoom_sample_kernel(const __grid_constant__ ZoomParams P, int smem_floats) {
   const float fx_hi = floorf(src_coord(i_last, stepx, wx, tx, nxm1));
   const float fy_lo = floorf(src_coord(j_first, stepy, wy, ty, nym1));
   const float fy_hi = floorf(src_coord(j_last, stepy, wy, ty, nym1));
-  // window pairs: columns x_lo .. x_hi (each with its right neighbour), rows y_lo .. y_hi+1
-  const float wwf = fx_hi - fx_lo + 1.0f, whf = fy_hi - fy_lo + 2.0f;
-  const bool staged = (wx > 0.f) && (wy > 0.f) && (wwf >= 1.0f) && (whf >= 2.0f) &&
-                      (2.0f * wwf * whf <= (float)smem_floats) && (fabsf(fx_lo) < 1e6f) &&
-                      (fabsf(fy_lo) < 1e6f);
+  // window: source columns x_lo .. x_hi+1 (widened to whole 4-float chunks), rows y_lo .. y_hi+1
+  const float whf = fy_hi - fy_lo + 2.0f;
+  const bool sane = (wx > 0.f) && (wy > 0.f) && (fx_hi >= fx_lo) && (fy_hi >= fy_lo) &&
+                    (fabsf(fx_lo) < 1e6f) && (fabsf(fx_hi) < 1e6f) && (fabsf(fy_lo) < 1e6f) &&
+                    (whf <= 32.0f) && P.src_aligned;
+  int x_lo = 0, y_lo = 0, nch = 1, wh = 2;
+  if (sane) {
+    x_lo = (int)fx_lo;
+    y_lo = (int)fy_lo;
+    wh = (int)whf;
+    const int xa_ = x_lo & ~3;  // floor to a multiple of 4 (two's complement: also for x_lo < 0)
+    nch = (((int)fx_hi + 1 - xa_) >> 2) + 1;
+  }
+  const int xa = x_lo & ~3;
+  const int plane_floats = nch * 4 * wh;
+  const bool staged = sane && plane_floats <= smem_floats;
   __syncthreads();  // ctx[] visible
   if (staged) {
-    const int x_lo = (int)fx_lo, y_lo = (int)fy_lo;
-    const int ww = (int)wwf, wh = (int)whf;
-    const int win_elems = ww * wh;
-    const int pps = max(1, min(P.n_planes, (smem_floats >> 1) / win_elems));  // planes per stage
-    const uint32_t win_s = (uint32_t)__cvta_generic_to_shared(win);
-    const uint32_t a_col = win_s + 8u * (uint32_t)(x0 - x_lo);
-    const uint32_t pitch = 8u * (uint32_t)ww;
-    const uint32_t plane_bytes = 8u * (uint32_t)win_elems;
+    const int pps = max(1, min(P.n_planes, smem_floats / plane_floats));  // planes per stage
+    const uint32_t win_s = (uint32_t)__cvta_generic_to_shared(win4);
+    const uint32_t pitch = 16u * (uint32_t)nch;
+    const uint32_t plane_bytes = 4u * (uint32_t)plane_floats;
     // Row stepping pattern of the tile: bit m of step_mask = row m reads one source row
     // further down than row m-1; jump_mask = any other change (zoom-out).  Block-uniform by
     // construction; the warp reduction makes that visible to the compiler, which then keeps
@@ -542,90 +607,63 @@ zoom_sample_kernel(const __grid_constant__ ZoomParams P, int smem_floats) {
     }
     const unsigned step_mask = __reduce_or_sync(0xffffffffu, sm_);
     const unsigned jump_mask = __reduce_or_sync(0xffffffffu, jm_);
-    uint32_t a_row0 = a_col + (uint32_t)(rows[0].y0 - y_lo) * pitch;
+    // does the window reach outside the image?  (then additive pre-operations must skip the
+    // zero fill); rowok bit r: window row rows[0].y0 + r is inside the image
+    const int r_first = rows[0].y0;
+    const int rk_lo = max(0, -r_first), rk_hi = min(31, H - 1 - r_first);
+    const unsigned rk_ = (rk_hi >= rk_lo) ? ((0xffffffffu >> (31 - rk_hi)) & (0xffffffffu << rk_lo)) : 0u;
+    const unsigned rowok_mask = __reduce_or_sync(0xffffffffu, rk_);
+    const bool edge_ = (xa < 0) || (xa + 4 * nch > W) || (y_lo < 0) || (y_lo + wh > H);
+    const bool edge = __reduce_or_sync(0xffffffffu, edge_ ? 1u : 0u) != 0u;
+    const bool okl = (x0 >= 0) && (x0 <= W - 1), okr = (x0 + 1 >= 0) && (x0 + 1 <= W - 1);
+    uint32_t a_row0 = win_s + 4u * (uint32_t)(x0 - xa) + (uint32_t)(r_first - y_lo) * pitch;
     asm volatile("" : "+r"(a_row0));  // keep the shared-window address in a register
+
     for (int p0 = 0; p0 < P.n_planes; p0 += pps) {
       const int np = min(pps, P.n_planes - p0);
       if (p0 > 0) __syncthreads();  // consumers of the previous stage are done
-      // Source columns x_lo .. x_lo + ww (one more than the pairs); every global element is
-      // loaded once and written to the .x slot of its own pair and the .y slot of the pair
-      // to its left.  Loads of up to ZT_BATCH planes are issued before any is consumed.
-      const int sw = ww + 1;
-      const int src_elems = sw * wh;
-      const float inv_sw = __frcp_rn((float)sw);
-      const uint32_t win_f = win_s;  // float-granular shared address of plane 0
-      for (int idx = threadIdx.x; idx < src_elems; idx += ZT_THREADS) {
-        int r = __float2int_rz(__fmul_rn((float)idx + 0.5f, inv_sw));
-        int c = idx - r * sw;
+      // stage: chunk q = (window row, 4-float column chunk); the same chunk of every plane
+      const int nchunks = nch * wh;
+      const float inv_nch = __frcp_rn((float)nch);
+      for (int q = threadIdx.x; q < nchunks; q += ZT_THREADS) {
+        int r = __float2int_rz(__fmul_rn((float)q + 0.5f, inv_nch));
+        int c = q - r * nch;
         if (c < 0) {
-          c += sw;
+          c += nch;
           --r;
-        } else if (c >= sw) {
-          c -= sw;
+        } else if (c >= nch) {
+          c -= nch;
           ++r;
         }
-        const int ys = y_lo + r, xs = x_lo + c;
-        const bool inb = (xs >= 0) && (xs <= W - 1) && (ys >= 0) && (ys <= H - 1);
+        const int ys = y_lo + r, xs = xa + 4 * c;
+        const bool inb = (xs >= 0) && (xs + 3 <= W - 1) && (ys >= 0) && (ys <= H - 1);
         const int goff = inb ? ys * W + xs : 0;
-        const int e = r * ww + c;
-        const bool has_x = c < ww, has_y = c >= 1;
-        uint32_t ax = win_f + 8u * (uint32_t)e;  // .x of pair (r, c); .y of pair (r, c-1) is ax - 4
-        if (inb) {
-#pragma unroll 1
-          for (int pb = 0; pb < np; pb += ZT_BATCH) {
-            float v[ZT_BATCH];
-#pragma unroll
-            for (int u = 0; u < ZT_BATCH; ++u)
-              if (pb + u < np) v[u] = __ldg(sctx[p0 + pb + u].src + goff);
-#pragma unroll
-            for (int u = 0; u < ZT_BATCH; ++u) {
-              if (pb + u < np) {
-                const StageCtx &s_ = sctx[p0 + pb + u];
-                const float t = v[u] > s_.thr ? 1.0f : __fmaf_rn(v[u], s_.keep, s_.add);
-                if (has_x) sts_f1(ax, t);
-                if (has_y) sts_f1(ax - 4u, t);
-                ax += plane_bytes;
-              }
-            }
-          }
-        } else {
-          for (int pl = 0; pl < np; ++pl, ax += plane_bytes) {
-            if (has_x) sts_f1(ax, 0.f);
-            if (has_y) sts_f1(ax - 4u, 0.f);
-          }
-        }
+        const int bytes = inb ? 16 : 0;
+        uint32_t sa = win_s + 16u * (uint32_t)q;
+        for (int pl = 0; pl < np; ++pl, sa += plane_bytes)
+          cp_async_16(sa, ctx[p0 + pl].src + goff, bytes);
       }
+      cp_async_wait_all();
       __syncthreads();
       uint32_t a_pl = a_row0;
       for (int pl = 0; pl < np; ++pl, a_pl += plane_bytes) {
         const PlaneCtx &c_ = ctx[p0 + pl];
-        float out[ZT_H];
-        if (jump_mask == 0u) {
-          // zoom-in: a row either shares both source rows with the row above or advances by one
-          uint32_t ab = a_pl;
-          float2 top = lds_f2(ab);  // {left, right} taps of the upper source row
-          ab += pitch;
-          float2 bot = lds_f2(ab);
-          out[0] = blend(top.x, top.y, bot.x, bot.y, rows[0].wt, rows[0].wb, wl, wr);
-#pragma unroll
-          for (int m = 1; m < ZT_H; ++m) {
-            if (step_mask & (1u << m)) {  // warp-uniform
-              top = bot;
-              ab += pitch;
-              bot = lds_f2(ab);
-            }
-            out[m] = blend(top.x, top.y, bot.x, bot.y, rows[m].wt, rows[m].wb, wl, wr);
-          }
-        } else {
-#pragma unroll
-          for (int m = 0; m < ZT_H; ++m) {
-            const uint32_t at = a_pl + (uint32_t)(rows[m].y0 - rows[0].y0) * pitch;
-            const float2 top = lds_f2(at), bot = lds_f2(at + pitch);
-            out[m] = blend(top.x, top.y, bot.x, bot.y, rows[m].wt, rows[m].wb, wl, wr);
-          }
-        }
-        const int post_op = c_.post_op, channel = c_.channel, acc = c_.accumulate;
+        const int pre_op = c_.pre_op;
         const float mean = c_.mean;
+        float out[ZT_H];
+        if (pre_op == RC_PRE_NONE)
+          blend_col<RC_PRE_NONE, false>(out, rows, a_pl, pitch, step_mask, jump_mask, rowok_mask,
+                                        mean, okl, okr, wl, wr);
+        else if (pre_op == RC_PRE_THRESH02)
+          blend_col<RC_PRE_THRESH02, false>(out, rows, a_pl, pitch, step_mask, jump_mask,
+                                            rowok_mask, mean, okl, okr, wl, wr);
+        else if (!edge)
+          blend_col<RC_PRE_ADD_MEAN, false>(out, rows, a_pl, pitch, step_mask, jump_mask,
+                                            rowok_mask, mean, okl, okr, wl, wr);
+        else
+          blend_col<RC_PRE_ADD_MEAN, true>(out, rows, a_pl, pitch, step_mask, jump_mask,
+                                           rowok_mask, mean, okl, okr, wl, wr);
+        const int post_op = c_.post_op, channel = c_.channel, acc = c_.accumulate;
         float *dst = c_.dst + col_off;
         post_col(out, post_op, mean, channel, P, wx_in, rwx, wx_ok, i, j_first);
         if (act) {
@@ -801,6 +839,9 @@ int rc_zoom_sample_dev(const float *zoom_factor, int inverse, const rc_zoom_grou
       z.mean = G.mean[c];
     }
   }
+  P.src_aligned = 1;
+  for (int g = 0; g < n_groups; ++g)
+    if (!rc::aligned16(groups[g].src)) P.src_aligned = 0;
   P.zoom_factor = zoom_factor;
   P.inverse = inverse ? 1 : 0;
   P.H = height;
@@ -810,10 +851,10 @@ int rc_zoom_sample_dev(const float *zoom_factor, int inverse, const rc_zoom_grou
   P.spot_x1 = (int)ceil((double)width / 2 + 5);
   P.spot_y0 = (int)floor((double)height / 2 - 5);
   P.spot_y1 = (int)ceil((double)height / 2 + 5);
-  // 26 KB of staging per block (+ the 1 KB plane context): eight 128-thread blocks stay
+  // 24 KB of staging per block (+ the 1 KB plane context): eight 128-thread blocks stay
   // resident per SM; all 13 planes of the default configuration fit in one stage for zoom
-  // factors up to ~0.45 (window (128*wx+1) x (8*wy+3) float2 per plane).
-  constexpr int kSmemFloats = 6656;
+  // factors up to ~0.5 (window (128*wx+8) x (8*wy+3) floats per plane).
+  constexpr int kSmemFloats = 6144;
   static bool attr_set = false;
   if (!attr_set) {
     RC_CUDA_TRY(cudaFuncSetAttribute(rc::zoom_sample_kernel<640>,
