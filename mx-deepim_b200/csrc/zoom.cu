@@ -456,43 +456,30 @@ __device__ __forceinline__ float2 load_taps(uint32_t addr, float mean, bool ok, 
 // Eight outputs of one column of one plane from the staged window.
 //   a_row0      shared address of the left tap of output row 0's upper source row
 //   pitch       bytes between window rows
-//   step_mask   bit m: row m reads one source row further down than row m-1 (zoom-in)
-//   jump_mask   any other row change (zoom-out): every row loads both of its source rows
+//   step_mask   bit m: row m reads one source row further down than row m-1; otherwise it
+//               shares both source rows with row m-1 (zoom-in: no other case exists)
 //   rowok_mask  bit r: window row (first row of output row 0) + r is inside the image (EDGE)
 template <int PRE, bool EDGE>
 __device__ __forceinline__ void blend_col(float (&out)[ZT_H], const RowCoord (&rows)[ZT_H],
                                           uint32_t a_row0, uint32_t pitch, unsigned step_mask,
-                                          unsigned jump_mask, unsigned rowok_mask, float mean,
+                                          unsigned rowok_mask, float mean,
                                           bool okl, bool okr, float wl, float wr) {
-  if (jump_mask == 0u) {
-    uint32_t ab = a_row0;
-    unsigned rk = rowok_mask;
-    float2 top = load_taps<PRE, EDGE>(ab, mean, rk & 1u, okl, okr);
-    ab += pitch;
-    rk >>= 1;
-    float2 bot = load_taps<PRE, EDGE>(ab, mean, rk & 1u, okl, okr);
-    out[0] = blend(top.x, top.y, bot.x, bot.y, rows[0].wt, rows[0].wb, wl, wr);
+  uint32_t ab = a_row0;
+  unsigned rk = rowok_mask;
+  float2 top = load_taps<PRE, EDGE>(ab, mean, rk & 1u, okl, okr);
+  ab += pitch;
+  rk >>= 1;
+  float2 bot = load_taps<PRE, EDGE>(ab, mean, rk & 1u, okl, okr);
+  out[0] = blend(top.x, top.y, bot.x, bot.y, rows[0].wt, rows[0].wb, wl, wr);
 #pragma unroll
-    for (int m = 1; m < ZT_H; ++m) {
-      if (step_mask & (1u << m)) {  // warp-uniform
-        top = bot;
-        ab += pitch;
-        rk >>= 1;
-        bot = load_taps<PRE, EDGE>(ab, mean, rk & 1u, okl, okr);
-      }
-      out[m] = blend(top.x, top.y, bot.x, bot.y, rows[m].wt, rows[m].wb, wl, wr);
+  for (int m = 1; m < ZT_H; ++m) {
+    if (step_mask & (1u << m)) {  // warp-uniform
+      top = bot;
+      ab += pitch;
+      rk >>= 1;
+      bot = load_taps<PRE, EDGE>(ab, mean, rk & 1u, okl, okr);
     }
-  } else {
-#pragma unroll
-    for (int m = 0; m < ZT_H; ++m) {
-      const int dr = rows[m].y0 - rows[0].y0;
-      const uint32_t at = a_row0 + (uint32_t)dr * pitch;
-      const bool ok0 = dr >= 0 && dr < 32 && ((rowok_mask >> dr) & 1u);
-      const bool ok1 = dr + 1 >= 0 && dr + 1 < 32 && ((rowok_mask >> (dr + 1)) & 1u);
-      const float2 top = load_taps<PRE, EDGE>(at, mean, ok0, okl, okr);
-      const float2 bot = load_taps<PRE, EDGE>(at + pitch, mean, ok1, okl, okr);
-      out[m] = blend(top.x, top.y, bot.x, bot.y, rows[m].wt, rows[m].wb, wl, wr);
-    }
+    out[m] = blend(top.x, top.y, bot.x, bot.y, rows[m].wt, rows[m].wb, wl, wr);
   }
 }
 
@@ -512,14 +499,14 @@ __device__ __forceinline__ void blend_col(float (&out)[ZT_H], const RowCoord (&r
 //  * the 32 lanes of a warp read 32*wx+1 consecutive floats of one window row: one
 //    conflict-free shared-memory wavefront per load, and every store instruction writes 128
 //    contiguous bytes per warp.
-// As many planes as fit are staged per barrier pair.  Tiles whose window does not fit
-// (strong zoom-out / inverse zoom) or whose sources are not 16-byte aligned fall back to
-// gathering through the read-only path.
+// As many planes as fit are staged per barrier pair.  Tiles that zoom out (a row skipping a
+// source row), whose window does not fit, or whose sources are not 16-byte aligned fall back
+// to gathering through the read-only path.
 //
 // WC: compile-time image width (0 = use P.W); with the width known the eight row stores of a
 // column use immediate offsets from one address.
 template <int WC>
-__global__ void __launch_bounds__(ZT_THREADS, 8)
+__global__ void __launch_bounds__(ZT_THREADS, 9)
 zoom_sample_kernel(const __grid_constant__ ZoomParams P, int smem_floats) {
   extern __shared__ float4 win4[];
   __shared__ PlaneCtx ctx[RC_ZOOM_MAX_PLANES];
@@ -587,26 +574,26 @@ zoom_sample_kernel(const __grid_constant__ ZoomParams P, int smem_floats) {
   }
   const int xa = x_lo & ~3;
   const int plane_floats = nch * 4 * wh;
-  const bool staged = sane && plane_floats <= smem_floats;
+  // Row stepping pattern of the tile: bit m of step_mask = row m reads one source row
+  // further down than row m-1; jump = any other change (zoom-out, not staged).  Block-uniform
+  // by construction; the warp reduction makes that visible to the compiler, which then keeps
+  // the mask in uniform registers and branches uniformly.
+  unsigned sm_ = 0u, jm_ = 0u;
+#pragma unroll
+  for (int m = 1; m < ZT_H; ++m) {
+    const int d = rows[m].y0 - rows[m - 1].y0;
+    if (d == 1) sm_ |= 1u << m;
+    else if (d != 0) jm_ = 1u;
+  }
+  const unsigned step_mask = __reduce_or_sync(0xffffffffu, sm_);
+  const bool jump = __reduce_or_sync(0xffffffffu, jm_) != 0u;
+  const bool staged = sane && !jump && plane_floats <= smem_floats;
   __syncthreads();  // ctx[] visible
   if (staged) {
     const int pps = max(1, min(P.n_planes, smem_floats / plane_floats));  // planes per stage
     const uint32_t win_s = (uint32_t)__cvta_generic_to_shared(win4);
     const uint32_t pitch = 16u * (uint32_t)nch;
     const uint32_t plane_bytes = 4u * (uint32_t)plane_floats;
-    // Row stepping pattern of the tile: bit m of step_mask = row m reads one source row
-    // further down than row m-1; jump_mask = any other change (zoom-out).  Block-uniform by
-    // construction; the warp reduction makes that visible to the compiler, which then keeps
-    // the masks in uniform registers and branches uniformly.
-    unsigned sm_ = 0u, jm_ = 0u;
-#pragma unroll
-    for (int m = 1; m < ZT_H; ++m) {
-      const int d = rows[m].y0 - rows[m - 1].y0;
-      if (d == 1) sm_ |= 1u << m;
-      else if (d != 0) jm_ |= 1u << m;
-    }
-    const unsigned step_mask = __reduce_or_sync(0xffffffffu, sm_);
-    const unsigned jump_mask = __reduce_or_sync(0xffffffffu, jm_);
     // does the window reach outside the image?  (then additive pre-operations must skip the
     // zero fill); rowok bit r: window row rows[0].y0 + r is inside the image
     const int r_first = rows[0].y0;
@@ -652,16 +639,16 @@ zoom_sample_kernel(const __grid_constant__ ZoomParams P, int smem_floats) {
         const float mean = c_.mean;
         float out[ZT_H];
         if (pre_op == RC_PRE_NONE)
-          blend_col<RC_PRE_NONE, false>(out, rows, a_pl, pitch, step_mask, jump_mask, rowok_mask,
+          blend_col<RC_PRE_NONE, false>(out, rows, a_pl, pitch, step_mask, rowok_mask,
                                         mean, okl, okr, wl, wr);
         else if (pre_op == RC_PRE_THRESH02)
-          blend_col<RC_PRE_THRESH02, false>(out, rows, a_pl, pitch, step_mask, jump_mask,
+          blend_col<RC_PRE_THRESH02, false>(out, rows, a_pl, pitch, step_mask,
                                             rowok_mask, mean, okl, okr, wl, wr);
         else if (!edge)
-          blend_col<RC_PRE_ADD_MEAN, false>(out, rows, a_pl, pitch, step_mask, jump_mask,
+          blend_col<RC_PRE_ADD_MEAN, false>(out, rows, a_pl, pitch, step_mask,
                                             rowok_mask, mean, okl, okr, wl, wr);
         else
-          blend_col<RC_PRE_ADD_MEAN, true>(out, rows, a_pl, pitch, step_mask, jump_mask,
+          blend_col<RC_PRE_ADD_MEAN, true>(out, rows, a_pl, pitch, step_mask,
                                            rowok_mask, mean, okl, okr, wl, wr);
         const int post_op = c_.post_op, channel = c_.channel, acc = c_.accumulate;
         float *dst = c_.dst + col_off;
@@ -851,10 +838,10 @@ int rc_zoom_sample_dev(const float *zoom_factor, int inverse, const rc_zoom_grou
   P.spot_x1 = (int)ceil((double)width / 2 + 5);
   P.spot_y0 = (int)floor((double)height / 2 - 5);
   P.spot_y1 = (int)ceil((double)height / 2 + 5);
-  // 24 KB of staging per block (+ the 1 KB plane context): eight 128-thread blocks stay
+  // 22 KB of staging per block (+ the 1 KB plane context): nine 128-thread blocks stay
   // resident per SM; all 13 planes of the default configuration fit in one stage for zoom
-  // factors up to ~0.5 (window (128*wx+8) x (8*wy+3) floats per plane).
-  constexpr int kSmemFloats = 6144;
+  // factors up to ~0.45 (window (128*wx+8) x (8*wy+3) floats per plane).
+  constexpr int kSmemFloats = 5632;
   static bool attr_set = false;
   if (!attr_set) {
     RC_CUDA_TRY(cudaFuncSetAttribute(rc::zoom_sample_kernel<640>,
