@@ -249,7 +249,7 @@ typedef struct rc_compare_step_args {
   const float *trans_est;          /* [B,3] */
   const float *trans_gt;           /* [B,3] */
   /* outputs */
-  float *flow;                     /* [B,2,H,W] */
+  float *flow;                     /* [B,2,H,W]; NULL = test phase: no GT flow, no flow planes */
   float *valid;                    /* [B,1,H,W] */
   float *zoom_factor;              /* [B,4] */
   int32_t *bbox;                   /* [B,8] or NULL */
@@ -357,6 +357,23 @@ int rc_pose_update_dev(const float *src_pose, const float *rot_est, const float 
                        const float *tgt_pose, const float *K, const float *T_means,
                        const float *T_stds, int rot_coord, float *refined_pose, float *rot_res,
                        float *trans_res, float *KT, int batch_size, void *stream);
+
+/* ------------------------------------------------ test-time mask policies (8(f) rank 1)
+ * The "box_rendered" / "box_observed" branches of update_data_batch,
+ * lib/pair_matching/data_pair.py:101-131 (fed by deepim/core/tester.py:571-594): the new
+ * observed mask is the bounding rectangle of the non-zero pixels of `mask` (the rendered
+ * mask for box_rendered, the observed one for box_observed),
+ *     out[y_start:y_end, x_start:x_end] = 1, 0 elsewhere
+ * with the reference's exclusive slice end (the last row and column of the box stay 0).
+ *   mask, out  dev [B,1,H,W] float32 (non-negative masks); may not alias
+ *   bbox       dev [B,4] int32: x_start, x_end, y_start, y_end (np.min / np.max of the
+ *              non-zero columns / rows); x_start > x_end marks an empty mask, for which the
+ *              reference raises and `out` is all zero
+ *   workspace  dev [B,RC_BOX_WS_INTS] int32, zero before the first call; left zeroed.
+ * Requires W % 4 == 0 and 16-byte aligned planes. */
+#define RC_BOX_WS_INTS 5
+int rc_mask_box_dev(const float *mask, float *out, int32_t *bbox, int32_t *workspace,
+                    int batch_size, int height, int width, void *stream);
 
 #ifdef __cplusplus
 }

@@ -26,6 +26,7 @@ RC_ZOOM_ACCUMULATE, RC_ZOOM_SRC_BROADCAST = 1, 2
 RC_ZOOM_MAX_GROUPS = 8
 RC_ZOOM_MAX_PLANES = 16
 RC_ZF_WS_INTS = 10
+RC_BOX_WS_INTS = 5
 
 ROT_COORD = {"model": RC_ROT_MODEL, "camera": RC_ROT_CAMERA, "camera_new": RC_ROT_CAMERA_NEW,
              "naive": RC_ROT_NAIVE}
@@ -137,6 +138,7 @@ SIGNATURES = {
     "rc_pm_loss_bwd_dev": (c_int, [_P, _P, _P, _P, _P, _P, POINTER(c_float), POINTER(c_float),
                                    c_int, c_int, c_float, c_float, c_float, _P, _P, c_int, c_int,
                                    _P]),
+    "rc_mask_box_dev": (c_int, [_P, _P, _P, _P, c_int, c_int, c_int, _P]),
 }
 
 _lib = None

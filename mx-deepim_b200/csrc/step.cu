@@ -36,6 +36,9 @@ int rc_compare_step_dev(const rc_compare_step_args *a) {
   cudaStream_t s = static_cast<cudaStream_t>(a->stream);
   int st;
   const bool do_loss = N > 0 && a->loss_sum;
+  // test phase (deepIM_flownet.py:778-838): no GT flow, no loss -- flow == NULL skips both the
+  // flow kernel and the flow planes of the resampler
+  const bool do_flow = a->flow != nullptr && a->valid != nullptr;
   // overlap unless the caller wants per-kernel marks of the overlapped kernels
   const bool serial = a->marks && (a->marks[0] || a->marks[1] || a->marks[4] || a->marks[5]);
   auto loss = [&]() -> int {
@@ -66,7 +69,7 @@ int rc_compare_step_dev(const rc_compare_step_args *a) {
       PdlScope scope(do_loss);
       if ((st = bbox()) != RC_OK) return st;
     }
-    {
+    if (do_flow) {
       PdlScope scope(true);
       st = rc_flow_dev(a->depth_rendered, a->depth_gt_observed, a->KT, a->Kinv, a->flow, a->valid,
                        B, H, W, a->stream);
@@ -74,9 +77,11 @@ int rc_compare_step_dev(const rc_compare_step_args *a) {
     }
   } else {
     if ((st = rc::mark(a->marks, 0, s)) != RC_OK) return st;
-    st = rc_flow_dev(a->depth_rendered, a->depth_gt_observed, a->KT, a->Kinv, a->flow, a->valid,
-                     B, H, W, a->stream);
-    if (st != RC_OK) return st;
+    if (do_flow) {
+      st = rc_flow_dev(a->depth_rendered, a->depth_gt_observed, a->KT, a->Kinv, a->flow,
+                       a->valid, B, H, W, a->stream);
+      if (st != RC_OK) return st;
+    }
     if ((st = rc::mark(a->marks, 1, s)) != RC_OK) return st;
     if ((st = bbox()) != RC_OK) return st;
   }
@@ -103,8 +108,8 @@ int rc_compare_step_dev(const rc_compare_step_args *a) {
     set(n++, a->image_observed, a->zoom_image_observed, 3, RC_PRE_ADD_MEAN, RC_POST_SUB_MEAN, 0);
   if (a->zoom_image_rendered)
     set(n++, a->image_rendered, a->zoom_image_rendered, 3, RC_PRE_ADD_MEAN, RC_POST_SUB_MEAN, 0);
-  if (a->zoom_flow) set(n++, a->flow, a->zoom_flow, 2, RC_PRE_NONE, RC_POST_DIV_WX, 0);
-  if (a->zoom_flow_weights)
+  if (do_flow && a->zoom_flow) set(n++, a->flow, a->zoom_flow, 2, RC_PRE_NONE, RC_POST_DIV_WX, 0);
+  if (do_flow && a->zoom_flow_weights)
     set(n++, a->valid, a->zoom_flow_weights, 2, RC_PRE_NONE, RC_POST_ROUND_M045,
         RC_ZOOM_SRC_BROADCAST);
   st = rc_zoom_sample_dev(a->zoom_factor, 0, g, n, B, H, W, a->stream);

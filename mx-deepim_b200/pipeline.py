@@ -110,20 +110,33 @@ class CompareStep(object):
         return int(sum(np.asarray(host[k]).nbytes for k in INPUT_KEYS))
 
     # ------------------------------------------------------------------- step
-    def bind(self, x):
+    def bind(self, x, test_phase=False):
         """Build the rc_compare_step_args for the input tensors in `x` (device, INPUT_KEYS).
-        The struct holds raw pointers: keep `x` alive while it is in use."""
+        The struct holds raw pointers: keep `x` alive while it is in use.
+
+        test_phase=True mirrors the test graph (deepim/symbols/deepIM_flownet.py:778-838):
+        there is no ground truth, so `mask_gt_observed` IS `mask_observed` (:781), no GT flow
+        and no point-matching loss are computed; only image_observed, image_rendered,
+        depth_rendered, mask_observed and src_pose are read."""
         a = _lib.rc_compare_step_args()
-        for k in ("image_observed", "image_rendered", "depth_gt_observed", "depth_rendered",
-                  "mask_observed", "mask_gt_observed", "src_pose", "KT", "Kinv",
-                  "point_cloud_model", "point_cloud_weights", "point_cloud_observed", "rot_est",
-                  "trans_est", "trans_gt"):
+        keys = ("image_observed", "image_rendered", "depth_gt_observed", "depth_rendered",
+                "mask_observed", "mask_gt_observed", "src_pose", "KT", "Kinv",
+                "point_cloud_model", "point_cloud_weights", "point_cloud_observed", "rot_est",
+                "trans_est", "trans_gt")
+        if test_phase:
+            keys = ("image_observed", "image_rendered", "depth_rendered", "mask_observed",
+                    "src_pose")
+        for k in keys:
             t = x[k]
             C.check_tensor(k, t)
             if t.device != self.device:
                 raise ValueError("%s is on %s, step is on %s" % (k, t.device, self.device))
             setattr(a, k, t.data_ptr())
         a.K = self.Kd.data_ptr()
+        if test_phase:
+            a.mask_gt_observed = x["mask_observed"].data_ptr()
+        skip = ("flow", "valid", "zoom_flow", "zoom_flow_weights", "zoom_trans_gt", "loss_map",
+                "loss_sum", "zoom_mask_gt_observed") if test_phase else ()
         for name, t in (("flow", self.flow), ("valid", self.valid),
                         ("zoom_factor", self.zoom_factor), ("bbox", self.bbox),
                         ("workspace", self.ws), ("zoom_mask_observed", self.zoom_mask_observed),
@@ -135,7 +148,7 @@ class CompareStep(object):
                         ("zoom_flow_weights", self.zoom_flow_weights),
                         ("zoom_trans_gt", self.zoom_trans_gt), ("loss_map", self.loss_map),
                         ("loss_sum", self.loss_sum)):
-            setattr(a, name, t.data_ptr() if t is not None else None)
+            setattr(a, name, t.data_ptr() if (t is not None and name not in skip) else None)
         for i in range(3):
             a.pixel_means[i] = float(self.means[i])
             a.T_means[i] = self.T_means[i]
@@ -145,6 +158,8 @@ class CompareStep(object):
         a.rot_coord = self.rot_coord
         a.loss_type = self.loss_type
         a.batch_size, a.height, a.width, a.num_points = self.B, self.H, self.W, self.N
+        if test_phase:
+            a.num_points = 0
         a.marks = None
         return a
 
@@ -187,6 +202,31 @@ class CompareStep(object):
             "zoom_flow_weights": self.zoom_flow_weights, "zoom_trans_gt": self.zoom_trans_gt,
             "point_matching_loss": self.loss_map, "point_matching_loss_sum": self.loss_sum,
         }
+
+
+def mask_box(mask, out=None, bbox=None, workspace=None, stream=None):
+    """Test-time mask policy "box_rendered" / "box_observed" of update_data_batch
+    (/root/reference/lib/pair_matching/data_pair.py:101-131): the bounding rectangle of the
+    non-zero pixels of `mask` [B,1,H,W] (exclusive slice end, as the reference writes it).
+    Returns (out [B,1,H,W], bbox [B,4] int32 = x_start, x_end, y_start, y_end); an empty mask
+    gives x_start > x_end and an all-zero `out` (the reference raises there -- check `bbox`
+    on the host if that matters).  No synchronisation."""
+    C.check_tensor("mask", mask)
+    B, _, H, W = mask.shape
+    dev = mask.device
+    if out is None:
+        out = torch.empty_like(mask)
+    if bbox is None:
+        bbox = torch.empty((B, 4), dtype=torch.int32, device=dev)
+    if workspace is None:
+        workspace = torch.zeros((B, _lib.RC_BOX_WS_INTS), dtype=torch.int32, device=dev)
+    if out.data_ptr() == mask.data_ptr():
+        raise ValueError("out must not alias mask")
+    with torch.cuda.device(dev):
+        st = _lib.load().rc_mask_box_dev(mask.data_ptr(), out.data_ptr(), bbox.data_ptr(),
+                                         workspace.data_ptr(), B, H, W, _lib.stream_ptr(stream))
+    _lib.check(st, "rc_mask_box_dev")
+    return out, bbox
 
 
 def pose_update(src_pose, rot_est, trans_est, tgt_pose, K, T_means=(0, 0, 0), T_stds=(1, 1, 1),
@@ -327,6 +367,53 @@ class RefineLoop(object):
     def run(self, iterations=4):
         for it in range(iterations):
             self.iterate(it)
+
+    # ------------------------------------------------------------------ test phase
+    def iterate_test(self, rot_est, trans_est, update_mask="box_rendered"):
+        """One TEST-time refinement iteration (deepim/core/tester.py:520-594 +
+        lib/pair_matching/data_pair.py:75-138) on the current stream, no synchronisation:
+
+            pose_rendered_update = RT_transform(pose_rendered, r, t)     (tester.py:520-530)
+            render at the new pose; mask_rendered = depth > 0.2          (:557-577)
+            mask_observed <- policy(update_mask)                         (:578-589, data_pair)
+            zoom-in of masks + images through the test graph             (deepIM_flownet :778-838)
+
+        update_mask: "init" keeps mask_observed; "box_rendered" replaces it with the bounding
+        rectangle of the PREVIOUS iteration's rendered mask (tester.py:583-585 reads the batch's
+        current mask_rendered blob before it is overwritten)."""
+        if update_mask not in ("init", "box_rendered"):
+            raise Exception("Unknown UPDATE_MASK type: {}".format(update_mask))  # tester.py:588
+        nxt = 1 - self.cur
+        if update_mask == "box_rendered":
+            if not hasattr(self, "_box_ws"):
+                self._box_ws = torch.zeros((self.B, _lib.RC_BOX_WS_INTS), dtype=torch.int32,
+                                           device=self.device)
+                self._box_bbox = torch.empty((self.B, 4), dtype=torch.int32, device=self.device)
+                self.mask_observed_test = torch.empty_like(self.mask_rendered)
+            mask_box(self.mask_rendered, out=self.mask_observed_test, bbox=self._box_bbox,
+                     workspace=self._box_ws)
+        pose_update(self.pose[self.cur], rot_est, trans_est, self.pose[self.cur], self.K,
+                    out=(self.pose[nxt], self._scratch_q(), self._scratch_t(), self.KT))
+        self.renderer.render_batch(self.cls, self.pose[nxt], pixel_means=self.render_means,
+                                   want=("depth", "image", "mask"),
+                                   out={"depth": self.depth_rendered, "image": self.image_rendered,
+                                        "mask": self.mask_rendered})
+        self.cur = nxt
+        mo = self.mask_observed_test if update_mask == "box_rendered" else self.obs["mask_observed"]
+        x = {"image_observed": self.obs["image_observed"], "image_rendered": self.image_rendered,
+             "depth_rendered": self.depth_rendered, "mask_observed": mo,
+             "src_pose": self.pose[nxt]}
+        self.step.run(None, args=self.step.bind(x, test_phase=True))
+
+    def _scratch_q(self):
+        if not hasattr(self, "_sq"):
+            self._sq = torch.empty_like(self.rot_gt)
+            self._st = torch.empty_like(self.trans_gt)
+        return self._sq
+
+    def _scratch_t(self):
+        self._scratch_q()
+        return self._st
 
 
 def make_refine_batch(meshes, batch, seed, K=synth.K_LINEMOD, num_points=synth.NUM_3D_SAMPLE,

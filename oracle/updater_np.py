@@ -82,3 +82,39 @@ def updater_forward(meshes, class_index, src_pose, tgt_pose, rot_est, trans_est,
             "trans": trans_res.astype(np.float32), "flow": flow,
             "flow_weights": np.tile(valid, [1, 2, 1, 1]), "mask_rendered": mask.astype(np.float32),
             "KT": KT.astype(np.float32)}
+
+
+def update_mask_observed(policy, mask_observed, mask_rendered):
+    """The mask_observed branch of update_data_batch,
+    /root/reference/lib/pair_matching/data_pair.py:101-134, for ONE 2-D mask pair (the
+    statements are lifted; only the MXNet `nd.array` wrap is dropped).  `mask_observed` is the
+    package's update_data, `mask_rendered` is package["mask_rendered"]."""
+    update_data = mask_observed
+    if policy == "box_rendered":
+        update_data = np.copy(mask_rendered)
+        out = np.zeros(update_data.shape)
+        x_max = np.max(update_data, 0)
+        y_max = np.max(update_data, 1)
+        nz_x = np.nonzero(x_max)[0]
+        nz_y = np.nonzero(y_max)[0]
+        x_start = np.min(nz_x)
+        x_end = np.max(nz_x)
+        y_start = np.min(nz_y)
+        y_end = np.max(nz_y)
+        out[y_start:y_end, x_start:x_end] = 1.0  # rectangle
+    elif policy == "box_observed":
+        out = np.zeros(update_data.shape)
+        x_max = np.max(update_data, 0)
+        y_max = np.max(update_data, 1)
+        nz_x = np.nonzero(x_max)[0]
+        nz_y = np.nonzero(y_max)[0]
+        if len(nz_x) == 0 or len(nz_y) == 0:
+            raise Exception("no point valid in mask_observed")
+        x_start = np.min(nz_x)
+        x_end = np.max(nz_x)
+        y_start = np.min(nz_y)
+        y_end = np.max(nz_y)
+        out[y_start:y_end, x_start:x_end] = 1.0  # rectangle
+    else:
+        out = update_data
+    return out

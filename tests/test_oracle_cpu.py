@@ -269,3 +269,21 @@ def test_synth_batch_shapes():
         assert h[k].dtype == np.float32, k
     assert h["image_observed"].shape == (2, 3, 480, 640) and h["KT"].shape == (2, 3, 4)
     assert pipeline.algorithmic_bytes_per_pair(480, 640, 3000) == (20 + 112) * 307200 + 144000
+
+
+def test_update_mask_observed_lift():
+    """data_pair.py:101-131: rectangle with the reference's exclusive slice end; empty masks raise."""
+    from oracle import updater_np
+
+    m = np.zeros((12, 16))
+    m[2:5, 3:7] = 1
+    m[8, 10] = 1
+    box = updater_np.update_mask_observed("box_rendered", np.ones((12, 16)), m)
+    assert box.sum() == (8 - 2) * (10 - 3) and box[2, 3] == 1 and box[8, 10] == 0
+    assert np.array_equal(updater_np.update_mask_observed("box_observed", m, None), box)
+    keep = updater_np.update_mask_observed("init", m, None)
+    assert keep is m
+    with pytest.raises(Exception):
+        updater_np.update_mask_observed("box_observed", np.zeros((4, 4)), None)
+    with pytest.raises(ValueError):
+        updater_np.update_mask_observed("box_rendered", None, np.zeros((4, 4)))
