@@ -375,6 +375,46 @@ int rc_pose_update_dev(const float *src_pose, const float *rot_est, const float 
 int rc_mask_box_dev(const float *mask, float *out, int32_t *bbox, int32_t *workspace,
                     int batch_size, int height, int width, void *stream);
 
+/* -------------------------------------------- iteration-0 input preparation (8(f) rank 2)
+ * image.transform, lib/utils/image.py:709-720: BGR HWC uint8 -> [B,3,H,W] float32 RGB with
+ * out[:, i] = im[:, :, 2 - i] - pixel_means[2 - i] (float64 arithmetic, float32 store).
+ *   bgr_hwc dev [B,H,W,3] uint8 (4-byte aligned)   pixel_means_bgr HOST [3] float64 (B,G,R order) */
+int rc_prep_image_dev(const uint8_t *bgr_hwc, float *out_chw, const double *pixel_means_bgr,
+                      int batch_size, int height, int width, void *stream);
+
+/* Depth decode, lib/utils/image.py:200-206 / :229-260: uint16 -> float32, optional
+ * `depth *= (mask == mask_idx)` (:244), then / depth_factor in float32.
+ *   raw dev [B,H,W] uint16 (8-byte aligned); mask dev [B,H,W] uint8 + mask_idx dev [B] int32,
+ *   both NULL to skip; out dev [B,1,H,W]. */
+int rc_prep_depth_dev(const uint16_t *raw, const uint8_t *mask, const int32_t *mask_idx,
+                      float *out, float depth_factor, int batch_size, int height, int width,
+                      void *stream);
+
+/* get_point_cloud_observed, lib/utils/image.py:592-596: out = R . X + T per sample
+ * (float64 accumulation, float32 store).  points/out dev [B,3,N]; pose dev [B,3,4]. */
+int rc_points_transform_dev(const float *points, const float *pose, float *out, int batch_size,
+                            int num_points, void *stream);
+
+/* calc_flow, lib/pair_matching/flow.py:12-81 (+ backproject_camera, lib/utils/projection.py:
+ * 47-67): the float64 numpy rule used for iteration-0 labels and test-time ground truth
+ * (np.round half-to-even, bound test on the rounded pixel, clamped look-up, visible needs
+ * depth_src != 0, |d_tgt - z| < thresh and |d_tgt| > 1e-10) -- NOT the CUDA rule of
+ * rc_flow_dev.
+ *   depth_src, depth_tgt dev [B,1,H,W] float32
+ *   transform  dev [B,3,4] float64 = K . se3_mul(pose_tgt, se3_inverse(pose_src)) (:31)
+ *   Kinv_host  HOST [9] float64 = inv(K)
+ *   flow       dev [B,2,H,W] float32; channel order (dh, dw), or (dw, dh) if standard_rep
+ *   visible    dev [B,1,H,W] float32 0/1
+ *   x_valid    dev [B,3,capacity] float32 or NULL: back-projected source points of the
+ *              visible pixels in pixel order (flow.py:80); counts dev [B] int32 receives
+ *              the number per sample (points beyond `capacity` are dropped);
+ *   workspace  dev [B * rc_calc_flow_blocks(H, W)] int32 scratch (needed with x_valid). */
+int rc_calc_flow_blocks(int height, int width);
+int rc_calc_flow_dev(const float *depth_src, const float *depth_tgt, const double *transform,
+                     const double *Kinv_host, double thresh, int standard_rep, float *flow,
+                     float *visible, float *x_valid, int32_t *counts, int32_t *workspace,
+                     int capacity, int batch_size, int height, int width, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

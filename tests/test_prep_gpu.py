@@ -109,3 +109,97 @@ def test_test_phase_iteration(cuda_device):
         assert np.abs(loop.step.zoom_image_rendered.cpu().numpy() - zi[1]).max() <= 1e-4
         prev_mask = loop.mask_rendered.cpu().numpy().copy()
         prev_pose = pose.copy()
+
+
+def test_prep_image_and_depth(cuda_device):
+    """image.transform and the depth decode of the loaders (lib/utils/image.py)."""
+    import torch
+
+    from mx_deepim_b200 import prep, synth
+
+    rng = np.random.default_rng(5)
+    B, H, W = 3, 480, 640
+    im = rng.integers(0, 256, size=(B, H, W, 3), dtype=np.uint8)
+    means = np.array([102.9801, 115.9465, 122.7717])  # B, G, R (config.network.PIXEL_MEANS)
+    out = prep.transform_batch(torch.from_numpy(im).to(cuda_device), means)
+    torch.cuda.synchronize()
+    ref = np.zeros((B, 3, H, W))
+    for b in range(B):  # image.py:717-720
+        for i in range(3):
+            ref[b, i] = im[b, :, :, 2 - i] - means[2 - i]
+    assert np.array_equal(out.cpu().numpy(), ref.astype(np.float32))
+    one = prep.transform(im[0], means)
+    assert one.shape == (1, 3, H, W) and np.array_equal(one[0], ref[0].astype(np.float32))
+
+    raw = rng.integers(0, 3000, size=(B, H, W)).astype(np.uint16)
+    mask = rng.integers(0, 4, size=(B, H, W)).astype(np.uint8)
+    idx = np.array([1, 2, 3], np.int32)
+    t = torch.from_numpy(raw.view(np.int16)).to(cuda_device)
+    d = prep.decode_depth(t, 1000.0)
+    dm = prep.decode_depth(t, 1000.0, torch.from_numpy(mask).to(cuda_device),
+                           torch.from_numpy(idx).to(cuda_device))
+    torch.cuda.synchronize()
+    ref_d = raw.astype(np.float32) / 1000.0  # image.py:200-206
+    assert np.array_equal(d.cpu().numpy()[:, 0], ref_d)
+    ref_m = raw.astype(np.float32)
+    ref_m *= mask == idx.reshape(B, 1, 1)    # image.py:244
+    assert np.array_equal(dm.cpu().numpy()[:, 0], ref_m / 1000.0)
+
+
+def test_point_cloud_model_and_observed(cuda_device):
+    import torch
+
+    from mx_deepim_b200 import prep, synth
+
+    rng = np.random.default_rng(9)
+    pts_obj = rng.normal(size=(1234, 3)) * 0.05
+    np.random.seed(4)
+    ps, pw = prep.get_point_cloud_model(pts_obj, 3000)
+    assert ps.shape == (1, 3, 3000) and pw.shape == (1, 3, 3000)
+    assert pw[0, :, :1234].min() == 1 and pw[0, :, 1234:].max() == 0 and np.all(ps[0, :, 1234:] == 0)
+    assert sorted(map(tuple, ps[0, :, :1234].T.tolist())) == sorted(map(tuple, pts_obj.tolist()))
+    B = 4
+    pts = np.repeat(ps.astype(np.float32), B, axis=0)
+    poses = np.stack([synth.random_pose_pair(rng, synth.K_LINEMOD)[1] for _ in range(B)])
+    out = prep.get_point_cloud_observed(torch.from_numpy(pts).to(cuda_device),
+                                        torch.from_numpy(poses).to(cuda_device))
+    torch.cuda.synchronize()
+    for b in range(B):  # image.py:592-596
+        R, T = poses[b][:, :3], poses[b][:, 3]
+        ref = np.dot(R.astype(np.float64), pts[b].astype(np.float64)) + T.reshape((3, 1))
+        np.testing.assert_allclose(out[b].cpu().numpy(), ref, rtol=0, atol=1e-6)
+
+
+def test_calc_flow_device_matches_reference_golden(cuda_device):
+    """prep.calc_flow (device, float64 numpy rule of flow.py:12-81) against the outputs of the
+    REFERENCE's own calc_flow stored by tests/golden/make_golden.py, and against the oracle
+    restatement on the standard_rep variant."""
+    import os
+
+    import helpers
+    from mx_deepim_b200 import prep
+    from oracle import flow_np
+
+    gold = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    for seed in (0, 4):
+        inp = helpers.make_flow_inputs(1, seed, occlude=(seed == 4))
+        d_src = inp["depth_src"][0, 0].astype(np.float64)
+        d_tgt = inp["depth_tgt"][0, 0].astype(np.float64)
+        g = np.load(os.path.join(gold, "flow_calc_flow_seed%d.npz" % seed))
+        flow, vis, xv = prep.calc_flow(d_src, inp["pose_src"][0], inp["pose_tgt"][0], helpers.K_LM, d_tgt)
+        assert flow.shape == d_src.shape + (2,) and vis.shape == d_src.shape
+        idx = np.flatnonzero(vis.reshape(-1))
+        assert np.array_equal(idx, g["visible_idx"])          # visibility mask: bit-exact
+        fa = flow.reshape(-1, 2)[idx]
+        assert np.abs(fa - g["flow_at_visible"]).max() < 1e-4  # float32 store of the float64 value
+        assert float(np.abs(flow.reshape(-1, 2)[np.setdiff1d(np.arange(vis.size), idx)]).max()) == 0
+        assert xv.shape == (3, int(g["n_X_valid"]))
+        np.testing.assert_allclose(xv.sum(axis=1), g["X_valid_sum"], rtol=1e-5)
+        # standard representation (dw, dh) and the point list, vs the restatement
+        f2, v2, x2 = prep.calc_flow(d_src, inp["pose_src"][0], inp["pose_tgt"][0], helpers.K_LM, d_tgt,
+                                    standard_rep=True)
+        rf, rv, rx = flow_np.calc_flow(d_src, inp["pose_src"][0], inp["pose_tgt"][0], helpers.K_LM,
+                                       d_tgt, standard_rep=True)
+        assert np.array_equal(v2, rv)
+        assert np.abs(f2 - rf).max() < 1e-4
+        np.testing.assert_allclose(x2, rx, rtol=1e-6, atol=1e-7)
