@@ -390,6 +390,11 @@ int rc_prep_depth_dev(const uint16_t *raw, const uint8_t *mask, const int32_t *m
                       float *out, float depth_factor, int batch_size, int height, int width,
                       void *stream);
 
+/* Mask decode, lib/utils/image.py:300-304 (get_pair_mask): out = (mask_png == mask_idx) ? 1 : 0.
+ *   mask dev [B,H,W] uint8 (4-byte aligned); mask_idx dev [B] int32; out dev [B,1,H,W]. */
+int rc_prep_mask_dev(const uint8_t *mask, const int32_t *mask_idx, float *out, int batch_size,
+                     int height, int width, void *stream);
+
 /* get_point_cloud_observed, lib/utils/image.py:592-596: out = R . X + T per sample
  * (float64 accumulation, float32 store).  points/out dev [B,3,N]; pose dev [B,3,4]. */
 int rc_points_transform_dev(const float *points, const float *pose, float *out, int batch_size,

@@ -160,6 +160,20 @@ prep_depth_kernel(const uint16_t *__restrict__ raw, const uint8_t *__restrict__ 
                     __fdiv_rn(v[3], factor)));
 }
 
+// Mask decode (lib/utils/image.py:300-304): cur_mask[mask_png == mask_idx] = 1.0, else 0.
+__global__ void __launch_bounds__(256)
+prep_mask_kernel(const uint8_t *__restrict__ mask, const int32_t *__restrict__ mask_idx,
+                 float *__restrict__ out, int plane_quads) {
+  const int b = blockIdx.y;
+  const int q = blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= plane_quads) return;
+  const uint32_t mw = __ldg(reinterpret_cast<const uint32_t *>(mask + (size_t)b * plane_quads * 4) + q);
+  const int want = mask_idx[b];
+  st_f4(reinterpret_cast<float4 *>(out + (size_t)b * plane_quads * 4) + q,
+        make_float4((int)(mw & 255u) == want ? 1.f : 0.f, (int)((mw >> 8) & 255u) == want ? 1.f : 0.f,
+                    (int)((mw >> 16) & 255u) == want ? 1.f : 0.f, (int)(mw >> 24) == want ? 1.f : 0.f));
+}
+
 // get_point_cloud_observed (lib/utils/image.py:592-596): R . X + T in float64, stored float32.
 __global__ void __launch_bounds__(256)
 points_transform_kernel(const float *__restrict__ pts, const float *__restrict__ pose,
@@ -369,6 +383,19 @@ int rc_prep_depth_dev(const uint16_t *raw, const uint8_t *mask, const int32_t *m
   dim3 grid((quads + 255) / 256, batch_size);
   rc::prep_depth_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(
       raw, mask, mask_idx, out, depth_factor, quads);
+  return rc::note_status(rc::check_launch());
+}
+
+int rc_prep_mask_dev(const uint8_t *mask, const int32_t *mask_idx, float *out, int batch_size,
+                     int height, int width, void *stream) {
+  RC_REQUIRE(batch_size >= 0 && height > 0 && width > 0, RC_ERR_INVALID_ARG);
+  if (batch_size == 0) return rc::note_status(RC_OK);
+  RC_REQUIRE(mask && mask_idx && out, RC_ERR_INVALID_ARG);
+  RC_REQUIRE(width % 4 == 0 && rc::aligned16(out) && ((uintptr_t)mask & 3u) == 0, RC_ERR_UNALIGNED);
+  RC_REQUIRE(batch_size <= 65535, RC_ERR_INVALID_ARG);
+  const int quads = height * width / 4;
+  dim3 grid((quads + 255) / 256, batch_size);
+  rc::prep_mask_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(mask, mask_idx, out, quads);
   return rc::note_status(rc::check_launch());
 }
 

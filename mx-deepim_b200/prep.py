@@ -80,6 +80,21 @@ def decode_depth(raw_u16, depth_factor, mask=None, mask_idx=None, out=None, stre
     return out
 
 
+def decode_mask(mask_u8, mask_idx, out=None, stream=None):
+    """get_pair_mask's instance selection (image.py:300-304): CUDA uint8 [B,H,W] + int32 [B]
+    -> float32 [B,1,H,W] with 1.0 where mask == mask_idx."""
+    if mask_u8.dtype != torch.uint8 or mask_u8.dim() != 3:
+        raise TypeError("mask_u8 must be a uint8 [B,H,W] tensor")
+    B, H, W = mask_u8.shape
+    if out is None:
+        out = torch.empty((B, 1, H, W), dtype=torch.float32, device=mask_u8.device)
+    with torch.cuda.device(mask_u8.device):
+        st = _lib.load().rc_prep_mask_dev(mask_u8.data_ptr(), mask_idx.data_ptr(), out.data_ptr(),
+                                          B, H, W, _lib.stream_ptr(stream))
+    _lib.check(st, "rc_prep_mask_dev")
+    return out
+
+
 def get_point_cloud_model(points_obj, num_sample, rng=np.random):
     """image.py:559-589 without the file cache: shuffle, keep <= num_sample points, zero-pad.
     Returns ([1,3,num_sample] points, [1,3,num_sample] weights) float64 numpy, like the

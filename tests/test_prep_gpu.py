@@ -144,6 +144,11 @@ def test_prep_image_and_depth(cuda_device):
     ref_m = raw.astype(np.float32)
     ref_m *= mask == idx.reshape(B, 1, 1)    # image.py:244
     assert np.array_equal(dm.cpu().numpy()[:, 0], ref_m / 1000.0)
+    mk = prep.decode_mask(torch.from_numpy(mask).to(cuda_device), torch.from_numpy(idx).to(cuda_device))
+    torch.cuda.synchronize()
+    ref_k = np.zeros(mask.shape)
+    ref_k[mask == idx.reshape(B, 1, 1)] = 1.0  # image.py:302-304
+    assert np.array_equal(mk.cpu().numpy()[:, 0], ref_k.astype(np.float32))
 
 
 def test_point_cloud_model_and_observed(cuda_device):
