@@ -420,6 +420,38 @@ int rc_calc_flow_dev(const float *depth_src, const float *depth_tgt, const doubl
                      float *visible, float *x_valid, int32_t *counts, int32_t *workspace,
                      int capacity, int batch_size, int height, int width, void *stream);
 
+/* ------------------------------------------------ evaluation reductions (8(f) rank 4)
+ * Pose errors of lib/utils/pose_error.py for B (estimate, ground truth) pose pairs:
+ *   out [B,5] float64: add (:71-86), adi (:89-109, nearest neighbour by exact search),
+ *                      arp_2d (:55-68), re in degrees (:126-131), te (:134-145)
+ *   pose_est, pose_gt dev [B,3,4] float32; points dev [B,3,N] float32, or [3,N] shared by all
+ *   pairs when points_shared != 0; n_valid dev [B] int32 (points beyond it are padding) or
+ *   NULL; K dev [3,3] float32; workspace dev [B * rc_pose_error_chunks(N) * 3] float64.
+ *   want_adi = 0 skips the O(N^2) search (adi column = 0). */
+int rc_pose_error_chunks(int num_points);
+int rc_pose_error_dev(const float *pose_est, const float *pose_gt, const float *points,
+                      int points_shared, const int32_t *n_valid, const float *K, int want_adi,
+                      double *out, double *workspace, int batch_size, int num_points,
+                      void *stream);
+
+/* Visibility masks of lib/utils/visibility.py:7-33 over `count` pixels (any batch shape):
+ *   out = d_test > 0 && d_model > 0 && d_model - d_test <= delta           (estimate_visib_mask)
+ *   with visib_gt != NULL additionally  || (visib_gt && d_model > 0)    (estimate_visib_mask_est)
+ * float32 0/1 output; count % 4 == 0 and 16-byte aligned pointers. */
+int rc_visib_mask_dev(const float *d_test, const float *d_model, const float *visib_gt,
+                      float delta, float *out, int64_t count, void *stream);
+
+/* Flow end-point errors, deepim/core/tester.py:719-736 (calc_EPE_one_pair):
+ *   out [B,6] float64: epe_all, num_all, epe_viz, num_viz, epe_vizbg, num_vizbg
+ *   flow_pred, flow_gt dev [B,2,H,W]; visible dev [B,1,H,W];
+ *   bg dev [B,1,H,W] or NULL -> visible == 0 && depth_rendered == 0 (tester.py:712) when
+ *   depth_rendered [B,1,H,W] is given, else empty;
+ *   workspace dev [B * rc_flow_epe_chunks() * 5] float64. */
+int rc_flow_epe_chunks(void);
+int rc_flow_epe_dev(const float *flow_pred, const float *flow_gt, const float *visible,
+                    const float *bg, const float *depth_rendered, double *out, double *workspace,
+                    int batch_size, int height, int width, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -139,6 +139,11 @@ SIGNATURES = {
                                    c_int, c_int, c_float, c_float, c_float, _P, _P, c_int, c_int,
                                    _P]),
     "rc_mask_box_dev": (c_int, [_P, _P, _P, _P, c_int, c_int, c_int, _P]),
+    "rc_pose_error_chunks": (c_int, [c_int]),
+    "rc_pose_error_dev": (c_int, [_P, _P, _P, c_int, _P, _P, c_int, _P, _P, c_int, c_int, _P]),
+    "rc_visib_mask_dev": (c_int, [_P, _P, _P, c_float, _P, c_int64, _P]),
+    "rc_flow_epe_chunks": (c_int, []),
+    "rc_flow_epe_dev": (c_int, [_P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, _P]),
     "rc_prep_image_dev": (c_int, [_P, _P, POINTER(ctypes.c_double), c_int, c_int, c_int, _P]),
     "rc_prep_depth_dev": (c_int, [_P, _P, _P, _P, c_float, c_int, c_int, c_int, _P]),
     "rc_prep_mask_dev": (c_int, [_P, _P, _P, c_int, c_int, c_int, _P]),

@@ -157,3 +157,27 @@ def make_points_inputs(batch, seed, num_points=3000, num_keep=None):
         poses_src[b], poses_tgt[b] = ps, pt
     return dict(points=pts, weights=wts, points_obs=obs, rotation=rot, translation=trans,
                 pose_src=poses_src, pose_tgt=poses_tgt)
+
+
+def make_eval_inputs(seed, batch=4, num_points=1500):
+    """Seeded inputs of the evaluation reductions: pose pairs, zero-padded model points with a
+    per-pair valid count, and three depth maps (test scene, GT render, estimate render)."""
+    rng = np.random.default_rng(seed)
+    pose_est = np.zeros((batch, 3, 4), np.float32)
+    pose_gt = np.zeros((batch, 3, 4), np.float32)
+    points = np.zeros((batch, 3, num_points), np.float32)
+    n_valid = np.zeros((batch,), np.int32)
+    for b in range(batch):
+        pose_est[b], pose_gt[b] = random_pose_pair(rng)
+        n = num_points if b == 0 else int(rng.integers(num_points // 3, num_points))
+        n_valid[b] = n
+        points[b, :, :n] = (rng.normal(size=(3, n)) * np.array([[0.04], [0.06], [0.03]])).astype(np.float32)
+    radii = rng.uniform(0.05, 0.1, size=3)
+    d_gt = ellipsoid_depth(pose_gt[0], radii)
+    d_est = ellipsoid_depth(pose_est[0], radii)
+    d_test = d_gt.copy()
+    d_test[d_test > 0] += rng.normal(0, 0.004, size=int((d_test > 0).sum())).astype(np.float32)
+    d_test[200:260, 280:360] = 0.45  # an occluder in front of part of the frame
+    d_test[:, :40] = 0
+    return dict(pose_est=pose_est, pose_gt=pose_gt, points=points, n_valid=n_valid,
+                d_test=d_test.astype(np.float32), d_gt=d_gt, d_est=d_est)

@@ -287,3 +287,25 @@ def test_update_mask_observed_lift():
         updater_np.update_mask_observed("box_observed", np.zeros((4, 4)), None)
     with pytest.raises(ValueError):
         updater_np.update_mask_observed("box_rendered", None, np.zeros((4, 4)))
+
+
+def test_eval_restatement_matches_reference_golden():
+    """oracle.eval_np == the reference's pose_error.py / visibility.py (make_golden_eval.py)."""
+    import helpers
+    from oracle import eval_np as E
+
+    g = np.load(os.path.join(GOLD, "eval_reference.npz"))
+    inp = helpers.make_eval_inputs(7)
+    K = helpers.K_LM.astype(np.float64)
+    for b in range(inp["pose_est"].shape[0]):
+        n = int(inp["n_valid"][b])
+        pts = inp["points"][b, :, :n].T.astype(np.float64)
+        Re, te = inp["pose_est"][b, :, :3].astype(np.float64), inp["pose_est"][b, :, 3].astype(np.float64)
+        Rg, tg = inp["pose_gt"][b, :, :3].astype(np.float64), inp["pose_gt"][b, :, 3].astype(np.float64)
+        got = [E.add(Re, te, Rg, tg, pts), E.adi(Re, te, Rg, tg, pts), E.arp_2d(Re, te, Rg, tg, pts, K),
+               E.re(Re, Rg), E.te(te, tg)]
+        np.testing.assert_allclose(got, g["pose_errors"][b], rtol=1e-12)
+    vg = E.estimate_visib_mask(inp["d_test"], inp["d_gt"], 0.015)
+    ve = E.estimate_visib_mask_est(inp["d_test"], inp["d_est"], vg, 0.015)
+    assert np.array_equal(np.packbits(vg), g["visib_gt"]) and np.array_equal(np.packbits(ve), g["visib_est"])
+    assert vg.any() and ve.any() and not vg[200:260, 280:360].any()
