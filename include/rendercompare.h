@@ -317,6 +317,9 @@ int rc_renderer_destroy(void *handle);
 
 #define RC_RENDER_TEXTURED 0  /* gl_FragColor = texture2D(u_texture, v_texcoord)          */
 #define RC_RENDER_LAMBERT 1   /* ... * ((1-r) + r*brightness) * light_intensity (ModelNet) */
+#define RC_RENDER_LIT_LINEMOD 2 /* ... * ((1-r) + r*brightness * light_intensity): the LINEMOD
+                                   light shaders, render_py_light.py:36-79 and
+                                   render_py_light_multi_program.py:38-80 */
 
 typedef struct rc_render_args {
   const int32_t *cls_idx;     /* dev [B] mesh index per render                         */

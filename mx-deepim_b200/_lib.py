@@ -79,7 +79,7 @@ class rc_compare_step_args(ctypes.Structure):
     ])
 
 
-RC_RENDER_TEXTURED, RC_RENDER_LAMBERT = 0, 1
+RC_RENDER_TEXTURED, RC_RENDER_LAMBERT, RC_RENDER_LIT_LINEMOD = 0, 1, 2
 RC_RENDER_MARKS = 5
 
 

@@ -425,7 +425,12 @@ __device__ Shaded shade_pixel(const Renderer &R, const RasterOut &O, const Cam &
   br = fmax(fmin(br, 1.0), 0.0);
 #pragma unroll
   for (int c = 0; c < 3; ++c) {
-    double v = ((double)__ldg(tex + c) / 255.0) * ((O.amb + O.dif * br) * (double)O.light_int[b * 3 + c]);
+    // ModelNet: t * ((a + b*br) * I), render_py_light_modelnet_multi.py:74;
+    // LINEMOD:  t * (a + b*br * I),   render_py_light.py:74 / render_py_light_multi_program.py:76
+    const double li = (double)O.light_int[b * 3 + c];
+    double v = (O.mode == RC_RENDER_LIT_LINEMOD)
+                   ? ((double)__ldg(tex + c) / 255.0) * (O.amb + O.dif * br * li)
+                   : ((double)__ldg(tex + c) / 255.0) * ((O.amb + O.dif * br) * li);
     v = fmax(fmin(v, 1.0), 0.0);
     s.c[c] = (float)floor(v * 255.0 + 0.5);  // unorm8 colour buffer, then np.round(rgb * 255)
   }
@@ -720,7 +725,9 @@ int rc_render_dev(void *handle, const rc_render_args *a) {
   RC_REQUIRE(B <= R.max_batch, RC_ERR_CAPACITY);
   if (B == 0) return rc::note_status(RC_OK);
   RC_REQUIRE(a->cls_idx && a->poses && a->depth, RC_ERR_INVALID_ARG);
-  RC_REQUIRE(a->mode == RC_RENDER_TEXTURED || a->mode == RC_RENDER_LAMBERT, RC_ERR_INVALID_ARG);
+  RC_REQUIRE(a->mode == RC_RENDER_TEXTURED || a->mode == RC_RENDER_LAMBERT ||
+                 a->mode == RC_RENDER_LIT_LINEMOD,
+             RC_ERR_INVALID_ARG);
   RC_REQUIRE(a->mode == RC_RENDER_TEXTURED || (a->light_pos && a->light_int), RC_ERR_INVALID_ARG);
   RC_REQUIRE(a->znear > 0.f && a->zfar > a->znear, RC_ERR_INVALID_ARG);
   RC_REQUIRE(rc::aligned16(a->depth) && rc::aligned16(a->image_chw) && rc::aligned16(a->bgr_hwc) &&

@@ -257,3 +257,117 @@ class Render_Py_Light_ModelNet_Multi(object):
     def render_batch(self, cls_idx, poses, **kw):
         kw.setdefault("mode", _lib.RC_RENDER_LAMBERT)
         return self.dev.render_batch(cls_idx, poses, **kw)
+
+
+# ------------------------------------------------ the remaining lib/render_glumpy classes
+def _load_linemod_model(model_folder):
+    m = load_obj("{}/textured.obj".format(model_folder), rescale=False)
+    m["texture"] = load_texture("{}/texture_map.png".format(model_folder))
+    return m
+
+
+class Render_Py_Single(object):
+    """Single-model textured renderer (reference render_py.py:48-128):
+    Render_Py(model_folder, K, ...).render(r, t, r_type="quat", K=None)
+        -> (bgr [H,W,3] float32 0..255, depth [H,W] float32 m)."""
+
+    def __init__(self, model_folder, K, width=640, height=480, zNear=0.25, zFar=6.0, mesh=None,
+                 max_batch=64, device=None):
+        self.width, self.height, self.zNear, self.zFar = width, height, zNear, zFar
+        self.K = K
+        self.model_folder = model_folder
+        mesh = _load_linemod_model(model_folder) if mesh is None else mesh
+        self.dev = DeviceRenderer([mesh], K, width, height, zNear, zFar, max_batch, device)
+
+    def render(self, r, t, r_type="quat", K=None):
+        R = P.quat2mat(r) if r_type == "quat" else np.asarray(r)
+        return self.dev._one(0, R, t, K)
+
+
+class Render_Py_Depth(Render_Py_Single):
+    """render_py_depth.Render_Py (render_py_depth.py:48-128): render(r, t, r_type="quat")
+    -> (bgr uint8 = np.round(rgb * 255), depth float32)."""
+
+    def render(self, r, t, r_type="quat"):
+        bgr, depth = Render_Py_Single.render(self, r, t, r_type)
+        return np.round(bgr).astype(np.uint8), depth
+
+
+class Render_Py_Light(object):
+    """LINEMOD renderer with a point light (reference render_py_light.py:80-213):
+    Render_Py_Light(model_folder, K, ..., brightness_ratios=[0.4, 0.3, 0.2])
+        .render(r, t, light_position, light_intensity, brightness_k=0, r_type="quat", K=None)
+        -> (bgr uint8, depth float32).  Fragment colour t * ((1-b) + b * brightness * I)."""
+
+    def __init__(self, model_folder, K, width=640, height=480, zNear=0.25, zFar=6.0,
+                 brightness_ratios=[0.4, 0.3, 0.2], mesh=None, max_batch=64, device=None):
+        self.width, self.height, self.zNear, self.zFar = width, height, zNear, zFar
+        self.K = K
+        self.model_folder = model_folder
+        self.brightness_ratios = list(brightness_ratios)
+        self.brightness_k = 0
+        mesh = _load_linemod_model(model_folder) if mesh is None else mesh
+        self.dev = DeviceRenderer([mesh], K, width, height, zNear, zFar, max_batch, device)
+
+    def _lit(self, idx, r, t, light_position, light_intensity, brightness_k, r_type, K, mode):
+        R = P.quat2mat(r) if r_type == "quat" else np.asarray(r)
+        d = self.dev.device
+        lp = torch.tensor(np.asarray(light_position, np.float32).reshape(1, 3), device=d)
+        li = torch.tensor(np.asarray(light_intensity, np.float32).reshape(1, 3), device=d)
+        self.brightness_k = brightness_k
+        bgr, depth = self.dev._one(idx, R, t, K, mode=mode, light_pos=lp, light_int=li,
+                                   brightness_ratio=self.brightness_ratios[brightness_k])
+        return bgr.astype(np.uint8), depth
+
+    def render(self, r, t, light_position, light_intensity, brightness_k=0, r_type="quat", K=None):
+        return self._lit(0, r, t, light_position, light_intensity, brightness_k, r_type, K,
+                         _lib.RC_RENDER_LIT_LINEMOD)
+
+
+class Render_Py_Light_MultiProgram(Render_Py_Light):
+    """Multi-class LINEMOD light renderer (reference render_py_light_multi_program.py:84-240):
+    Render_Py_Light_MultiProgram(class_name_list, model_folder_dict, K, ...)
+        .render(r, t, light_position, light_intensity, class_name, brightness_k=0, r_type="quat")."""
+
+    def __init__(self, class_name_list, model_folder_dict, K, width=640, height=480, zNear=0.25,
+                 zFar=6.0, brightness_ratios=[0.4, 0.3, 0.2], meshes=None, max_batch=64,
+                 device=None):
+        self.width, self.height, self.zNear, self.zFar = width, height, zNear, zFar
+        self.K = K
+        self.model_folder_dict = model_folder_dict
+        self.class_name_list = list(class_name_list)
+        self.brightness_ratios = list(brightness_ratios)
+        self.brightness_k = 0
+        self.class_name = self.class_name_list[-1]
+        if meshes is None:
+            meshes = [_load_linemod_model(model_folder_dict[c]) for c in self.class_name_list]
+        self.dev = DeviceRenderer(meshes, K, width, height, zNear, zFar, max_batch, device)
+
+    def render(self, r, t, light_position, light_intensity, class_name, brightness_k=0,
+               r_type="quat"):
+        self.class_name = class_name
+        return self._lit(self.class_name_list.index(class_name), r, t, light_position,
+                         light_intensity, brightness_k, r_type, None, _lib.RC_RENDER_LIT_LINEMOD)
+
+
+class Render_Py_Light_ModelNet(Render_Py_Light):
+    """Single-model ModelNet renderer (reference render_py_light_modelnet.py:82-211):
+    Render_Py_Light_ModelNet(model_path, texture_path, K, ..., brightness_ratios=[0.7])
+        .render(r, t, light_position, light_intensity, brightness_k=0, r_type="quat")."""
+
+    def __init__(self, model_path, texture_path, K, width=640, height=480, zNear=0.25, zFar=6.0,
+                 brightness_ratios=[0.7], mesh=None, max_batch=64, device=None):
+        self.width, self.height, self.zNear, self.zFar = width, height, zNear, zFar
+        self.K = K
+        self.model_path = model_path
+        self.brightness_ratios = list(brightness_ratios)
+        self.brightness_k = 0
+        if mesh is None:
+            mesh = load_obj(model_path, rescale=True)
+            mesh["vertices"] = mesh["vertices"] / 10.0  # :103
+            mesh["texture"] = load_texture(texture_path)
+        self.dev = DeviceRenderer([mesh], K, width, height, zNear, zFar, max_batch, device)
+
+    def render(self, r, t, light_position, light_intensity, brightness_k=0, r_type="quat"):
+        return self._lit(0, r, t, light_position, light_intensity, brightness_k, r_type, None,
+                         _lib.RC_RENDER_LAMBERT)

@@ -116,3 +116,14 @@ def render_py_light_modelnet(mesh, r, t, light_position, light_intensity, K, r_t
     bgr, depth = _render(mesh, R, t, K, width, height, zNear, zFar, 1, light_position,
                          light_intensity, brightness_ratio)
     return bgr.astype(np.uint8), depth
+
+
+def render_py_light(mesh, r, t, light_position, light_intensity, K, r_type="quat", width=640,
+                    height=480, zNear=0.25, zFar=6.0, brightness_ratio=0.4):
+    """Render_Py_Light.render / Render_Py_Light_MultiProgram.render
+    (/root/reference/lib/render_glumpy/render_py_light.py:136-213,
+    render_py_light_multi_program.py:156-240): returns (bgr uint8 [H,W,3], depth float32)."""
+    R = pose_np.quat2mat(r) if r_type == "quat" else np.asarray(r)
+    bgr, depth = _render(mesh, R, t, K, width, height, zNear, zFar, 2, light_position,
+                         light_intensity, brightness_ratio)
+    return bgr.astype(np.uint8), depth

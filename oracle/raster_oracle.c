@@ -70,7 +70,7 @@ typedef struct {
 } OTarget;
 
 typedef struct {
-  int mode;                  /* 0 textured, 1 textured * Lambert */
+  int mode;                  /* 0 textured, 1 textured * Lambert (ModelNet), 2 LINEMOD light */
   const unsigned char *tex;  /* [Ht,Wt,3] RGB, row 0 = top of the PNG */
   int Ht, Wt;
   double view[16];           /* GLSL view matrix (column-vector convention), row-major here */
@@ -111,7 +111,10 @@ static void shade(const OShade *S, const double *attr, unsigned char *out3) {
   double br = (n[0] * s2l[0] + n[1] * s2l[1] + n[2] * s2l[2]) / (ls * ln);
   br = fmax(fmin(br, 1.0), 0.0);
   for (int c = 0; c < 3; ++c) {
-    double v = (t[c] / 255.0) * ((S->amb + S->dif * br) * S->light_int[c]);
+    /* ModelNet: t * ((a + b*br) * I)   render_py_light_modelnet_multi.py:74
+     * LINEMOD : t * (a + b*br * I)     render_py_light.py:74, render_py_light_multi_program.py:76 */
+    double v = (S->mode == 2) ? (t[c] / 255.0) * (S->amb + S->dif * br * S->light_int[c])
+                              : (t[c] / 255.0) * ((S->amb + S->dif * br) * S->light_int[c]);
     v = fmax(fmin(v, 1.0), 0.0);
     out3[c] = (unsigned char)floor(v * 255.0 + 0.5); /* unorm8 conversion of the colour buffer */
   }
@@ -203,7 +206,7 @@ void oracle_render(const double *verts, const double *uv, const double *normals,
   memset(&S, 0, sizeof(S));
   S.mode = mode; S.tex = tex; S.Ht = Ht; S.Wt = Wt;
   for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) S.view[r * 4 + c] = view_np[c * 4 + r];
-  if (mode == 1) {
+  if (mode >= 1) {
     for (int i = 0; i < 3; ++i) { S.light_pos[i] = light_pos[i]; S.light_int[i] = light_int[i]; }
     S.amb = 1.0 - brightness_ratio; S.dif = brightness_ratio;
   }

@@ -159,3 +159,58 @@ def test_lambert_modelnet(cuda_device):
                                                             light_intensity, K, r_type="mat")
         _compare(o_bgr.astype(np.float32), o_depth, bgr.astype(np.float32), depth, colour_tol=1.0)
         assert bgr[depth > 0].std() > 1.0  # shading varies over the surface
+
+
+def test_linemod_light_and_single_model_renderers(cuda_device):
+    """The remaining lib/render_glumpy classes, imported by the reference's module names."""
+    from mx_deepim_b200.render_glumpy.render_py import Render_Py as Render_Py_1
+    from mx_deepim_b200.render_glumpy.render_py_depth import Render_Py as Render_Py_D
+    from mx_deepim_b200.render_glumpy.render_py_light import Render_Py_Light
+    from mx_deepim_b200.render_glumpy.render_py_light_modelnet import Render_Py_Light_ModelNet
+    from mx_deepim_b200.render_glumpy.render_py_light_multi_program import Render_Py_Light_MultiProgram
+    from mx_deepim_b200.render_glumpy.render_py_multi import Render_Py as Render_Py_M  # noqa: F401
+
+    meshes = _meshes()
+    poses = _poses(3, 33)
+    R, t = poses[0, :, :3], poses[0, :, 3]
+    # single-model textured + its uint8 "depth" twin
+    r1 = Render_Py_1(None, K, mesh=meshes[2], max_batch=1)
+    bgr, depth = r1.render(R, t, r_type="mat")
+    o_bgr, o_depth = raster_np.render_py(meshes[2], R, t, K, r_type="mat")
+    _compare(o_bgr, o_depth, bgr, depth)
+    rd = Render_Py_D(None, K, mesh=meshes[2], max_batch=1)
+    bgr8, depth8 = rd.render(R, t, r_type="mat")
+    assert bgr8.dtype == np.uint8 and np.array_equal(depth8, depth)
+    assert np.array_equal(bgr8, np.round(bgr).astype(np.uint8))
+    # LINEMOD light shader: t * ((1-b) + b * brightness * I), three brightness programs
+    lp = np.array([0.3, -0.4, -0.2])
+    li = np.array([1.3, 0.9, 1.1])
+    rl = Render_Py_Light(None, K, mesh=meshes[2], max_batch=1)
+    outs = []
+    for k, ratio in enumerate([0.4, 0.3, 0.2]):
+        bgr, depth = rl.render(R, t, lp, li, brightness_k=k, r_type="mat")
+        assert bgr.dtype == np.uint8
+        o_bgr, o_depth = raster_np.render_py_light(meshes[2], R, t, lp, li, K, r_type="mat",
+                                                   brightness_ratio=ratio)
+        _compare(o_bgr.astype(np.float32), o_depth, bgr.astype(np.float32), depth, colour_tol=1.0)
+        outs.append(bgr.astype(np.float32)[depth > 0].mean())
+    assert len(set(np.round(outs, 3))) == 3  # the three programs shade differently
+    # ... and it is NOT the ModelNet formula
+    m_bgr, _ = raster_np.render_py_light_modelnet(meshes[2], R, t, lp, li, K, r_type="mat",
+                                                  brightness_ratio=0.4)
+    bgr, depth = rl.render(R, t, lp, li, brightness_k=0, r_type="mat")
+    assert np.abs(bgr.astype(np.float32) - m_bgr.astype(np.float32))[depth > 0].max() > 2
+    # multi-class by name
+    names = ["ape", "can", "cat"]
+    rm = Render_Py_Light_MultiProgram(names, None, K, meshes=meshes, max_batch=1)
+    for i, n in enumerate(names):
+        Ri, ti = poses[i, :, :3], poses[i, :, 3]
+        bgr, depth = rm.render(Ri, ti, lp, li, n, brightness_k=1, r_type="mat")
+        o_bgr, o_depth = raster_np.render_py_light(meshes[i], Ri, ti, lp, li, K, r_type="mat",
+                                                   brightness_ratio=0.3)
+        _compare(o_bgr.astype(np.float32), o_depth, bgr.astype(np.float32), depth, colour_tol=1.0)
+    # single-model ModelNet
+    rn = Render_Py_Light_ModelNet(None, None, K, mesh=meshes[0], max_batch=1)
+    bgr, depth = rn.render(R, t, lp, li, r_type="mat")
+    o_bgr, o_depth = raster_np.render_py_light_modelnet(meshes[0], R, t, lp, li, K, r_type="mat")
+    _compare(o_bgr.astype(np.float32), o_depth, bgr.astype(np.float32), depth, colour_tol=1.0)
