@@ -431,7 +431,9 @@ def run_refine(args, rank, world, local_rank):
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
-    loop = pipeline.RefineLoop(meshes, B, dev, seed=rank)
+    # cfg 5 (BASELINE.json configs[4]): "with loss/zoom backward" -- the PM-loss backward and
+    # invZoomTrans.backward run inside every iteration; the zoom ops' backwards are constant zeros
+    loop = pipeline.RefineLoop(meshes, B, dev, seed=rank, backward=(args.config == 5))
     host = pipeline.make_refine_batch(meshes, B, shard.rank_seed(20181804 + args.config, rank),
                                       renderer=loop.renderer, occlusion=(args.config == 4))
     iters = 4
@@ -490,6 +492,7 @@ def run_refine(args, rank, world, local_rank):
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": cfg["name"], "batch_per_gpu": B, "iterations_per_loop": iters,
                        "triangles_per_mesh": len(meshes[0]["triangles"]), "meshes": len(meshes),
+                       "backward": bool(loop.step.backward),
                        "l2": "per-iteration traffic %.0f MB > 126 MB L2" % (
                            (pipeline.algorithmic_bytes_per_pair(synth.H, synth.W, synth.NUM_3D_SAMPLE)
                             + 20 * px) * B / 1e6)},

@@ -227,7 +227,8 @@ int rc_pm_loss_bwd_dev(const float *points, const float *points_obs,
  * be NULL.  `marks` (host array of cudaEvent_t, or NULL) receives up to
  * RC_STEP_MARKS event records: [0] before flow, [1] after flow, [2] after
  * zoom factor (+ fused ZoomTrans), [3] after the resampler, [4] = [3], [5] after
- * the loss; NULL entries are skipped.
+ * the loss; NULL entries are skipped.  With grad_rot/grad_trans set the step also runs the
+ * loss backward (one more launch) and, with grad_zoom_trans, the ZoomTrans backward (one more).
  */
 #define RC_STEP_MARKS 6
 typedef struct rc_compare_step_args {
@@ -264,14 +265,21 @@ typedef struct rc_compare_step_args {
   float *zoom_trans_gt;            /* [B,3] */
   float *loss_map;                 /* [B,3,N] or NULL */
   float *loss_sum;                 /* [B] */
+  /* backward leg (training; transform3d.py:120-327 + MakeLoss grad_scale, zoom_trans.py:50-76);
+   * all three NULL = forward only */
+  float *grad_rot;                 /* [B,4] d loss / d rot_est */
+  float *grad_trans;               /* [B,3] d loss / d trans_est (un-zoomed) */
+  float *grad_zoom_trans;          /* [B,3] ZoomTrans(b_inv_zoom=True).backward of grad_trans, or NULL */
   /* constants (host values) */
   float pixel_means[4];            /* per image channel, already in channel order */
   float T_means[3];
   float T_stds[3];
   float norm_term;
   float sl1_scalar;
+  float grad_scale;                /* MakeLoss grad_scale = LW_PM / NUM_3D_SAMPLE (deepIM_flownet.py:493-498) */
   int32_t rot_coord;
   int32_t loss_type;
+  int32_t zoom_grad;               /* b_zoom_grad of invZoomTrans (deepIM_flownet.py:376-383: False) */
   int32_t batch_size, height, width, num_points;
   void *stream;                    /* cudaStream_t */
   void **marks;                    /* host array of RC_STEP_MARKS cudaEvent_t, or NULL */

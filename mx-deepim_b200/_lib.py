@@ -57,7 +57,7 @@ _STEP_IN = ("image_observed", "image_rendered", "depth_gt_observed", "depth_rend
 _STEP_OUT = ("flow", "valid", "zoom_factor", "bbox", "workspace", "zoom_mask_observed",
              "zoom_mask_gt_observed", "zoom_mask_rendered", "zoom_image_observed",
              "zoom_image_rendered", "zoom_flow", "zoom_flow_weights", "zoom_trans_gt", "loss_map",
-             "loss_sum")
+             "loss_sum", "grad_rot", "grad_trans", "grad_zoom_trans")
 
 
 class rc_compare_step_args(ctypes.Structure):
@@ -68,8 +68,10 @@ class rc_compare_step_args(ctypes.Structure):
         ("T_stds", c_float * 3),
         ("norm_term", c_float),
         ("sl1_scalar", c_float),
+        ("grad_scale", c_float),
         ("rot_coord", c_int32),
         ("loss_type", c_int32),
+        ("zoom_grad", c_int32),
         ("batch_size", c_int32),
         ("height", c_int32),
         ("width", c_int32),

@@ -266,6 +266,7 @@ pm_bwd_kernel(const float *__restrict__ out_grad, const float *__restrict__ poin
               const float *__restrict__ pose_src, PoseParams pp, int loss_type,
               float norm_term, float sigma, float grad_scale, float *__restrict__ grad_rot,
               float *__restrict__ grad_trans, int N, int accumulate) {
+  pdl_launch_dependents();
   const int b = blockIdx.x / PM_CLUSTER;
   const int crank = blockIdx.x % PM_CLUSTER;
   __shared__ PoseOut po;
@@ -435,9 +436,12 @@ int rc_pm_loss_fwd_dev(const float *points, const float *points_obs, const float
   RC_REQUIRE(rc::fill_pose_params(pp, T_means, T_stds, rot_coord) == RC_OK, RC_ERR_INVALID_ARG);
   if (batch_size == 0) return rc::note_status(RC_OK);
   RC_REQUIRE(points && points_obs && weights && rotation && trans && pose_src, RC_ERR_INVALID_ARG);
-  rc::pm_fwd_kernel<<<batch_size * rc::PM_CLUSTER, rc::PM_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
-      points, points_obs, weights, rotation, trans, pose_src, pp, loss_type, norm_term,
-      sl1_scalar, est, loss_map, loss_sum, num_points, 0);
+  // rc::tl_pdl: the fused step issues the forward beside the backward (neither reads the other)
+  RC_CUDA_TRY(rc::launch_maybe_pdl(rc::pm_fwd_kernel, dim3(batch_size * rc::PM_CLUSTER),
+                                   dim3(rc::PM_THREADS), 0, static_cast<cudaStream_t>(stream),
+                                   rc::tl_pdl, points, points_obs, weights, rotation, trans,
+                                   pose_src, pp, loss_type, norm_term, sl1_scalar, est, loss_map,
+                                   loss_sum, num_points, 0));
   return rc::note_status(rc::check_launch());
 }
 

@@ -36,6 +36,8 @@ int rc_compare_step_dev(const rc_compare_step_args *a) {
   cudaStream_t s = static_cast<cudaStream_t>(a->stream);
   int st;
   const bool do_loss = N > 0 && a->loss_sum;
+  // training backward (cfg 5): d loss / d (rot_est, trans_est) with MakeLoss's grad_scale
+  const bool do_bwd = N > 0 && a->grad_rot && a->grad_trans;
   // test phase (deepIM_flownet.py:778-838): no GT flow, no loss -- flow == NULL skips both the
   // flow kernel and the flow planes of the resampler
   const bool do_flow = a->flow != nullptr && a->valid != nullptr;
@@ -46,6 +48,13 @@ int rc_compare_step_dev(const rc_compare_step_args *a) {
                               a->point_cloud_weights, a->rot_est, a->trans_est, a->src_pose,
                               a->T_means, a->T_stds, a->rot_coord, a->loss_type, a->norm_term,
                               a->sl1_scalar, nullptr, a->loss_map, a->loss_sum, B, N, a->stream);
+  };
+  auto loss_bwd = [&]() -> int {
+    return rc_pm_loss_bwd_dev(a->point_cloud_model, a->point_cloud_observed,
+                              a->point_cloud_weights, a->rot_est, a->trans_est, a->src_pose,
+                              a->T_means, a->T_stds, a->rot_coord, a->loss_type, a->norm_term,
+                              a->sl1_scalar, a->grad_scale, a->grad_rot, a->grad_trans, B, N,
+                              a->stream);
   };
   // crop boxes + zoom factor (ZoomMask, first half); ZoomTrans of the GT translation label
   // rides in the finalising block of the same kernel.
@@ -64,9 +73,15 @@ int rc_compare_step_dev(const rc_compare_step_args *a) {
     // loss (normal launch: waits for everything before it) -> bbox -> flow, the last two
     // programmatically serialised, so all three are resident together; the resampler is a
     // normal launch again and therefore waits for all of them.
-    if (do_loss && (st = loss()) != RC_OK) return st;
+    // backward first (normal launch, releases its dependents at once), then the forward loss
+    // beside it: neither reads the other's output
+    if (do_bwd && (st = loss_bwd()) != RC_OK) return st;
+    if (do_loss) {
+      PdlScope scope(do_bwd);
+      if ((st = loss()) != RC_OK) return st;
+    }
     {
-      PdlScope scope(do_loss);
+      PdlScope scope(do_loss || do_bwd);
       if ((st = bbox()) != RC_OK) return st;
     }
     if (do_flow) {
@@ -118,6 +133,13 @@ int rc_compare_step_dev(const rc_compare_step_args *a) {
   if ((st = rc::mark(a->marks, 4, s)) != RC_OK) return st;
   // Transform3D + point-matching loss (already issued when overlapped)
   if (serial && do_loss && (st = loss()) != RC_OK) return st;
+  if (serial && do_bwd && (st = loss_bwd()) != RC_OK) return st;
+  // invZoomTrans.backward (zoom_trans.py:50-76): needs this step's zoom factor
+  if (do_bwd && a->grad_zoom_trans) {
+    st = rc_zoom_trans_dev(a->zoom_factor, a->grad_trans, a->grad_zoom_trans, B, 1,
+                           a->zoom_grad ? 1 : 0, 0, a->stream);
+    if (st != RC_OK) return st;
+  }
   if ((st = rc::mark(a->marks, 5, s)) != RC_OK) return st;
   return rc::note_status(RC_OK);
 }

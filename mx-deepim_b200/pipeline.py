@@ -64,7 +64,14 @@ class CompareStep(object):
     def __init__(self, batch, device, height=synth.H, width=synth.W,
                  num_points=synth.NUM_3D_SAMPLE, K=synth.K_LINEMOD, pixel_means=synth.PIXEL_MEANS,
                  T_means=(0, 0, 0), T_stds=(1, 1, 1), rot_coord="CAMERA", loss_type="L1",
-                 norm_term=synth.NORMALIZE_3D_POINT, want_loss_map=True):
+                 norm_term=synth.NORMALIZE_3D_POINT, want_loss_map=True, backward=False,
+                 lw_pm=1.0, zoom_grad=False):
+        """backward=True adds the training backward leg to every step: d loss / d rot_est,
+        d loss / d trans_est (Transform3D.backward under MakeLoss(grad_scale=LW_PM/N),
+        transform3d.py:120-327, deepIM_flownet.py:493-498) and the gradient the network's
+        zoomed translation head receives (invZoomTrans.backward, zoom_trans.py:50-76,
+        b_zoom_grad=`zoom_grad`).  The zoom ops' own backwards are constant zeros
+        (zoom_mask.py:136-140 ...) and are not materialised."""
         self.B, self.H, self.W, self.N = batch, height, width, num_points
         self.device = torch.device(device)
         self.K = np.asarray(K, np.float32)
@@ -91,9 +98,16 @@ class CompareStep(object):
         self.zoom_trans_gt = torch.empty((B, 3), **f)
         self.loss_map = torch.empty((B, 3, N), **f) if want_loss_map else None
         self.loss_sum = torch.empty((B,), **f)
+        self.backward = bool(backward)
+        self.grad_scale = float(lw_pm) / float(max(N, 1))
+        self.zoom_grad = bool(zoom_grad)
+        self.grad_rot = torch.empty((B, 4), **f) if backward else None
+        self.grad_trans = torch.empty((B, 3), **f) if backward else None
+        self.grad_zoom_trans = torch.empty((B, 3), **f) if backward else None
         self.Kd = C.device_const(self.K, self.device)
         self.graph = None
-        self.launches_per_step = 4  # flow, bbox+zoom factor(+ZoomTrans), resampler, pm loss
+        # flow, bbox+zoom factor(+ZoomTrans), resampler, pm loss (+ loss bwd, ZoomTrans bwd)
+        self.launches_per_step = 6 if backward else 4
         self._lib = _lib.load()
 
     # ------------------------------------------------------------------ inputs
@@ -136,7 +150,8 @@ class CompareStep(object):
         if test_phase:
             a.mask_gt_observed = x["mask_observed"].data_ptr()
         skip = ("flow", "valid", "zoom_flow", "zoom_flow_weights", "zoom_trans_gt", "loss_map",
-                "loss_sum", "zoom_mask_gt_observed") if test_phase else ()
+                "loss_sum", "zoom_mask_gt_observed", "grad_rot", "grad_trans",
+                "grad_zoom_trans") if test_phase else ()
         for name, t in (("flow", self.flow), ("valid", self.valid),
                         ("zoom_factor", self.zoom_factor), ("bbox", self.bbox),
                         ("workspace", self.ws), ("zoom_mask_observed", self.zoom_mask_observed),
@@ -147,7 +162,9 @@ class CompareStep(object):
                         ("zoom_flow", self.zoom_flow),
                         ("zoom_flow_weights", self.zoom_flow_weights),
                         ("zoom_trans_gt", self.zoom_trans_gt), ("loss_map", self.loss_map),
-                        ("loss_sum", self.loss_sum)):
+                        ("loss_sum", self.loss_sum), ("grad_rot", self.grad_rot),
+                        ("grad_trans", self.grad_trans),
+                        ("grad_zoom_trans", self.grad_zoom_trans)):
             setattr(a, name, t.data_ptr() if (t is not None and name not in skip) else None)
         for i in range(3):
             a.pixel_means[i] = float(self.means[i])
@@ -155,6 +172,8 @@ class CompareStep(object):
             a.T_stds[i] = self.T_stds[i]
         a.norm_term = self.norm_term
         a.sl1_scalar = 1.0
+        a.grad_scale = self.grad_scale
+        a.zoom_grad = 1 if self.zoom_grad else 0
         a.rot_coord = self.rot_coord
         a.loss_type = self.loss_type
         a.batch_size, a.height, a.width, a.num_points = self.B, self.H, self.W, self.N
@@ -201,6 +220,8 @@ class CompareStep(object):
             "zoom_image_rendered": self.zoom_image_rendered, "zoom_flow": self.zoom_flow,
             "zoom_flow_weights": self.zoom_flow_weights, "zoom_trans_gt": self.zoom_trans_gt,
             "point_matching_loss": self.loss_map, "point_matching_loss_sum": self.loss_sum,
+            "grad_rot": self.grad_rot, "grad_trans": self.grad_trans,
+            "grad_zoom_trans": self.grad_zoom_trans,
         }
 
 
@@ -270,7 +291,8 @@ class RefineLoop(object):
     """
 
     def __init__(self, meshes, batch, device, K=synth.K_LINEMOD, pixel_means=synth.PIXEL_MEANS,
-                 num_points=synth.NUM_3D_SAMPLE, damping=0.5, predict=None, seed=0):
+                 num_points=synth.NUM_3D_SAMPLE, damping=0.5, predict=None, seed=0,
+                 backward=False, lw_pm=1.0):
         from .render import DeviceRenderer
 
         self.B = batch
@@ -279,7 +301,7 @@ class RefineLoop(object):
         self.renderer = DeviceRenderer(meshes, self.K, synth.W, synth.H, synth.ZNEAR, synth.ZFAR,
                                        max_batch=batch, device=self.device)
         self.step = CompareStep(batch, self.device, K=self.K, pixel_means=pixel_means,
-                                num_points=num_points)
+                                num_points=num_points, backward=backward, lw_pm=lw_pm)
         # the updater subtracts PIXEL_MEANS[[2,1,0]] from the RGB image (:24-25, :279-284)
         self.render_means = np.asarray(pixel_means, np.float32)[[2, 1, 0]].copy()
         f = dict(dtype=torch.float32, device=self.device)
@@ -302,7 +324,7 @@ class RefineLoop(object):
         self.cur = 0
         self.bound = [None, None]
         self.obs = None
-        self.launches_per_iteration = 1 + 1 + 4 + 4
+        self.launches_per_iteration = 1 + 1 + 4 + self.step.launches_per_step
 
     def _damped_gt(self, it, rot_gt, trans_gt):
         """Stand-in for the FlowNet heads: move `damping` of the way to the target, plus noise."""

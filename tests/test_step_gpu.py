@@ -1,0 +1,105 @@
+"""The fused compare step (rc_compare_step_dev) against the CPU oracles: forward, the training
+backward leg (cfg 5), the overlapped and the serialised issue orders, and CUDA-graph replay."""
+import numpy as np
+import pytest
+
+from oracle import flow_np, transform3d_np, zoom_np
+
+pytestmark = pytest.mark.gpu
+
+MEANS, STDS = np.zeros(3, np.float32), np.ones(3, np.float32)
+LW_PM = 0.1
+
+
+def _oracle(host, synth):
+    ref = {}
+    ref["flow"], ref["valid"] = flow_np.flow_kernel_cpu(host["depth_rendered"], host["depth_gt_observed"],
+                                                        host["KT"], host["Kinv"])
+    zm = zoom_np.zoom_mask_forward(host["mask_observed"], host["mask_gt_observed"],
+                                   host["depth_rendered"], host["src_pose"], synth.K_LINEMOD)
+    ref["zm"] = zm
+    ref["zi"] = zoom_np.zoom_image_with_factor_forward(zm[3], host["image_observed"],
+                                                       host["image_rendered"], synth.PIXEL_MEANS[::-1])
+    ref["zflow"], ref["zw"] = zoom_np.zoom_flow_forward(zm[3], ref["flow"],
+                                                        np.tile(ref["valid"], [1, 2, 1, 1]))
+    args = [host[k] for k in ("point_cloud_model", "point_cloud_observed", "point_cloud_weights",
+                              "rot_est", "trans_est", "src_pose")]
+    ref["loss_map"], _, ref["loss_sum"] = transform3d_np.pm_loss_forward(*args, MEANS, STDS)
+    gs = LW_PM / host["point_cloud_model"].shape[2]
+    ref["g_rot"], ref["g_tr"] = transform3d_np.pm_loss_backward(*args, MEANS, STDS, gs)
+    return ref
+
+
+def _check(out, ref, backward, zoom_grad=False):
+    assert np.array_equal(out["flow_weights_valid"], ref["valid"])
+    assert np.array_equal(out["flow"], ref["flow"])
+    zm = ref["zm"]
+    assert np.array_equal(out["zoom_factor"], zm[3])
+    assert np.array_equal(out["bbox"].astype(np.int64), zm[4])
+    for k, i in (("zoom_mask_observed", 0), ("zoom_mask_gt_observed", 1), ("zoom_mask_rendered", 2)):
+        assert (out[k] != zm[i]).mean() < 1e-5, k
+    assert np.abs(out["zoom_image_observed"] - ref["zi"][0]).max() <= 1e-4
+    assert np.abs(out["zoom_image_rendered"] - ref["zi"][1]).max() <= 1e-4
+    assert np.abs(out["zoom_flow"] - ref["zflow"]).max() <= 4e-4  # 1e-4 px / wx
+    assert (out["zoom_flow_weights"] != ref["zw"]).mean() < 1e-5
+    np.testing.assert_allclose(out["point_matching_loss"], ref["loss_map"], rtol=1e-4, atol=1e-4)
+    np.testing.assert_allclose(out["point_matching_loss_sum"], ref["loss_sum"], rtol=1e-4)
+    if backward:
+        np.testing.assert_allclose(out["grad_rot"], ref["g_rot"], rtol=5e-4, atol=1e-6)
+        np.testing.assert_allclose(out["grad_trans"], ref["g_tr"], rtol=5e-4, atol=1e-6)
+        # invZoomTrans.backward (zoom_trans.py:50-76): identity unless b_zoom_grad, then x,y * wx
+        g = out["grad_trans"].copy()
+        if zoom_grad:
+            g[:, 0] *= zm[3][:, 0]
+            g[:, 1] *= zm[3][:, 0]
+        assert np.array_equal(out["grad_zoom_trans"], g)
+    else:
+        assert out["grad_rot"] is None
+
+
+@pytest.mark.parametrize("backward,zoom_grad,serial", [(False, False, False), (True, False, False),
+                                                       (True, True, True)])
+def test_compare_step_matches_oracles(cuda_device, backward, zoom_grad, serial):
+    import torch
+
+    from mx_deepim_b200 import _lib, pipeline, synth
+
+    B = 3
+    host = synth.make_compare_batch(B, seed=77, occlusion=True)
+    step = pipeline.CompareStep(B, cuda_device, backward=backward, lw_pm=LW_PM, zoom_grad=zoom_grad)
+    x = step.to_device(host, non_blocking=False)
+    marks = [_lib.Event() for _ in range(_lib.RC_STEP_MARKS)] if serial else None
+    step.run(x, marks=marks)
+    torch.cuda.synchronize()
+    out = {k: (v.cpu().numpy() if v is not None else None) for k, v in step.outputs().items()}
+    _check(out, _oracle(host, synth), backward, zoom_grad)
+    if serial:
+        assert marks[0].elapsed_ms(marks[5]) > 0.0
+
+
+def test_compare_step_graph_replay_is_deterministic(cuda_device):
+    """Captured into a CUDA graph, the step replays bit-identically (no atomics on floats, the
+    bbox workspace cleans itself) and still matches the oracle after 5 replays."""
+    import torch
+
+    from mx_deepim_b200 import pipeline, synth
+
+    B = 2
+    host = synth.make_compare_batch(B, seed=78)
+    step = pipeline.CompareStep(B, cuda_device, backward=True, lw_pm=LW_PM)
+    x = step.to_device(host, non_blocking=False)
+    s = torch.cuda.Stream(device=cuda_device)
+    with torch.cuda.stream(s):
+        g = step.capture(x)
+        first = None
+        for _ in range(5):
+            g.replay()
+            s.synchronize()
+            cur = {k: v.clone() for k, v in step.outputs().items() if v is not None}
+            if first is None:
+                first = cur
+            else:
+                for k in cur:
+                    assert torch.equal(cur[k], first[k]), k
+    out = {k: (v.cpu().numpy() if v is not None else None) for k, v in step.outputs().items()}
+    _check(out, _oracle(host, synth), True)
