@@ -13,12 +13,14 @@
 //               warp-aggregated atomics (__match_any_sync on the tile id).
 //   2. scan   : exclusive scan of the per-tile counts (one block per pair).
 //   3. fill   : tile lists (record indices), again warp-aggregated.
-//   4. raster : one CTA per (tile, pair); threads take triangles of the tile's list and
-//               atomicMin a packed (bits(window depth) << 32 | record) key into a shared-memory
-//               z-buffer; after one barrier every thread resolves four adjacent pixels
-//               (perspective-correct attributes by ray/triangle intersection, nearest texel,
-//               optional Lambert term) and writes depth, CHW RGB - mean, HWC BGR, mask with
-//               128-bit stores.  Background tiles skip straight to the stores.
+//   4. raster : ONE persistent launch writes the whole frame once.  CTAs draw work units from a
+//               ticket counter: non-empty (tile, pair) items first, then the empty tiles in
+//               chunks (streaming background stores overlap the rasterising CTAs).  Per
+//               non-empty tile: threads take triangles of the tile's list and atomicMin a
+//               packed (bits(window depth) << 32 | record) key into a shared-memory z-buffer;
+//               then one pixel per thread resolves (perspective-correct attributes, nearest
+//               texel, optional Lambert term) into shared-memory planes, and depth, CHW RGB -
+//               mean, HWC BGR, mask leave with 128-bit stores.
 // The frame is written exactly once (20 B/px), the mesh is read once per pair.
 //
 // Compiled with -fmad=false: the float64 geometry must round exactly like the C oracle.
@@ -31,9 +33,14 @@
 
 namespace rc {
 
-constexpr int RT_TILE = 32;          // tile edge in pixels
+constexpr int RT_TW = 16;            // tile width  in pixels (multiple of 4, power of two)
+constexpr int RT_TH = 16;            // tile height in pixels
+constexpr int RT_PIX = RT_TW * RT_TH;
+constexpr int RT_TW_SHIFT = 4;       // log2(RT_TW)
 constexpr int RT_THREADS = 256;
 constexpr int RT_SUB = 8;            // sub-pixel bits (GL-style 1/256 px snapping)
+static_assert((1 << RT_TW_SHIFT) == RT_TW && RT_TW % 4 == 0, "tile width");
+static_assert(RT_THREADS % (RT_PIX / 4) == 0, "whole tiles per background pass");
 
 struct __align__(16) TriRec {  // 64 bytes = four 128-bit loads
   int x0, y0, x1, y1;    // fixed-point vertices, oriented so that the area is positive
@@ -53,11 +60,24 @@ struct Renderer {
   int64_t *tex_off;
   int32_t *tex_hw;                           // [M,2]
   TriRec *recs;                              // [max_batch][2*max_tris]
+  int2 *bbox;                                // [max_batch][2*max_tris] (bb_min, bb_max); bb_max < 0 = unused slot
+  int32_t *clip_list;                        // [max_batch * max_tris] b * max_tris + t of near-plane straddlers
   int32_t *tile_count, *tile_start, *tile_fill;  // [max_batch][n_tiles (+1)]
   int32_t *tile_list;                        // [max_batch][list_cap]
-  int32_t *work_count;                       // [1] number of non-empty (tile, pair) items
-  int32_t *work_list;                        // [max_batch * n_tiles] b * n_tiles + tile
+  int32_t *work_count;                       // [RT_WC_INTS] header (see RT_WC_*), then tile_count
+  int32_t *work_list;                        // [max_batch * n_tiles] b * n_tiles + tile: non-empty from the front, empty from the back
 };
+
+// work_count header
+constexpr int RT_WC_HEAVY = 0;     // non-empty (tile, pair) items (scan)
+constexpr int RT_WC_EMPTY = 1;     // empty items (scan)
+constexpr int RT_WC_CLIP = 3;      // clip-list length (setup)
+constexpr int RT_WC_TICKET_H = 4;  // next non-empty item (raster)
+constexpr int RT_WC_TICKET_L = 5;  // next background chunk (raster)
+constexpr int RT_WC_INTS = 8;
+
+// work item: pair << 16 | tile row << 8 | tile column
+__device__ __forceinline__ int pack_work(int b, int ty, int tx) { return (b << 16) | (ty << 8) | tx; }
 
 struct Cam {
   double fx, fy, cx, cy, znear, zfar;
@@ -72,57 +92,94 @@ __device__ __forceinline__ int tie_bias(long long dx, long long dy) {
   return (dy > 0 || (dy == 0 && dx < 0)) ? 0 : -1;
 }
 
-// Emit one screen-space triangle (camera-space vertices P[3]) into `rec`; returns false if culled.
 constexpr int RT_FLAG_SWAPPED = 1 << 30;  // record vertices are (0, 2, 1) of the source triangle
 constexpr int RT_FLAG_CLIPPED = 1 << 29;  // record is a near-clipped piece (vertices are not mesh vertices)
 constexpr int RT_TRI_MASK = (1 << 29) - 1;
 
-__device__ bool make_record(const double (*P)[3], const Cam &cam, int W, int H, int tri, bool clipped,
-                            TriRec &r) {
-  long long X[3], Y[3];
-  double zw[3];
+struct RecQ {  // a TriRec as the four 128-bit words it is stored and loaded as
+  int4 q0, q1, q2, q3;
+  int bb_min, bb_max;  // bb_max < 0: nothing to draw
+};
+
+// Screen-space record of one triangle given by camera-space vertices (x,y,z) x 3 (all with
+// z >= znear).  Culls (bb_max = -1) what cannot produce a fragment: behind the camera,
+// degenerate, off-screen, or -- for boxes of at most 3x3 pixels -- no pixel centre inside under
+// the very rule the raster kernel applies (integer edge functions + top-left tie bias).
+// Everything stays in registers: no dynamically indexed arrays.
+__device__ __forceinline__ void make_record(double ax_, double ay_, double az_, double bx_,
+                                            double by_, double bz_, double cx_, double cy_,
+                                            double cz_, const Cam &cam, int W, int H, int tri,
+                                            bool clipped, RecQ &r) {
+  r.bb_max = -1;
+  r.bb_min = 0;
+  if (!(az_ > 0.0) || !(bz_ > 0.0) || !(cz_ > 0.0)) return;
   // window depth of a camera-space z: ndc.z = (f+n)/(f-n) - 2fn/((f-n) z), d = (ndc.z + 1)/2
   const double pa = (cam.zfar + cam.znear) / (cam.zfar - cam.znear);
   const double pb = (2.0 * cam.zfar * cam.znear) / (cam.zfar - cam.znear);
-#pragma unroll
-  for (int i = 0; i < 3; ++i) {
-    const double z = P[i][2];
-    if (!(z > 0.0)) return false;
-    const double u = cam.fx * P[i][0] / z + cam.cx;
-    const double v = cam.fy * P[i][1] / z + cam.cy;
-    if (!(fabs(u) < 1e6 && fabs(v) < 1e6)) return false;
-    X[i] = (long long)rint(u * 256.0);
-    Y[i] = (long long)rint(v * 256.0);
-    zw[i] = ((pa * z - pb) / z + 1.0) * 0.5;
+  // one reciprocal per vertex (the perspective divide as hardware does it); FP64 runs at half
+  // rate on sm_100 and a division is ~30 instructions, so they are counted
+  const double ia = 1.0 / az_, ib = 1.0 / bz_, ic = 1.0 / cz_;
+  const double u0 = cam.fx * ax_ * ia + cam.cx, v0 = cam.fy * ay_ * ia + cam.cy;
+  const double u1 = cam.fx * bx_ * ib + cam.cx, v1 = cam.fy * by_ * ib + cam.cy;
+  const double u2 = cam.fx * cx_ * ic + cam.cx, v2 = cam.fy * cy_ * ic + cam.cy;
+  if (!(fabs(u0) < 1e6 && fabs(v0) < 1e6 && fabs(u1) < 1e6 && fabs(v1) < 1e6 && fabs(u2) < 1e6 &&
+        fabs(v2) < 1e6))
+    return;
+  const long long X0 = (long long)rint(u0 * 256.0), Y0 = (long long)rint(v0 * 256.0);
+  long long X1 = (long long)rint(u1 * 256.0), Y1 = (long long)rint(v1 * 256.0);
+  long long X2 = (long long)rint(u2 * 256.0), Y2 = (long long)rint(v2 * 256.0);
+  const double zw0 = ((pa - pb * ia) + 1.0) * 0.5;
+  double zw1 = ((pa - pb * ib) + 1.0) * 0.5;
+  double zw2 = ((pa - pb * ic) + 1.0) * 0.5;
+  const long long area = edge_fn(X0, Y0, X1, Y1, X2, Y2);
+  if (area == 0) return;
+  const bool sw = area < 0;
+  if (sw) {  // orient so that the area is positive: record vertices (0, 2, 1)
+    long long t = X1; X1 = X2; X2 = t;
+    t = Y1; Y1 = Y2; Y2 = t;
+    const double z = zw1; zw1 = zw2; zw2 = z;
   }
-  long long area = edge_fn(X[0], Y[0], X[1], Y[1], X[2], Y[2]);
-  if (area == 0) return false;
-  int ib = 1, ic = 2;
-  if (area < 0) {
-    ib = 2;
-    ic = 1;
-    area = -area;
-  }
-  const long long minx = min(X[0], min(X[1], X[2])), maxx = max(X[0], max(X[1], X[2]));
-  const long long miny = min(Y[0], min(Y[1], Y[2])), maxy = max(Y[0], max(Y[1], Y[2]));
+  const long long minx = min(X0, min(X1, X2)), maxx = max(X0, max(X1, X2));
+  const long long miny = min(Y0, min(Y1, Y2)), maxy = max(Y0, max(Y1, Y2));
   long long px0 = (minx + 255) >> RT_SUB, px1 = maxx >> RT_SUB;
   long long py0 = (miny + 255) >> RT_SUB, py1 = maxy >> RT_SUB;
   if (px0 < 0) px0 = 0;
   if (py0 < 0) py0 = 0;
   if (px1 > W - 1) px1 = W - 1;
   if (py1 > H - 1) py1 = H - 1;
-  if (px0 > px1 || py0 > py1) return false;
-  r.x0 = (int)X[0]; r.y0 = (int)Y[0];
-  r.x1 = (int)X[ib]; r.y1 = (int)Y[ib];
-  r.x2 = (int)X[ic]; r.y2 = (int)Y[ic];
-  r.zw0 = zw[0];
-  r.zw1 = zw[ib];
-  r.zw2 = zw[ic];
-  r.pad_ = 0;
-  r.tri = tri | (ib == 2 ? RT_FLAG_SWAPPED : 0) | (clipped ? RT_FLAG_CLIPPED : 0);
+  if (px0 > px1 || py0 > py1) return;
+  if (px1 - px0 <= 2 && py1 - py0 <= 2) {
+    // micro-triangle: test the (at most nine) pixel centres now; most sub-pixel triangles of a
+    // dense mesh contain none and never reach the tile lists
+    const int bias0 = tie_bias(X2 - X1, Y2 - Y1), bias1 = tie_bias(X0 - X2, Y0 - Y2),
+              bias2 = tie_bias(X1 - X0, Y1 - Y0);
+    bool any = false;
+    for (long long y = py0; y <= py1; ++y)
+      for (long long x = px0; x <= px1; ++x) {
+        const long long px = x << RT_SUB, py = y << RT_SUB;
+        const long long w0 = edge_fn(X1, Y1, X2, Y2, px, py);
+        const long long w1 = edge_fn(X2, Y2, X0, Y0, px, py);
+        const long long w2 = edge_fn(X0, Y0, X1, Y1, px, py);
+        any = any || (((w0 + bias0) | (w1 + bias1) | (w2 + bias2)) >= 0);
+      }
+    if (!any) return;
+  }
   r.bb_min = (int)((py0 << 16) | px0);
   r.bb_max = (int)((py1 << 16) | px1);
-  return true;
+  r.q0 = make_int4((int)X0, (int)Y0, (int)X1, (int)Y1);
+  r.q1 = make_int4((int)X2, (int)Y2,
+                   tri | (sw ? RT_FLAG_SWAPPED : 0) | (clipped ? RT_FLAG_CLIPPED : 0), r.bb_min);
+  r.q2 = make_int4(r.bb_max, 0, __double2loint(zw0), __double2hiint(zw0));
+  r.q3 = make_int4(__double2loint(zw1), __double2hiint(zw1), __double2loint(zw2),
+                   __double2hiint(zw2));
+}
+
+__device__ __forceinline__ void store_record(TriRec *dst, const RecQ &r) {
+  int4 *p = reinterpret_cast<int4 *>(dst);
+  p[0] = r.q0;
+  p[1] = r.q1;
+  p[2] = r.q2;
+  p[3] = r.q3;
 }
 
 // Warp-aggregated tile counting / slot allocation.  Every lane of the warp calls this the same
@@ -144,10 +201,83 @@ __device__ __forceinline__ int tile_atomic(int32_t *counters, int key, bool want
   return slot;
 }
 
+// The tiles a pixel bbox overlaps, visited in lock step by the whole warp.
+template <typename F>
+__device__ __forceinline__ void for_each_tile(int bb_min, int bb_max, int tiles_x, F &&f) {
+  int tx0 = 0, tx1 = -1, ty0 = 0, ty1 = -1;
+  if (bb_max >= 0) {
+    tx0 = (bb_min & 0xffff) / RT_TW;
+    ty0 = (bb_min >> 16) / RT_TH;
+    tx1 = (bb_max & 0xffff) / RT_TW;
+    ty1 = (bb_max >> 16) / RT_TH;
+  }
+  const int nx = tx1 - tx0 + 1, n_mine = (bb_max >= 0) ? nx * (ty1 - ty0 + 1) : 0;
+  const int n_max = __reduce_max_sync(0xffffffffu, n_mine);
+  for (int i = 0; i < n_max; ++i) {
+    int key = -1;
+    if (i < n_mine) key = (ty0 + i / nx) * tiles_x + tx0 + i % nx;
+    f(key);
+  }
+}
+
 // ------------------------------------------------------------------ 1. setup
+// Near-plane clipping (Sutherland-Hodgman against z >= znear, GL primitive clipping) of a
+// triangle that straddles the plane: rare, kept out of line so that its dynamically indexed
+// arrays do not cost the common path a stack frame.
+__device__ __forceinline__ int4 clip_and_emit(const double *Pc /* [3][3] */, const Cam &cam, int W,
+                                           int H, int t, TriRec *slots /* 2t, 2t+1 */) {
+  double Q[4][3];
+  int nq = 0;
+  bool clipped_any = false;
+  for (int i = 0; i < 3; ++i) {
+    const int j = (i + 1) % 3;
+    const double *Pi = Pc + 3 * i, *Pj = Pc + 3 * j;
+    const double da = Pi[2] - cam.znear, db = Pj[2] - cam.znear;
+    if (da >= 0.0) {
+      Q[nq][0] = Pi[0]; Q[nq][1] = Pi[1]; Q[nq][2] = Pi[2];
+      ++nq;
+    }
+    if ((da >= 0.0) != (db >= 0.0)) {
+      clipped_any = true;
+      const double *in = da >= 0.0 ? Pi : Pj;
+      const double *out = da >= 0.0 ? Pj : Pi;
+      const double din = da >= 0.0 ? da : db, dout = da >= 0.0 ? db : da;
+      const double s = din / (din - dout);
+      Q[nq][0] = in[0] + s * (out[0] - in[0]);
+      Q[nq][1] = in[1] + s * (out[1] - in[1]);
+      Q[nq][2] = cam.znear;
+      ++nq;
+    }
+  }
+  // live records occupy the slots in order (slot 2t first)
+  int4 bb = make_int4(0, -1, 0, -1);
+  int n_rec = 0;
+  for (int k = 0; k < 2; ++k) {
+    if (k == 0 ? nq < 3 : nq != 4) continue;
+    const int i1 = k == 0 ? 1 : 2, i2 = k == 0 ? 2 : 3;
+    RecQ r;
+    make_record(Q[0][0], Q[0][1], Q[0][2], Q[i1][0], Q[i1][1], Q[i1][2], Q[i2][0], Q[i2][1],
+                Q[i2][2], cam, W, H, t, k == 1 || nq == 4 || clipped_any, r);
+    if (r.bb_max < 0) continue;
+    store_record(slots + n_rec, r);
+    if (n_rec == 0) {
+      bb.x = r.bb_min;
+      bb.y = r.bb_max;
+    } else {
+      bb.z = r.bb_min;
+      bb.w = r.bb_max;
+    }
+    ++n_rec;
+  }
+  return bb;
+}
+
 // grid = (ceil(max_tris / 256), B); block = 256 (whole warps always run to the end: the tile
-// loop uses full-mask warp primitives).
-__global__ void __launch_bounds__(256)
+// loop uses full-mask warp primitives).  One thread per (triangle, pair): pose transform in
+// float64, projection, snapping, culling; the 64-byte record leaves as four 128-bit stores, its
+// pixel box additionally as one int2 (what the fill pass re-reads), and the 16x16 tiles it
+// overlaps are counted with warp-aggregated atomics.
+__global__ void __launch_bounds__(256, 3)
 raster_setup_kernel(Renderer R, const int32_t *__restrict__ cls_idx,
                     const float *__restrict__ poses, Cam cam, int n_tiles) {
   const int b = blockIdx.y;
@@ -156,156 +286,172 @@ raster_setup_kernel(Renderer R, const int32_t *__restrict__ cls_idx,
   const int t_off = __ldg(R.mesh_tri_off + mesh);
   const int n_tri = __ldg(R.mesh_tri_off + mesh + 1) - t_off;
   TriRec *recs = R.recs + (size_t)b * 2 * R.max_tris;
+  int2 *bbox = R.bbox + (size_t)b * 2 * R.max_tris;
   int32_t *count = R.tile_count + (size_t)b * n_tiles;
 
-  TriRec rec[2];
-  int n_rec = 0;
+  int4 bb = make_int4(0, -1, 0, -1);  // (bb_min, bb_max) of slots 2t and 2t+1; bb_max < 0 = unused
   if (t < n_tri) {
     const float *pose = poses + b * 12;
-    double Pc[3][3];
+    const int vidx[3] = {__ldg(R.tris + (size_t)(t_off + t) * 3 + 0),
+                         __ldg(R.tris + (size_t)(t_off + t) * 3 + 1),
+                         __ldg(R.tris + (size_t)(t_off + t) * 3 + 2)};
+    double Pc[9];
 #pragma unroll
     for (int i = 0; i < 3; ++i) {
-      const int vi = __ldg(R.tris + (size_t)(t_off + t) * 3 + i);
+      const double x = (double)__ldg(R.verts + (size_t)vidx[i] * 3 + 0);
+      const double y = (double)__ldg(R.verts + (size_t)vidx[i] * 3 + 1);
+      const double z = (double)__ldg(R.verts + (size_t)vidx[i] * 3 + 2);
+#pragma unroll
+      for (int r = 0; r < 3; ++r)
+        Pc[i * 3 + r] = (double)__ldg(pose + r * 4 + 0) * x + (double)__ldg(pose + r * 4 + 1) * y +
+                        (double)__ldg(pose + r * 4 + 2) * z + (double)__ldg(pose + r * 4 + 3);
+    }
+    const bool in0 = Pc[2] - cam.znear >= 0.0, in1 = Pc[5] - cam.znear >= 0.0,
+               in2 = Pc[8] - cam.znear >= 0.0;
+    if (in0 && in1 && in2) {
+      RecQ r;
+      make_record(Pc[0], Pc[1], Pc[2], Pc[3], Pc[4], Pc[5], Pc[6], Pc[7], Pc[8], cam, R.W, R.H, t,
+                  false, r);
+      if (r.bb_max >= 0) {
+        store_record(recs + 2 * t, r);
+        bb.x = r.bb_min;
+        bb.y = r.bb_max;
+      }
+    } else if (in0 || in1 || in2) {
+      // straddles the near plane (rare): left to raster_clip_kernel, which needs dynamically
+      // indexed polygons and would cost this kernel its registers
+      const int slot = atomicAdd(R.work_count + RT_WC_CLIP, 1);
+      R.clip_list[slot] = b * R.max_tris + t;
+    }
+  }
+  // fixed slots 2t, 2t+1: deterministic layout; the compact boxes are what the fill pass reads
+  if (t < R.max_tris) *reinterpret_cast<int4 *>(bbox + 2 * t) = bb;
+  // count the tiles each record overlaps (warp-aggregated)
+  for_each_tile(bb.x, bb.y, R.tiles_x, [&](int key) { tile_atomic(count, key, false); });
+  if (__any_sync(0xffffffffu, bb.w >= 0))
+    for_each_tile(bb.z, bb.w, R.tiles_x, [&](int key) { tile_atomic(count, key, false); });
+}
+
+// grid-stride over the triangles raster_setup_kernel found straddling the near plane (usually
+// none): clip, emit up to two records into the triangle's slots, count their tiles.
+__global__ void __launch_bounds__(128)
+raster_clip_kernel(Renderer R, const int32_t *__restrict__ cls_idx,
+                   const float *__restrict__ poses, Cam cam, int n_tiles) {
+  const int n = R.work_count[RT_WC_CLIP];
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+    const int item = R.clip_list[i];
+    const int b = item / R.max_tris, t = item - b * R.max_tris;
+    const int t_off = __ldg(R.mesh_tri_off + __ldg(cls_idx + b));
+    const float *pose = poses + b * 12;
+    double Pc[9];
+    for (int k = 0; k < 3; ++k) {
+      const int vi = __ldg(R.tris + (size_t)(t_off + t) * 3 + k);
       const double x = (double)__ldg(R.verts + (size_t)vi * 3 + 0);
       const double y = (double)__ldg(R.verts + (size_t)vi * 3 + 1);
       const double z = (double)__ldg(R.verts + (size_t)vi * 3 + 2);
-#pragma unroll
       for (int r = 0; r < 3; ++r)
-        Pc[i][r] = (double)pose[r * 4 + 0] * x + (double)pose[r * 4 + 1] * y +
-                   (double)pose[r * 4 + 2] * z + (double)pose[r * 4 + 3];
+        Pc[k * 3 + r] = (double)__ldg(pose + r * 4 + 0) * x + (double)__ldg(pose + r * 4 + 1) * y +
+                        (double)__ldg(pose + r * 4 + 2) * z + (double)__ldg(pose + r * 4 + 3);
     }
-    // near-plane clipping (Sutherland-Hodgman against z >= znear), GL primitive clipping
-    double Q[4][3];
-    int nq = 0;
-    bool clipped_any = false;
-#pragma unroll
-    for (int i = 0; i < 3; ++i) {
-      const int j = (i + 1) % 3;
-      const double da = Pc[i][2] - cam.znear, db = Pc[j][2] - cam.znear;
-      if (da >= 0.0) {
-        Q[nq][0] = Pc[i][0]; Q[nq][1] = Pc[i][1]; Q[nq][2] = Pc[i][2];
-        ++nq;
-      }
-      if ((da >= 0.0) != (db >= 0.0)) {
-        clipped_any = true;
-        const double *in = da >= 0.0 ? Pc[i] : Pc[j];
-        const double *out = da >= 0.0 ? Pc[j] : Pc[i];
-        const double din = da >= 0.0 ? da : db, dout = da >= 0.0 ? db : da;
-        const double s = din / (din - dout);
-        Q[nq][0] = in[0] + s * (out[0] - in[0]);
-        Q[nq][1] = in[1] + s * (out[1] - in[1]);
-        Q[nq][2] = cam.znear;
-        ++nq;
-      }
-    }
-    if (nq >= 3) {
-      const double T0[3][3] = {{Q[0][0], Q[0][1], Q[0][2]}, {Q[1][0], Q[1][1], Q[1][2]},
-                               {Q[2][0], Q[2][1], Q[2][2]}};
-      if (make_record(T0, cam, R.W, R.H, t, nq == 4 || clipped_any, rec[n_rec])) ++n_rec;
-    }
-    if (nq == 4) {
-      const double T1[3][3] = {{Q[0][0], Q[0][1], Q[0][2]}, {Q[2][0], Q[2][1], Q[2][2]},
-                               {Q[3][0], Q[3][1], Q[3][2]}};
-      if (make_record(T1, cam, R.W, R.H, t, true, rec[n_rec])) ++n_rec;
-    }
-  }
-  // fixed slots 2t, 2t+1: deterministic layout; an unused slot is marked by bb_max < 0
-  if (t < R.max_tris) {
+    const int4 bb = clip_and_emit(Pc, cam, R.W, R.H, t, R.recs + (size_t)b * 2 * R.max_tris + 2 * t);
+    *reinterpret_cast<int4 *>(R.bbox + (size_t)b * 2 * R.max_tris + 2 * t) = bb;
+    int32_t *count = R.tile_count + (size_t)b * n_tiles;
     for (int k = 0; k < 2; ++k) {
-      if (k < n_rec) recs[2 * t + k] = rec[k];
-      else recs[2 * t + k].bb_max = -1;
-    }
-  }
-  // count the tiles each record overlaps (warp-aggregated)
-  for (int k = 0; k < 2; ++k) {
-    int tx0 = 0, tx1 = -1, ty0 = 0, ty1 = -1;
-    if (k < n_rec) {
-      tx0 = (rec[k].bb_min & 0xffff) / RT_TILE;
-      ty0 = (rec[k].bb_min >> 16) / RT_TILE;
-      tx1 = (rec[k].bb_max & 0xffff) / RT_TILE;
-      ty1 = (rec[k].bb_max >> 16) / RT_TILE;
-    }
-    const int nx = tx1 - tx0 + 1, n_mine = (k < n_rec) ? nx * (ty1 - ty0 + 1) : 0;
-    const int n_max = __reduce_max_sync(0xffffffffu, n_mine);
-    for (int i = 0; i < n_max; ++i) {
-      int key = -1;
-      if (i < n_mine) key = (ty0 + i / nx) * R.tiles_x + tx0 + i % nx;
-      tile_atomic(count, key, false);
+      const int lo = k ? bb.z : bb.x, hi = k ? bb.w : bb.y;
+      if (hi < 0) continue;
+      for (int ty = (lo >> 16) / RT_TH; ty <= (hi >> 16) / RT_TH; ++ty)
+        for (int tx = (lo & 0xffff) / RT_TW; tx <= (hi & 0xffff) / RT_TW; ++tx)
+          atomicAdd(count + ty * R.tiles_x + tx, 1);
     }
   }
 }
 
 // ------------------------------------------------------------------- 2. scan
-// grid = B; block = 256.  Exclusive scan of tile_count -> tile_start, clears tile_fill.
+__device__ __forceinline__ int block_excl_scan(int v, int *smem /* [8] */, int &total) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int inc = v;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int n = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += n;
+  }
+  __syncthreads();  // smem free (a previous scan's readers are done)
+  if (lane == 31) smem[warp] = inc;
+  __syncthreads();
+  int base = 0, tot = 0;
+#pragma unroll
+  for (int w = 0; w < 8; ++w) {
+    const int s = smem[w];
+    if (w < warp) base += s;
+    tot += s;
+  }
+  total = tot;
+  return base + inc - v;
+}
+
+// grid = B; block = 256.  Exclusive scan of tile_count -> tile_start, clears tile_fill, and
+// appends the pair's tiles to the work list: non-empty ones from the front, empty ones from the
+// back (two atomics per pair; the order inside a pair is the tile order).
 __global__ void __launch_bounds__(256)
 raster_scan_kernel(Renderer R, int n_tiles, int32_t *__restrict__ status) {
   const int b = blockIdx.x;
+  const int n_total = gridDim.x * n_tiles;
   const int32_t *count = R.tile_count + (size_t)b * n_tiles;
   int32_t *start = R.tile_start + (size_t)b * (n_tiles + 1);
   int32_t *fill = R.tile_fill + (size_t)b * n_tiles;
-  __shared__ int part[256];
+  __shared__ int part[8];
+  __shared__ int s_base[2];
   const int per = (n_tiles + 255) / 256;
-  const int lo = threadIdx.x * per, hi = min(lo + per, n_tiles);
-  int s = 0;
-  for (int i = lo; i < hi; ++i) s += count[i];
-  part[threadIdx.x] = s;
-  __syncthreads();
+  const int lo = min((int)threadIdx.x * per, n_tiles), hi = min(lo + per, n_tiles);
+  int s = 0, ne = 0;
+  for (int i = lo; i < hi; ++i) {
+    const int c = count[i];
+    s += c;
+    ne += c > 0;
+  }
+  int total, total_ne;
+  int acc = block_excl_scan(s, part, total);
+  int ne_off = block_excl_scan(ne, part, total_ne);
   if (threadIdx.x == 0) {
-    int acc = 0;
-    for (int i = 0; i < 256; ++i) {
-      const int v = part[i];
-      part[i] = acc;
-      acc += v;
-    }
-    start[n_tiles] = acc;
-    if (acc > R.list_cap && status) atomicExch(status, 1);
+    start[n_tiles] = total;
+    if (total > R.list_cap && status) atomicExch(status, 1);
+    s_base[0] = atomicAdd(R.work_count + RT_WC_HEAVY, total_ne);
+    s_base[1] = atomicAdd(R.work_count + RT_WC_EMPTY, n_tiles - total_ne);
   }
   __syncthreads();
-  int acc = part[threadIdx.x];
+  int front = s_base[0] + ne_off;
+  int back = n_total - 1 - (s_base[1] + (lo - ne_off));
   for (int i = lo; i < hi; ++i) {
     start[i] = acc;
     const int c = count[i];
     acc += c;
     fill[i] = 0;
-    if (c > 0) R.work_list[atomicAdd(R.work_count, 1)] = b * n_tiles + i;  // non-empty tiles only
+    const int work = pack_work(b, i / R.tiles_x, i % R.tiles_x);
+    if (c > 0) R.work_list[front++] = work;
+    else R.work_list[back--] = work;
   }
 }
 
 // ------------------------------------------------------------------- 3. fill
-// grid = (ceil(2 * max_tris / 256), B); one thread per record slot.
+// grid = (ceil(2 * max_tris / 256), B); one thread per record slot; reads the compact boxes.
 __global__ void __launch_bounds__(256)
 raster_fill_kernel(Renderer R, const int32_t *__restrict__ cls_idx, int n_tiles) {
   const int b = blockIdx.y;
   const int s = blockIdx.x * blockDim.x + threadIdx.x;
   const int mesh = __ldg(cls_idx + b);
   const int n_tri = __ldg(R.mesh_tri_off + mesh + 1) - __ldg(R.mesh_tri_off + mesh);
-  const TriRec *recs = R.recs + (size_t)b * 2 * R.max_tris;
   const int32_t *start = R.tile_start + (size_t)b * (n_tiles + 1);
   int32_t *fill = R.tile_fill + (size_t)b * n_tiles;
   int32_t *list = R.tile_list + (size_t)b * R.list_cap;
-  int tx0 = 0, tx1 = -1, ty0 = 0, ty1 = -1;
-  bool live = false;
-  if (s < 2 * n_tri) {
-    const int bb_min = recs[s].bb_min, bb_max = recs[s].bb_max;
-    if (bb_max >= 0) {
-      live = true;
-      tx0 = (bb_min & 0xffff) / RT_TILE;
-      ty0 = (bb_min >> 16) / RT_TILE;
-      tx1 = (bb_max & 0xffff) / RT_TILE;
-      ty1 = (bb_max >> 16) / RT_TILE;
-    }
-  }
-  const int nx = tx1 - tx0 + 1, n_mine = live ? nx * (ty1 - ty0 + 1) : 0;
-  const int n_max = __reduce_max_sync(0xffffffffu, n_mine);
-  for (int i = 0; i < n_max; ++i) {
-    int key = -1;
-    if (i < n_mine) key = (ty0 + i / nx) * R.tiles_x + tx0 + i % nx;
+  int2 bb = make_int2(0, -1);
+  if (s < 2 * n_tri) bb = __ldg(R.bbox + (size_t)b * 2 * R.max_tris + s);
+  for_each_tile(bb.x, bb.y, R.tiles_x, [&](int key) {
     const int slot = tile_atomic(fill, key, true);
     if (key >= 0) {
       const int pos = start[key] + slot;
       if (pos < R.list_cap) list[pos] = s;
     }
-  }
+  });
 }
 
 // ----------------------------------------------------------------- 4. raster
@@ -353,14 +499,14 @@ __device__ Shaded shade_pixel(const Renderer &R, const RasterOut &O, const Cam &
     const long long w0 = edge_fn(rec.x1, rec.y1, rec.x2, rec.y2, px, py);
     const long long w1 = edge_fn(rec.x2, rec.y2, rec.x0, rec.y0, px, py);
     const long long w2 = edge_fn(rec.x0, rec.y0, rec.x1, rec.y1, px, py);
-    const double area = (double)(w0 + w1 + w2);
     const bool sw = (rec.tri & RT_FLAG_SWAPPED) != 0;
-    const int ib = sw ? 2 : 1, ic = sw ? 1 : 2;
-    const double q0 = ((double)w0 / area) * (1.0 / Pc[0][2]);
-    const double qb = ((double)w1 / area) * (1.0 / Pc[ib][2]);
-    const double qc = ((double)w2 / area) * (1.0 / Pc[ic][2]);
-    const double qs = q0 + qb + qc;
-    const double lb = qb / qs, lc = qc / qs;
+    const double zb = sw ? Pc[2][2] : Pc[1][2], zc = sw ? Pc[1][2] : Pc[2][2];
+    // q_i = l_i / z_i up to the common factor 1 / area, which cancels in q_i / sum(q)
+    const double q0 = (double)w0 * (1.0 / Pc[0][2]);
+    const double qb = (double)w1 * (1.0 / zb);
+    const double qc = (double)w2 * (1.0 / zc);
+    const double iqs = 1.0 / (q0 + qb + qc);
+    const double lb = qb * iqs, lc = qc * iqs;
     b1 = sw ? lc : lb;
     b2 = sw ? lb : lc;
   } else {
@@ -437,70 +583,158 @@ __device__ Shaded shade_pixel(const Renderer &R, const RasterOut &O, const Cam &
   return s;
 }
 
-// ------------------------------------------------------------------ 4a. clear
-// Streams the background of every output: depth 0, mask 0, image = 0 - mean, bgr 0, tri -1.
-// Plain 128-bit stores, grid-stride; ~20 B/px at HBM write speed.
-__global__ void __launch_bounds__(256)
-raster_clear_kernel(RasterOut O, long long plane_quads, int n_batch) {
-  const long long total = plane_quads * n_batch;  // float4 per single-channel output
-  const long long stride = (long long)gridDim.x * blockDim.x;
-  for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < total; q += stride) {
-    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
-    st_f4(reinterpret_cast<float4 *>(O.depth) + q, z);
-    if (O.mask) st_f4(reinterpret_cast<float4 *>(O.mask) + q, z);
-    if (O.tri_id) reinterpret_cast<int4 *>(O.tri_id)[q] = make_int4(-1, -1, -1, -1);
-    if (O.image_chw) {
-      const long long b = q / plane_quads, r = q - b * plane_quads;
-      float4 *img = reinterpret_cast<float4 *>(O.image_chw) + b * 3 * plane_quads + r;
-#pragma unroll
-      for (int c = 0; c < 3; ++c) {
-        const float m = 0.f - O.mean[c];
-        st_f4(img + c * plane_quads, make_float4(m, m, m, m));
-      }
-    }
-    if (O.bgr_hwc) {
-      float4 *o = reinterpret_cast<float4 *>(O.bgr_hwc) + q * 3;
-      st_f4(o, z);
-      st_f4(o + 1, z);
-      st_f4(o + 2, z);
-    }
+// ------------------------------------------------------------- 4. raster + background
+// One persistent launch writes the whole frame exactly once.  Work units come from two global
+// ticket counters: the non-empty (tile, pair) items, one per unit, and the empty tiles in chunks
+// of RT_BG_CHUNK.  Three CTAs in four start on the (latency-bound) rasterising items, the fourth
+// on the (bandwidth-bound) background, and each switches when its kind runs out, so the
+// streaming stores fill the time the rasterising CTAs leave HBM idle and the tail is balanced
+// dynamically.
+//
+// Non-empty tile: (1) coverage: threads take triangles of the tile's list and atomicMin a packed
+// (bits(window depth) << 32 | record) key into the shared-memory z-buffer; (2) resolve: one
+// pixel per thread: depth linearisation + shading, results staged in shared memory as planes;
+// (3) store: four adjacent pixels per thread, 128-bit stores of depth, mask, CHW RGB - mean,
+// HWC BGR, triangle ids.
+constexpr int RT_QUADS = RT_PIX / 4;                 // 128-bit stores per plane and tile
+constexpr int RT_BG_TILES = RT_THREADS / RT_QUADS;   // empty tiles written per pass
+constexpr int RT_BG_CHUNK = 8 * RT_BG_TILES;         // empty tiles per work unit
+
+struct TileOut {          // staged results of one tile, planes of RT_PIX
+  float d[RT_PIX], r[RT_PIX], g[RT_PIX], b[RT_PIX];
+};
+
+__device__ __forceinline__ void store_quad(const RasterOut &O, int b, int H, int W, int y, int x,
+                                           const float4 dz, const float4 cr, const float4 cg,
+                                           const float4 cb, const int4 tid4) {
+  const size_t plane = (size_t)H * W;
+  const size_t pix = (size_t)y * W + x;
+  st_f4(reinterpret_cast<float4 *>(O.depth + b * plane + pix), dz);
+  if (O.mask) {
+    const float th = O.mask_thresh;
+    st_f4(reinterpret_cast<float4 *>(O.mask + b * plane + pix),
+          make_float4(dz.x > th ? 1.f : 0.f, dz.y > th ? 1.f : 0.f, dz.z > th ? 1.f : 0.f,
+                      dz.w > th ? 1.f : 0.f));
   }
+  if (O.image_chw) {
+    float *img = O.image_chw + (size_t)b * 3 * plane + pix;
+    st_f4(reinterpret_cast<float4 *>(img),
+          make_float4(cr.x - O.mean[0], cr.y - O.mean[0], cr.z - O.mean[0], cr.w - O.mean[0]));
+    st_f4(reinterpret_cast<float4 *>(img + plane),
+          make_float4(cg.x - O.mean[1], cg.y - O.mean[1], cg.z - O.mean[1], cg.w - O.mean[1]));
+    st_f4(reinterpret_cast<float4 *>(img + 2 * plane),
+          make_float4(cb.x - O.mean[2], cb.y - O.mean[2], cb.z - O.mean[2], cb.w - O.mean[2]));
+  }
+  if (O.bgr_hwc) {
+    float4 *o = reinterpret_cast<float4 *>(O.bgr_hwc + ((size_t)b * plane + pix) * 3);
+    st_f4(o, make_float4(cb.x, cg.x, cr.x, cb.y));
+    st_f4(o + 1, make_float4(cg.y, cr.y, cb.z, cg.z));
+    st_f4(o + 2, make_float4(cr.z, cb.w, cg.w, cr.w));
+  }
+  if (O.tri_id) *reinterpret_cast<int4 *>(O.tri_id + b * plane + pix) = tid4;
 }
 
-// grid = a few CTAs per SM (persistent over the non-empty tiles); block = 256; 8 KB z-buffer.
-__global__ void __launch_bounds__(RT_THREADS)
+// grid = resident CTAs (persistent); block = 256.
+constexpr int RT_BIG_AREA = 32;   // pixel-box area (inside the tile) above which a triangle is rasterised by the whole CTA
+constexpr int RT_BIG_CAP = 192;   // queue of such triangles per tile (overflow: the owning thread loops)
+constexpr int RT_UNIT_DONE = INT_MAX;
+static_assert(RT_PIX == RT_THREADS, "one pixel per thread in the cooperative and resolve phases");
+
+// Next work unit for this CTA (thread 0 only): >= 0 a non-empty item, < 0 background chunk
+// -(k + 1).  A CTA keeps drawing its preferred kind until that runs out, then switches.
+__device__ __forceinline__ int next_unit(int32_t *wc, int n_heavy, int n_light_units,
+                                         bool &prefer_light) {
+#pragma unroll 1
+  for (int k = 0; k < 2; ++k) {
+    if (prefer_light) {
+      const int u = atomicAdd(wc + RT_WC_TICKET_L, 1);
+      if (u < n_light_units) return -(u + 1);
+    } else {
+      const int u = atomicAdd(wc + RT_WC_TICKET_H, 1);
+      if (u < n_heavy) return u;
+    }
+    prefer_light = !prefer_light;
+  }
+  return RT_UNIT_DONE;
+}
+
+__global__ void __launch_bounds__(RT_THREADS, 4)
 raster_tile_kernel(Renderer R, const int32_t *__restrict__ cls_idx,
                    const float *__restrict__ poses, Cam cam, RasterOut O, int n_tiles, int n_batch) {
-  __shared__ unsigned long long zbuf[RT_TILE * RT_TILE];
+  __shared__ unsigned long long zbuf[RT_PIX];
+  __shared__ TileOut out;
+  __shared__ int s_unit[2];
+  __shared__ int s_big[RT_BIG_CAP];
+  __shared__ int s_nbig;
   const int W = R.W, H = R.H;
-  // persistent CTAs walk the compacted list of NON-EMPTY (tile, pair) items; the background of
-  // the frame is written by raster_clear_kernel at streaming speed.
-  const int n_work = *R.work_count;
-  for (int wi = blockIdx.x; wi < n_work; wi += gridDim.x) {
-  const int work = R.work_list[wi];
-  const int b = work / n_tiles, tile = work - b * n_tiles;
-  const int tx0 = (tile % R.tiles_x) * RT_TILE, ty0 = (tile / R.tiles_x) * RT_TILE;
-  const int32_t *start = R.tile_start + (size_t)b * (n_tiles + 1);
-  const int first = start[tile];
-  const int n = min(start[tile + 1], R.list_cap) - first;
-  const TriRec *recs = R.recs + (size_t)b * 2 * R.max_tris;
-  if (n > 0) {
-    for (int i = threadIdx.x; i < RT_TILE * RT_TILE; i += RT_THREADS) zbuf[i] = ~0ull;
+  const int n_total = n_tiles * n_batch;
+  const int n_heavy = R.work_count[RT_WC_HEAVY];
+  const int n_light_units = (n_total - n_heavy + RT_BG_CHUNK - 1) / RT_BG_CHUNK;
+  // the rasterising items are latency-bound, the background chunks bandwidth-bound: one CTA in
+  // four starts on the background so that its stores overlap the others' rasterisation
+  bool prefer_light = (blockIdx.x & 3) == 3;
+  // store phase: quad q of a tile = 4 adjacent pixels of one row
+  const int sub = threadIdx.x / RT_QUADS, q = threadIdx.x % RT_QUADS;
+  const int row4 = q / (RT_TW / 4), xq = (q % (RT_TW / 4)) * 4;
+  if (threadIdx.x == 0) s_unit[0] = next_unit(R.work_count, n_heavy, n_light_units, prefer_light);
+  __syncthreads();
+  for (int par = 0;; par ^= 1) {
+    const int unit = s_unit[par];
+    if (unit == RT_UNIT_DONE) break;
+    if (threadIdx.x == 0)  // next ticket, early
+      s_unit[par ^ 1] = next_unit(R.work_count, n_heavy, n_light_units, prefer_light);
+    if (unit < 0) {
+      // ---- background chunk: depth 0, mask 0, image 0 - mean, bgr 0, tri -1
+      const int first = n_heavy + (-unit - 1) * RT_BG_CHUNK;
+      const int last = min(first + RT_BG_CHUNK, n_total);
+      const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 2
+      for (int wi = first + sub; wi < last; wi += RT_BG_TILES) {
+        const int work = __ldg(R.work_list + wi);
+        const int b = work >> 16;
+        const int y = ((work >> 8) & 0xff) * RT_TH + row4, x = (work & 0xff) * RT_TW + xq;
+        if (y < H && x < W) store_quad(O, b, H, W, y, x, z, z, z, z, make_int4(-1, -1, -1, -1));
+      }
+      __syncthreads();  // s_unit[par ^ 1] visible; s_unit[par] free for the ticket after next
+      continue;
+    }
+    const int work = R.work_list[unit];
+    const int b = work >> 16;
+    const int tx0 = (work & 0xff) * RT_TW, ty0 = ((work >> 8) & 0xff) * RT_TH;
+    const int tile = ((work >> 8) & 0xff) * R.tiles_x + (work & 0xff);
+    const int32_t *start = R.tile_start + (size_t)b * (n_tiles + 1);
+    const int first = start[tile];
+    const int n = min(start[tile + 1], R.list_cap) - first;
+    const TriRec *recs = R.recs + (size_t)b * 2 * R.max_tris;
+    zbuf[threadIdx.x] = ~0ull;
+    if (threadIdx.x == 0) s_nbig = 0;
     __syncthreads();
+    // ---- (1a) coverage, one thread per triangle of the tile's list; triangles whose pixel box
+    // inside the tile is large are queued for the whole CTA instead
     const int32_t *list = R.tile_list + (size_t)b * R.list_cap + first;
     for (int i = threadIdx.x; i < n; i += RT_THREADS) {
       const int ri = list[i];
       const int4 *rp = reinterpret_cast<const int4 *>(recs + ri);
       const int4 q0 = __ldg(rp), q1 = __ldg(rp + 1), q2 = __ldg(rp + 2), q3 = __ldg(rp + 3);
+      const int xl = max(q1.w & 0xffff, tx0), xh = min(q2.x & 0xffff, tx0 + RT_TW - 1);
+      const int yl = max(q1.w >> 16, ty0), yh = min(q2.x >> 16, ty0 + RT_TH - 1);
+      if ((xh - xl + 1) * (yh - yl + 1) > RT_BIG_AREA) {
+        const int slot = atomicAdd(&s_nbig, 1);
+        if (slot < RT_BIG_CAP) {
+          s_big[slot] = ri;
+          continue;
+        }
+      }
       const long long ax = q0.x, ay = q0.y, bx = q0.z, by = q0.w, cx = q1.x, cy = q1.y;
       const double zwa = __hiloint2double(q2.w, q2.z), zwb = __hiloint2double(q3.y, q3.x),
                    zwc = __hiloint2double(q3.w, q3.z);
-      const int xl = max(q1.w & 0xffff, tx0), xh = min(q2.x & 0xffff, tx0 + RT_TILE - 1);
-      const int yl = max(q1.w >> 16, ty0), yh = min(q2.x >> 16, ty0 + RT_TILE - 1);
       const int bias0 = tie_bias(cx - bx, cy - by), bias1 = tie_bias(ax - cx, ay - cy),
                 bias2 = tie_bias(bx - ax, by - ay);
       const long long s0 = -(cy - by) * 256, s1 = -(ay - cy) * 256, s2 = -(by - ay) * 256;
-      const double area = (double)edge_fn(ax, ay, bx, by, cx, cy);
+      // window depth is affine in the pixel: d = zwa + w1 * dzb + w2 * dzc (one division per
+      // triangle; the same expression in the cooperative path below)
+      const double inv_area = 1.0 / (double)edge_fn(ax, ay, bx, by, cx, cy);
+      const double dzb = (zwb - zwa) * inv_area, dzc = (zwc - zwa) * inv_area;
       for (int y = yl; y <= yh; ++y) {
         const long long px = (long long)xl << RT_SUB, py = (long long)y << RT_SUB;
         long long w0 = edge_fn(bx, by, cx, cy, px, py);
@@ -509,12 +743,11 @@ raster_tile_kernel(Renderer R, const int32_t *__restrict__ cls_idx,
         for (int x = xl; x <= xh; ++x) {
           if (((w0 + bias0) | (w1 + bias1) | (w2 + bias2)) >= 0) {
             // window depth, interpolated linearly in screen space, stored as float32
-            const double l0 = (double)w0 / area, l1 = (double)w1 / area, l2 = (double)w2 / area;
-            const float d = (float)(l0 * zwa + l1 * zwb + l2 * zwc);
+            const float d = (float)(zwa + (double)w1 * dzb + (double)w2 * dzc);
             if (d >= 0.0f && d <= 1.0f) {  // depth clipping of the fragment (far plane)
               const unsigned long long key =
                   ((unsigned long long)__float_as_uint(d) << 32) | (unsigned)ri;  // GL_LESS
-              atomicMin(&zbuf[(y - ty0) * RT_TILE + (x - tx0)], key);
+              atomicMin(&zbuf[(y - ty0) * RT_TW + (x - tx0)], key);
             }
           }
           w0 += s0;
@@ -524,65 +757,79 @@ raster_tile_kernel(Renderer R, const int32_t *__restrict__ cls_idx,
       }
     }
     __syncthreads();
-  }
-  // resolve: four adjacent pixels per thread
-  const int row = threadIdx.x >> 3, xq = (threadIdx.x & 7) * 4;
-  const int y = ty0 + row, x = tx0 + xq;
-  if (y < H && x < W) {
-  const int mesh = __ldg(cls_idx + b);
-  const float *pose = poses + b * 12;
-  float dz[4], cr[4], cg[4], cb[4];
-  int tid4[4];
-#pragma unroll
-  for (int k = 0; k < 4; ++k) {
-    dz[k] = 0.f;
-    cr[k] = cg[k] = cb[k] = 0.f;
-    tid4[k] = -1;
-    if (n > 0 && x + k < W) {
-      const unsigned long long key = zbuf[row * RT_TILE + xq + k];
-      if (key != ~0ull) {
-        // readback linearisation, render_py_multi.py:139-145, float32 like numpy
-        const float d = __uint_as_float((unsigned)(key >> 32));
-        dz[k] = (d == 1.0f) ? 0.f : O.lin_c0 / (O.lin_c1 - O.lin_c2 * (2.0f * d - 1.0f));
-        const TriRec rec = recs[(unsigned)key];
-        tid4[k] = rec.tri & RT_TRI_MASK;
-        if (O.image_chw || O.bgr_hwc) {
-          const Shaded s = shade_pixel(R, O, cam, mesh, rec, pose, b, x + k, y);
-          cr[k] = s.c[0];
-          cg[k] = s.c[1];
-          cb[k] = s.c[2];
+    // ---- (1b) the queued large triangles: every thread tests its own pixel (same integer edge
+    // functions, same depth expression), so no atomics are needed
+    const int px_x = tx0 + (threadIdx.x & (RT_TW - 1)), px_y = ty0 + (threadIdx.x >> RT_TW_SHIFT);
+    unsigned long long best = zbuf[threadIdx.x];
+    {
+      const int n_big = min(s_nbig, RT_BIG_CAP);
+      const long long px = (long long)px_x << RT_SUB, py = (long long)px_y << RT_SUB;
+#pragma unroll 1
+      for (int j = 0; j < n_big; ++j) {
+        const int ri = s_big[j];
+        const int4 *rp = reinterpret_cast<const int4 *>(recs + ri);
+        const int4 q0 = __ldg(rp), q1 = __ldg(rp + 1), q2 = __ldg(rp + 2);
+        if (px_x < (q1.w & 0xffff) || px_x > (q2.x & 0xffff) || px_y < (q1.w >> 16) ||
+            px_y > (q2.x >> 16))
+          continue;
+        const long long ax = q0.x, ay = q0.y, bx = q0.z, by = q0.w, cx = q1.x, cy = q1.y;
+        const long long w0 = edge_fn(bx, by, cx, cy, px, py);
+        const long long w1 = edge_fn(cx, cy, ax, ay, px, py);
+        const long long w2 = edge_fn(ax, ay, bx, by, px, py);
+        const int bias0 = tie_bias(cx - bx, cy - by), bias1 = tie_bias(ax - cx, ay - cy),
+                  bias2 = tie_bias(bx - ax, by - ay);
+        if (((w0 + bias0) | (w1 + bias1) | (w2 + bias2)) >= 0) {
+          const int4 q3 = __ldg(rp + 3);
+          const double zwa = __hiloint2double(q2.w, q2.z), zwb = __hiloint2double(q3.y, q3.x),
+                       zwc = __hiloint2double(q3.w, q3.z);
+          const double inv_area = 1.0 / (double)edge_fn(ax, ay, bx, by, cx, cy);
+          const double dzb = (zwb - zwa) * inv_area, dzc = (zwc - zwa) * inv_area;
+          const float d = (float)(zwa + (double)w1 * dzb + (double)w2 * dzc);
+          if (d >= 0.0f && d <= 1.0f) {
+            const unsigned long long key =
+                ((unsigned long long)__float_as_uint(d) << 32) | (unsigned)ri;
+            best = min(best, key);
+          }
         }
       }
     }
-  }
-  const size_t plane = (size_t)H * W;
-  const size_t pix = (size_t)y * W + x;
-  st_f4(reinterpret_cast<float4 *>(O.depth + b * plane + pix), make_float4(dz[0], dz[1], dz[2], dz[3]));
-  if (O.mask) {
-    const float th = O.mask_thresh;
-    st_f4(reinterpret_cast<float4 *>(O.mask + b * plane + pix),
-          make_float4(dz[0] > th ? 1.f : 0.f, dz[1] > th ? 1.f : 0.f, dz[2] > th ? 1.f : 0.f,
-                      dz[3] > th ? 1.f : 0.f));
-  }
-  if (O.image_chw) {
-    float *img = O.image_chw + (size_t)b * 3 * plane + pix;
-    st_f4(reinterpret_cast<float4 *>(img),
-          make_float4(cr[0] - O.mean[0], cr[1] - O.mean[0], cr[2] - O.mean[0], cr[3] - O.mean[0]));
-    st_f4(reinterpret_cast<float4 *>(img + plane),
-          make_float4(cg[0] - O.mean[1], cg[1] - O.mean[1], cg[2] - O.mean[1], cg[3] - O.mean[1]));
-    st_f4(reinterpret_cast<float4 *>(img + 2 * plane),
-          make_float4(cb[0] - O.mean[2], cb[1] - O.mean[2], cb[2] - O.mean[2], cb[3] - O.mean[2]));
-  }
-  if (O.bgr_hwc) {
-    float4 *o = reinterpret_cast<float4 *>(O.bgr_hwc + ((size_t)b * plane + pix) * 3);
-    st_f4(o, make_float4(cb[0], cg[0], cr[0], cb[1]));
-    st_f4(o + 1, make_float4(cg[1], cr[1], cb[2], cg[2]));
-    st_f4(o + 2, make_float4(cr[2], cb[3], cg[3], cr[3]));
-  }
-  if (O.tri_id)
-    *reinterpret_cast<int4 *>(O.tri_id + b * plane + pix) = make_int4(tid4[0], tid4[1], tid4[2], tid4[3]);
-  }
-  if (n > 0) __syncthreads();  // z-buffer is re-initialised by the next work item
+    // ---- (2) resolve: this thread's pixel; the results are staged in shared memory as planes
+    {
+      float dz = 0.f, cr = 0.f, cg = 0.f, cb = 0.f;
+      int tid = -1;
+      if (best != ~0ull && px_x < W && px_y < H) {
+        // readback linearisation, render_py_multi.py:139-145, float32 like numpy
+        const float d = __uint_as_float((unsigned)(best >> 32));
+        dz = (d == 1.0f) ? 0.f : O.lin_c0 / (O.lin_c1 - O.lin_c2 * (2.0f * d - 1.0f));
+        const TriRec rec = recs[(unsigned)best];
+        tid = rec.tri & RT_TRI_MASK;
+        if (O.image_chw || O.bgr_hwc) {
+          const Shaded s = shade_pixel(R, O, cam, __ldg(cls_idx + b), rec, poses + b * 12, b, px_x, px_y);
+          cr = s.c[0];
+          cg = s.c[1];
+          cb = s.c[2];
+        }
+      }
+      out.d[threadIdx.x] = dz;
+      out.r[threadIdx.x] = cr;
+      out.g[threadIdx.x] = cg;
+      out.b[threadIdx.x] = cb;
+      zbuf[threadIdx.x] = (unsigned long long)(unsigned)tid;  // own slot: nobody else reads the key
+    }
+    __syncthreads();
+    // ---- (3) store: four adjacent pixels per thread
+    if (threadIdx.x < RT_QUADS) {
+      const int y = ty0 + row4, x = tx0 + xq, p = row4 * RT_TW + xq;
+      if (y < H && x < W) {
+        const float4 dz = *reinterpret_cast<const float4 *>(out.d + p);
+        const float4 cr = *reinterpret_cast<const float4 *>(out.r + p);
+        const float4 cg = *reinterpret_cast<const float4 *>(out.g + p);
+        const float4 cb = *reinterpret_cast<const float4 *>(out.b + p);
+        const int4 t4 = make_int4((int)zbuf[p], (int)zbuf[p + 1], (int)zbuf[p + 2], (int)zbuf[p + 3]);
+        store_quad(O, b, H, W, y, x, dz, cr, cg, cb, t4);
+      }
+    }
+    __syncthreads();  // z-buffer / staging reused by the next unit; next ticket visible
   }
 }
 
@@ -601,7 +848,7 @@ static int dev_alloc(T **p, size_t n) {
 static void renderer_free(Renderer *r) {
   if (!r) return;
   void *ptrs[] = {r->verts, r->uv, r->normals, r->tris, r->mesh_tri_off, r->mesh_has, r->tex,
-                  r->tex_off, r->tex_hw, r->recs, r->work_count, r->tile_start, r->tile_fill,
+                  r->tex_off, r->tex_hw, r->recs, r->bbox, r->clip_list, r->work_count, r->tile_start, r->tile_fill,
                   r->tile_list, r->work_list};
   for (void *p : ptrs)
     if (p) cudaFree(p);
@@ -625,7 +872,10 @@ int rc_renderer_create(const rc_mesh_desc *meshes, int n_meshes, int height, int
                        int max_batch, int device_id, void **handle) {
   RC_REQUIRE(meshes && handle && n_meshes > 0 && height > 0 && width > 0 && max_batch > 0,
              RC_ERR_INVALID_ARG);
-  RC_REQUIRE(width % 4 == 0 && width < 32768 && height < 32768, RC_ERR_UNALIGNED);
+  RC_REQUIRE(width % 4 == 0, RC_ERR_UNALIGNED);
+  // work items pack (pair, tile row, tile column) into 15 + 8 + 8 bits
+  RC_REQUIRE(width <= 255 * rc::RT_TW && height <= 255 * rc::RT_TH && max_batch <= 32767,
+             RC_ERR_CAPACITY);
   size_t V = 0, T = 0, TX = 0;
   int max_tris = 0;
   for (int m = 0; m < n_meshes; ++m) {
@@ -649,8 +899,8 @@ int rc_renderer_create(const rc_mesh_desc *meshes, int n_meshes, int height, int
   r->max_batch = max_batch;
   r->n_meshes = n_meshes;
   r->max_tris = max_tris;
-  r->tiles_x = (width + rc::RT_TILE - 1) / rc::RT_TILE;
-  r->tiles_y = (height + rc::RT_TILE - 1) / rc::RT_TILE;
+  r->tiles_x = (width + rc::RT_TW - 1) / rc::RT_TW;
+  r->tiles_y = (height + rc::RT_TH - 1) / rc::RT_TH;
   const int n_tiles = r->tiles_x * r->tiles_y;
   r->list_cap = 8 * max_tris + 16 * n_tiles;
   // host staging of the concatenated mesh arrays
@@ -693,8 +943,10 @@ int rc_renderer_create(const rc_mesh_desc *meshes, int n_meshes, int height, int
   RC_TRY(rc::dev_alloc(&r->tex_off, (size_t)n_meshes));
   RC_TRY(rc::dev_alloc(&r->tex_hw, (size_t)n_meshes * 2));
   RC_TRY(rc::dev_alloc(&r->recs, (size_t)max_batch * 2 * max_tris));
-  RC_TRY(rc::dev_alloc(&r->work_count, (size_t)max_batch * n_tiles + 4));  // [4 | tile counts]
-  r->tile_count = r->work_count + 4;
+  RC_TRY(rc::dev_alloc(&r->bbox, (size_t)max_batch * 2 * max_tris));
+  RC_TRY(rc::dev_alloc(&r->clip_list, (size_t)max_batch * max_tris));
+  RC_TRY(rc::dev_alloc(&r->work_count, (size_t)max_batch * n_tiles + rc::RT_WC_INTS));  // [header | tile counts]
+  r->tile_count = r->work_count + rc::RT_WC_INTS;
   RC_TRY(rc::dev_alloc(&r->work_list, (size_t)max_batch * n_tiles));
   RC_TRY(rc::dev_alloc(&r->tile_start, (size_t)max_batch * (n_tiles + 1)));
   RC_TRY(rc::dev_alloc(&r->tile_fill, (size_t)max_batch * n_tiles));
@@ -765,28 +1017,32 @@ int rc_render_dev(void *handle, const rc_render_args *a) {
   };
   int st;
   if ((st = mark(0)) != RC_OK) return st;
-  RC_CUDA_TRY(cudaMemsetAsync(R.work_count, 0, sizeof(int32_t) * ((size_t)B * n_tiles + 4), s));
+  RC_CUDA_TRY(cudaMemsetAsync(R.work_count, 0,
+                              sizeof(int32_t) * ((size_t)B * n_tiles + rc::RT_WC_INTS), s));
   dim3 gs((R.max_tris + 255) / 256, B);
   rc::raster_setup_kernel<<<gs, 256, 0, s>>>(R, a->cls_idx, a->poses, cam, n_tiles);
+  rc::raster_clip_kernel<<<32, 128, 0, s>>>(R, a->cls_idx, a->poses, cam, n_tiles);
   if ((st = mark(1)) != RC_OK) return st;
   rc::raster_scan_kernel<<<B, 256, 0, s>>>(R, n_tiles, a->status);
   if ((st = mark(2)) != RC_OK) return st;
   dim3 gf((2 * R.max_tris + 255) / 256, B);
   rc::raster_fill_kernel<<<gf, 256, 0, s>>>(R, a->cls_idx, n_tiles);
   if ((st = mark(3)) != RC_OK) return st;
-  static int sm_count = 0;
-  if (sm_count == 0 &&
-      cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, R.device) != cudaSuccess)
-    sm_count = 148;
-  {
-    const long long plane_quads = (long long)R.H * R.W / 4;
-    long long blocks = (plane_quads * B + 255) / 256;
-    if (blocks > sm_count * 16) blocks = sm_count * 16;
-    rc::raster_clear_kernel<<<(int)blocks, 256, 0, s>>>(O, plane_quads, B);
+  // persistent grid: every CTA that can be resident, no more (units come from a ticket counter)
+  static int sm_count = 0, per_sm = 0;
+  if (sm_count == 0) {
+    if (cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, R.device) != cudaSuccess)
+      sm_count = 148;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rc::raster_tile_kernel,
+                                                      rc::RT_THREADS, 0) != cudaSuccess ||
+        per_sm < 1)
+      per_sm = 2;
   }
-  int gr = sm_count * 4;
-  if (gr > n_tiles * B) gr = n_tiles * B;
-  rc::raster_tile_kernel<<<gr, rc::RT_THREADS, 0, s>>>(R, a->cls_idx, a->poses, cam, O, n_tiles, B);
+  const long long n_total = (long long)n_tiles * B;
+  long long gr = (long long)sm_count * per_sm;
+  if (gr > n_total) gr = n_total;
+  rc::raster_tile_kernel<<<(int)gr, rc::RT_THREADS, 0, s>>>(R, a->cls_idx, a->poses, cam, O,
+                                                             n_tiles, B);
   if ((st = mark(4)) != RC_OK) return st;
   return rc::note_status(rc::check_launch());
 }
@@ -800,13 +1056,13 @@ int rc_render_stats(void *handle, int batch_size, void *stream, int64_t *out) {
   RC_CUDA_TRY(cudaStreamSynchronize(s));
   std::vector<int32_t> st((size_t)batch_size * (n_tiles + 1));
   RC_CUDA_TRY(cudaMemcpy(st.data(), R.tile_start, st.size() * sizeof(int32_t), cudaMemcpyDeviceToHost));
-  std::vector<int32_t> bb((size_t)batch_size * 2 * R.max_tris * 16);
-  RC_CUDA_TRY(cudaMemcpy(bb.data(), R.recs, bb.size() * sizeof(int32_t), cudaMemcpyDeviceToHost));
+  std::vector<int2> bb((size_t)batch_size * 2 * R.max_tris);
+  RC_CUDA_TRY(cudaMemcpy(bb.data(), R.bbox, bb.size() * sizeof(int2), cudaMemcpyDeviceToHost));
   int64_t recs = 0, entries = 0;
   for (int b = 0; b < batch_size; ++b) entries += st[(size_t)b * (n_tiles + 1) + n_tiles];
-  for (size_t i = 0; i < (size_t)batch_size * 2 * R.max_tris; ++i)
-    if (bb[i * 16 + 8] >= 0) ++recs;  // bb_max of live records (slots of absent triangles excluded
-                                       // only when the mesh has max_tris triangles)
+  for (size_t i = 0; i < bb.size(); ++i)
+    if (bb[i].y >= 0) ++recs;  // live records (slots of absent triangles excluded only when the
+                               // mesh has max_tris triangles)
   out[0] = recs;
   out[1] = entries;
   return rc::note_status(RC_OK);

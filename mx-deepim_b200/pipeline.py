@@ -462,13 +462,17 @@ def make_refine_batch(meshes, batch, seed, K=synth.K_LINEMOD, num_points=synth.N
     depth = out["depth"].cpu().numpy()
     image = out["image"].cpu().numpy()
     depth = (np.round(depth.astype(np.float64) * 1000.0) / 1000.0).astype(np.float32)  # 1 mm PNG
+    # mask_gt_observed is the object's LABEL mask (label == cls_idx, lib/dataset/LM6D_REFINE.py),
+    # so a nearer occluder removes pixels from it but never adds any; depth_gt_observed is the
+    # sensor depth and does contain the occluder (Occlusion-LINEMOD-shaped)
+    mask_gt = (depth > 0).astype(np.float32)
     if occlusion:
         for b in range(B):
             x0, y0 = rng.integers(0, synth.W - 80), rng.integers(0, synth.H - 80)
             depth[b, 0, y0:y0 + 80, x0:x0 + 80] = 0.4
+            mask_gt[b, 0, y0:y0 + 80, x0:x0 + 80] = 0
     bg = rng.uniform(1, 255, size=image.shape).astype(np.float32) - pm.reshape(1, 3, 1, 1)
-    image = np.where(depth > 0, image, bg).astype(np.float32)
-    mask_gt = (depth > 0).astype(np.float32)
+    image = np.where(mask_gt[:, :1] > 0, image, bg).astype(np.float32)
     mask_obs = mask_gt.copy()
     for b in range(B):
         y0, x0 = rng.integers(0, synth.H - 40), rng.integers(0, synth.W - 40)

@@ -115,14 +115,17 @@ def make_compare_batch(batch, seed, K=K_LINEMOD, num_points=NUM_3D_SAMPLE, occlu
         "trans_est": np.zeros((batch, 3), np.float32),
         "trans_gt": np.zeros((batch, 3), np.float32),
     }
+    label = np.zeros((batch, 1, H, W), np.float32)
     for b in range(batch):
         ps, pt = random_pose_pair(rng, K)
         radii = rng.uniform(0.04, 0.12, size=3)
         out["depth_rendered"][b, 0] = ellipsoid_depth(ps, radii, K)
         d = np.round(ellipsoid_depth(pt, radii, K).astype(np.float64) * 1000.0) / 1000.0
+        label[b, 0] = d > 0  # object label mask: an occluder only ever removes pixels from it
         if occlusion:
             x0, y0 = rng.integers(0, W - 80), rng.integers(0, H - 80)
             d[y0:y0 + 80, x0:x0 + 80] = 0.4
+            label[b, 0, y0:y0 + 80, x0:x0 + 80] = 0
         out["depth_gt_observed"][b, 0] = d.astype(np.float32)
         out["src_pose"][b], out["tgt_pose"][b] = ps, pt
         out["KT"][b] = P.make_KT(K, ps, pt)
@@ -138,7 +141,7 @@ def make_compare_batch(batch, seed, K=K_LINEMOD, num_points=NUM_3D_SAMPLE, occlu
         out["trans_est"][b] = t + rng.normal(0, 0.01, size=3)
     out["Kinv"] = P.make_Kinv(K)
     dr, do = out["depth_rendered"], out["depth_gt_observed"]
-    out["mask_gt_observed"] = (do > 0).astype(np.float32)
+    out["mask_gt_observed"] = label
     mo = out["mask_gt_observed"].copy()
     for b in range(batch):
         y0, x0 = rng.integers(0, H - 40), rng.integers(0, W - 40)
@@ -147,7 +150,7 @@ def make_compare_batch(batch, seed, K=K_LINEMOD, num_points=NUM_3D_SAMPLE, occlu
     tex = rng.uniform(0, 255, size=(batch, 3, H, W)).astype(np.float32)
     out["image_rendered"] = (tex * (dr > 0) - pm).astype(np.float32)
     bg = rng.uniform(1, 255, size=(batch, 3, H, W)).astype(np.float32)
-    out["image_observed"] = (np.where(do > 0, tex[:, ::-1], bg) - pm).astype(np.float32)
+    out["image_observed"] = (np.where(label > 0, tex[:, ::-1], bg) - pm).astype(np.float32)
     return out
 
 
