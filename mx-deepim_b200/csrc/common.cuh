@@ -100,6 +100,12 @@ __device__ __forceinline__ void pdl_launch_dependents() {
   asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 }
 
+// Blocks until the grids this one was programmatically launched after have completed and
+// their writes are visible; a no-op for a normal launch.
+__device__ __forceinline__ void pdl_wait() {
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
 __device__ __forceinline__ void st_f1(float *p, float v) {
   asm volatile("st.global.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
 }

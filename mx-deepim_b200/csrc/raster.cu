@@ -6,25 +6,27 @@
 // and the post-render block
 //   /root/reference/lib/pair_matching/batch_updater_py_multi.py:279-320.
 //
-// B200 design (one render call = 4 launches for a whole batch, any mix of meshes):
-//   1. setup  : one thread per (triangle, pair): pose transform in float64, near-plane
-//               clipping, pinhole projection, snap to 1/256 px, edge orientation, GL window depth;
-//               writes a 64-byte record and counts the 32x32 tiles it overlaps with
-//               warp-aggregated atomics (__match_any_sync on the tile id).
-//   2. scan   : exclusive scan of the per-tile counts (one block per pair).
+// B200 design (one render call = 8 launches for a whole batch, any mix of meshes):
+//   1. setup  : one thread per (triangle, pair): pose transform in float64, pinhole projection,
+//               snap to 1/256 px, edge orientation, GL window depth, culling (incl. micro-
+//               triangles that contain no pixel centre); writes a 64-byte record + its pixel box
+//               and counts the 16x16 tiles it overlaps with warp-aggregated atomics
+//               (__match_any_sync on the tile id).  Triangles straddling the near plane go to a
+//               list for the (usually idle) clip kernel.
+//   2. scan   : exclusive scan of the per-tile counts (one block per pair) + the list of
+//               non-empty (tile, pair) items.
 //   3. fill   : tile lists (record indices), again warp-aggregated.
-//   4. raster : ONE persistent launch writes the whole frame once.  CTAs draw work units from a
-//               ticket counter: non-empty (tile, pair) items first, then the empty tiles in
-//               chunks (streaming background stores overlap the rasterising CTAs).  Per
-//               non-empty tile: threads take triangles of the tile's list and atomicMin a
+//   4a clear  : streams the background in row order, skipping non-empty tiles (HBM bound).
+//   4b cover  : beside 4a (programmatic dependent launch): per non-empty tile, atomicMin of a
 //               packed (bits(window depth) << 32 | record) key into a shared-memory z-buffer;
-//               then one pixel per thread resolves (perspective-correct attributes, nearest
-//               texel, optional Lambert term) into shared-memory planes, and depth, CHW RGB -
-//               mean, HWC BGR, mask leave with 128-bit stores.
+//               large triangles are tested cooperatively, one pixel per thread.
+//   4c resolve: one thread per pixel of the non-empty tiles: perspective-correct attributes,
+//               nearest texel, optional Lambert term, fused BGR->RGB / CHW / -mean and mask.
 // The frame is written exactly once (20 B/px), the mesh is read once per pair.
 //
 // Compiled with -fmad=false: the float64 geometry must round exactly like the C oracle.
 #include <limits.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <vector>
@@ -65,15 +67,14 @@ struct Renderer {
   int32_t *tile_count, *tile_start, *tile_fill;  // [max_batch][n_tiles (+1)]
   int32_t *tile_list;                        // [max_batch][list_cap]
   int32_t *work_count;                       // [RT_WC_INTS] header (see RT_WC_*), then tile_count
-  int32_t *work_list;                        // [max_batch * n_tiles] b * n_tiles + tile: non-empty from the front, empty from the back
+  unsigned long long *zwin;                  // [max_batch * n_tiles][RT_PIX] winning keys of the non-empty items
+  int32_t *work_list;                        // [max_batch * n_tiles] packed non-empty (tile, pair) items
 };
 
 // work_count header
 constexpr int RT_WC_HEAVY = 0;     // non-empty (tile, pair) items (scan)
-constexpr int RT_WC_EMPTY = 1;     // empty items (scan)
 constexpr int RT_WC_CLIP = 3;      // clip-list length (setup)
-constexpr int RT_WC_TICKET_H = 4;  // next non-empty item (raster)
-constexpr int RT_WC_TICKET_L = 5;  // next background chunk (raster)
+constexpr int RT_WC_TICKET_H = 4;  // next non-empty item (coverage)
 constexpr int RT_WC_INTS = 8;
 
 // work item: pair << 16 | tile row << 8 | tile column
@@ -280,6 +281,7 @@ __device__ __forceinline__ int4 clip_and_emit(const double *Pc /* [3][3] */, con
 __global__ void __launch_bounds__(256, 3)
 raster_setup_kernel(Renderer R, const int32_t *__restrict__ cls_idx,
                     const float *__restrict__ poses, Cam cam, int n_tiles) {
+  pdl_launch_dependents();  // the clip kernel waits (griddepcontrol.wait) for this grid's end
   const int b = blockIdx.y;
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   const int mesh = __ldg(cls_idx + b);
@@ -337,6 +339,8 @@ raster_setup_kernel(Renderer R, const int32_t *__restrict__ cls_idx,
 __global__ void __launch_bounds__(128)
 raster_clip_kernel(Renderer R, const int32_t *__restrict__ cls_idx,
                    const float *__restrict__ poses, Cam cam, int n_tiles) {
+  pdl_wait();  // setup's clip list and counters
+  pdl_launch_dependents();
   const int n = R.work_count[RT_WC_CLIP];
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
     const int item = R.clip_list[i];
@@ -390,17 +394,18 @@ __device__ __forceinline__ int block_excl_scan(int v, int *smem /* [8] */, int &
 }
 
 // grid = B; block = 256.  Exclusive scan of tile_count -> tile_start, clears tile_fill, and
-// appends the pair's tiles to the work list: non-empty ones from the front, empty ones from the
-// back (two atomics per pair; the order inside a pair is the tile order).
+// appends the pair's non-empty tiles to the work list (one atomic per pair; the order inside a
+// pair is the tile order).
 __global__ void __launch_bounds__(256)
 raster_scan_kernel(Renderer R, int n_tiles, int32_t *__restrict__ status) {
+  pdl_wait();
+  pdl_launch_dependents();
   const int b = blockIdx.x;
-  const int n_total = gridDim.x * n_tiles;
   const int32_t *count = R.tile_count + (size_t)b * n_tiles;
   int32_t *start = R.tile_start + (size_t)b * (n_tiles + 1);
   int32_t *fill = R.tile_fill + (size_t)b * n_tiles;
   __shared__ int part[8];
-  __shared__ int s_base[2];
+  __shared__ int s_base;
   const int per = (n_tiles + 255) / 256;
   const int lo = min((int)threadIdx.x * per, n_tiles), hi = min(lo + per, n_tiles);
   int s = 0, ne = 0;
@@ -415,20 +420,16 @@ raster_scan_kernel(Renderer R, int n_tiles, int32_t *__restrict__ status) {
   if (threadIdx.x == 0) {
     start[n_tiles] = total;
     if (total > R.list_cap && status) atomicExch(status, 1);
-    s_base[0] = atomicAdd(R.work_count + RT_WC_HEAVY, total_ne);
-    s_base[1] = atomicAdd(R.work_count + RT_WC_EMPTY, n_tiles - total_ne);
+    s_base = atomicAdd(R.work_count + RT_WC_HEAVY, total_ne);
   }
   __syncthreads();
-  int front = s_base[0] + ne_off;
-  int back = n_total - 1 - (s_base[1] + (lo - ne_off));
+  int front = s_base + ne_off;
   for (int i = lo; i < hi; ++i) {
     start[i] = acc;
     const int c = count[i];
     acc += c;
     fill[i] = 0;
-    const int work = pack_work(b, i / R.tiles_x, i % R.tiles_x);
-    if (c > 0) R.work_list[front++] = work;
-    else R.work_list[back--] = work;
+    if (c > 0) R.work_list[front++] = pack_work(b, i / R.tiles_x, i % R.tiles_x);
   }
 }
 
@@ -436,6 +437,8 @@ raster_scan_kernel(Renderer R, int n_tiles, int32_t *__restrict__ status) {
 // grid = (ceil(2 * max_tris / 256), B); one thread per record slot; reads the compact boxes.
 __global__ void __launch_bounds__(256)
 raster_fill_kernel(Renderer R, const int32_t *__restrict__ cls_idx, int n_tiles) {
+  pdl_wait();
+  pdl_launch_dependents();
   const int b = blockIdx.y;
   const int s = blockIdx.x * blockDim.x + threadIdx.x;
   const int mesh = __ldg(cls_idx + b);
@@ -583,26 +586,23 @@ __device__ Shaded shade_pixel(const Renderer &R, const RasterOut &O, const Cam &
   return s;
 }
 
-// ------------------------------------------------------------- 4. raster + background
-// One persistent launch writes the whole frame exactly once.  Work units come from two global
-// ticket counters: the non-empty (tile, pair) items, one per unit, and the empty tiles in chunks
-// of RT_BG_CHUNK.  Three CTAs in four start on the (latency-bound) rasterising items, the fourth
-// on the (bandwidth-bound) background, and each switches when its kind runs out, so the
-// streaming stores fill the time the rasterising CTAs leave HBM idle and the tail is balanced
-// dynamically.
-//
-// Non-empty tile: (1) coverage: threads take triangles of the tile's list and atomicMin a packed
-// (bits(window depth) << 32 | record) key into the shared-memory z-buffer; (2) resolve: one
-// pixel per thread: depth linearisation + shading, results staged in shared memory as planes;
-// (3) store: four adjacent pixels per thread, 128-bit stores of depth, mask, CHW RGB - mean,
-// HWC BGR, triangle ids.
-constexpr int RT_QUADS = RT_PIX / 4;                 // 128-bit stores per plane and tile
-constexpr int RT_BG_TILES = RT_THREADS / RT_QUADS;   // empty tiles written per pass
-constexpr int RT_BG_CHUNK = 8 * RT_BG_TILES;         // empty tiles per work unit
-
-struct TileOut {          // staged results of one tile, planes of RT_PIX
-  float d[RT_PIX], r[RT_PIX], g[RT_PIX], b[RT_PIX];
-};
+// ------------------------------------------------- 4. background, coverage, resolve
+// Three launches write the frame exactly once:
+//   4a clear   : streams the background (depth 0, mask 0, image 0 - mean, bgr 0, tri -1) in row
+//                order with 128-bit stores, skipping the quads of non-empty tiles.  Bandwidth
+//                bound; it releases its dependents at once and runs on a few CTAs per SM, so
+//   4b cover   : (launched with programmatic stream serialisation, resident beside 4a) works
+//                through the non-empty (tile, pair) items: threads take triangles of the tile's
+//                list and atomicMin a packed (bits(window depth) << 32 | record) key into a
+//                shared-memory z-buffer; triangles with a large pixel box inside the tile are
+//                queued and tested by every thread at its own pixels instead.  Latency bound.
+//                The winning keys of the tile go to a compact buffer (2 KB per item).
+//   4c resolve : one thread per pixel of the non-empty tiles, no barriers: depth linearisation,
+//                shading, fused image post-processing, stores.
+constexpr int RT_CV_THREADS = 128;
+constexpr int RT_BIG_AREA = 32;   // pixel-box area (inside the tile) above which a triangle is rasterised by the whole CTA
+constexpr int RT_BIG_CAP = 192;   // queue of such triangles per tile (overflow: the owning thread loops)
+static_assert(RT_PIX % RT_CV_THREADS == 0 && RT_PIX == RT_THREADS, "pixels per thread");
 
 __device__ __forceinline__ void store_quad(const RasterOut &O, int b, int H, int W, int y, int x,
                                            const float4 dz, const float4 cr, const float4 cg,
@@ -634,69 +634,41 @@ __device__ __forceinline__ void store_quad(const RasterOut &O, int b, int H, int
   if (O.tri_id) *reinterpret_cast<int4 *>(O.tri_id + b * plane + pix) = tid4;
 }
 
-// grid = resident CTAs (persistent); block = 256.
-constexpr int RT_BIG_AREA = 32;   // pixel-box area (inside the tile) above which a triangle is rasterised by the whole CTA
-constexpr int RT_BIG_CAP = 192;   // queue of such triangles per tile (overflow: the owning thread loops)
-constexpr int RT_UNIT_DONE = INT_MAX;
-static_assert(RT_PIX == RT_THREADS, "one pixel per thread in the cooperative and resolve phases");
-
-// Next work unit for this CTA (thread 0 only): >= 0 a non-empty item, < 0 background chunk
-// -(k + 1).  A CTA keeps drawing its preferred kind until that runs out, then switches.
-__device__ __forceinline__ int next_unit(int32_t *wc, int n_heavy, int n_light_units,
-                                         bool &prefer_light) {
-#pragma unroll 1
-  for (int k = 0; k < 2; ++k) {
-    if (prefer_light) {
-      const int u = atomicAdd(wc + RT_WC_TICKET_L, 1);
-      if (u < n_light_units) return -(u + 1);
-    } else {
-      const int u = atomicAdd(wc + RT_WC_TICKET_H, 1);
-      if (u < n_heavy) return u;
-    }
-    prefer_light = !prefer_light;
+// 4a.  One warp per image row (grid-stride over the B * H rows); a lane's quads are 32 apart, so
+// every store instruction of the warp writes 512 contiguous bytes.  Launched FIRST in the render
+// call: it depends on nothing the other passes produce, releases its dependents at once and
+// occupies a few CTAs per SM, so setup ... cover run beside it; only 4c waits for it.
+__global__ void __launch_bounds__(256, 8)
+raster_clear_kernel(Renderer R, RasterOut O, int n_batch) {
+  pdl_launch_dependents();
+  const int W = R.W, H = R.H, lane = threadIdx.x & 31;
+  const int n_warps = (gridDim.x * blockDim.x) >> 5;
+  const int n_rows = n_batch * H;
+  const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; row < n_rows; row += n_warps) {
+    const int b = row / H, y = row - b * H;
+    for (int x = lane * 4; x < W; x += 128)
+      store_quad(O, b, H, W, y, x, z, z, z, z, make_int4(-1, -1, -1, -1));
   }
-  return RT_UNIT_DONE;
 }
 
-__global__ void __launch_bounds__(RT_THREADS, 4)
-raster_tile_kernel(Renderer R, const int32_t *__restrict__ cls_idx,
-                   const float *__restrict__ poses, Cam cam, RasterOut O, int n_tiles, int n_batch) {
+// 4b.  Persistent; one non-empty (tile, pair) item per ticket.
+__global__ void __launch_bounds__(RT_CV_THREADS, 8)
+raster_cover_kernel(Renderer R, int n_tiles) {
   __shared__ unsigned long long zbuf[RT_PIX];
-  __shared__ TileOut out;
   __shared__ int s_unit[2];
   __shared__ int s_big[RT_BIG_CAP];
   __shared__ int s_nbig;
-  const int W = R.W, H = R.H;
-  const int n_total = n_tiles * n_batch;
+  pdl_wait();
   const int n_heavy = R.work_count[RT_WC_HEAVY];
-  const int n_light_units = (n_total - n_heavy + RT_BG_CHUNK - 1) / RT_BG_CHUNK;
-  // the rasterising items are latency-bound, the background chunks bandwidth-bound: one CTA in
-  // four starts on the background so that its stores overlap the others' rasterisation
-  bool prefer_light = (blockIdx.x & 3) == 3;
-  // store phase: quad q of a tile = 4 adjacent pixels of one row
-  const int sub = threadIdx.x / RT_QUADS, q = threadIdx.x % RT_QUADS;
-  const int row4 = q / (RT_TW / 4), xq = (q % (RT_TW / 4)) * 4;
-  if (threadIdx.x == 0) s_unit[0] = next_unit(R.work_count, n_heavy, n_light_units, prefer_light);
+  if (threadIdx.x == 0) s_unit[0] = atomicAdd(R.work_count + RT_WC_TICKET_H, 1);
   __syncthreads();
   for (int par = 0;; par ^= 1) {
     const int unit = s_unit[par];
-    if (unit == RT_UNIT_DONE) break;
-    if (threadIdx.x == 0)  // next ticket, early
-      s_unit[par ^ 1] = next_unit(R.work_count, n_heavy, n_light_units, prefer_light);
-    if (unit < 0) {
-      // ---- background chunk: depth 0, mask 0, image 0 - mean, bgr 0, tri -1
-      const int first = n_heavy + (-unit - 1) * RT_BG_CHUNK;
-      const int last = min(first + RT_BG_CHUNK, n_total);
-      const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll 2
-      for (int wi = first + sub; wi < last; wi += RT_BG_TILES) {
-        const int work = __ldg(R.work_list + wi);
-        const int b = work >> 16;
-        const int y = ((work >> 8) & 0xff) * RT_TH + row4, x = (work & 0xff) * RT_TW + xq;
-        if (y < H && x < W) store_quad(O, b, H, W, y, x, z, z, z, z, make_int4(-1, -1, -1, -1));
-      }
-      __syncthreads();  // s_unit[par ^ 1] visible; s_unit[par] free for the ticket after next
-      continue;
+    if (unit >= n_heavy) break;
+    if (threadIdx.x == 0) {  // next ticket, early
+      s_unit[par ^ 1] = atomicAdd(R.work_count + RT_WC_TICKET_H, 1);
+      s_nbig = 0;
     }
     const int work = R.work_list[unit];
     const int b = work >> 16;
@@ -706,13 +678,12 @@ raster_tile_kernel(Renderer R, const int32_t *__restrict__ cls_idx,
     const int first = start[tile];
     const int n = min(start[tile + 1], R.list_cap) - first;
     const TriRec *recs = R.recs + (size_t)b * 2 * R.max_tris;
-    zbuf[threadIdx.x] = ~0ull;
-    if (threadIdx.x == 0) s_nbig = 0;
+#pragma unroll
+    for (int k = 0; k < RT_PIX / RT_CV_THREADS; ++k) zbuf[threadIdx.x + k * RT_CV_THREADS] = ~0ull;
     __syncthreads();
-    // ---- (1a) coverage, one thread per triangle of the tile's list; triangles whose pixel box
-    // inside the tile is large are queued for the whole CTA instead
+    // ---- one thread per triangle of the tile's list
     const int32_t *list = R.tile_list + (size_t)b * R.list_cap + first;
-    for (int i = threadIdx.x; i < n; i += RT_THREADS) {
+    for (int i = threadIdx.x; i < n; i += RT_CV_THREADS) {
       const int ri = list[i];
       const int4 *rp = reinterpret_cast<const int4 *>(recs + ri);
       const int4 q0 = __ldg(rp), q1 = __ldg(rp + 1), q2 = __ldg(rp + 2), q3 = __ldg(rp + 3);
@@ -757,79 +728,99 @@ raster_tile_kernel(Renderer R, const int32_t *__restrict__ cls_idx,
       }
     }
     __syncthreads();
-    // ---- (1b) the queued large triangles: every thread tests its own pixel (same integer edge
+    // ---- the queued large triangles: every thread tests its own pixels (same integer edge
     // functions, same depth expression), so no atomics are needed
-    const int px_x = tx0 + (threadIdx.x & (RT_TW - 1)), px_y = ty0 + (threadIdx.x >> RT_TW_SHIFT);
-    unsigned long long best = zbuf[threadIdx.x];
+    unsigned long long best[RT_PIX / RT_CV_THREADS];
+#pragma unroll
+    for (int k = 0; k < RT_PIX / RT_CV_THREADS; ++k) best[k] = zbuf[threadIdx.x + k * RT_CV_THREADS];
     {
       const int n_big = min(s_nbig, RT_BIG_CAP);
-      const long long px = (long long)px_x << RT_SUB, py = (long long)px_y << RT_SUB;
 #pragma unroll 1
       for (int j = 0; j < n_big; ++j) {
         const int ri = s_big[j];
         const int4 *rp = reinterpret_cast<const int4 *>(recs + ri);
-        const int4 q0 = __ldg(rp), q1 = __ldg(rp + 1), q2 = __ldg(rp + 2);
-        if (px_x < (q1.w & 0xffff) || px_x > (q2.x & 0xffff) || px_y < (q1.w >> 16) ||
-            px_y > (q2.x >> 16))
-          continue;
+        const int4 q0 = __ldg(rp), q1 = __ldg(rp + 1), q2 = __ldg(rp + 2), q3 = __ldg(rp + 3);
         const long long ax = q0.x, ay = q0.y, bx = q0.z, by = q0.w, cx = q1.x, cy = q1.y;
-        const long long w0 = edge_fn(bx, by, cx, cy, px, py);
-        const long long w1 = edge_fn(cx, cy, ax, ay, px, py);
-        const long long w2 = edge_fn(ax, ay, bx, by, px, py);
         const int bias0 = tie_bias(cx - bx, cy - by), bias1 = tie_bias(ax - cx, ay - cy),
                   bias2 = tie_bias(bx - ax, by - ay);
-        if (((w0 + bias0) | (w1 + bias1) | (w2 + bias2)) >= 0) {
-          const int4 q3 = __ldg(rp + 3);
-          const double zwa = __hiloint2double(q2.w, q2.z), zwb = __hiloint2double(q3.y, q3.x),
-                       zwc = __hiloint2double(q3.w, q3.z);
-          const double inv_area = 1.0 / (double)edge_fn(ax, ay, bx, by, cx, cy);
-          const double dzb = (zwb - zwa) * inv_area, dzc = (zwc - zwa) * inv_area;
-          const float d = (float)(zwa + (double)w1 * dzb + (double)w2 * dzc);
-          if (d >= 0.0f && d <= 1.0f) {
-            const unsigned long long key =
-                ((unsigned long long)__float_as_uint(d) << 32) | (unsigned)ri;
-            best = min(best, key);
+        const double zwa = __hiloint2double(q2.w, q2.z), zwb = __hiloint2double(q3.y, q3.x),
+                     zwc = __hiloint2double(q3.w, q3.z);
+        const double inv_area = 1.0 / (double)edge_fn(ax, ay, bx, by, cx, cy);
+        const double dzb = (zwb - zwa) * inv_area, dzc = (zwc - zwa) * inv_area;
+#pragma unroll
+        for (int k = 0; k < RT_PIX / RT_CV_THREADS; ++k) {
+          const int p = threadIdx.x + k * RT_CV_THREADS;
+          const int px_x = tx0 + (p & (RT_TW - 1)), px_y = ty0 + (p >> RT_TW_SHIFT);
+          if (px_x < (q1.w & 0xffff) || px_x > (q2.x & 0xffff) || px_y < (q1.w >> 16) ||
+              px_y > (q2.x >> 16))
+            continue;
+          const long long px = (long long)px_x << RT_SUB, py = (long long)px_y << RT_SUB;
+          const long long w0 = edge_fn(bx, by, cx, cy, px, py);
+          const long long w1 = edge_fn(cx, cy, ax, ay, px, py);
+          const long long w2 = edge_fn(ax, ay, bx, by, px, py);
+          if (((w0 + bias0) | (w1 + bias1) | (w2 + bias2)) >= 0) {
+            const float d = (float)(zwa + (double)w1 * dzb + (double)w2 * dzc);
+            if (d >= 0.0f && d <= 1.0f) {
+              const unsigned long long key =
+                  ((unsigned long long)__float_as_uint(d) << 32) | (unsigned)ri;
+              best[k] = min(best[k], key);
+            }
           }
         }
       }
     }
-    // ---- (2) resolve: this thread's pixel; the results are staged in shared memory as planes
-    {
-      float dz = 0.f, cr = 0.f, cg = 0.f, cb = 0.f;
-      int tid = -1;
-      if (best != ~0ull && px_x < W && px_y < H) {
-        // readback linearisation, render_py_multi.py:139-145, float32 like numpy
-        const float d = __uint_as_float((unsigned)(best >> 32));
-        dz = (d == 1.0f) ? 0.f : O.lin_c0 / (O.lin_c1 - O.lin_c2 * (2.0f * d - 1.0f));
-        const TriRec rec = recs[(unsigned)best];
-        tid = rec.tri & RT_TRI_MASK;
-        if (O.image_chw || O.bgr_hwc) {
-          const Shaded s = shade_pixel(R, O, cam, __ldg(cls_idx + b), rec, poses + b * 12, b, px_x, px_y);
-          cr = s.c[0];
-          cg = s.c[1];
-          cb = s.c[2];
-        }
+    unsigned long long *zw = R.zwin + (size_t)unit * RT_PIX;
+#pragma unroll
+    for (int k = 0; k < RT_PIX / RT_CV_THREADS; ++k) zw[threadIdx.x + k * RT_CV_THREADS] = best[k];
+    __syncthreads();  // z-buffer and queue reused by the next item; next ticket visible
+  }
+}
+
+// 4c.  Grid-stride over the non-empty items, one thread per pixel, no shared memory.
+__global__ void __launch_bounds__(RT_THREADS, 3)
+raster_resolve_kernel(Renderer R, const int32_t *__restrict__ cls_idx,
+                      const float *__restrict__ poses, Cam cam, RasterOut O) {
+  const int W = R.W, H = R.H;
+  const int n_heavy = R.work_count[RT_WC_HEAVY];
+  const size_t plane = (size_t)H * W;
+  for (int unit = blockIdx.x; unit < n_heavy; unit += gridDim.x) {
+    const int work = __ldg(R.work_list + unit);
+    const int b = work >> 16;
+    const int x = (work & 0xff) * RT_TW + (threadIdx.x & (RT_TW - 1));
+    const int y = ((work >> 8) & 0xff) * RT_TH + (threadIdx.x >> RT_TW_SHIFT);
+    if (x >= W || y >= H) continue;
+    const unsigned long long key = R.zwin[(size_t)unit * RT_PIX + threadIdx.x];
+    float dz = 0.f, cr = 0.f, cg = 0.f, cb = 0.f;
+    int tid = -1;
+    if (key != ~0ull) {
+      // readback linearisation, render_py_multi.py:139-145, float32 like numpy
+      const float d = __uint_as_float((unsigned)(key >> 32));
+      dz = (d == 1.0f) ? 0.f : O.lin_c0 / (O.lin_c1 - O.lin_c2 * (2.0f * d - 1.0f));
+      const TriRec rec = R.recs[(size_t)b * 2 * R.max_tris + (unsigned)key];
+      tid = rec.tri & RT_TRI_MASK;
+      if (O.image_chw || O.bgr_hwc) {
+        const Shaded s = shade_pixel(R, O, cam, __ldg(cls_idx + b), rec, poses + b * 12, b, x, y);
+        cr = s.c[0];
+        cg = s.c[1];
+        cb = s.c[2];
       }
-      out.d[threadIdx.x] = dz;
-      out.r[threadIdx.x] = cr;
-      out.g[threadIdx.x] = cg;
-      out.b[threadIdx.x] = cb;
-      zbuf[threadIdx.x] = (unsigned long long)(unsigned)tid;  // own slot: nobody else reads the key
     }
-    __syncthreads();
-    // ---- (3) store: four adjacent pixels per thread
-    if (threadIdx.x < RT_QUADS) {
-      const int y = ty0 + row4, x = tx0 + xq, p = row4 * RT_TW + xq;
-      if (y < H && x < W) {
-        const float4 dz = *reinterpret_cast<const float4 *>(out.d + p);
-        const float4 cr = *reinterpret_cast<const float4 *>(out.r + p);
-        const float4 cg = *reinterpret_cast<const float4 *>(out.g + p);
-        const float4 cb = *reinterpret_cast<const float4 *>(out.b + p);
-        const int4 t4 = make_int4((int)zbuf[p], (int)zbuf[p + 1], (int)zbuf[p + 2], (int)zbuf[p + 3]);
-        store_quad(O, b, H, W, y, x, dz, cr, cg, cb, t4);
-      }
+    const size_t pix = (size_t)y * W + x;
+    O.depth[b * plane + pix] = dz;
+    if (O.mask) O.mask[b * plane + pix] = dz > O.mask_thresh ? 1.f : 0.f;
+    if (O.image_chw) {
+      float *img = O.image_chw + (size_t)b * 3 * plane + pix;
+      img[0] = cr - O.mean[0];
+      img[plane] = cg - O.mean[1];
+      img[2 * plane] = cb - O.mean[2];
     }
-    __syncthreads();  // z-buffer / staging reused by the next unit; next ticket visible
+    if (O.bgr_hwc) {
+      float *o = O.bgr_hwc + ((size_t)b * plane + pix) * 3;
+      o[0] = cb;
+      o[1] = cg;
+      o[2] = cr;
+    }
+    if (O.tri_id) O.tri_id[b * plane + pix] = tid;
   }
 }
 
@@ -848,7 +839,7 @@ static int dev_alloc(T **p, size_t n) {
 static void renderer_free(Renderer *r) {
   if (!r) return;
   void *ptrs[] = {r->verts, r->uv, r->normals, r->tris, r->mesh_tri_off, r->mesh_has, r->tex,
-                  r->tex_off, r->tex_hw, r->recs, r->bbox, r->clip_list, r->work_count, r->tile_start, r->tile_fill,
+                  r->tex_off, r->tex_hw, r->recs, r->bbox, r->clip_list, r->zwin, r->work_count, r->tile_start, r->tile_fill,
                   r->tile_list, r->work_list};
   for (void *p : ptrs)
     if (p) cudaFree(p);
@@ -948,6 +939,7 @@ int rc_renderer_create(const rc_mesh_desc *meshes, int n_meshes, int height, int
   RC_TRY(rc::dev_alloc(&r->work_count, (size_t)max_batch * n_tiles + rc::RT_WC_INTS));  // [header | tile counts]
   r->tile_count = r->work_count + rc::RT_WC_INTS;
   RC_TRY(rc::dev_alloc(&r->work_list, (size_t)max_batch * n_tiles));
+  RC_TRY(rc::dev_alloc(&r->zwin, (size_t)max_batch * n_tiles * rc::RT_PIX));
   RC_TRY(rc::dev_alloc(&r->tile_start, (size_t)max_batch * (n_tiles + 1)));
   RC_TRY(rc::dev_alloc(&r->tile_fill, (size_t)max_batch * n_tiles));
   RC_TRY(rc::dev_alloc(&r->tile_list, (size_t)max_batch * r->list_cap));
@@ -1016,33 +1008,60 @@ int rc_render_dev(void *handle, const rc_render_args *a) {
     return RC_OK;
   };
   int st;
-  if ((st = mark(0)) != RC_OK) return st;
-  RC_CUDA_TRY(cudaMemsetAsync(R.work_count, 0,
-                              sizeof(int32_t) * ((size_t)B * n_tiles + rc::RT_WC_INTS), s));
-  dim3 gs((R.max_tris + 255) / 256, B);
-  rc::raster_setup_kernel<<<gs, 256, 0, s>>>(R, a->cls_idx, a->poses, cam, n_tiles);
-  rc::raster_clip_kernel<<<32, 128, 0, s>>>(R, a->cls_idx, a->poses, cam, n_tiles);
-  if ((st = mark(1)) != RC_OK) return st;
-  rc::raster_scan_kernel<<<B, 256, 0, s>>>(R, n_tiles, a->status);
-  if ((st = mark(2)) != RC_OK) return st;
-  dim3 gf((2 * R.max_tris + 255) / 256, B);
-  rc::raster_fill_kernel<<<gf, 256, 0, s>>>(R, a->cls_idx, n_tiles);
-  if ((st = mark(3)) != RC_OK) return st;
-  // persistent grid: every CTA that can be resident, no more (units come from a ticket counter)
-  static int sm_count = 0, per_sm = 0;
+  static int sm_count = 0, cover_per_sm = 0, resolve_per_sm = 0;
   if (sm_count == 0) {
     if (cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, R.device) != cudaSuccess)
       sm_count = 148;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, rc::raster_tile_kernel,
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&cover_per_sm, rc::raster_cover_kernel,
+                                                      rc::RT_CV_THREADS, 0) != cudaSuccess ||
+        cover_per_sm < 1)
+      cover_per_sm = 4;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resolve_per_sm, rc::raster_resolve_kernel,
                                                       rc::RT_THREADS, 0) != cudaSuccess ||
-        per_sm < 1)
-      per_sm = 2;
+        resolve_per_sm < 1)
+      resolve_per_sm = 2;
   }
   const long long n_total = (long long)n_tiles * B;
-  long long gr = (long long)sm_count * per_sm;
-  if (gr > n_total) gr = n_total;
-  rc::raster_tile_kernel<<<(int)gr, rc::RT_THREADS, 0, s>>>(R, a->cls_idx, a->poses, cam, O,
-                                                             n_tiles, B);
+  // With event marks every launch is a normal one (clean per-kernel times); without, setup ...
+  // cover are chained by programmatic dependent launches behind the background pass: each waits
+  // (griddepcontrol.wait) for its predecessor only, none for the clear, which they never touch.
+  const bool chain = a->marks == nullptr;
+  if ((st = mark(0)) != RC_OK) return st;
+  RC_CUDA_TRY(cudaMemsetAsync(R.work_count, 0,
+                              sizeof(int32_t) * ((size_t)B * n_tiles + rc::RT_WC_INTS), s));
+  // 4a background first: a few CTAs per SM saturate the HBM write path and leave room beside them
+  static int clear_ctas = 0;
+  if (clear_ctas == 0) {
+    const char *e = getenv("RC_CLEAR_CTAS_PER_SM");  // tuning knob; default below
+    clear_ctas = e ? atoi(e) : 2;
+    if (clear_ctas < 1 || clear_ctas > 8) clear_ctas = 2;
+  }
+  rc::raster_clear_kernel<<<sm_count * clear_ctas, 256, 0, s>>>(R, O, B);
+  dim3 gs((R.max_tris + 255) / 256, B);
+  RC_CUDA_TRY(rc::launch_maybe_pdl(rc::raster_setup_kernel, gs, dim3(256), 0, s, chain, R,
+                                   a->cls_idx, a->poses, cam, n_tiles));
+  RC_CUDA_TRY(rc::launch_maybe_pdl(rc::raster_clip_kernel, dim3(32), dim3(128), 0, s, chain, R,
+                                   a->cls_idx, a->poses, cam, n_tiles));
+  if ((st = mark(1)) != RC_OK) return st;
+  RC_CUDA_TRY(rc::launch_maybe_pdl(rc::raster_scan_kernel, dim3(B), dim3(256), 0, s, chain, R,
+                                   n_tiles, a->status));
+  if ((st = mark(2)) != RC_OK) return st;
+  dim3 gf((2 * R.max_tris + 255) / 256, B);
+  RC_CUDA_TRY(rc::launch_maybe_pdl(rc::raster_fill_kernel, gf, dim3(256), 0, s, chain, R,
+                                   a->cls_idx, n_tiles));
+  if ((st = mark(3)) != RC_OK) return st;
+  {
+    long long g = (long long)sm_count * cover_per_sm;
+    if (g > n_total) g = n_total;
+    RC_CUDA_TRY(rc::launch_maybe_pdl(rc::raster_cover_kernel, dim3((unsigned)g),
+                                     dim3(rc::RT_CV_THREADS), 0, s, chain, R, n_tiles));
+  }
+  // 4c resolve: a normal launch, waits for everything before it, the background included
+  {
+    long long g = (long long)sm_count * resolve_per_sm * 2;
+    if (g > n_total) g = n_total;
+    rc::raster_resolve_kernel<<<(int)g, rc::RT_THREADS, 0, s>>>(R, a->cls_idx, a->poses, cam, O);
+  }
   if ((st = mark(4)) != RC_OK) return st;
   return rc::note_status(rc::check_launch());
 }

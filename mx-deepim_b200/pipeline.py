@@ -284,7 +284,7 @@ class RefineLoop(object):
         per iteration:  network stand-in -> pose update -> rasterise at the refined pose
                         (+ fused image post / mask) -> GT flow -> zoom (13 planes) -> PM loss
 
-    Everything stays on the device; one iteration is 1 (pose) + 1 memset + 4 (render) +
+    Everything stays on the device; one iteration is 1 (pose) + 1 memset + 7 (render) +
     4 (compare step) launches plus the stand-in's few elementwise torch kernels, and no host
     synchronisation.  The CNN is out of scope (north_star): `predict` is a pluggable callback
     (labels -> predictions); the default is the damped ground-truth update of SURVEY.md 8(d).
@@ -324,7 +324,8 @@ class RefineLoop(object):
         self.cur = 0
         self.bound = [None, None]
         self.obs = None
-        self.launches_per_iteration = 1 + 1 + 4 + self.step.launches_per_step
+        # pose update + 7 render kernels (clear, setup, clip, scan, fill, cover, resolve) + step
+        self.launches_per_iteration = 1 + 7 + self.step.launches_per_step
 
     def _damped_gt(self, it, rot_gt, trans_gt):
         """Stand-in for the FlowNet heads: move `damping` of the way to the target, plus noise."""

@@ -12,7 +12,7 @@ python - <<PY
 import json
 try:
     d=json.load(open("$OUT/bench_cfg${c}_$TAG.json"))
-    print("cfg$c", round(d["value"]), "pair-it/s  ms/step", round(d["ms_per_step"],3), {k:round(v,1) for k,v in d["kernel_us"].items()})
+    print("cfg$c", round(d["value"]), "pair-it/s  ms/step", round(d["ms_per_step"],3), {k:round(v,1) for k,v in d["kernel_us_serialised"].items()})
 except Exception as e: print("cfg$c failed", e)
 PY
 done
