@@ -154,15 +154,22 @@ __device__ __forceinline__ void make_record(double ax_, double ay_, double az_, 
     // dense mesh contain none and never reach the tile lists
     const int bias0 = tie_bias(X2 - X1, Y2 - Y1), bias1 = tie_bias(X0 - X2, Y0 - Y2),
               bias2 = tie_bias(X1 - X0, Y1 - Y0);
+    // edge functions at (px0, py0), then stepped: +256 in x adds -(dy) * 256, in y adds dx * 256
+    const long long qx = px0 << RT_SUB, qy = py0 << RT_SUB;
+    const long long r0 = edge_fn(X1, Y1, X2, Y2, qx, qy) + bias0;
+    const long long r1 = edge_fn(X2, Y2, X0, Y0, qx, qy) + bias1;
+    const long long r2 = edge_fn(X0, Y0, X1, Y1, qx, qy) + bias2;
+    const long long sx0 = -(Y2 - Y1) * 256, sx1 = -(Y0 - Y2) * 256, sx2 = -(Y1 - Y0) * 256;
+    const long long sy0 = (X2 - X1) * 256, sy1 = (X0 - X2) * 256, sy2 = (X1 - X0) * 256;
     bool any = false;
-    for (long long y = py0; y <= py1; ++y)
-      for (long long x = px0; x <= px1; ++x) {
-        const long long px = x << RT_SUB, py = y << RT_SUB;
-        const long long w0 = edge_fn(X1, Y1, X2, Y2, px, py);
-        const long long w1 = edge_fn(X2, Y2, X0, Y0, px, py);
-        const long long w2 = edge_fn(X0, Y0, X1, Y1, px, py);
-        any = any || (((w0 + bias0) | (w1 + bias1) | (w2 + bias2)) >= 0);
-      }
+    const int ny = (int)(py1 - py0), nx = (int)(px1 - px0);
+#pragma unroll
+    for (int j = 0; j < 3; ++j)
+#pragma unroll
+      for (int i = 0; i < 3; ++i)
+        if (j <= ny && i <= nx)
+          any = any || (((r0 + j * sy0 + i * sx0) | (r1 + j * sy1 + i * sx1) |
+                         (r2 + j * sy2 + i * sx2)) >= 0);
     if (!any) return;
   }
   r.bb_min = (int)((py0 << 16) | px0);
@@ -434,27 +441,31 @@ raster_scan_kernel(Renderer R, int n_tiles, int32_t *__restrict__ status) {
 }
 
 // ------------------------------------------------------------------- 3. fill
-// grid = (ceil(2 * max_tris / 256), B); one thread per record slot; reads the compact boxes.
+// grid = (ceil(max_tris / 256), B); one thread per triangle = its two record slots (the second
+// is live only for near-clipped triangles); reads the compact boxes with one 128-bit load.
 __global__ void __launch_bounds__(256)
 raster_fill_kernel(Renderer R, const int32_t *__restrict__ cls_idx, int n_tiles) {
   pdl_wait();
   pdl_launch_dependents();
   const int b = blockIdx.y;
-  const int s = blockIdx.x * blockDim.x + threadIdx.x;
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
   const int mesh = __ldg(cls_idx + b);
   const int n_tri = __ldg(R.mesh_tri_off + mesh + 1) - __ldg(R.mesh_tri_off + mesh);
   const int32_t *start = R.tile_start + (size_t)b * (n_tiles + 1);
   int32_t *fill = R.tile_fill + (size_t)b * n_tiles;
   int32_t *list = R.tile_list + (size_t)b * R.list_cap;
-  int2 bb = make_int2(0, -1);
-  if (s < 2 * n_tri) bb = __ldg(R.bbox + (size_t)b * 2 * R.max_tris + s);
-  for_each_tile(bb.x, bb.y, R.tiles_x, [&](int key) {
+  int4 bb = make_int4(0, -1, 0, -1);
+  if (t < n_tri) bb = __ldg(reinterpret_cast<const int4 *>(R.bbox + (size_t)b * 2 * R.max_tris) + t);
+  auto place = [&](int s, int key) {
     const int slot = tile_atomic(fill, key, true);
     if (key >= 0) {
       const int pos = start[key] + slot;
       if (pos < R.list_cap) list[pos] = s;
     }
-  });
+  };
+  for_each_tile(bb.x, bb.y, R.tiles_x, [&](int key) { place(2 * t, key); });
+  if (__any_sync(0xffffffffu, bb.w >= 0))
+    for_each_tile(bb.z, bb.w, R.tiles_x, [&](int key) { place(2 * t + 1, key); });
 }
 
 // ----------------------------------------------------------------- 4. raster
@@ -1046,7 +1057,7 @@ int rc_render_dev(void *handle, const rc_render_args *a) {
   RC_CUDA_TRY(rc::launch_maybe_pdl(rc::raster_scan_kernel, dim3(B), dim3(256), 0, s, chain, R,
                                    n_tiles, a->status));
   if ((st = mark(2)) != RC_OK) return st;
-  dim3 gf((2 * R.max_tris + 255) / 256, B);
+  dim3 gf((R.max_tris + 255) / 256, B);
   RC_CUDA_TRY(rc::launch_maybe_pdl(rc::raster_fill_kernel, gf, dim3(256), 0, s, chain, R,
                                    a->cls_idx, n_tiles));
   if ((st = mark(3)) != RC_OK) return st;
