@@ -49,6 +49,20 @@ def _peaks():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+def _traffic(kernel, grid):
+    """DRAM bytes per launch of `kernel` from the committed ncu --set full capture
+    (profiles/dram_traffic.json, written by scripts/ncu_summary.py), if it was captured on the
+    same launch shape; else None."""
+    path = os.path.join(ROOT, "profiles", "dram_traffic.json")
+    try:
+        rec = json.load(open(path))[kernel]
+        if int(rec["grid"]) == int(grid):
+            return rec["bytes_per_launch"], rec["source"]
+    except Exception:
+        pass
+    return None, None
+
+
 class ClockSampler(object):
     """nvidia-smi clocks / throttle reasons sampled every 100 ms while the GPU is under load."""
 
@@ -375,6 +389,9 @@ def run_ours(args, rank, world, local_rank):
         px = synth.H * synth.W
         kbytes = pipeline.BYTES_PER_PX_ZOOM_SAMPLE * px * B
         achieved = kbytes / (kernel_ms * 1e-3) / 1e9
+        # resampler grid: (W/128, H/8, B) -- the capture must be of the same launch shape
+        traffic, traffic_src = _traffic("zoom_sample_kernel",
+                                        ((synth.W + 127) // 128) * ((synth.H + 7) // 8) * B)
         step_bytes = pipeline.algorithmic_bytes_per_pair(synth.H, synth.W, synth.NUM_3D_SAMPLE) * B
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K,
@@ -392,9 +409,11 @@ def run_ours(args, rank, world, local_rank):
                            "formats": "uint8 BGR HWC images, uint16 mm depth, uint8 masks; decoded on "
                                       "device (image.transform / DEPTH_FACTOR / mask == idx); +6 launches"},
             "gpu_launches": step.launches_per_step * K,
+            # traffic < algorithmic bytes: zoom-in reads only the crop window of each source plane
             "roofline": {"bound": "hbm", "kernel": "zoom_sample_kernel", "achieved": achieved,
                          "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_source": peak_src,
+                         "traffic": traffic, "traffic_source": traffic_src,
+                         "peak_source": peak_src,
                          "kernel_us": kernel_ms * 1e3,
                          "algorithmic_bytes_per_launch": kbytes,
                          "step_achieved_gbs": step_bytes * K / (ms_max * 1e-3) / 1e9},

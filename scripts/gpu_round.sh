@@ -14,6 +14,7 @@ python bench.py --config $c --steps 40 --warmup 3 > $OUT/bench_cfg${c}_$TAG.json
 done
 python scripts/bench_kernels.py --batch 16 > $OUT/kernels_b16_$TAG.json 2> $OUT/kernels_b16_$TAG.err
 python scripts/bench_kernels.py --batch 64 > $OUT/kernels_b64_$TAG.json 2> $OUT/kernels_b64_$TAG.err
+python scripts/bench_raster.py > $OUT/raster_$TAG.json 2> $OUT/raster_$TAG.err
 CMD="python bench.py --steps 6 --warmup 3 --no-cpu-baseline"
 $CMD > $OUT/plain_$TAG.log 2>&1 && \
 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file $OUT/launches_$TAG.csv $CMD > $OUT/ncu_l_$TAG.log 2>&1
@@ -21,5 +22,5 @@ ncu --set full --clock-control none --import-source on -k regex:"zoom_sample|zoo
 CMD3="python bench.py --config 3 --steps 4 --warmup 3"
 $CMD3 > $OUT/plain3_$TAG.log 2>&1 && \
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $OUT/launches_cfg3_$TAG.csv $CMD3 > $OUT/ncu_l3_$TAG.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:"raster_" -s 30 -c 5 -o $OUT/prof_cfg3_$TAG -f $CMD3 > $OUT/ncu_f3_$TAG.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:"raster_" -s 42 -c 7 -o $OUT/prof_cfg3_$TAG -f $CMD3 > $OUT/ncu_f3_$TAG.log 2>&1
 tail -3 $OUT/pytest_$TAG.log; tail -1 $OUT/smoke_$TAG.log; cat $OUT/bench_$TAG.json; cat $OUT/bench_ref_$TAG.json; cat $OUT/bench_cfg3_$TAG.json $OUT/bench_cfg4_$TAG.json $OUT/bench_cfg5_$TAG.json

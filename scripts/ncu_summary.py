@@ -164,6 +164,19 @@ def main():
                 g(d, "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum"),
                 g(d, "smsp__inst_executed.sum")))
         md.append("")
+    if F:
+        # per-launch DRAM traffic of each captured kernel: what bench.py reports as roofline.traffic
+        tpath = os.path.join(PROF, "dram_traffic.json")
+        traffic = json.load(open(tpath)) if os.path.exists(tpath) else {}
+        for d in F:
+            name = re.sub(r"<.*", "", d["kernel"])
+            traffic[name] = {
+                "bytes_per_launch": g(d, "dram__bytes_read.sum") + g(d, "dram__bytes_write.sum"),
+                "read": g(d, "dram__bytes_read.sum"), "write": g(d, "dram__bytes_write.sum"),
+                "grid": g(d, "launch__grid_size"),
+                "source": "profiles/%s_ncu_full.csv (ncu --set full, one launch)" % tag}
+        with open(tpath, "w") as fh:
+            json.dump(traffic, fh, indent=1, sort_keys=True)
     with open(os.path.join(PROF, "%s_summary.md" % tag), "w") as fh:
         fh.write("\n".join(md) + "\n")
     print("\n".join(md))

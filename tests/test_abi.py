@@ -99,3 +99,39 @@ def test_gpu_flow_argument_checks():
     e = np.zeros((0, 1, 8, 8), np.float32)
     flow, valid = gpu_flow(e, e, np.zeros((0, 3, 4), np.float32), np.eye(3, dtype=np.float32))
     assert flow.shape == (0, 2, 8, 8) and valid.shape == (0, 1, 8, 8)
+
+
+def test_struct_layouts_match_header(tmp_path):
+    """sizeof / offsetof of every argument struct as gcc sees include/rendercompare.h against
+    the ctypes mirrors in _lib.py: a field added on one side only fails here, not on the GPU."""
+    import subprocess
+
+    from mx_deepim_b200 import _lib
+
+    structs = {
+        "rc_zoom_group": (_lib.rc_zoom_group, ["src", "dst", "channels", "flags", "mean"]),
+        "rc_compare_step_args": (_lib.rc_compare_step_args,
+                                 ["image_observed", "trans_gt", "flow", "loss_sum", "grad_rot",
+                                  "grad_zoom_trans", "pixel_means", "T_stds", "grad_scale",
+                                  "rot_coord", "zoom_grad", "batch_size", "num_points", "stream",
+                                  "marks"]),
+        "rc_mesh_desc": (_lib.rc_mesh_desc, ["vertices", "texture", "n_vertices", "tex_w"]),
+        "rc_render_args": (_lib.rc_render_args, ["cls_idx", "status", "K", "pixel_means", "znear",
+                                                 "mode", "batch_size", "stream", "marks"]),
+    }
+    lines = ['#include <stdio.h>', '#include <stddef.h>', '#include "rendercompare.h"',
+             'int main(void) {']
+    for name, (_, fields) in structs.items():
+        lines.append('printf("%s %%zu\\n", sizeof(%s));' % (name, name))
+        for f in fields:
+            lines.append('printf("%s.%s %%zu\\n", offsetof(%s, %s));' % (name, f, name, f))
+    lines += ['return 0;', '}']
+    src = tmp_path / "layout.c"
+    src.write_text("\n".join(lines))
+    exe = tmp_path / "layout"
+    subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)])
+    out = dict(l.split() for l in subprocess.check_output([str(exe)], text=True).splitlines())
+    for name, (cls, fields) in structs.items():
+        assert ctypes.sizeof(cls) == int(out[name]), name
+        for f in fields:
+            assert getattr(cls, f).offset == int(out["%s.%s" % (name, f)]), (name, f)
