@@ -84,12 +84,14 @@ struct Cam {
   double fx, fy, cx, cy, znear, zfar;
 };
 
-__device__ __forceinline__ long long edge_fn(long long ax, long long ay, long long bx, long long by,
-                                             long long px, long long py) {
-  return (bx - ax) * (py - ay) - (by - ay) * (px - ax);
+// Edge function on snapped coordinates.  |X|, |Y| < 2^28 (|u|, |v| < 1e6 px at 1/256 px), so every
+// difference fits in 32 bits and each product is ONE widening multiply (IMAD.WIDE) instead of a
+// 64 x 64-bit multiply sequence.
+__device__ __forceinline__ long long edge_fn(int ax, int ay, int bx, int by, int px, int py) {
+  return (long long)(bx - ax) * (long long)(py - ay) - (long long)(by - ay) * (long long)(px - ax);
 }
 
-__device__ __forceinline__ int tie_bias(long long dx, long long dy) {
+__device__ __forceinline__ int tie_bias(int dx, int dy) {
   return (dy > 0 || (dy == 0 && dx < 0)) ? 0 : -1;
 }
 
@@ -126,9 +128,9 @@ __device__ __forceinline__ void make_record(double ax_, double ay_, double az_, 
   if (!(fabs(u0) < 1e6 && fabs(v0) < 1e6 && fabs(u1) < 1e6 && fabs(v1) < 1e6 && fabs(u2) < 1e6 &&
         fabs(v2) < 1e6))
     return;
-  const long long X0 = (long long)rint(u0 * 256.0), Y0 = (long long)rint(v0 * 256.0);
-  long long X1 = (long long)rint(u1 * 256.0), Y1 = (long long)rint(v1 * 256.0);
-  long long X2 = (long long)rint(u2 * 256.0), Y2 = (long long)rint(v2 * 256.0);
+  const int X0 = __double2int_rn(u0 * 256.0), Y0 = __double2int_rn(v0 * 256.0);  // < 2^28 in magnitude
+  int X1 = __double2int_rn(u1 * 256.0), Y1 = __double2int_rn(v1 * 256.0);
+  int X2 = __double2int_rn(u2 * 256.0), Y2 = __double2int_rn(v2 * 256.0);
   const double zw0 = ((pa - pb * ia) + 1.0) * 0.5;
   double zw1 = ((pa - pb * ib) + 1.0) * 0.5;
   double zw2 = ((pa - pb * ic) + 1.0) * 0.5;
@@ -136,14 +138,14 @@ __device__ __forceinline__ void make_record(double ax_, double ay_, double az_, 
   if (area == 0) return;
   const bool sw = area < 0;
   if (sw) {  // orient so that the area is positive: record vertices (0, 2, 1)
-    long long t = X1; X1 = X2; X2 = t;
+    int t = X1; X1 = X2; X2 = t;
     t = Y1; Y1 = Y2; Y2 = t;
     const double z = zw1; zw1 = zw2; zw2 = z;
   }
-  const long long minx = min(X0, min(X1, X2)), maxx = max(X0, max(X1, X2));
-  const long long miny = min(Y0, min(Y1, Y2)), maxy = max(Y0, max(Y1, Y2));
-  long long px0 = (minx + 255) >> RT_SUB, px1 = maxx >> RT_SUB;
-  long long py0 = (miny + 255) >> RT_SUB, py1 = maxy >> RT_SUB;
+  const int minx = min(X0, min(X1, X2)), maxx = max(X0, max(X1, X2));
+  const int miny = min(Y0, min(Y1, Y2)), maxy = max(Y0, max(Y1, Y2));
+  int px0 = (minx + 255) >> RT_SUB, px1 = maxx >> RT_SUB;
+  int py0 = (miny + 255) >> RT_SUB, py1 = maxy >> RT_SUB;
   if (px0 < 0) px0 = 0;
   if (py0 < 0) py0 = 0;
   if (px1 > W - 1) px1 = W - 1;
@@ -155,14 +157,16 @@ __device__ __forceinline__ void make_record(double ax_, double ay_, double az_, 
     const int bias0 = tie_bias(X2 - X1, Y2 - Y1), bias1 = tie_bias(X0 - X2, Y0 - Y2),
               bias2 = tie_bias(X1 - X0, Y1 - Y0);
     // edge functions at (px0, py0), then stepped: +256 in x adds -(dy) * 256, in y adds dx * 256
-    const long long qx = px0 << RT_SUB, qy = py0 << RT_SUB;
+    const int qx = px0 << RT_SUB, qy = py0 << RT_SUB;
     const long long r0 = edge_fn(X1, Y1, X2, Y2, qx, qy) + bias0;
     const long long r1 = edge_fn(X2, Y2, X0, Y0, qx, qy) + bias1;
     const long long r2 = edge_fn(X0, Y0, X1, Y1, qx, qy) + bias2;
-    const long long sx0 = -(Y2 - Y1) * 256, sx1 = -(Y0 - Y2) * 256, sx2 = -(Y1 - Y0) * 256;
-    const long long sy0 = (X2 - X1) * 256, sy1 = (X0 - X2) * 256, sy2 = (X1 - X0) * 256;
+    const long long sx0 = -(long long)(Y2 - Y1) * 256, sx1 = -(long long)(Y0 - Y2) * 256,
+                    sx2 = -(long long)(Y1 - Y0) * 256;
+    const long long sy0 = (long long)(X2 - X1) * 256, sy1 = (long long)(X0 - X2) * 256,
+                    sy2 = (long long)(X1 - X0) * 256;
     bool any = false;
-    const int ny = (int)(py1 - py0), nx = (int)(px1 - px0);
+    const int ny = py1 - py0, nx = px1 - px0;
 #pragma unroll
     for (int j = 0; j < 3; ++j)
 #pragma unroll
@@ -174,8 +178,8 @@ __device__ __forceinline__ void make_record(double ax_, double ay_, double az_, 
   }
   r.bb_min = (int)((py0 << 16) | px0);
   r.bb_max = (int)((py1 << 16) | px1);
-  r.q0 = make_int4((int)X0, (int)Y0, (int)X1, (int)Y1);
-  r.q1 = make_int4((int)X2, (int)Y2,
+  r.q0 = make_int4(X0, Y0, X1, Y1);
+  r.q1 = make_int4(X2, Y2,
                    tri | (sw ? RT_FLAG_SWAPPED : 0) | (clipped ? RT_FLAG_CLIPPED : 0), r.bb_min);
   r.q2 = make_int4(r.bb_max, 0, __double2loint(zw0), __double2hiint(zw0));
   r.q3 = make_int4(__double2loint(zw1), __double2hiint(zw1), __double2loint(zw2),
@@ -509,7 +513,7 @@ __device__ Shaded shade_pixel(const Renderer &R, const RasterOut &O, const Cam &
   if (!(rec.tri & RT_FLAG_CLIPPED)) {
     // GL-style: screen-space barycentrics from the SNAPPED vertices (integer edge functions),
     // made perspective-correct with 1/w of the vertices.
-    const long long px = (long long)x << RT_SUB, py = (long long)y << RT_SUB;
+    const int px = x << RT_SUB, py = y << RT_SUB;
     const long long w0 = edge_fn(rec.x1, rec.y1, rec.x2, rec.y2, px, py);
     const long long w1 = edge_fn(rec.x2, rec.y2, rec.x0, rec.y0, px, py);
     const long long w2 = edge_fn(rec.x0, rec.y0, rec.x1, rec.y1, px, py);
@@ -707,18 +711,19 @@ raster_cover_kernel(Renderer R, int n_tiles) {
           continue;
         }
       }
-      const long long ax = q0.x, ay = q0.y, bx = q0.z, by = q0.w, cx = q1.x, cy = q1.y;
+      const int ax = q0.x, ay = q0.y, bx = q0.z, by = q0.w, cx = q1.x, cy = q1.y;
       const double zwa = __hiloint2double(q2.w, q2.z), zwb = __hiloint2double(q3.y, q3.x),
                    zwc = __hiloint2double(q3.w, q3.z);
       const int bias0 = tie_bias(cx - bx, cy - by), bias1 = tie_bias(ax - cx, ay - cy),
                 bias2 = tie_bias(bx - ax, by - ay);
-      const long long s0 = -(cy - by) * 256, s1 = -(ay - cy) * 256, s2 = -(by - ay) * 256;
+      const long long s0 = -(long long)(cy - by) * 256, s1 = -(long long)(ay - cy) * 256,
+                      s2 = -(long long)(by - ay) * 256;
       // window depth is affine in the pixel: d = zwa + w1 * dzb + w2 * dzc (one division per
       // triangle; the same expression in the cooperative path below)
       const double inv_area = 1.0 / (double)edge_fn(ax, ay, bx, by, cx, cy);
       const double dzb = (zwb - zwa) * inv_area, dzc = (zwc - zwa) * inv_area;
       for (int y = yl; y <= yh; ++y) {
-        const long long px = (long long)xl << RT_SUB, py = (long long)y << RT_SUB;
+        const int px = xl << RT_SUB, py = y << RT_SUB;
         long long w0 = edge_fn(bx, by, cx, cy, px, py);
         long long w1 = edge_fn(cx, cy, ax, ay, px, py);
         long long w2 = edge_fn(ax, ay, bx, by, px, py);
@@ -751,7 +756,7 @@ raster_cover_kernel(Renderer R, int n_tiles) {
         const int ri = s_big[j];
         const int4 *rp = reinterpret_cast<const int4 *>(recs + ri);
         const int4 q0 = __ldg(rp), q1 = __ldg(rp + 1), q2 = __ldg(rp + 2), q3 = __ldg(rp + 3);
-        const long long ax = q0.x, ay = q0.y, bx = q0.z, by = q0.w, cx = q1.x, cy = q1.y;
+        const int ax = q0.x, ay = q0.y, bx = q0.z, by = q0.w, cx = q1.x, cy = q1.y;
         const int bias0 = tie_bias(cx - bx, cy - by), bias1 = tie_bias(ax - cx, ay - cy),
                   bias2 = tie_bias(bx - ax, by - ay);
         const double zwa = __hiloint2double(q2.w, q2.z), zwb = __hiloint2double(q3.y, q3.x),
@@ -765,7 +770,7 @@ raster_cover_kernel(Renderer R, int n_tiles) {
           if (px_x < (q1.w & 0xffff) || px_x > (q2.x & 0xffff) || px_y < (q1.w >> 16) ||
               px_y > (q2.x >> 16))
             continue;
-          const long long px = (long long)px_x << RT_SUB, py = (long long)px_y << RT_SUB;
+          const int px = px_x << RT_SUB, py = px_y << RT_SUB;
           const long long w0 = edge_fn(bx, by, cx, cy, px, py);
           const long long w1 = edge_fn(cx, cy, ax, ay, px, py);
           const long long w2 = edge_fn(ax, ay, bx, by, px, py);

@@ -763,6 +763,9 @@ int launch_zoom_factor(const float *obs, const float *rend, const float *src_pos
   }
   const int max_bps = (quads + 256 * 4 - 1) / (256 * 4);
   int bps = (sm_count * (channels == 1 ? 2 : 1)) / batch_size;
+  // large batches fill the GPU several times over anyway: four blocks per sample keep the last
+  // wave short (1024 whole-sample blocks would be 1.7 waves of 592 resident blocks)
+  if (bps < 4 && batch_size >= sm_count) bps = 4;
   if (bps > max_bps) bps = max_bps;
   if (bps < 1) bps = 1;
   dim3 grid(bps, batch_size);

@@ -214,3 +214,46 @@ def test_linemod_light_and_single_model_renderers(cuda_device):
     bgr, depth = rn.render(R, t, lp, li, r_type="mat")
     o_bgr, o_depth = raster_np.render_py_light_modelnet(meshes[0], R, t, lp, li, K, r_type="mat")
     _compare(o_bgr.astype(np.float32), o_depth, bgr.astype(np.float32), depth, colour_tol=1.0)
+
+
+def test_chained_render_equals_serialised_full_size(cuda_device):
+    """BASELINE-sized property test (cfg 3 batch, cfg 5 mesh density): the production issue order
+    (setup ... cover chained behind the background pass by programmatic dependent launches) gives
+    bit-identical frames to the serialised order that event marks force, back to back over
+    changing poses, and every output plane is consistent with the depth plane."""
+    import torch
+
+    from mx_deepim_b200 import _lib, synth
+    from mx_deepim_b200.render import DeviceRenderer
+
+    rng = np.random.default_rng(5)
+    meshes = [synth.make_mesh(rng, level=4), synth.make_mesh(rng, level=5),
+              synth.make_mesh(rng, level=3, kind=2)]
+    B = 64
+    ren = DeviceRenderer(meshes, synth.K_LINEMOD, synth.W, synth.H, synth.ZNEAR, synth.ZFAR,
+                         max_batch=B, device=cuda_device)
+    cls = torch.from_numpy(rng.integers(0, len(meshes), size=B).astype(np.int32)).to(cuda_device)
+    means = (1.0, 2.0, 3.0)
+    want = ("depth", "image", "mask", "tri_id")
+    chained, serial = {}, {}
+    for rep, zr in enumerate(((0.6, 1.2), (0.3, 0.6), (0.6, 1.2))):
+        poses = _poses(B, 900 + rep)
+        poses[:, 2, 3] = rng.uniform(zr[0], zr[1], size=B)
+        pd = torch.from_numpy(poses).to(cuda_device)
+        ren.render_batch(cls, pd, pixel_means=means, want=want, out=chained)
+        marks = [_lib.Event() for _ in range(_lib.RC_RENDER_MARKS)]
+        ren.render_batch(cls, pd, pixel_means=means, want=want, out=serial, marks=marks)
+        torch.cuda.synchronize()
+        assert int(ren.status.item()) == 0
+        for k in want:
+            assert torch.equal(chained[k], serial[k]), (rep, k)
+        depth, tri = chained["depth"], chained["tri_id"]
+        assert torch.equal(chained["mask"], (depth > 0.2).float())
+        assert torch.equal(tri[:, None] >= 0, depth > 0)  # a winner everywhere a depth was written
+        bg = (depth == 0).expand(-1, 3, -1, -1)
+        img = chained["image"]
+        for c in range(3):
+            assert bool((img[:, c][bg[:, c]] == -means[c]).all())
+        fg = depth[depth > 0]
+        assert float(fg.min()) >= synth.ZNEAR * (1 - 1e-6) and float(fg.max()) <= synth.ZFAR
+        assert int((depth > 0).sum()) > 1000 * B / 4
