@@ -369,6 +369,13 @@ int rc_pose_update_dev(const float *src_pose, const float *rot_est, const float 
                        const float *T_stds, int rot_coord, float *refined_pose, float *rot_res,
                        float *trans_res, float *KT, int batch_size, void *stream);
 
+/* Synthetic-workload utility (not a reference interface): the network stand-in of SURVEY.md 8(d)
+ * for refine loops without the CNN -- rot_est = normalise((1-a) * identity + a * rot_gt + noise_q),
+ * trans_est = a * trans_gt + noise_t; all arrays device float32 ([B,4] / [B,3]). */
+int rc_standin_predict_dev(const float *rot_gt, const float *trans_gt, const float *noise_q,
+                           const float *noise_t, float damping, float *rot_est, float *trans_est,
+                           int batch_size, void *stream);
+
 /* ------------------------------------------------ test-time mask policies (8(f) rank 1)
  * The "box_rendered" / "box_observed" branches of update_data_batch,
  * lib/pair_matching/data_pair.py:101-131 (fed by deepim/core/tester.py:571-594): the new

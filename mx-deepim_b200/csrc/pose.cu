@@ -52,6 +52,54 @@ __device__ void sym4_max_eigvec(double A[4][4], double v[4]) {
   for (int k = 0; k < 4; ++k) v[k] = V[k][best];
 }
 
+// Fast path for the matrices mat2quat actually sees.  For a rotation matrix the 4x4 K of
+// RT_transform.py:497-507 has the eigenvalues {1, -1/3, -1/3, -1/3}; the float32-rounded poses
+// of the path perturb them by ~1e-7.  Power iteration on K + I/3 therefore contracts everything
+// but the wanted eigenvector by ~1e-7 per step: five steps from the largest column reach double
+// precision, where 24 Jacobi sweeps are a ~35k-cycle dependent chain on ONE thread per pair (the
+// whole refine iteration waits for this kernel).  The result is accepted only if it is an
+// eigenvector to 1e-14 AND its Rayleigh quotient dominates the spectrum bound of the rest
+// (trace argument); anything else (a far-from-orthonormal M) falls back to Jacobi.
+__device__ bool sym4_max_eigvec_shifted_power(const double K[4][4], double v[4]) {
+  double S[4][4];
+  for (int i = 0; i < 4; ++i)
+    for (int j = 0; j < 4; ++j) S[i][j] = K[i][j] + (i == j ? 1.0 / 3.0 : 0.0);
+  int best = 0;
+  double bn = -1.0;
+  for (int j = 0; j < 4; ++j) {
+    const double n = S[0][j] * S[0][j] + S[1][j] * S[1][j] + S[2][j] * S[2][j] + S[3][j] * S[3][j];
+    if (n > bn) {
+      bn = n;
+      best = j;
+    }
+  }
+  if (!(bn > 1e-4)) return false;
+  double x[4] = {S[0][best], S[1][best], S[2][best], S[3][best]};
+  for (int it = 0; it < 5; ++it) {
+    double y[4];
+    for (int i = 0; i < 4; ++i) y[i] = S[i][0] * x[0] + S[i][1] * x[1] + S[i][2] * x[2] + S[i][3] * x[3];
+    const double inv = rsqrt(y[0] * y[0] + y[1] * y[1] + y[2] * y[2] + y[3] * y[3]);
+    for (int i = 0; i < 4; ++i) x[i] = y[i] * inv;
+  }
+  // residual of K x = lambda x
+  double kx[4], lam = 0.0;
+  for (int i = 0; i < 4; ++i) {
+    kx[i] = K[i][0] * x[0] + K[i][1] * x[1] + K[i][2] * x[2] + K[i][3] * x[3];
+    lam += kx[i] * x[i];
+  }
+  double res = 0.0;
+  for (int i = 0; i < 4; ++i) res += (kx[i] - lam * x[i]) * (kx[i] - lam * x[i]);
+  // the other three eigenvalues sum to trace - lam; with sum of squares ||K||_F^2 - lam^2 none of
+  // them can exceed sqrt(that): lam must beat it to be the largest
+  double fro = 0.0;
+  for (int i = 0; i < 4; ++i)
+    for (int j = 0; j < 4; ++j) fro += K[i][j] * K[i][j];
+  const double rest = fro - lam * lam;
+  if (!(res < 1e-28) || !(lam > 0.0) || !(rest < lam * lam)) return false;
+  for (int i = 0; i < 4; ++i) v[i] = x[i];
+  return true;
+}
+
 // mat2quat, RT_transform.py:446-523 (w, x, y, z with w >= 0).
 __device__ void mat2quat(const double M[9], double q[4]) {
   const double Qxx = M[0], Qyx = M[1], Qzx = M[2], Qxy = M[3], Qyy = M[4], Qzy = M[5], Qxz = M[6],
@@ -70,7 +118,7 @@ __device__ void mat2quat(const double M[9], double q[4]) {
   for (int i = 0; i < 4; ++i)
     for (int j = i + 1; j < 4; ++j) K[i][j] = K[j][i];  // eigh reads the lower triangle
   double v[4];
-  sym4_max_eigvec(K, v);
+  if (!sym4_max_eigvec_shifted_power(K, v)) sym4_max_eigvec(K, v);
   q[0] = v[3];
   q[1] = v[0];
   q[2] = v[1];
@@ -207,6 +255,25 @@ __global__ void pose_update_kernel(const float *__restrict__ src_pose, const flo
     }
 }
 
+// Stand-in for the FlowNet heads in synthetic refine loops ("predicted (q, t) =
+// calc_RT_delta(src, tgt) damped by 0.5 + N(0, small)").  The CNN is out of scope; this keeps the
+// stand-in at one launch so that it does not weigh on the measured loop.
+__global__ void standin_predict_kernel(const float *__restrict__ rot_gt, const float *__restrict__ trans_gt,
+                                       const float *__restrict__ noise_q, const float *__restrict__ noise_t,
+                                       float damping, float *__restrict__ rot_est,
+                                       float *__restrict__ trans_est, int B) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  float q[4], n2 = 0.f;
+  for (int i = 0; i < 4; ++i) {
+    q[i] = (1.f - damping) * (i == 0 ? 1.f : 0.f) + damping * rot_gt[b * 4 + i] + noise_q[b * 4 + i];
+    n2 += q[i] * q[i];
+  }
+  const float inv = 1.f / sqrtf(n2);  // L2Normalization upstream of the pose update
+  for (int i = 0; i < 4; ++i) rot_est[b * 4 + i] = q[i] * inv;
+  for (int i = 0; i < 3; ++i) trans_est[b * 3 + i] = damping * trans_gt[b * 3 + i] + noise_t[b * 3 + i];
+}
+
 }  // namespace rc
 
 extern "C" {
@@ -231,6 +298,17 @@ int rc_pose_update_dev(const float *src_pose, const float *rot_est, const float 
   rc::pose_update_kernel<<<(batch_size + 63) / 64, 64, 0, static_cast<cudaStream_t>(stream)>>>(
       src_pose, rot_est, trans_est, tgt_pose, K, pp, refined_pose, rot_res, trans_res, KT,
       batch_size);
+  return rc::note_status(rc::check_launch());
+}
+
+int rc_standin_predict_dev(const float *rot_gt, const float *trans_gt, const float *noise_q,
+                           const float *noise_t, float damping, float *rot_est, float *trans_est,
+                           int batch_size, void *stream) {
+  RC_REQUIRE(batch_size >= 0, RC_ERR_INVALID_ARG);
+  if (batch_size == 0) return rc::note_status(RC_OK);
+  RC_REQUIRE(rot_gt && trans_gt && noise_q && noise_t && rot_est && trans_est, RC_ERR_INVALID_ARG);
+  rc::standin_predict_kernel<<<(batch_size + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(
+      rot_gt, trans_gt, noise_q, noise_t, damping, rot_est, trans_est, batch_size);
   return rc::note_status(rc::check_launch());
 }
 

@@ -324,15 +324,19 @@ class RefineLoop(object):
         self.cur = 0
         self.bound = [None, None]
         self.obs = None
-        # pose update + 7 render kernels (clear, setup, clip, scan, fill, cover, resolve) + step
-        self.launches_per_iteration = 1 + 7 + self.step.launches_per_step
+        # stand-in + pose update + 7 render kernels (clear, setup, clip, scan, fill, cover,
+        # resolve) + step
+        self.launches_per_iteration = 1 + 1 + 7 + self.step.launches_per_step
 
     def _damped_gt(self, it, rot_gt, trans_gt):
-        """Stand-in for the FlowNet heads: move `damping` of the way to the target, plus noise."""
-        a = self.damping
-        q = (1.0 - a) * self.identity_q + a * rot_gt + self.noise_q[it % 8]
-        torch.div(q, q.norm(dim=1, keepdim=True), out=self.rot_est)  # L2Normalization upstream
-        torch.add(a * trans_gt, self.noise_t[it % 8], out=self.trans_est)
+        """Stand-in for the FlowNet heads: move `damping` of the way to the target, plus noise
+        (one launch: rc_standin_predict_dev)."""
+        with torch.cuda.device(self.device):
+            st = _lib.load().rc_standin_predict_dev(
+                rot_gt.data_ptr(), trans_gt.data_ptr(), self.noise_q[it % 8].data_ptr(),
+                self.noise_t[it % 8].data_ptr(), self.damping, self.rot_est.data_ptr(),
+                self.trans_est.data_ptr(), self.B, _lib.stream_ptr(None))
+        _lib.check(st, "rc_standin_predict_dev")
 
     def set_batch(self, host):
         """Observed side of the batch + initial poses.  `host`: numpy dict with image_observed,
