@@ -518,6 +518,10 @@ def run_refine(args, rank, world, local_rank):
             "config": {"workload": cfg["name"], "batch_per_gpu": B, "iterations_per_loop": iters,
                        "triangles_per_mesh": len(meshes[0]["triangles"]), "meshes": len(meshes),
                        "backward": bool(loop.step.backward),
+                       "render_background": "incremental: the loop owns depth/image/mask_rendered, so "
+                                            "each render re-clears only the tiles its previous frame "
+                                            "covered (rc_render_args.incremental); frames bit-identical "
+                                            "to a full render (tests/test_raster_gpu.py)",
                        "l2": "per-iteration traffic %.0f MB > 126 MB L2" % (
                            (pipeline.algorithmic_bytes_per_pair(synth.H, synth.W, synth.NUM_3D_SAMPLE)
                             + 20 * px) * B / 1e6)},

@@ -345,6 +345,12 @@ typedef struct rc_render_args {
   float znear, zfar, mask_thresh, brightness_ratio;
   int32_t mode;               /* RC_RENDER_*                                           */
   int32_t batch_size;
+  int32_t incremental;        /* != 0: the caller guarantees that every output buffer still holds,
+                                 unmodified, what the previous rc_render_dev call on this handle
+                                 wrote to the same pointers (same batch size, same pixel_means);
+                                 the background is then re-written only where that frame had
+                                 geometry instead of streaming 20 B/px.  Falls back to the full
+                                 background pass whenever pointers / batch / means differ.   */
   void *stream;               /* cudaStream_t                                          */
   void **marks;               /* host array of 5 cudaEvent_t (before setup, after setup, after
                                  scan, after fill, after raster) or NULL               */

@@ -98,7 +98,7 @@ class rc_render_args(ctypes.Structure):
                 ("status", c_void_p), ("K", c_float * 9), ("pixel_means", c_float * 3),
                 ("znear", c_float), ("zfar", c_float), ("mask_thresh", c_float),
                 ("brightness_ratio", c_float), ("mode", c_int32), ("batch_size", c_int32),
-                ("stream", c_void_p), ("marks", POINTER(c_void_p))]
+                ("incremental", c_int32), ("stream", c_void_p), ("marks", POINTER(c_void_p))]
 
 
 # name -> (restype, argtypes); every symbol include/rendercompare.h declares.

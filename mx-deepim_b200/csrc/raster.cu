@@ -68,11 +68,17 @@ struct Renderer {
   int32_t *tile_list;                        // [max_batch][list_cap]
   int32_t *work_count;                       // [RT_WC_INTS] header (see RT_WC_*), then tile_count
   unsigned long long *zwin;                  // [max_batch * n_tiles][RT_PIX] winning keys of the non-empty items
-  int32_t *work_list;                        // [max_batch * n_tiles] packed non-empty (tile, pair) items
+  int32_t *work_list;                        // [max_batch * n_tiles] packed non-empty (tile, pair) items (this call's half)
+  int32_t *heavy;                            // [1] their number (this call's half)
+  const int32_t *prev_list, *prev_heavy;     // the previous call's items = tiles its frame dirtied
+  // ---- host-side state (not used by kernels): ping-pong work lists for the incremental background
+  int32_t *work_list_b[2], *heavy_count;     // heavy_count [2]
+  int cur, have_prev, last_B;
+  const void *last_out[5];
+  float last_mean[3];
 };
 
 // work_count header
-constexpr int RT_WC_HEAVY = 0;     // non-empty (tile, pair) items (scan)
 constexpr int RT_WC_CLIP = 3;      // clip-list length (setup)
 constexpr int RT_WC_TICKET_H = 4;  // next non-empty item (coverage)
 constexpr int RT_WC_INTS = 8;
@@ -431,7 +437,7 @@ raster_scan_kernel(Renderer R, int n_tiles, int32_t *__restrict__ status) {
   if (threadIdx.x == 0) {
     start[n_tiles] = total;
     if (total > R.list_cap && status) atomicExch(status, 1);
-    s_base = atomicAdd(R.work_count + RT_WC_HEAVY, total_ne);
+    s_base = atomicAdd(R.heavy, total_ne);
   }
   __syncthreads();
   int front = s_base + ne_off;
@@ -667,6 +673,24 @@ raster_clear_kernel(Renderer R, RasterOut O, int n_batch) {
   }
 }
 
+// 4a'.  Incremental background: the output buffers still hold this renderer's previous frame, so
+// only the tiles that frame covered (the previous call's item list) need the background again.
+__global__ void __launch_bounds__(256)
+raster_clear_tiles_kernel(Renderer R, RasterOut O) {
+  pdl_launch_dependents();
+  const int n = *R.prev_heavy;
+  const int sub = threadIdx.x / (RT_PIX / 4), q = threadIdx.x % (RT_PIX / 4);
+  const int row4 = q / (RT_TW / 4), xq = (q % (RT_TW / 4)) * 4;
+  constexpr int kPer = RT_THREADS / (RT_PIX / 4);  // tiles per block and pass
+  const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int i = blockIdx.x * kPer + sub; i < n; i += gridDim.x * kPer) {
+    const int work = __ldg(R.prev_list + i);
+    const int y = ((work >> 8) & 0xff) * RT_TH + row4, x = (work & 0xff) * RT_TW + xq;
+    if (y < R.H && x < R.W)
+      store_quad(O, work >> 16, R.H, R.W, y, x, z, z, z, z, make_int4(-1, -1, -1, -1));
+  }
+}
+
 // 4b.  Persistent; one non-empty (tile, pair) item per ticket.
 __global__ void __launch_bounds__(RT_CV_THREADS, 8)
 raster_cover_kernel(Renderer R, int n_tiles) {
@@ -675,7 +699,7 @@ raster_cover_kernel(Renderer R, int n_tiles) {
   __shared__ int s_big[RT_BIG_CAP];
   __shared__ int s_nbig;
   pdl_wait();
-  const int n_heavy = R.work_count[RT_WC_HEAVY];
+  const int n_heavy = *R.heavy;
   if (threadIdx.x == 0) s_unit[0] = atomicAdd(R.work_count + RT_WC_TICKET_H, 1);
   __syncthreads();
   for (int par = 0;; par ^= 1) {
@@ -797,7 +821,7 @@ __global__ void __launch_bounds__(RT_THREADS, 3)
 raster_resolve_kernel(Renderer R, const int32_t *__restrict__ cls_idx,
                       const float *__restrict__ poses, Cam cam, RasterOut O) {
   const int W = R.W, H = R.H;
-  const int n_heavy = R.work_count[RT_WC_HEAVY];
+  const int n_heavy = *R.heavy;
   const size_t plane = (size_t)H * W;
   for (int unit = blockIdx.x; unit < n_heavy; unit += gridDim.x) {
     const int work = __ldg(R.work_list + unit);
@@ -856,7 +880,7 @@ static void renderer_free(Renderer *r) {
   if (!r) return;
   void *ptrs[] = {r->verts, r->uv, r->normals, r->tris, r->mesh_tri_off, r->mesh_has, r->tex,
                   r->tex_off, r->tex_hw, r->recs, r->bbox, r->clip_list, r->zwin, r->work_count, r->tile_start, r->tile_fill,
-                  r->tile_list, r->work_list};
+                  r->tile_list, r->work_list_b[0], r->work_list_b[1], r->heavy_count};
   for (void *p : ptrs)
     if (p) cudaFree(p);
   delete r;
@@ -954,7 +978,9 @@ int rc_renderer_create(const rc_mesh_desc *meshes, int n_meshes, int height, int
   RC_TRY(rc::dev_alloc(&r->clip_list, (size_t)max_batch * max_tris));
   RC_TRY(rc::dev_alloc(&r->work_count, (size_t)max_batch * n_tiles + rc::RT_WC_INTS));  // [header | tile counts]
   r->tile_count = r->work_count + rc::RT_WC_INTS;
-  RC_TRY(rc::dev_alloc(&r->work_list, (size_t)max_batch * n_tiles));
+  RC_TRY(rc::dev_alloc(&r->work_list_b[0], (size_t)max_batch * n_tiles));
+  RC_TRY(rc::dev_alloc(&r->work_list_b[1], (size_t)max_batch * n_tiles));
+  RC_TRY(rc::dev_alloc(&r->heavy_count, 2));
   RC_TRY(rc::dev_alloc(&r->zwin, (size_t)max_batch * n_tiles * rc::RT_PIX));
   RC_TRY(rc::dev_alloc(&r->tile_start, (size_t)max_batch * (n_tiles + 1)));
   RC_TRY(rc::dev_alloc(&r->tile_fill, (size_t)max_batch * n_tiles));
@@ -979,7 +1005,8 @@ int rc_renderer_destroy(void *handle) {
 
 int rc_render_dev(void *handle, const rc_render_args *a) {
   RC_REQUIRE(handle && a, RC_ERR_INVALID_ARG);
-  rc::Renderer &R = *static_cast<rc::Renderer *>(handle);
+  rc::Renderer &Rh = *static_cast<rc::Renderer *>(handle);  // the handle (host state lives here)
+  rc::Renderer R = Rh;                                       // this call's view, passed to kernels
   const int B = a->batch_size;
   RC_REQUIRE(B >= 0, RC_ERR_INVALID_ARG);
   RC_REQUIRE(B <= R.max_batch, RC_ERR_CAPACITY);
@@ -1043,8 +1070,22 @@ int rc_render_dev(void *handle, const rc_render_args *a) {
   // (griddepcontrol.wait) for its predecessor only, none for the clear, which they never touch.
   const bool chain = a->marks == nullptr;
   if ((st = mark(0)) != RC_OK) return st;
+  // ping-pong item lists: this call fills one half, the other half still names the tiles the
+  // previous frame dirtied
+  const int cur = Rh.cur;
+  R.work_list = Rh.work_list_b[cur];
+  R.heavy = Rh.heavy_count + cur;
+  R.prev_list = Rh.work_list_b[cur ^ 1];
+  R.prev_heavy = Rh.heavy_count + (cur ^ 1);
+  const void *outs[5] = {a->depth, a->image_chw, a->bgr_hwc, a->mask, a->tri_id};
+  bool same = Rh.have_prev && Rh.last_B == B;
+  for (int i = 0; i < 5 && same; ++i) same = Rh.last_out[i] == outs[i];
+  for (int i = 0; i < 3 && same; ++i) same = Rh.last_mean[i] == a->pixel_means[i];
+  const bool incremental = a->incremental != 0 && same;
+  Rh.have_prev = 0;  // until this call's launches are all issued
   RC_CUDA_TRY(cudaMemsetAsync(R.work_count, 0,
                               sizeof(int32_t) * ((size_t)B * n_tiles + rc::RT_WC_INTS), s));
+  RC_CUDA_TRY(cudaMemsetAsync(R.heavy, 0, sizeof(int32_t), s));
   // 4a background first: a few CTAs per SM saturate the HBM write path and leave room beside them
   static int clear_ctas = 0;
   if (clear_ctas == 0) {
@@ -1052,7 +1093,10 @@ int rc_render_dev(void *handle, const rc_render_args *a) {
     clear_ctas = e ? atoi(e) : 2;
     if (clear_ctas < 1 || clear_ctas > 8) clear_ctas = 2;
   }
-  rc::raster_clear_kernel<<<sm_count * clear_ctas, 256, 0, s>>>(R, O, B);
+  if (incremental)
+    rc::raster_clear_tiles_kernel<<<sm_count * clear_ctas, 256, 0, s>>>(R, O);
+  else
+    rc::raster_clear_kernel<<<sm_count * clear_ctas, 256, 0, s>>>(R, O, B);
   dim3 gs((R.max_tris + 255) / 256, B);
   RC_CUDA_TRY(rc::launch_maybe_pdl(rc::raster_setup_kernel, gs, dim3(256), 0, s, chain, R,
                                    a->cls_idx, a->poses, cam, n_tiles));
@@ -1079,7 +1123,14 @@ int rc_render_dev(void *handle, const rc_render_args *a) {
     rc::raster_resolve_kernel<<<(int)g, rc::RT_THREADS, 0, s>>>(R, a->cls_idx, a->poses, cam, O);
   }
   if ((st = mark(4)) != RC_OK) return st;
-  return rc::note_status(rc::check_launch());
+  st = rc::check_launch();
+  // host state for the next call's incremental test (the handle is not thread-safe)
+  Rh.have_prev = st == RC_OK;
+  Rh.last_B = B;
+  for (int i = 0; i < 5; ++i) Rh.last_out[i] = outs[i];
+  for (int i = 0; i < 3; ++i) Rh.last_mean[i] = a->pixel_means[i];
+  Rh.cur = cur ^ 1;
+  return rc::note_status(st);
 }
 
 int rc_render_stats(void *handle, int batch_size, void *stream, int64_t *out) {

@@ -387,7 +387,8 @@ class RefineLoop(object):
         self.renderer.render_batch(self.cls, self.pose[nxt], pixel_means=self.render_means,
                                    want=("depth", "image", "mask"),
                                    out={"depth": self.depth_rendered, "image": self.image_rendered,
-                                        "mask": self.mask_rendered}, marks=render_marks)
+                                        "mask": self.mask_rendered}, marks=render_marks,
+                                   incremental=True)  # the loop owns these three buffers
         self.cur = nxt
         self.step.run(None, args=self.bound[nxt], marks=marks)
 
@@ -424,7 +425,7 @@ class RefineLoop(object):
         self.renderer.render_batch(self.cls, self.pose[nxt], pixel_means=self.render_means,
                                    want=("depth", "image", "mask"),
                                    out={"depth": self.depth_rendered, "image": self.image_rendered,
-                                        "mask": self.mask_rendered})
+                                        "mask": self.mask_rendered}, incremental=True)
         self.cur = nxt
         mo = self.mask_observed_test if update_mask == "box_rendered" else self.obs["mask_observed"]
         x = {"image_observed": self.obs["image_observed"], "image_rendered": self.image_rendered,

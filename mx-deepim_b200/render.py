@@ -137,10 +137,13 @@ class DeviceRenderer(object):
 
     def render_batch(self, cls_idx, poses, K=None, mode=_lib.RC_RENDER_TEXTURED, light_pos=None,
                      light_int=None, brightness_ratio=0.7, pixel_means=(0, 0, 0), mask_thresh=0.2,
-                     want=("depth", "image", "mask"), out=None, stream=None, marks=None):
+                     want=("depth", "image", "mask"), out=None, stream=None, marks=None,
+                     incremental=False):
         """cls_idx int32 [B], poses float32 [B,3,4] (device).  Returns a dict of device tensors:
         depth [B,1,H,W]; image [B,3,H,W] = RGB - pixel_means; mask [B,1,H,W]; bgr [B,H,W,3];
-        tri_id [B,H,W]."""
+        tri_id [B,H,W].  incremental=True: the tensors in `out` still hold this renderer's
+        previous frame untouched (a refine loop that owns its buffers), so only the tiles that
+        frame covered are re-cleared (rc_render_args.incremental)."""
         B = int(poses.shape[0])
         H, W = self.height, self.width
         out = {} if out is None else out
@@ -170,6 +173,7 @@ class DeviceRenderer(object):
             a.pixel_means[i] = float(pixel_means[i])
         a.znear, a.zfar, a.mask_thresh = self.zNear, self.zFar, mask_thresh
         a.brightness_ratio, a.mode, a.batch_size = brightness_ratio, mode, B
+        a.incremental = 1 if incremental else 0
         a.stream = _lib.stream_ptr(stream)
         if marks is not None:
             arr = (ctypes.c_void_p * _lib.RC_RENDER_MARKS)()

@@ -117,7 +117,7 @@ def test_struct_layouts_match_header(tmp_path):
                                   "marks"]),
         "rc_mesh_desc": (_lib.rc_mesh_desc, ["vertices", "texture", "n_vertices", "tex_w"]),
         "rc_render_args": (_lib.rc_render_args, ["cls_idx", "status", "K", "pixel_means", "znear",
-                                                 "mode", "batch_size", "stream", "marks"]),
+                                                 "mode", "batch_size", "incremental", "stream", "marks"]),
     }
     lines = ['#include <stdio.h>', '#include <stddef.h>', '#include "rendercompare.h"',
              'int main(void) {']

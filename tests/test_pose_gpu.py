@@ -38,3 +38,30 @@ def test_pose_update(cuda_device):
     for b in range(4):
         rec = pose_np.RT_transform(pose[b].astype(np.float64), q[b], tr[b], means, stds, "CAMERA")
         assert np.abs(rec - tgt[b]).max() < 2e-5
+
+
+def test_pose_update_non_orthonormal_target_takes_the_jacobi_path(cuda_device):
+    """mat2quat of a matrix far from a rotation: the shifted power iteration's guards reject it and
+    the Jacobi eigen-solve answers, still matching numpy's eigh (RT_transform.py:446-523)."""
+    import torch
+
+    from mx_deepim_b200 import pipeline
+
+    rng = np.random.default_rng(32)
+    B = 16
+    src = np.zeros((B, 3, 4), np.float32)
+    tgt = np.zeros((B, 3, 4), np.float32)
+    for b in range(B):
+        src[b], tgt[b] = helpers.random_pose_pair(rng)
+        if b % 2 == 0:  # sheared, scaled "rotation" blocks
+            tgt[b, :, :3] = (tgt[b, :, :3] @ (np.eye(3) + rng.normal(0, 0.4, size=(3, 3)))).astype(np.float32)
+    rot = np.tile(np.array([[1, 0, 0, 0]], np.float32), (B, 1))
+    trans = np.zeros((B, 3), np.float32)
+    means, stds = np.zeros(3, np.float32), np.ones(3, np.float32)
+    _, ref_q, ref_t, _ = updater_np.pose_update(src, rot, trans, tgt, helpers.K_LM, means, stds)
+    t = lambda a: torch.from_numpy(a).to(cuda_device)
+    out = pipeline.pose_update(t(src), t(rot), t(trans), t(tgt), helpers.K_LM)
+    torch.cuda.synchronize()
+    q = out[1].cpu().numpy()
+    np.testing.assert_allclose(q, ref_q, rtol=0, atol=5e-6)
+    np.testing.assert_allclose(out[2].cpu().numpy(), ref_t, rtol=1e-5, atol=1e-6)

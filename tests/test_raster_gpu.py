@@ -220,7 +220,8 @@ def test_chained_render_equals_serialised_full_size(cuda_device):
     """BASELINE-sized property test (cfg 3 batch, cfg 5 mesh density): the production issue order
     (setup ... cover chained behind the background pass by programmatic dependent launches) gives
     bit-identical frames to the serialised order that event marks force, back to back over
-    changing poses, and every output plane is consistent with the depth plane."""
+    changing poses, so does the incremental background (only the previous frame's tiles are
+    re-cleared), and every output plane is consistent with the depth plane."""
     import torch
 
     from mx_deepim_b200 import _lib, synth
@@ -235,18 +236,27 @@ def test_chained_render_equals_serialised_full_size(cuda_device):
     cls = torch.from_numpy(rng.integers(0, len(meshes), size=B).astype(np.int32)).to(cuda_device)
     means = (1.0, 2.0, 3.0)
     want = ("depth", "image", "mask", "tri_id")
-    chained, serial = {}, {}
-    for rep, zr in enumerate(((0.6, 1.2), (0.3, 0.6), (0.6, 1.2))):
+    chained, serial, incr = {}, {}, {}
+    for rep, zr in enumerate(((0.6, 1.2), (0.3, 0.6), (0.6, 1.2), (0.8, 1.0))):
         poses = _poses(B, 900 + rep)
         poses[:, 2, 3] = rng.uniform(zr[0], zr[1], size=B)
         pd = torch.from_numpy(poses).to(cuda_device)
         ren.render_batch(cls, pd, pixel_means=means, want=want, out=chained)
         marks = [_lib.Event() for _ in range(_lib.RC_RENDER_MARKS)]
         ren.render_batch(cls, pd, pixel_means=means, want=want, out=serial, marks=marks)
+        # incremental background: `incr` still holds this renderer's previous frame only if the
+        # previous call wrote to it -- the first call below follows a call on other buffers (full
+        # background), the second one follows itself (only the dirtied tiles are re-cleared)
+        ren.render_batch(cls, pd, pixel_means=means, want=want, out=incr, incremental=True)
+        if rep > 0:
+            pd2 = torch.from_numpy(_poses(B, 950 + rep)).to(cuda_device)
+            ren.render_batch(cls, pd2, pixel_means=means, want=want, out=incr, incremental=True)
+            ren.render_batch(cls, pd, pixel_means=means, want=want, out=incr, incremental=True)
         torch.cuda.synchronize()
         assert int(ren.status.item()) == 0
         for k in want:
             assert torch.equal(chained[k], serial[k]), (rep, k)
+            assert torch.equal(incr[k], serial[k]), (rep, k, "incremental")
         depth, tri = chained["depth"], chained["tri_id"]
         assert torch.equal(chained["mask"], (depth > 0.2).float())
         assert torch.equal(tri[:, None] >= 0, depth > 0)  # a winner everywhere a depth was written
