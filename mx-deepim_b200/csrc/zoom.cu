@@ -464,22 +464,30 @@ __device__ __forceinline__ void blend_col(float (&out)[ZT_H], const RowCoord (&r
                                           uint32_t a_row0, uint32_t pitch, unsigned step_mask,
                                           unsigned rowok_mask, float mean,
                                           bool okl, bool okr, float wl, float wr) {
+  // Horizontal blend first: h(row) = l * wl + r * wr is shared by every output row that reads
+  // the source row (zooming in, eight output rows touch ~8*wy+2 source rows), so an output costs
+  // one FMUL + one FFMA plus its share of the row blends instead of the eight operations of the
+  // operator's tap-by-tap association.  Same four products, summed in another order: the
+  // difference is <= 2 ulp of the result (1e-7 relative), three decades inside the 1e-4 bar.
   uint32_t ab = a_row0;
   unsigned rk = rowok_mask;
-  float2 top = load_taps<PRE, EDGE>(ab, mean, rk & 1u, okl, okr);
+  float2 t = load_taps<PRE, EDGE>(ab, mean, rk & 1u, okl, okr);
+  float ht = __fmaf_rn(t.y, wr, __fmul_rn(t.x, wl));
   ab += pitch;
   rk >>= 1;
-  float2 bot = load_taps<PRE, EDGE>(ab, mean, rk & 1u, okl, okr);
-  out[0] = blend(top.x, top.y, bot.x, bot.y, rows[0].wt, rows[0].wb, wl, wr);
+  t = load_taps<PRE, EDGE>(ab, mean, rk & 1u, okl, okr);
+  float hb = __fmaf_rn(t.y, wr, __fmul_rn(t.x, wl));
+  out[0] = __fmaf_rn(hb, rows[0].wb, __fmul_rn(ht, rows[0].wt));
 #pragma unroll
   for (int m = 1; m < ZT_H; ++m) {
     if (step_mask & (1u << m)) {  // warp-uniform
-      top = bot;
+      ht = hb;
       ab += pitch;
       rk >>= 1;
-      bot = load_taps<PRE, EDGE>(ab, mean, rk & 1u, okl, okr);
+      t = load_taps<PRE, EDGE>(ab, mean, rk & 1u, okl, okr);
+      hb = __fmaf_rn(t.y, wr, __fmul_rn(t.x, wl));
     }
-    out[m] = blend(top.x, top.y, bot.x, bot.y, rows[m].wt, rows[m].wb, wl, wr);
+    out[m] = __fmaf_rn(hb, rows[m].wb, __fmul_rn(ht, rows[m].wt));
   }
 }
 
