@@ -173,13 +173,21 @@ __device__ __forceinline__ void make_record(double ax_, double ay_, double az_, 
                     sy2 = (long long)(X1 - X0) * 256;
     bool any = false;
     const int ny = py1 - py0, nx = px1 - px0;
+    long long a0 = r0, a1 = r1, a2 = r2;  // edge values at the start of the pixel row
 #pragma unroll
-    for (int j = 0; j < 3; ++j)
+    for (int j = 0; j < 3; ++j) {
+      long long b0 = a0, b1 = a1, b2 = a2;
 #pragma unroll
-      for (int i = 0; i < 3; ++i)
-        if (j <= ny && i <= nx)
-          any = any || (((r0 + j * sy0 + i * sx0) | (r1 + j * sy1 + i * sx1) |
-                         (r2 + j * sy2 + i * sx2)) >= 0);
+      for (int i = 0; i < 3; ++i) {
+        any = any || (j <= ny && i <= nx && ((b0 | b1 | b2) >= 0));
+        b0 += sx0;
+        b1 += sx1;
+        b2 += sx2;
+      }
+      a0 += sy0;
+      a1 += sy1;
+      a2 += sy2;
+    }
     if (!any) return;
   }
   r.bb_min = (int)((py0 << 16) | px0);
