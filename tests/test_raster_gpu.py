@@ -267,3 +267,40 @@ def test_chained_render_equals_serialised_full_size(cuda_device):
         fg = depth[depth > 0]
         assert float(fg.min()) >= synth.ZNEAR * (1 - 1e-6) and float(fg.max()) <= synth.ZFAR
         assert int((depth > 0).sum()) > 1000 * B / 4
+
+
+@pytest.mark.parametrize("width,height", [(200, 150), (332, 250), (1024, 64)])
+def test_render_other_frame_sizes(cuda_device, width, height):
+    """Frames whose size is not a multiple of the 16x16 raster tile (partial tiles at the right
+    and bottom border) or of the 128-px row chunks of the background pass, against the oracle."""
+    import torch
+
+    from mx_deepim_b200 import synth
+    from mx_deepim_b200.render import DeviceRenderer
+
+    rng = np.random.default_rng(width)
+    mesh = synth.make_mesh(rng, level=3, kind=1)
+    Ks = np.array([[250.0, 0, width / 2 - 3.3], [0, 251.0, height / 2 + 1.7], [0, 0, 1]], np.float32)
+    ren = DeviceRenderer([mesh], Ks, width, height, 0.25, 6.0, max_batch=3, device=cuda_device)
+    poses = np.zeros((3, 3, 4), np.float32)
+    for b in range(3):
+        poses[b, :, :3] = synth.random_rotation(rng)
+        # the third one hangs over the right / bottom border
+        poses[b, :, 3] = [(0.0, 0.0, 0.7), (-0.05, 0.02, 0.5), (0.26 * width / 250, 0.2 * height / 251, 0.9)][b]
+    cls = torch.zeros(3, dtype=torch.int32, device=cuda_device)
+    out = {}
+    for incremental in (False, True, True):
+        ren.render_batch(cls, torch.from_numpy(poses).to(cuda_device), want=("depth", "bgr", "mask", "tri_id"),
+                         out=out, incremental=incremental)
+    torch.cuda.synchronize()
+    assert int(ren.status.item()) == 0
+    depth, bgr = out["depth"].cpu().numpy(), out["bgr"].cpu().numpy()
+    for b in range(3):
+        o_bgr, o_depth = raster_np.render_py(mesh, poses[b, :, :3], poses[b, :, 3], Ks, r_type="mat",
+                                             width=width, height=height)
+        assert ((depth[b, 0] > 0) == (o_depth > 0)).mean() >= 0.999
+        both = (depth[b, 0] > 0) & (o_depth > 0)
+        if both.any():
+            assert (np.abs(depth[b, 0][both] - o_depth[both]) / o_depth[both]).max() <= 1e-5
+            assert (np.abs(bgr[b][both] - o_bgr[both]).max(axis=-1) == 0).mean() >= 0.999
+    assert (depth[0] > 0).sum() > 200

@@ -189,3 +189,44 @@ def test_req_add_and_null(cuda_device):
             depth_rendered=d["depth_rendered"], out=out, req=["add", "null"])
     assert np.abs(out[0].cpu().numpy() - (ref[0] + 2.0)).max() <= TOL
     assert float((out[1] - 2.0).abs().max()) == 0.0
+
+
+@pytest.mark.parametrize("height,width", [(152, 200), (250, 332)])
+def test_zoom_other_frame_sizes(cuda_device, height, width):
+    """The plugins take `height` / `width` kwargs (zoom_mask.py:143-150): a frame that is neither a
+    multiple of the resampler's 128x8 tile nor 640 wide goes through the generic-width kernel;
+    boxes and zoom factors stay bit-exact, samples within the 1e-4 bar."""
+    rng = np.random.default_rng(height)
+    B = 3
+    K = np.array([[180.0, 0, width / 2 + 2.5], [0, 181.0, height / 2 - 1.5], [0, 0, 1]], np.float32)
+    mask_gt = np.zeros((B, 1, height, width), np.float32)
+    rend = np.zeros((B, 1, height, width), np.float32)
+    src_pose = np.zeros((B, 3, 4), np.float32)
+    for b in range(B):
+        cy, cx = rng.integers(40, height - 40), rng.integers(50, width - 50)
+        ry, rx = rng.integers(8, 30), rng.integers(8, 30)
+        mask_gt[b, 0, cy - ry:cy + ry, cx - rx:cx + rx] = 1.0
+        rend[b, 0, cy - ry + 3:cy + ry + 5, cx - rx - 4:cx + rx + 2] = rng.uniform(0.5, 1.0)
+        src_pose[b, :, :3] = np.eye(3)
+        z = 0.8
+        src_pose[b, :, 3] = [(cx - K[0, 2]) / K[0, 0] * z, (cy - K[1, 2]) / K[1, 1] * z, z]
+    mask_obs = mask_gt.copy()
+    mask_obs[:, :, ::7] = 0
+    r0, r1, r2, zf, bbox, pre = zoom_np.zoom_mask_forward(mask_obs, mask_gt, rend, src_pose, K,
+                                                          height=height, width=width,
+                                                          return_pre_round=True)
+    h = _custom(cuda_device, op_type="ZoomMask", mask_observed=mask_obs, mask_gt_observed=mask_gt,
+                mask_rendered=rend, src_pose=src_pose, K=K.flatten(), height=height, width=width)
+    out = [o.cpu().numpy() for o in h.outputs]
+    assert np.array_equal(out[3].view(np.uint32), zf.view(np.uint32))
+    for got, ref, p in zip(out[:3], (r0, r1, r2), pre):
+        bad = got != ref
+        assert not (bad & (np.abs(p - 0.5) > TOL)).any()
+    pm = helpers.PIXEL_MEANS
+    img_o = rng.uniform(-120, 130, size=(B, 3, height, width)).astype(np.float32)
+    img_r = rng.uniform(-120, 130, size=(B, 3, height, width)).astype(np.float32)
+    ref_o, ref_r = zoom_np.zoom_image_with_factor_forward(zf, img_o, img_r, pm[::-1])
+    h = _custom(cuda_device, op_type="ZoomImageWithFactor", zoom_factor=zf, image_observed=img_o,
+                image_rendered=img_r, height=height, width=width, pixel_means=pm.flatten())
+    out = [o.cpu().numpy() for o in h.outputs]
+    assert np.abs(out[0] - ref_o).max() <= TOL and np.abs(out[1] - ref_r).max() <= TOL
