@@ -6,25 +6,32 @@
 // and the post-render block
 //   /root/reference/lib/pair_matching/batch_updater_py_multi.py:279-320.
 //
-// B200 design (one render call = 8 launches for a whole batch, any mix of meshes):
-//   1. setup  : one thread per (triangle, pair): pose transform in float64, pinhole projection,
-//               snap to 1/256 px, edge orientation, GL window depth, culling (incl. micro-
-//               triangles that contain no pixel centre); writes a 64-byte record + its pixel box
-//               and counts the 16x16 tiles it overlaps with warp-aggregated atomics
-//               (__match_any_sync on the tile id).  Triangles straddling the near plane go to a
-//               list for the (usually idle) clip kernel.
-//   2. scan   : exclusive scan of the per-tile counts (one block per pair) + the list of
-//               non-empty (tile, pair) items.
-//   3. fill   : tile lists (record indices), again warp-aggregated.
-//   4a clear  : streams the background in row order, skipping non-empty tiles (HBM bound).
-//   4b cover  : beside 4a (programmatic dependent launch): per non-empty tile, atomicMin of a
-//               packed (bits(window depth) << 32 | record) key into a shared-memory z-buffer;
-//               large triangles are tested cooperatively, one pixel per thread.
-//   4c resolve: one thread per pixel of the non-empty tiles: perspective-correct attributes,
-//               nearest texel, optional Lambert term, fused BGR->RGB / CHW / -mean and mask.
-// The frame is written exactly once (20 B/px), the mesh is read once per pair.
+// B200 design (one render call = a memset + 7 launches for a whole batch, any mix of meshes;
+// launch order: clear, setup, clip, scan, fill, cover, resolve):
+//   clear   : the background (depth 0, mask 0, image 0 - mean ...) in row order with 128-bit
+//             stores -- the whole frame, or in incremental mode (a caller that owns its frame
+//             buffers) only the tiles the previous frame covered.  Launched first; it releases
+//             its dependents at once and the passes below run beside it (programmatic dependent
+//             launches, each waiting for its predecessor only); only resolve waits for it.
+//   setup   : one thread per (triangle, pair): pose transform in float64, pinhole projection,
+//             snap to 1/256 px, edge orientation, GL window depth, culling (incl. micro-
+//             triangles that contain no pixel centre); writes a 64-byte record + its pixel box
+//             and counts the 16x16 tiles it overlaps with warp-aggregated atomics
+//             (__match_any_sync on the tile id).  Triangles straddling the near plane go to a
+//             list for the (usually idle) clip kernel.
+//   scan    : exclusive scan of the per-tile counts (one block per pair) + the list of non-empty
+//             (tile, pair) items.
+//   fill    : tile lists (record indices), again warp-aggregated, one thread per triangle.
+//   cover   : per non-empty tile, atomicMin of a packed (bits(window depth) << 32 | record) key
+//             into a shared-memory z-buffer; large triangles are tested cooperatively, one pixel
+//             per thread; the winners go to a 2 KB block per item.
+//   resolve : one thread per pixel of the non-empty tiles: perspective-correct attributes,
+//             nearest texel, optional Lambert term, fused BGR->RGB / CHW / -mean and mask.
+// Every pixel of the frame ends up written by exactly one of clear / resolve; the mesh is read
+// once per pair.
 //
-// Compiled with -fmad=false: the float64 geometry must round exactly like the C oracle.
+// Compiled with -fmad=false: no compiler-chosen contraction in the float64 geometry (the results
+// are checked against the C oracle's literal GL pipeline at the snapping / float32 level).
 #include <limits.h>
 #include <stdlib.h>
 #include <string.h>
