@@ -304,3 +304,39 @@ def test_render_other_frame_sizes(cuda_device, width, height):
             assert (np.abs(depth[b, 0][both] - o_depth[both]) / o_depth[both]).max() <= 1e-5
             assert (np.abs(bgr[b][both] - o_bgr[both]).max(axis=-1) == 0).mean() >= 0.999
     assert (depth[0] > 0).sum() > 200
+
+
+def test_render_py_from_model_dir(cuda_device, tmp_path):
+    """The reference's constructor path (render_py_multi.py:49-82): `<model_dir>/<class>/
+    textured.obj` + `texture_map.png` read from disk, rendered, and compared with the oracle's
+    render of the same files' contents."""
+    import cv2
+
+    from mx_deepim_b200 import synth
+    from mx_deepim_b200.render import Render_Py, load_obj, load_texture
+
+    rng = np.random.default_rng(41)
+    classes = ["ape", "can"]
+    for i, cls in enumerate(classes):
+        m = synth.make_mesh(rng, level=2, kind=i, texture_size=64)
+        d = tmp_path / cls
+        d.mkdir()
+        with open(d / "textured.obj", "w") as fh:
+            for v in m["vertices"]:
+                fh.write("v %.9g %.9g %.9g\n" % tuple(v))
+            for t in m["uv"]:
+                fh.write("vt %.9g %.9g\n" % tuple(t))
+            for n in m["normals"]:
+                fh.write("vn %.9g %.9g %.9g\n" % tuple(n))
+            for a, b, c in m["triangles"] + 1:
+                fh.write("f %d/%d/%d %d/%d/%d %d/%d/%d\n" % (a, a, a, b, b, b, c, c, c))
+        cv2.imwrite(str(d / "texture_map.png"), np.ascontiguousarray(m["texture"][:, :, ::-1]))
+    r = Render_Py(str(tmp_path), classes, K, max_batch=2)
+    poses = _poses(2, 43)
+    for i, cls in enumerate(classes):
+        mesh = load_obj(str(tmp_path / cls / "textured.obj"))
+        mesh["texture"] = load_texture(str(tmp_path / cls / "texture_map.png"))
+        bgr, depth = r.render(i, poses[i, :, :3], poses[i, :, 3], r_type="mat")
+        o_bgr, o_depth = raster_np.render_py(mesh, poses[i, :, :3], poses[i, :, 3], K, r_type="mat")
+        _compare(o_bgr, o_depth, bgr, depth)
+        assert (depth > 0).sum() > 500
