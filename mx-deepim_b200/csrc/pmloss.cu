@@ -129,30 +129,49 @@ __device__ __forceinline__ float loss_grad(float x, int type, float sigma2, floa
   return fabsf(x) < inv_sigma2 ? sigma2 * x : sgn;
 }
 
-template <int NT>
-__device__ __forceinline__ double block_sum(double v, double *sm) {
-  v = warp_sum(v);
+constexpr int PM_THREADS = 256;
+constexpr int PM_CLUSTER = 8;  // CTAs per sample at small batches (portable cluster size limit)
+
+// Sum NV per-thread values over the block in ONE pass: warp shuffles, one shared-memory stage
+// (sm [PM_THREADS / 32][NV]) between two barriers, warps added in index order by thread 0.
+// The result is valid in thread 0.
+template <int NV>
+__device__ __forceinline__ void block_sum_n(const double (&v)[NV], double *sm, double (&out)[NV]) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  double w[NV];
+#pragma unroll
+  for (int i = 0; i < NV; ++i) w[i] = warp_sum(v[i]);
+  __syncthreads();  // sm may still be read by a previous call
+  if (lane == 0) {
+#pragma unroll
+    for (int i = 0; i < NV; ++i) sm[warp * NV + i] = w[i];
+  }
   __syncthreads();
-  if (lane == 0) sm[warp] = v;
-  __syncthreads();
-  double r = 0.0;
   if (threadIdx.x == 0) {
 #pragma unroll
-    for (int i = 0; i < NT / 32; ++i) r += sm[i];
+    for (int i = 0; i < NV; ++i) {
+      double r = 0.0;
+#pragma unroll
+      for (int k = 0; k < PM_THREADS / 32; ++k) r += sm[k * NV + i];
+      out[i] = r;
+    }
   }
-  return r;  // valid in thread 0
 }
 
-constexpr int PM_THREADS = 256;
-constexpr int PM_CLUSTER = 8;  // CTAs per sample (portable cluster size limit)
-
-// Sum `n` per-CTA partials across the cluster through distributed shared memory:
+// Sum NV per-CTA partials across the cluster of CL CTAs through distributed shared memory:
 // every CTA writes its values into rank 0's table, rank 0 adds them in rank order.
-// Returns true in (rank 0, thread 0), where out[0..n) holds the totals.
-template <int NV>
-__device__ __forceinline__ bool cluster_sum(const double (&mine)[NV], double *table /* smem [PM_CLUSTER][NV] */,
+// Returns true in (rank 0, thread 0), where out[0..NV) holds the totals.  CL == 1: no exchange.
+template <int NV, int CL>
+__device__ __forceinline__ bool cluster_sum(const double (&mine)[NV], double *table /* smem [CL][NV] */,
                                             double (&out)[NV]) {
+  if (CL == 1) {
+    if (threadIdx.x == 0) {
+#pragma unroll
+      for (int i = 0; i < NV; ++i) out[i] = mine[i];
+      return true;
+    }
+    return false;
+  }
   cg::cluster_group cluster = cg::this_cluster();
   const unsigned rank = cluster.block_rank();
   if (threadIdx.x == 0) {
@@ -165,7 +184,7 @@ __device__ __forceinline__ bool cluster_sum(const double (&mine)[NV], double *ta
 #pragma unroll
     for (int i = 0; i < NV; ++i) {
       double a = 0.0;
-      for (int r = 0; r < PM_CLUSTER; ++r) a += table[r * NV + i];
+      for (int r = 0; r < CL; ++r) a += table[r * NV + i];
       out[i] = a;
     }
     return true;
@@ -173,9 +192,17 @@ __device__ __forceinline__ bool cluster_sum(const double (&mine)[NV], double *ta
   return false;
 }
 
-// One cluster of PM_CLUSTER blocks per sample.  est / loss_map / loss_sum are optional
+// CTAs per sample: eight (a thread-block cluster, <= 2 points per thread) while the batch is too
+// small to fill the GPU -- the pass is then pure latency; two, then one (12 points per thread)
+// as the batch grows and the per-CTA barriers / cluster exchange become the cost.
+static inline int pm_cluster_for(int batch_size) {
+  return batch_size >= 512 ? 1 : (batch_size >= 128 ? 2 : PM_CLUSTER);
+}
+
+// One cluster of CL blocks per sample.  est / loss_map / loss_sum are optional
 // outputs; obs == nullptr turns the kernel into plain Transform3D forward.
-__global__ void __cluster_dims__(PM_CLUSTER, 1, 1) __launch_bounds__(PM_THREADS)
+template <int CL>
+__global__ void __cluster_dims__(CL, 1, 1) __launch_bounds__(PM_THREADS)
 pm_fwd_kernel(const float *__restrict__ points, const float *__restrict__ obs,
               const float *__restrict__ weights, const float *__restrict__ rotation,
               const float *__restrict__ trans, const float *__restrict__ pose_src,
@@ -183,11 +210,11 @@ pm_fwd_kernel(const float *__restrict__ points, const float *__restrict__ obs,
               float *__restrict__ loss_map, float *__restrict__ loss_sum, int N,
               int accumulate) {
   pdl_launch_dependents();
-  const int b = blockIdx.x / PM_CLUSTER;
-  const int crank = blockIdx.x % PM_CLUSTER;
+  const int b = blockIdx.x / CL;
+  const int crank = blockIdx.x % CL;
   __shared__ PoseOut po;
   __shared__ double red[PM_THREADS / 32];
-  __shared__ double table[PM_CLUSTER];
+  __shared__ double table[CL];
   if (threadIdx.x == 0) compose_pose(rotation + b * 4, trans + b * 3, pose_src + b * 12, pp, po);
   __syncthreads();
   float R[9], T[3];
@@ -198,7 +225,7 @@ pm_fwd_kernel(const float *__restrict__ points, const float *__restrict__ obs,
   const float sigma2 = sigma * sigma, inv_sigma2 = 1.f / (sigma * sigma);
   const size_t base = (size_t)b * 3 * N;
   double acc = 0.0;
-  for (int n = crank * PM_THREADS + threadIdx.x; n < N; n += PM_THREADS * PM_CLUSTER) {
+  for (int n = crank * PM_THREADS + threadIdx.x; n < N; n += PM_THREADS * CL) {
     const float p0 = __ldg(points + base + n);
     const float p1 = __ldg(points + base + N + n);
     const float p2 = __ldg(points + base + 2 * N + n);
@@ -219,9 +246,9 @@ pm_fwd_kernel(const float *__restrict__ points, const float *__restrict__ obs,
     }
   }
   // every CTA of the cluster takes part in the reduction (cluster.sync inside)
-  double mine[1], tot[1];
-  mine[0] = block_sum<PM_THREADS>(acc, red);
-  if (cluster_sum<1>(mine, table, tot) && loss_sum) loss_sum[b] = (float)tot[0];
+  double part[1] = {acc}, mine[1], tot[1];
+  block_sum_n<1>(part, red, mine);
+  if (cluster_sum<1, CL>(mine, table, tot) && loss_sum) loss_sum[b] = (float)tot[0];
 }
 
 // quat2mat_backward, transform3d.py:256-327 (float64 tail, float32 result).
@@ -258,8 +285,8 @@ __device__ void quat2mat_bwd(const double *D, const float *q, float *gq, int acc
 // One block per sample.  FROM_LOSS: the head gradient is computed from the
 // loss definition (MakeLoss grad_scale, weights, d|x|/dx, 1/norm); otherwise
 // it is read from out_grad (plain Transform3D backward).
-template <bool FROM_LOSS>
-__global__ void __cluster_dims__(PM_CLUSTER, 1, 1) __launch_bounds__(PM_THREADS)
+template <bool FROM_LOSS, int CL>
+__global__ void __cluster_dims__(CL, 1, 1) __launch_bounds__(PM_THREADS)
 pm_bwd_kernel(const float *__restrict__ out_grad, const float *__restrict__ points,
               const float *__restrict__ obs, const float *__restrict__ weights,
               const float *__restrict__ rotation, const float *__restrict__ trans,
@@ -267,11 +294,11 @@ pm_bwd_kernel(const float *__restrict__ out_grad, const float *__restrict__ poin
               float norm_term, float sigma, float grad_scale, float *__restrict__ grad_rot,
               float *__restrict__ grad_trans, int N, int accumulate) {
   pdl_launch_dependents();
-  const int b = blockIdx.x / PM_CLUSTER;
-  const int crank = blockIdx.x % PM_CLUSTER;
+  const int b = blockIdx.x / CL;
+  const int crank = blockIdx.x % CL;
   __shared__ PoseOut po;
-  __shared__ double red[PM_THREADS / 32];
-  __shared__ double table[PM_CLUSTER * 12];
+  __shared__ double red[(PM_THREADS / 32) * 12];
+  __shared__ double table[CL * 12];
   if (threadIdx.x == 0) compose_pose(rotation + b * 4, trans + b * 3, pose_src + b * 12, pp, po);
   __syncthreads();
   float R[9], T[3], Rs[9], Ts[3];
@@ -289,7 +316,7 @@ pm_bwd_kernel(const float *__restrict__ out_grad, const float *__restrict__ poin
   const size_t base = (size_t)b * 3 * N;
   double gt[3] = {0, 0, 0};  // sum_n G            (transform3d.py:138)
   double gr[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};  // G X^T (:154-157)
-  for (int n = crank * PM_THREADS + threadIdx.x; n < N; n += PM_THREADS * PM_CLUSTER) {
+  for (int n = crank * PM_THREADS + threadIdx.x; n < N; n += PM_THREADS * CL) {
     float p[3];
     p[0] = __ldg(points + base + n);
     p[1] = __ldg(points + base + N + n);
@@ -325,12 +352,13 @@ pm_bwd_kernel(const float *__restrict__ out_grad, const float *__restrict__ poin
       gr[k * 3 + 2] += (double)g * xr[2];
     }
   }
-  double mine[12], sums[12];
+  double part[12], mine[12], sums[12];
 #pragma unroll
-  for (int k = 0; k < 3; ++k) mine[k] = block_sum<PM_THREADS>(gt[k], red);
+  for (int k = 0; k < 3; ++k) part[k] = gt[k];
 #pragma unroll
-  for (int k = 0; k < 9; ++k) mine[3 + k] = block_sum<PM_THREADS>(gr[k], red);
-  if (!cluster_sum<12>(mine, table, sums)) return;
+  for (int k = 0; k < 9; ++k) part[3 + k] = gr[k];
+  block_sum_n<12>(part, red, mine);  // one pass: twelve sums between two barriers
+  if (!cluster_sum<12, CL>(mine, table, sums)) return;
   // values the reference holds as float32 NDArrays
   float Df[3], Gf[9];
 #pragma unroll
@@ -390,6 +418,16 @@ static int fill_pose_params(PoseParams &pp, const float *means, const float *std
 
 }  // namespace rc
 
+// Launch KERNEL<..., CL> with CL = pm_cluster_for(batch) CTAs per sample.
+#define RC_PM_DISPATCH(batch, LAUNCH)           \
+  do {                                          \
+    switch (rc::pm_cluster_for(batch)) {        \
+      case 1: { constexpr int CL = 1; LAUNCH; } break; \
+      case 2: { constexpr int CL = 2; LAUNCH; } break; \
+      default: { constexpr int CL = rc::PM_CLUSTER; LAUNCH; } break; \
+    }                                           \
+  } while (0)
+
 extern "C" {
 
 int rc_transform3d_fwd_dev(const float *points, const float *rotation, const float *trans,
@@ -401,9 +439,11 @@ int rc_transform3d_fwd_dev(const float *points, const float *rotation, const flo
   RC_REQUIRE(rc::fill_pose_params(pp, T_means, T_stds, rot_coord) == RC_OK, RC_ERR_INVALID_ARG);
   if (batch_size == 0 || num_points == 0) return rc::note_status(RC_OK);
   RC_REQUIRE(points && rotation && trans && pose_src && out, RC_ERR_INVALID_ARG);
-  rc::pm_fwd_kernel<<<batch_size * rc::PM_CLUSTER, rc::PM_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
-      points, nullptr, nullptr, rotation, trans, pose_src, pp, RC_PM_L1, 1.f, 1.f, out, nullptr,
-      nullptr, num_points, accumulate);
+  RC_PM_DISPATCH(batch_size,
+                 (rc::pm_fwd_kernel<CL><<<batch_size * CL, rc::PM_THREADS, 0,
+                                          static_cast<cudaStream_t>(stream)>>>(
+                     points, nullptr, nullptr, rotation, trans, pose_src, pp, RC_PM_L1, 1.f, 1.f,
+                     out, nullptr, nullptr, num_points, accumulate)));
   return rc::note_status(rc::check_launch());
 }
 
@@ -418,9 +458,11 @@ int rc_transform3d_bwd_dev(const float *out_grad, const float *points, const flo
   if (batch_size == 0) return rc::note_status(RC_OK);
   RC_REQUIRE(out_grad && points && rotation && trans && pose_src && grad_rot && grad_trans,
              RC_ERR_INVALID_ARG);
-  rc::pm_bwd_kernel<false><<<batch_size * rc::PM_CLUSTER, rc::PM_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
-      out_grad, points, nullptr, nullptr, rotation, trans, pose_src, pp, RC_PM_L1, 1.f, 1.f, 1.f,
-      grad_rot, grad_trans, num_points, accumulate);
+  RC_PM_DISPATCH(batch_size,
+                 (rc::pm_bwd_kernel<false, CL><<<batch_size * CL, rc::PM_THREADS, 0,
+                                                 static_cast<cudaStream_t>(stream)>>>(
+                     out_grad, points, nullptr, nullptr, rotation, trans, pose_src, pp, RC_PM_L1,
+                     1.f, 1.f, 1.f, grad_rot, grad_trans, num_points, accumulate)));
   return rc::note_status(rc::check_launch());
 }
 
@@ -437,11 +479,12 @@ int rc_pm_loss_fwd_dev(const float *points, const float *points_obs, const float
   if (batch_size == 0) return rc::note_status(RC_OK);
   RC_REQUIRE(points && points_obs && weights && rotation && trans && pose_src, RC_ERR_INVALID_ARG);
   // rc::tl_pdl: the fused step issues the forward beside the backward (neither reads the other)
-  RC_CUDA_TRY(rc::launch_maybe_pdl(rc::pm_fwd_kernel, dim3(batch_size * rc::PM_CLUSTER),
-                                   dim3(rc::PM_THREADS), 0, static_cast<cudaStream_t>(stream),
-                                   rc::tl_pdl, points, points_obs, weights, rotation, trans,
-                                   pose_src, pp, loss_type, norm_term, sl1_scalar, est, loss_map,
-                                   loss_sum, num_points, 0));
+  RC_PM_DISPATCH(batch_size,
+                 RC_CUDA_TRY(rc::launch_maybe_pdl(
+                     rc::pm_fwd_kernel<CL>, dim3(batch_size * CL), dim3(rc::PM_THREADS), 0,
+                     static_cast<cudaStream_t>(stream), rc::tl_pdl, points, points_obs, weights,
+                     rotation, trans, pose_src, pp, loss_type, norm_term, sl1_scalar, est,
+                     loss_map, loss_sum, num_points, 0)));
   return rc::note_status(rc::check_launch());
 }
 
@@ -459,9 +502,12 @@ int rc_pm_loss_bwd_dev(const float *points, const float *points_obs, const float
   RC_REQUIRE(points && points_obs && weights && rotation && trans && pose_src && grad_rot &&
                  grad_trans,
              RC_ERR_INVALID_ARG);
-  rc::pm_bwd_kernel<true><<<batch_size * rc::PM_CLUSTER, rc::PM_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
-      nullptr, points, points_obs, weights, rotation, trans, pose_src, pp, loss_type, norm_term,
-      sl1_scalar, grad_scale, grad_rot, grad_trans, num_points, 0);
+  RC_PM_DISPATCH(batch_size,
+                 (rc::pm_bwd_kernel<true, CL><<<batch_size * CL, rc::PM_THREADS, 0,
+                                                static_cast<cudaStream_t>(stream)>>>(
+                     nullptr, points, points_obs, weights, rotation, trans, pose_src, pp,
+                     loss_type, norm_term, sl1_scalar, grad_scale, grad_rot, grad_trans,
+                     num_points, 0)));
   return rc::note_status(rc::check_launch());
 }
 
