@@ -61,16 +61,30 @@ struct __align__(16) TriRec {  // 64 bytes = four 128-bit loads
   double zw1, zw2;
 };
 
+// One projected vertex: snapped screen position (1/256 px), GL window depth.  In the vertex
+// buffer the first word carries the flags in its two low bits: (X << 2) | RT_VF_*.
+struct __align__(16) VtxS {
+  int X, Y;
+  double zw;
+};
+constexpr int RT_VF_VALID = 1;  // in front of the camera and |u|, |v| < 1e6 px
+constexpr int RT_VF_NEAR = 2;   // z >= znear (inside the near plane)
+constexpr unsigned RT_TBOX_NONE = 0xffu;  // packed tile box with tx0 = 255 > tx1 = 0: no record
+
 struct Renderer {
   int device, H, W, max_batch, n_meshes, max_tris, tiles_x, tiles_y, list_cap;
   float *verts, *uv, *normals;
   int32_t *tris, *mesh_tri_off, *mesh_has;  // has: bit0 uv, bit1 normals
+  int32_t *mesh_vert_off;                    // [M+1] first vertex of each mesh in the concatenated arrays
+  int max_verts;
+  VtxS *vtx;                                 // [max_batch][max_verts] projected vertices of this call
   uint8_t *tex;
   int64_t *tex_off;
   int32_t *tex_hw;                           // [M,2]
   TriRec *recs;                              // [max_batch][2*max_tris]
-  int2 *bbox;                                // [max_batch][2*max_tris] (bb_min, bb_max); bb_max < 0 = unused slot
+  uint32_t *tbox;                            // [max_batch][max_tris] tile box of slot 2t: tx0 | ty0<<8 | tx1<<16 | ty1<<24
   int32_t *clip_list;                        // [max_batch * max_tris] b * max_tris + t of near-plane straddlers
+  uint2 *clip_box;                           // [max_batch * max_tris] tile boxes of the two pieces of clip_list[i]
   int32_t *tile_count, *tile_start, *tile_fill;  // [max_batch][n_tiles (+1)]
   int32_t *tile_list;                        // [max_batch][list_cap]
   int32_t *work_count;                       // [RT_WC_INTS] header (see RT_WC_*), then tile_count
@@ -117,36 +131,38 @@ struct RecQ {  // a TriRec as the four 128-bit words it is stored and loaded as
   int bb_min, bb_max;  // bb_max < 0: nothing to draw
 };
 
-// Screen-space record of one triangle given by camera-space vertices (x,y,z) x 3 (all with
-// z >= znear).  Culls (bb_max = -1) what cannot produce a fragment: behind the camera,
-// degenerate, off-screen, or -- for boxes of at most 3x3 pixels -- no pixel centre inside under
-// the very rule the raster kernel applies (integer edge functions + top-left tie bias).
-// Everything stays in registers: no dynamically indexed arrays.
-__device__ __forceinline__ void make_record(double ax_, double ay_, double az_, double bx_,
-                                            double by_, double bz_, double cx_, double cy_,
-                                            double cz_, const Cam &cam, int W, int H, int tri,
-                                            bool clipped, RecQ &r) {
-  r.bb_max = -1;
-  r.bb_min = 0;
-  if (!(az_ > 0.0) || !(bz_ > 0.0) || !(cz_ > 0.0)) return;
+// Camera-space point -> VtxS.  One reciprocal per vertex (the perspective divide as hardware does
+// it); FP64 runs at half rate on sm_100 and a division is ~30 instructions, so they are counted.
+__device__ __forceinline__ int project_vertex(double x, double y, double z, const Cam &cam, VtxS &o) {
+  o.X = 0;
+  o.Y = 0;
+  o.zw = 0.0;
+  int flag = (z - cam.znear >= 0.0) ? RT_VF_NEAR : 0;
+  if (!(z > 0.0)) return flag;
   // window depth of a camera-space z: ndc.z = (f+n)/(f-n) - 2fn/((f-n) z), d = (ndc.z + 1)/2
   const double pa = (cam.zfar + cam.znear) / (cam.zfar - cam.znear);
   const double pb = (2.0 * cam.zfar * cam.znear) / (cam.zfar - cam.znear);
-  // one reciprocal per vertex (the perspective divide as hardware does it); FP64 runs at half
-  // rate on sm_100 and a division is ~30 instructions, so they are counted
-  const double ia = 1.0 / az_, ib = 1.0 / bz_, ic = 1.0 / cz_;
-  const double u0 = cam.fx * ax_ * ia + cam.cx, v0 = cam.fy * ay_ * ia + cam.cy;
-  const double u1 = cam.fx * bx_ * ib + cam.cx, v1 = cam.fy * by_ * ib + cam.cy;
-  const double u2 = cam.fx * cx_ * ic + cam.cx, v2 = cam.fy * cy_ * ic + cam.cy;
-  if (!(fabs(u0) < 1e6 && fabs(v0) < 1e6 && fabs(u1) < 1e6 && fabs(v1) < 1e6 && fabs(u2) < 1e6 &&
-        fabs(v2) < 1e6))
-    return;
-  const int X0 = __double2int_rn(u0 * 256.0), Y0 = __double2int_rn(v0 * 256.0);  // < 2^28 in magnitude
-  int X1 = __double2int_rn(u1 * 256.0), Y1 = __double2int_rn(v1 * 256.0);
-  int X2 = __double2int_rn(u2 * 256.0), Y2 = __double2int_rn(v2 * 256.0);
-  const double zw0 = ((pa - pb * ia) + 1.0) * 0.5;
-  double zw1 = ((pa - pb * ib) + 1.0) * 0.5;
-  double zw2 = ((pa - pb * ic) + 1.0) * 0.5;
+  const double iz = 1.0 / z;
+  const double u = cam.fx * x * iz + cam.cx, v = cam.fy * y * iz + cam.cy;
+  if (!(fabs(u) < 1e6 && fabs(v) < 1e6)) return flag;
+  o.X = __double2int_rn(u * 256.0);  // < 2^28 in magnitude
+  o.Y = __double2int_rn(v * 256.0);
+  o.zw = ((pa - pb * iz) + 1.0) * 0.5;
+  return flag | RT_VF_VALID;
+}
+
+// Screen-space record of one triangle from its three projected vertices.  Culls (bb_max = -1)
+// what cannot produce a fragment: degenerate, off-screen, or -- for boxes of at most 3x3 pixels --
+// no pixel centre inside under the very rule the raster kernel applies (integer edge functions +
+// top-left tie bias).  Everything stays in registers: no dynamically indexed arrays.
+__device__ __forceinline__ void make_record(const VtxS &va, const VtxS &vb, const VtxS &vc, int W,
+                                            int H, int tri, bool clipped, RecQ &r) {
+  r.bb_max = -1;
+  r.bb_min = 0;
+  const int X0 = va.X, Y0 = va.Y;
+  int X1 = vb.X, Y1 = vb.Y, X2 = vc.X, Y2 = vc.Y;
+  const double zw0 = va.zw;
+  double zw1 = vb.zw, zw2 = vc.zw;
   const long long area = edge_fn(X0, Y0, X1, Y1, X2, Y2);
   if (area == 0) return;
   const bool sw = area < 0;
@@ -164,36 +180,35 @@ __device__ __forceinline__ void make_record(double ax_, double ay_, double az_, 
   if (px1 > W - 1) px1 = W - 1;
   if (py1 > H - 1) py1 = H - 1;
   if (px0 > px1 || py0 > py1) return;
-  if (px1 - px0 <= 2 && py1 - py0 <= 2) {
+  if (px1 - px0 <= 2 && py1 - py0 <= 2 && maxx - minx < 1024 && maxy - miny < 1024) {
     // micro-triangle: test the (at most nine) pixel centres now; most sub-pixel triangles of a
-    // dense mesh contain none and never reach the tile lists
-    const int bias0 = tie_bias(X2 - X1, Y2 - Y1), bias1 = tie_bias(X0 - X2, Y0 - Y2),
-              bias2 = tie_bias(X1 - X0, Y1 - Y0);
-    // edge functions at (px0, py0), then stepped: +256 in x adds -(dy) * 256, in y adds dx * 256
+    // dense mesh contain none and never reach the tile lists.  Relative to the box corner every
+    // coordinate is below 2^11 in magnitude, so the edge functions fit 32 bits (same values as
+    // the 64-bit ones the coverage pass evaluates: the test is exact, not conservative).
     const int qx = px0 << RT_SUB, qy = py0 << RT_SUB;
-    const long long r0 = edge_fn(X1, Y1, X2, Y2, qx, qy) + bias0;
-    const long long r1 = edge_fn(X2, Y2, X0, Y0, qx, qy) + bias1;
-    const long long r2 = edge_fn(X0, Y0, X1, Y1, qx, qy) + bias2;
-    const long long sx0 = -(long long)(Y2 - Y1) * 256, sx1 = -(long long)(Y0 - Y2) * 256,
-                    sx2 = -(long long)(Y1 - Y0) * 256;
-    const long long sy0 = (long long)(X2 - X1) * 256, sy1 = (long long)(X0 - X2) * 256,
-                    sy2 = (long long)(X1 - X0) * 256;
+    const int x0 = X0 - qx, y0 = Y0 - qy, x1 = X1 - qx, y1 = Y1 - qy, x2 = X2 - qx, y2 = Y2 - qy;
+    const int dx0 = x2 - x1, dy0 = y2 - y1, dx1 = x0 - x2, dy1 = y0 - y2, dx2 = x1 - x0,
+              dy2 = y1 - y0;
+    // edge functions at the corner (0, 0), then stepped: +256 in x adds -dy * 256, in y dx * 256
+    const int a0i = dy0 * x1 - dx0 * y1 + tie_bias(dx0, dy0);
+    const int a1i = dy1 * x2 - dx1 * y2 + tie_bias(dx1, dy1);
+    const int a2i = dy2 * x0 - dx2 * y0 + tie_bias(dx2, dy2);
     bool any = false;
     const int ny = py1 - py0, nx = px1 - px0;
-    long long a0 = r0, a1 = r1, a2 = r2;  // edge values at the start of the pixel row
+    int a0 = a0i, a1 = a1i, a2 = a2i;  // edge values at the start of the pixel row
 #pragma unroll
     for (int j = 0; j < 3; ++j) {
-      long long b0 = a0, b1 = a1, b2 = a2;
+      int b0 = a0, b1 = a1, b2 = a2;
 #pragma unroll
       for (int i = 0; i < 3; ++i) {
         any = any || (j <= ny && i <= nx && ((b0 | b1 | b2) >= 0));
-        b0 += sx0;
-        b1 += sx1;
-        b2 += sx2;
+        b0 -= dy0 << RT_SUB;
+        b1 -= dy1 << RT_SUB;
+        b2 -= dy2 << RT_SUB;
       }
-      a0 += sy0;
-      a1 += sy1;
-      a2 += sy2;
+      a0 += dx0 << RT_SUB;
+      a1 += dx1 << RT_SUB;
+      a2 += dx2 << RT_SUB;
     }
     if (!any) return;
   }
@@ -234,17 +249,19 @@ __device__ __forceinline__ int tile_atomic(int32_t *counters, int key, bool want
   return slot;
 }
 
-// The tiles a pixel bbox overlaps, visited in lock step by the whole warp.
+// Packed tile box of a pixel box ((y << 16) | x corners; bb_max < 0: none).
+__device__ __forceinline__ unsigned tile_box(int bb_min, int bb_max) {
+  if (bb_max < 0) return RT_TBOX_NONE;
+  return (unsigned)((bb_min & 0xffff) / RT_TW) | ((unsigned)((bb_min >> 16) / RT_TH) << 8) |
+         ((unsigned)((bb_max & 0xffff) / RT_TW) << 16) | ((unsigned)((bb_max >> 16) / RT_TH) << 24);
+}
+
+// The tiles of a packed tile box, visited in lock step by the whole warp.
 template <typename F>
-__device__ __forceinline__ void for_each_tile(int bb_min, int bb_max, int tiles_x, F &&f) {
-  int tx0 = 0, tx1 = -1, ty0 = 0, ty1 = -1;
-  if (bb_max >= 0) {
-    tx0 = (bb_min & 0xffff) / RT_TW;
-    ty0 = (bb_min >> 16) / RT_TH;
-    tx1 = (bb_max & 0xffff) / RT_TW;
-    ty1 = (bb_max >> 16) / RT_TH;
-  }
-  const int nx = tx1 - tx0 + 1, n_mine = (bb_max >= 0) ? nx * (ty1 - ty0 + 1) : 0;
+__device__ __forceinline__ void for_each_tile(unsigned tb, int tiles_x, F &&f) {
+  const int tx0 = tb & 255, ty0 = (tb >> 8) & 255, tx1 = (tb >> 16) & 255, ty1 = tb >> 24;
+  const int nx = tx1 - tx0 + 1;  // <= 0 for RT_TBOX_NONE
+  const int n_mine = nx > 0 ? nx * (ty1 - ty0 + 1) : 0;
   const int n_max = __reduce_max_sync(0xffffffffu, n_mine);
   for (int i = 0; i < n_max; ++i) {
     int key = -1;
@@ -257,7 +274,7 @@ __device__ __forceinline__ void for_each_tile(int bb_min, int bb_max, int tiles_
 // Near-plane clipping (Sutherland-Hodgman against z >= znear, GL primitive clipping) of a
 // triangle that straddles the plane: rare, kept out of line so that its dynamically indexed
 // arrays do not cost the common path a stack frame.
-__device__ __forceinline__ int4 clip_and_emit(const double *Pc /* [3][3] */, const Cam &cam, int W,
+__device__ __forceinline__ uint2 clip_and_emit(const double *Pc /* [3][3] */, const Cam &cam, int W,
                                            int H, int t, TriRec *slots /* 2t, 2t+1 */) {
   double Q[4][3];
   int nq = 0;
@@ -283,87 +300,128 @@ __device__ __forceinline__ int4 clip_and_emit(const double *Pc /* [3][3] */, con
     }
   }
   // live records occupy the slots in order (slot 2t first)
-  int4 bb = make_int4(0, -1, 0, -1);
+  uint2 bb = make_uint2(RT_TBOX_NONE, RT_TBOX_NONE);
   int n_rec = 0;
   for (int k = 0; k < 2; ++k) {
     if (k == 0 ? nq < 3 : nq != 4) continue;
     const int i1 = k == 0 ? 1 : 2, i2 = k == 0 ? 2 : 3;
     RecQ r;
-    make_record(Q[0][0], Q[0][1], Q[0][2], Q[i1][0], Q[i1][1], Q[i1][2], Q[i2][0], Q[i2][1],
-                Q[i2][2], cam, W, H, t, k == 1 || nq == 4 || clipped_any, r);
+    r.bb_max = -1;
+    VtxS pv[3];
+    const int f0 = project_vertex(Q[0][0], Q[0][1], Q[0][2], cam, pv[0]);
+    const int f1 = project_vertex(Q[i1][0], Q[i1][1], Q[i1][2], cam, pv[1]);
+    const int f2 = project_vertex(Q[i2][0], Q[i2][1], Q[i2][2], cam, pv[2]);
+    if (f0 & f1 & f2 & RT_VF_VALID)
+      make_record(pv[0], pv[1], pv[2], W, H, t, k == 1 || nq == 4 || clipped_any, r);
     if (r.bb_max < 0) continue;
     store_record(slots + n_rec, r);
-    if (n_rec == 0) {
-      bb.x = r.bb_min;
-      bb.y = r.bb_max;
-    } else {
-      bb.z = r.bb_min;
-      bb.w = r.bb_max;
-    }
+    if (n_rec == 0)
+      bb.x = tile_box(r.bb_min, r.bb_max);
+    else
+      bb.y = tile_box(r.bb_min, r.bb_max);
     ++n_rec;
   }
   return bb;
 }
 
-// grid = (ceil(max_tris / 256), B); block = 256 (whole warps always run to the end: the tile
-// loop uses full-mask warp primitives).  One thread per (triangle, pair): pose transform in
-// float64, projection, snapping, culling; the 64-byte record leaves as four 128-bit stores, its
-// pixel box additionally as one int2 (what the fill pass re-reads), and the 16x16 tiles it
-// overlaps are counted with warp-aggregated atomics.
-__global__ void __launch_bounds__(256, 3)
-raster_setup_kernel(Renderer R, const int32_t *__restrict__ cls_idx,
-                    const float *__restrict__ poses, Cam cam, int n_tiles) {
-  pdl_launch_dependents();  // the clip kernel waits (griddepcontrol.wait) for this grid's end
+// 0. vertices: one thread per (vertex, pair): pose transform in float64, projection, snapping,
+// window depth -- once per vertex instead of once per triangle corner (a closed mesh has ~6
+// corners per vertex).  grid = (ceil(max_verts / 256), B); block = 256.
+__global__ void __launch_bounds__(256)
+raster_vertex_kernel(Renderer R, const int32_t *__restrict__ cls_idx,
+                     const float *__restrict__ poses, Cam cam) {
+  pdl_launch_dependents();  // setup waits (griddepcontrol.wait) for this grid's end
   const int b = blockIdx.y;
-  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  const int v = blockIdx.x * blockDim.x + threadIdx.x;
+  const int mesh = __ldg(cls_idx + b);
+  const int v_off = __ldg(R.mesh_vert_off + mesh);
+  if (v >= __ldg(R.mesh_vert_off + mesh + 1) - v_off) return;
+  const float *pose = poses + b * 12;
+  const double x = (double)__ldg(R.verts + (size_t)(v_off + v) * 3 + 0);
+  const double y = (double)__ldg(R.verts + (size_t)(v_off + v) * 3 + 1);
+  const double z = (double)__ldg(R.verts + (size_t)(v_off + v) * 3 + 2);
+  double Pc[3];
+#pragma unroll
+  for (int r = 0; r < 3; ++r)
+    Pc[r] = (double)__ldg(pose + r * 4 + 0) * x + (double)__ldg(pose + r * 4 + 1) * y +
+            (double)__ldg(pose + r * 4 + 2) * z + (double)__ldg(pose + r * 4 + 3);
+  VtxS o;
+  const int flag = project_vertex(Pc[0], Pc[1], Pc[2], cam, o);
+  *reinterpret_cast<int4 *>(R.vtx + (size_t)b * R.max_verts + v) =
+      make_int4((o.X << 2) | flag, o.Y, __double2loint(o.zw), __double2hiint(o.zw));
+}
+
+// 1. setup.  grid = (ceil(max_tris / (256 * RT_SETUP_PER)), B); block = 256 (whole warps always
+// run to the end: the tile loop uses full-mask warp primitives).  One thread per RT_SETUP_PER
+// (triangle, pair)s, 256 apart: the kernel is bound by the latency of its dependent gathers
+// (indices -> projected vertices), so each thread keeps several in flight.  Integer work only:
+// culling, the 64-byte record as four 128-bit stores, the packed tile box (what the fill pass
+// re-reads: 4 bytes per triangle), and the 16x16 tiles counted with warp-aggregated atomics.
+constexpr int RT_SETUP_PER = 2;
+
+__global__ void __launch_bounds__(256, 4)
+raster_setup_kernel(Renderer R, const int32_t *__restrict__ cls_idx, int n_tiles) {
+  pdl_wait();               // the projected vertices
+  pdl_launch_dependents();  // the clip kernel waits for this grid's end in turn
+  const int b = blockIdx.y;
+  const int t_base = blockIdx.x * (256 * RT_SETUP_PER) + threadIdx.x;
   const int mesh = __ldg(cls_idx + b);
   const int t_off = __ldg(R.mesh_tri_off + mesh);
   const int n_tri = __ldg(R.mesh_tri_off + mesh + 1) - t_off;
+  const int v_off = __ldg(R.mesh_vert_off + mesh);
   TriRec *recs = R.recs + (size_t)b * 2 * R.max_tris;
-  int2 *bbox = R.bbox + (size_t)b * 2 * R.max_tris;
+  uint32_t *tbox = R.tbox + (size_t)b * R.max_tris;
   int32_t *count = R.tile_count + (size_t)b * n_tiles;
+  const VtxS *vtx = R.vtx + (size_t)b * R.max_verts - v_off;  // indexed by the global vertex id
 
-  int4 bb = make_int4(0, -1, 0, -1);  // (bb_min, bb_max) of slots 2t and 2t+1; bb_max < 0 = unused
-  if (t < n_tri) {
-    const float *pose = poses + b * 12;
-    const int vidx[3] = {__ldg(R.tris + (size_t)(t_off + t) * 3 + 0),
-                         __ldg(R.tris + (size_t)(t_off + t) * 3 + 1),
-                         __ldg(R.tris + (size_t)(t_off + t) * 3 + 2)};
-    double Pc[9];
+  int idx[RT_SETUP_PER][3];
 #pragma unroll
-    for (int i = 0; i < 3; ++i) {
-      const double x = (double)__ldg(R.verts + (size_t)vidx[i] * 3 + 0);
-      const double y = (double)__ldg(R.verts + (size_t)vidx[i] * 3 + 1);
-      const double z = (double)__ldg(R.verts + (size_t)vidx[i] * 3 + 2);
+  for (int k = 0; k < RT_SETUP_PER; ++k) {
+    const int t = t_base + k * 256;
 #pragma unroll
-      for (int r = 0; r < 3; ++r)
-        Pc[i * 3 + r] = (double)__ldg(pose + r * 4 + 0) * x + (double)__ldg(pose + r * 4 + 1) * y +
-                        (double)__ldg(pose + r * 4 + 2) * z + (double)__ldg(pose + r * 4 + 3);
-    }
-    const bool in0 = Pc[2] - cam.znear >= 0.0, in1 = Pc[5] - cam.znear >= 0.0,
-               in2 = Pc[8] - cam.znear >= 0.0;
-    if (in0 && in1 && in2) {
-      RecQ r;
-      make_record(Pc[0], Pc[1], Pc[2], Pc[3], Pc[4], Pc[5], Pc[6], Pc[7], Pc[8], cam, R.W, R.H, t,
-                  false, r);
-      if (r.bb_max >= 0) {
-        store_record(recs + 2 * t, r);
-        bb.x = r.bb_min;
-        bb.y = r.bb_max;
-      }
-    } else if (in0 || in1 || in2) {
-      // straddles the near plane (rare): left to raster_clip_kernel, which needs dynamically
-      // indexed polygons and would cost this kernel its registers
-      const int slot = atomicAdd(R.work_count + RT_WC_CLIP, 1);
-      R.clip_list[slot] = b * R.max_tris + t;
-    }
+    for (int c = 0; c < 3; ++c)
+      idx[k][c] = t < n_tri ? __ldg(R.tris + (size_t)(t_off + t) * 3 + c) : v_off;
   }
-  // fixed slots 2t, 2t+1: deterministic layout; the compact boxes are what the fill pass reads
-  if (t < R.max_tris) *reinterpret_cast<int4 *>(bbox + 2 * t) = bb;
+  int4 pv[RT_SETUP_PER][3];
+#pragma unroll
+  for (int k = 0; k < RT_SETUP_PER; ++k)
+#pragma unroll
+    for (int c = 0; c < 3; ++c) pv[k][c] = *reinterpret_cast<const int4 *>(vtx + idx[k][c]);
+
+  unsigned tb[RT_SETUP_PER];
+#pragma unroll
+  for (int k = 0; k < RT_SETUP_PER; ++k) {
+    const int t = t_base + k * 256;
+    tb[k] = RT_TBOX_NONE;  // slot 2t unused
+    if (t < n_tri) {
+      const int f_and = pv[k][0].x & pv[k][1].x & pv[k][2].x;
+      const int f_or = pv[k][0].x | pv[k][1].x | pv[k][2].x;
+      if (f_and & RT_VF_NEAR) {
+        if (f_and & RT_VF_VALID) {
+          VtxS va, vb, vc;
+          va.X = pv[k][0].x >> 2; va.Y = pv[k][0].y; va.zw = __hiloint2double(pv[k][0].w, pv[k][0].z);
+          vb.X = pv[k][1].x >> 2; vb.Y = pv[k][1].y; vb.zw = __hiloint2double(pv[k][1].w, pv[k][1].z);
+          vc.X = pv[k][2].x >> 2; vc.Y = pv[k][2].y; vc.zw = __hiloint2double(pv[k][2].w, pv[k][2].z);
+          RecQ r;
+          make_record(va, vb, vc, R.W, R.H, t, false, r);
+          if (r.bb_max >= 0) {
+            store_record(recs + 2 * t, r);
+            tb[k] = tile_box(r.bb_min, r.bb_max);
+          }
+        }
+      } else if (f_or & RT_VF_NEAR) {
+        // straddles the near plane (rare): left to raster_clip_kernel, which needs dynamically
+        // indexed polygons and would cost this kernel its registers
+        const int slot = atomicAdd(R.work_count + RT_WC_CLIP, 1);
+        R.clip_list[slot] = b * R.max_tris + t;
+      }
+    }
+    if (t < R.max_tris) tbox[t] = tb[k];
+  }
   // count the tiles each record overlaps (warp-aggregated)
-  for_each_tile(bb.x, bb.y, R.tiles_x, [&](int key) { tile_atomic(count, key, false); });
-  if (__any_sync(0xffffffffu, bb.w >= 0))
-    for_each_tile(bb.z, bb.w, R.tiles_x, [&](int key) { tile_atomic(count, key, false); });
+#pragma unroll
+  for (int k = 0; k < RT_SETUP_PER; ++k)
+    for_each_tile(tb[k], R.tiles_x, [&](int key) { tile_atomic(count, key, false); });
 }
 
 // grid-stride over the triangles raster_setup_kernel found straddling the near plane (usually
@@ -389,14 +447,14 @@ raster_clip_kernel(Renderer R, const int32_t *__restrict__ cls_idx,
         Pc[k * 3 + r] = (double)__ldg(pose + r * 4 + 0) * x + (double)__ldg(pose + r * 4 + 1) * y +
                         (double)__ldg(pose + r * 4 + 2) * z + (double)__ldg(pose + r * 4 + 3);
     }
-    const int4 bb = clip_and_emit(Pc, cam, R.W, R.H, t, R.recs + (size_t)b * 2 * R.max_tris + 2 * t);
-    *reinterpret_cast<int4 *>(R.bbox + (size_t)b * 2 * R.max_tris + 2 * t) = bb;
+    const uint2 bb = clip_and_emit(Pc, cam, R.W, R.H, t, R.recs + (size_t)b * 2 * R.max_tris + 2 * t);
+    R.clip_box[i] = bb;  // setup left tbox[t] = none: the fill pass places these from the clip list
     int32_t *count = R.tile_count + (size_t)b * n_tiles;
     for (int k = 0; k < 2; ++k) {
-      const int lo = k ? bb.z : bb.x, hi = k ? bb.w : bb.y;
-      if (hi < 0) continue;
-      for (int ty = (lo >> 16) / RT_TH; ty <= (hi >> 16) / RT_TH; ++ty)
-        for (int tx = (lo & 0xffff) / RT_TW; tx <= (hi & 0xffff) / RT_TW; ++tx)
+      const unsigned q = k ? bb.y : bb.x;
+      const int tx0 = q & 255, ty0 = (q >> 8) & 255, tx1 = (q >> 16) & 255, ty1 = q >> 24;
+      for (int ty = ty0; ty <= ty1; ++ty)
+        for (int tx = tx0; tx <= tx1; ++tx)  // empty for RT_TBOX_NONE
           atomicAdd(count + ty * R.tiles_x + tx, 1);
     }
   }
@@ -466,8 +524,9 @@ raster_scan_kernel(Renderer R, int n_tiles, int32_t *__restrict__ status) {
 }
 
 // ------------------------------------------------------------------- 3. fill
-// grid = (ceil(max_tris / 256), B); one thread per triangle = its two record slots (the second
-// is live only for near-clipped triangles); reads the compact boxes with one 128-bit load.
+// grid = (ceil(max_tris / 256), B); one thread per triangle: reads its packed tile box (4 bytes)
+// and places record slot 2t; the pieces of near-clipped triangles (slots 2t, 2t + 1 of the few
+// triangles on the clip list) are placed from the clip list by the first threads of the grid.
 __global__ void __launch_bounds__(256)
 raster_fill_kernel(Renderer R, const int32_t *__restrict__ cls_idx, int n_tiles) {
   pdl_wait();
@@ -479,18 +538,38 @@ raster_fill_kernel(Renderer R, const int32_t *__restrict__ cls_idx, int n_tiles)
   const int32_t *start = R.tile_start + (size_t)b * (n_tiles + 1);
   int32_t *fill = R.tile_fill + (size_t)b * n_tiles;
   int32_t *list = R.tile_list + (size_t)b * R.list_cap;
-  int4 bb = make_int4(0, -1, 0, -1);
-  if (t < n_tri) bb = __ldg(reinterpret_cast<const int4 *>(R.bbox + (size_t)b * 2 * R.max_tris) + t);
-  auto place = [&](int s, int key) {
+  unsigned tb = RT_TBOX_NONE;
+  if (t < n_tri) tb = __ldg(R.tbox + (size_t)b * R.max_tris + t);
+  for_each_tile(tb, R.tiles_x, [&](int key) {
     const int slot = tile_atomic(fill, key, true);
     if (key >= 0) {
       const int pos = start[key] + slot;
-      if (pos < R.list_cap) list[pos] = s;
+      if (pos < R.list_cap) list[pos] = 2 * t;
     }
-  };
-  for_each_tile(bb.x, bb.y, R.tiles_x, [&](int key) { place(2 * t, key); });
-  if (__any_sync(0xffffffffu, bb.w >= 0))
-    for_each_tile(bb.z, bb.w, R.tiles_x, [&](int key) { place(2 * t + 1, key); });
+  });
+  const int n_clip = R.work_count[RT_WC_CLIP];
+  const int gid = (blockIdx.y * gridDim.x + blockIdx.x) * blockDim.x + threadIdx.x;
+  if (gid < n_clip) {
+    const int stride = gridDim.x * gridDim.y * blockDim.x;
+    for (int i = gid; i < n_clip; i += stride) {
+      const int item = R.clip_list[i];
+      const int cb = item / R.max_tris, ct = item - cb * R.max_tris;
+      const uint2 bb = R.clip_box[i];
+      const int32_t *cstart = R.tile_start + (size_t)cb * (n_tiles + 1);
+      int32_t *cfill = R.tile_fill + (size_t)cb * n_tiles;
+      int32_t *clist = R.tile_list + (size_t)cb * R.list_cap;
+      for (int k = 0; k < 2; ++k) {
+        const unsigned q = k ? bb.y : bb.x;
+        const int tx0 = q & 255, ty0 = (q >> 8) & 255, tx1 = (q >> 16) & 255, ty1 = q >> 24;
+        for (int ty = ty0; ty <= ty1; ++ty)
+          for (int tx = tx0; tx <= tx1; ++tx) {
+            const int key = ty * R.tiles_x + tx;
+            const int pos = cstart[key] + atomicAdd(cfill + key, 1);
+            if (pos < R.list_cap) clist[pos] = 2 * ct + k;
+          }
+      }
+    }
+  }
 }
 
 // ----------------------------------------------------------------- 4. raster
@@ -893,8 +972,9 @@ static int dev_alloc(T **p, size_t n) {
 
 static void renderer_free(Renderer *r) {
   if (!r) return;
-  void *ptrs[] = {r->verts, r->uv, r->normals, r->tris, r->mesh_tri_off, r->mesh_has, r->tex,
-                  r->tex_off, r->tex_hw, r->recs, r->bbox, r->clip_list, r->zwin, r->work_count, r->tile_start, r->tile_fill,
+  void *ptrs[] = {r->verts, r->uv, r->normals, r->tris, r->mesh_tri_off, r->mesh_vert_off, r->vtx,
+                  r->mesh_has, r->tex,
+                  r->tex_off, r->tex_hw, r->recs, r->tbox, r->clip_list, r->clip_box, r->zwin, r->work_count, r->tile_start, r->tile_fill,
                   r->tile_list, r->work_list_b[0], r->work_list_b[1], r->heavy_count};
   for (void *p : ptrs)
     if (p) cudaFree(p);
@@ -923,7 +1003,7 @@ int rc_renderer_create(const rc_mesh_desc *meshes, int n_meshes, int height, int
   RC_REQUIRE(width <= 255 * rc::RT_TW && height <= 255 * rc::RT_TH && max_batch <= 32767,
              RC_ERR_CAPACITY);
   size_t V = 0, T = 0, TX = 0;
-  int max_tris = 0;
+  int max_tris = 0, max_verts = 0;
   for (int m = 0; m < n_meshes; ++m) {
     const rc_mesh_desc &d = meshes[m];
     RC_REQUIRE(d.vertices && d.triangles && d.n_vertices > 0 && d.n_triangles > 0,
@@ -933,6 +1013,7 @@ int rc_renderer_create(const rc_mesh_desc *meshes, int n_meshes, int height, int
     T += d.n_triangles;
     TX += (size_t)d.tex_h * d.tex_w * 3;
     if (d.n_triangles > max_tris) max_tris = d.n_triangles;
+    if (d.n_vertices > max_verts) max_verts = d.n_vertices;
   }
   int cur = -1;
   RC_CUDA_TRY(cudaGetDevice(&cur));
@@ -945,13 +1026,15 @@ int rc_renderer_create(const rc_mesh_desc *meshes, int n_meshes, int height, int
   r->max_batch = max_batch;
   r->n_meshes = n_meshes;
   r->max_tris = max_tris;
+  r->max_verts = max_verts;
   r->tiles_x = (width + rc::RT_TW - 1) / rc::RT_TW;
   r->tiles_y = (height + rc::RT_TH - 1) / rc::RT_TH;
   const int n_tiles = r->tiles_x * r->tiles_y;
   r->list_cap = 8 * max_tris + 16 * n_tiles;
   // host staging of the concatenated mesh arrays
   std::vector<float> hv(V * 3), huv(V * 2, 0.f), hn(V * 3, 0.f);
-  std::vector<int32_t> ht(T * 3), hoff(n_meshes + 1), hhas(n_meshes), hhw(n_meshes * 2);
+  std::vector<int32_t> ht(T * 3), hoff(n_meshes + 1), hvoff(n_meshes + 1), hhas(n_meshes),
+      hhw(n_meshes * 2);
   std::vector<int64_t> htoff(n_meshes);
   std::vector<uint8_t> htex(TX);
   size_t v0 = 0, t0 = 0, x0 = 0;
@@ -969,6 +1052,7 @@ int rc_renderer_create(const rc_mesh_desc *meshes, int n_meshes, int height, int
       ht[t0 * 3 + i] = idx + (int32_t)v0;
     }
     hoff[m] = (int32_t)t0;
+    hvoff[m] = (int32_t)v0;
     hhas[m] = (d.uv ? 1 : 0) | (d.normals ? 2 : 0);
     hhw[m * 2] = d.tex_h;
     hhw[m * 2 + 1] = d.tex_w;
@@ -979,18 +1063,22 @@ int rc_renderer_create(const rc_mesh_desc *meshes, int n_meshes, int height, int
     x0 += (size_t)d.tex_h * d.tex_w * 3;
   }
   hoff[n_meshes] = (int32_t)t0;
+  hvoff[n_meshes] = (int32_t)v0;
   RC_TRY(rc::dev_alloc(&r->verts, V * 3));
   RC_TRY(rc::dev_alloc(&r->uv, V * 2));
   RC_TRY(rc::dev_alloc(&r->normals, V * 3));
   RC_TRY(rc::dev_alloc(&r->tris, T * 3));
   RC_TRY(rc::dev_alloc(&r->mesh_tri_off, (size_t)n_meshes + 1));
+  RC_TRY(rc::dev_alloc(&r->mesh_vert_off, (size_t)n_meshes + 1));
+  RC_TRY(rc::dev_alloc(&r->vtx, (size_t)max_batch * max_verts));
   RC_TRY(rc::dev_alloc(&r->mesh_has, (size_t)n_meshes));
   RC_TRY(rc::dev_alloc(&r->tex, TX));
   RC_TRY(rc::dev_alloc(&r->tex_off, (size_t)n_meshes));
   RC_TRY(rc::dev_alloc(&r->tex_hw, (size_t)n_meshes * 2));
   RC_TRY(rc::dev_alloc(&r->recs, (size_t)max_batch * 2 * max_tris));
-  RC_TRY(rc::dev_alloc(&r->bbox, (size_t)max_batch * 2 * max_tris));
+  RC_TRY(rc::dev_alloc(&r->tbox, (size_t)max_batch * max_tris));
   RC_TRY(rc::dev_alloc(&r->clip_list, (size_t)max_batch * max_tris));
+  RC_TRY(rc::dev_alloc(&r->clip_box, (size_t)max_batch * max_tris));
   RC_TRY(rc::dev_alloc(&r->work_count, (size_t)max_batch * n_tiles + rc::RT_WC_INTS));  // [header | tile counts]
   r->tile_count = r->work_count + rc::RT_WC_INTS;
   RC_TRY(rc::dev_alloc(&r->work_list_b[0], (size_t)max_batch * n_tiles));
@@ -1006,7 +1094,8 @@ int rc_renderer_create(const rc_mesh_desc *meshes, int n_meshes, int height, int
     return rc::note_status(RC_ERR_CUDA); \
   }
   RC_UP(r->verts, hv) RC_UP(r->uv, huv) RC_UP(r->normals, hn) RC_UP(r->tris, ht)
-  RC_UP(r->mesh_tri_off, hoff) RC_UP(r->mesh_has, hhas) RC_UP(r->tex, htex)
+  RC_UP(r->mesh_tri_off, hoff) RC_UP(r->mesh_vert_off, hvoff) RC_UP(r->mesh_has, hhas)
+  RC_UP(r->tex, htex)
   RC_UP(r->tex_off, htoff) RC_UP(r->tex_hw, hhw)
 #undef RC_UP
   *handle = r;
@@ -1112,9 +1201,13 @@ int rc_render_dev(void *handle, const rc_render_args *a) {
     rc::raster_clear_tiles_kernel<<<sm_count * clear_ctas, 256, 0, s>>>(R, O);
   else
     rc::raster_clear_kernel<<<sm_count * clear_ctas, 256, 0, s>>>(R, O, B);
-  dim3 gs((R.max_tris + 255) / 256, B);
+  dim3 gv((R.max_verts + 255) / 256, B);
+  RC_CUDA_TRY(rc::launch_maybe_pdl(rc::raster_vertex_kernel, gv, dim3(256), 0, s, chain, R,
+                                   a->cls_idx, a->poses, cam));
+  const int per_block = 256 * rc::RT_SETUP_PER;
+  dim3 gs((R.max_tris + per_block - 1) / per_block, B);
   RC_CUDA_TRY(rc::launch_maybe_pdl(rc::raster_setup_kernel, gs, dim3(256), 0, s, chain, R,
-                                   a->cls_idx, a->poses, cam, n_tiles));
+                                   a->cls_idx, n_tiles));
   RC_CUDA_TRY(rc::launch_maybe_pdl(rc::raster_clip_kernel, dim3(32), dim3(128), 0, s, chain, R,
                                    a->cls_idx, a->poses, cam, n_tiles));
   if ((st = mark(1)) != RC_OK) return st;
@@ -1157,13 +1250,20 @@ int rc_render_stats(void *handle, int batch_size, void *stream, int64_t *out) {
   RC_CUDA_TRY(cudaStreamSynchronize(s));
   std::vector<int32_t> st((size_t)batch_size * (n_tiles + 1));
   RC_CUDA_TRY(cudaMemcpy(st.data(), R.tile_start, st.size() * sizeof(int32_t), cudaMemcpyDeviceToHost));
-  std::vector<int2> bb((size_t)batch_size * 2 * R.max_tris);
-  RC_CUDA_TRY(cudaMemcpy(bb.data(), R.bbox, bb.size() * sizeof(int2), cudaMemcpyDeviceToHost));
+  std::vector<uint32_t> bb((size_t)batch_size * R.max_tris);
+  RC_CUDA_TRY(cudaMemcpy(bb.data(), R.tbox, bb.size() * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+  int32_t n_clip = 0;
+  RC_CUDA_TRY(cudaMemcpy(&n_clip, R.work_count + rc::RT_WC_CLIP, sizeof(int32_t), cudaMemcpyDeviceToHost));
+  std::vector<uint2> cb((size_t)n_clip);
+  if (n_clip > 0)
+    RC_CUDA_TRY(cudaMemcpy(cb.data(), R.clip_box, cb.size() * sizeof(uint2), cudaMemcpyDeviceToHost));
   int64_t recs = 0, entries = 0;
   for (int b = 0; b < batch_size; ++b) entries += st[(size_t)b * (n_tiles + 1) + n_tiles];
-  for (size_t i = 0; i < bb.size(); ++i)
-    if (bb[i].y >= 0) ++recs;  // live records (slots of absent triangles excluded only when the
-                               // mesh has max_tris triangles)
+  // live records (slots of absent triangles count only when the mesh has max_tris triangles:
+  // stale boxes beyond a smaller mesh's triangles are never read by the passes)
+  for (size_t i = 0; i < bb.size(); ++i) recs += bb[i] != rc::RT_TBOX_NONE;
+  for (size_t i = 0; i < cb.size(); ++i)
+    recs += (cb[i].x != rc::RT_TBOX_NONE) + (cb[i].y != rc::RT_TBOX_NONE);
   out[0] = recs;
   out[1] = entries;
   return rc::note_status(RC_OK);

@@ -324,9 +324,9 @@ class RefineLoop(object):
         self.cur = 0
         self.bound = [None, None]
         self.obs = None
-        # stand-in + pose update + 7 render kernels (clear, setup, clip, scan, fill, cover,
+        # stand-in + pose update + 8 render kernels (clear, vertex, setup, clip, scan, fill, cover,
         # resolve) + step
-        self.launches_per_iteration = 1 + 1 + 7 + self.step.launches_per_step
+        self.launches_per_iteration = 1 + 1 + 8 + self.step.launches_per_step
 
     def _damped_gt(self, it, rot_gt, trans_gt):
         """Stand-in for the FlowNet heads: move `damping` of the way to the target, plus noise
