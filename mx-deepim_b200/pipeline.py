@@ -225,6 +225,89 @@ class CompareStep(object):
         }
 
 
+PACKED_KEYS = ("image_observed", "image_rendered", "depth_gt_observed", "depth_rendered",
+               "mask_observed", "mask_gt_observed")
+
+
+class HostFeed(object):
+    """Feeds a CompareStep from pinned host batches with the upload of batch i+1 overlapped
+    with the step of batch i: `depth` device staging sets, uploads on a private copy stream,
+    the step (and the storage-format decode, if `packed`) on the caller's current stream.
+
+    packed=False: every INPUT_KEYS entry is float32 as the reference's data loader hands it to
+    the executor.  packed=True: the six image-sized inputs arrive in the dataset's storage
+    formats (uint8 BGR HWC images, 16-bit depth in 1/depth_factor m, uint8 instance masks) and
+    are decoded on the device (prep.py: image.transform, DEPTH_FACTOR, mask == idx) into the
+    float32 staging set; the small inputs stay float32.
+
+    submit(host) returns the staging-set index i; after a synchronize (or `done[i]`) the
+    step's loss sums / zoom factors for that batch are in `loss[i]` / `zoom_factor[i]` (pinned).
+    """
+
+    def __init__(self, step, example, packed=False, depth_factor=1000.0, pixel_means_bgr=None,
+                 depth=2):
+        from . import prep
+
+        self.prep = prep
+        self.step, self.packed, self.depth = step, bool(packed), int(depth)
+        self.depth_factor = float(depth_factor)
+        self.means_bgr = np.asarray(
+            synth.PIXEL_MEANS if pixel_means_bgr is None else pixel_means_bgr, np.float64).reshape(-1)
+        dev, B = step.device, step.B
+        f = dict(dtype=torch.float32, device=dev)
+        self.sets, self.raw, self.args = [], [], []
+        for _ in range(self.depth):
+            st = {}
+            for k in INPUT_KEYS:
+                e = example[k]
+                if self.packed and k in PACKED_KEYS:
+                    ch = 3 if k.startswith("image") else 1
+                    st[k] = torch.empty((B, ch, step.H, step.W), **f)
+                else:
+                    st[k] = torch.empty(tuple(e.shape), **f)
+            self.sets.append(st)
+            self.raw.append({k: torch.empty_like(example[k], device=dev) for k in PACKED_KEYS}
+                            if self.packed else None)
+            self.args.append(step.bind(st))
+        self.one = torch.ones((B,), dtype=torch.int32, device=dev)
+        self.copy_stream = torch.cuda.Stream(device=dev)
+        self.uploaded = [torch.cuda.Event() for _ in range(self.depth)]
+        self.done = [torch.cuda.Event() for _ in range(self.depth)]
+        self.loss = torch.empty((self.depth, B), dtype=torch.float32).pin_memory()
+        self.zoom_factor = torch.empty((self.depth, B, 4), dtype=torch.float32).pin_memory()
+        self.n = 0
+        self.h2d_bytes = int(sum(example[k].numel() * example[k].element_size() for k in INPUT_KEYS))
+        self.d2h_bytes = int(B * 4 + B * 16)
+        self.launches_per_submit = step.launches_per_step + (6 if self.packed else 0)
+
+    def submit(self, host):
+        i = self.n % self.depth
+        compute = torch.cuda.current_stream(self.step.device)
+        st, raw = self.sets[i], self.raw[i]
+        with torch.cuda.stream(self.copy_stream):
+            if self.n >= self.depth:  # the set's previous batch has been consumed
+                self.copy_stream.wait_event(self.done[i])
+            for k in INPUT_KEYS:
+                dst = raw[k] if (self.packed and k in PACKED_KEYS) else st[k]
+                dst.copy_(host[k], non_blocking=True)
+            self.uploaded[i].record(self.copy_stream)
+        compute.wait_event(self.uploaded[i])
+        if self.packed:
+            p = self.prep
+            p.transform_batch(raw["image_observed"], self.means_bgr, out=st["image_observed"])
+            p.transform_batch(raw["image_rendered"], self.means_bgr, out=st["image_rendered"])
+            p.decode_depth(raw["depth_gt_observed"], self.depth_factor, out=st["depth_gt_observed"])
+            p.decode_depth(raw["depth_rendered"], self.depth_factor, out=st["depth_rendered"])
+            p.decode_mask(raw["mask_observed"], self.one, out=st["mask_observed"])
+            p.decode_mask(raw["mask_gt_observed"], self.one, out=st["mask_gt_observed"])
+        self.step.run(None, args=self.args[i])
+        self.loss[i].copy_(self.step.loss_sum, non_blocking=True)
+        self.zoom_factor[i].copy_(self.step.zoom_factor, non_blocking=True)
+        self.done[i].record(compute)
+        self.n += 1
+        return i
+
+
 def mask_box(mask, out=None, bbox=None, workspace=None, stream=None):
     """Test-time mask policy "box_rendered" / "box_observed" of update_data_batch
     (/root/reference/lib/pair_matching/data_pair.py:101-131): the bounding rectangle of the

@@ -103,3 +103,55 @@ def test_compare_step_graph_replay_is_deterministic(cuda_device):
                     assert torch.equal(cur[k], first[k]), k
     out = {k: (v.cpu().numpy() if v is not None else None) for k, v in step.outputs().items()}
     _check(out, _oracle(host, synth), True)
+
+
+@pytest.mark.parametrize("packed", [False, True])
+def test_host_feed_overlapped_uploads_keep_batches_apart(cuda_device, packed):
+    """pipeline.HostFeed: six different batches submitted back to back through two staging sets
+    (upload of batch i+1 on the copy stream while batch i's step runs): every batch's loss sums
+    and zoom factors equal the oracle's on that batch's (decoded) inputs."""
+    import torch
+
+    from mx_deepim_b200 import pipeline, synth
+
+    B, n = 2, 6
+    hosts = [synth.make_compare_batch(B, seed=300 + i, occlusion=bool(i % 2)) for i in range(n)]
+    step = pipeline.CompareStep(B, cuda_device)
+    means_bgr = np.asarray(synth.PIXEL_MEANS, np.float64).reshape(-1)
+    feeds = []
+    for h in hosts:
+        d = {k: torch.from_numpy(np.ascontiguousarray(h[k])).pin_memory() for k in pipeline.INPUT_KEYS}
+        if packed:
+            for k in ("image_observed", "image_rendered"):
+                rgb = np.clip(np.rint(h[k].astype(np.float64) + means_bgr[::-1].reshape(1, 3, 1, 1)),
+                              0, 255).astype(np.uint8)
+                d[k] = torch.from_numpy(np.ascontiguousarray(rgb[:, ::-1].transpose(0, 2, 3, 1))).pin_memory()
+            for k in ("depth_gt_observed", "depth_rendered"):
+                mm = np.rint(h[k][:, 0].astype(np.float64) * 1000.0).astype(np.uint16)
+                d[k] = torch.from_numpy(np.ascontiguousarray(mm.view(np.int16))).pin_memory()
+                h[k] = (mm.astype(np.float32) / np.float32(1000.0))[:, None]  # what the step sees
+            for k in ("mask_observed", "mask_gt_observed"):
+                d[k] = torch.from_numpy(np.ascontiguousarray(h[k][:, 0].astype(np.uint8))).pin_memory()
+        feeds.append(d)
+    feed = pipeline.HostFeed(step, feeds[0], packed=packed, pixel_means_bgr=means_bgr)
+    assert feed.h2d_bytes == sum(v.numel() * v.element_size() for v in feeds[0].values())
+    snaps = []
+    for d in feeds:
+        feed.submit(d)
+        # stream-ordered snapshots: taken after this batch's step, before the next one's
+        snaps.append((step.loss_sum.clone(), step.zoom_factor.clone(), step.valid.clone()))
+    torch.cuda.synchronize()
+    for i, h in enumerate(hosts):
+        zm = zoom_np.zoom_mask_forward(h["mask_observed"], h["mask_gt_observed"], h["depth_rendered"],
+                                       h["src_pose"], synth.K_LINEMOD)
+        assert np.array_equal(snaps[i][1].cpu().numpy(), zm[3]), i
+        args = [h[k] for k in ("point_cloud_model", "point_cloud_observed", "point_cloud_weights",
+                               "rot_est", "trans_est", "src_pose")]
+        _, _, loss_sum = transform3d_np.pm_loss_forward(*args, MEANS, STDS)
+        np.testing.assert_allclose(snaps[i][0].cpu().numpy(), loss_sum, rtol=1e-4)
+        _, valid = flow_np.flow_kernel_cpu(h["depth_rendered"], h["depth_gt_observed"], h["KT"], h["Kinv"])
+        assert np.array_equal(snaps[i][2].cpu().numpy(), valid), i
+    # the pinned read-backs hold the last two batches
+    for i in (n - 2, n - 1):
+        assert torch.equal(feed.loss[i % 2], snaps[i][0].cpu())
+        assert torch.equal(feed.zoom_factor[i % 2], snaps[i][1].cpu())
