@@ -447,8 +447,21 @@ def run_refine(args, rank, world, local_rank):
                          render_marks=render_marks[it] if render_marks else None)
 
     loop.set_batch(host)
+    # the timed loops replay ONE CUDA graph per 4-iteration loop (RefineLoop.capture) unless
+    # --no-graph: the host then issues one launch call per loop instead of ~64
+    graph_note = "eager launches (--no-graph)"
+    run_loop = one_loop
+    if not args.no_graph:
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            loop.capture(host, iterations=iters)
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize()
+        run_loop = loop.graph.replay
+        graph_note = "one CUDA graph per %d-iteration loop (RefineLoop.capture)" % iters
     for _ in range(Wm):
-        one_loop()
+        run_loop()
     torch.cuda.synchronize()
     n_loops = max(1, (K + iters - 1) // iters)
     e0, e1 = _lib.Event(), _lib.Event()
@@ -457,7 +470,7 @@ def run_refine(args, rank, world, local_rank):
     torch.cuda.synchronize()
     e0.record()
     for l in range(n_loops):
-        one_loop()  # no event marks: the render passes overlap (programmatic dependent launches)
+        run_loop()  # no event marks: the render passes overlap (programmatic dependent launches)
     e1.record()
     torch.cuda.synchronize()
     if world > 1:
@@ -498,6 +511,7 @@ def run_refine(args, rank, world, local_rank):
             "ms_per_step": ms / steps, "higher_is_better": True, "scaling": "strong" if args.config > 3 else "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": cfg["name"], "batch_per_gpu": B, "iterations_per_loop": iters,
+                       "issue": graph_note,
                        "triangles_per_mesh": len(meshes[0]["triangles"]), "meshes": len(meshes),
                        "backward": bool(loop.step.backward),
                        "render_background": "incremental: the loop owns depth/image/mask_rendered, so "
@@ -531,6 +545,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-graph", action="store_true",
+                    help="refine-loop configs: issue every launch from the host instead of "
+                         "replaying one CUDA graph per loop")
     ap.add_argument("--config", type=int, default=2, choices=[2, 3, 4, 5],
                     help="BASELINE.json config (2 = default bench workload; 3-5 = full refine loop)")
     args = ap.parse_args()

@@ -479,6 +479,31 @@ class RefineLoop(object):
         for it in range(iterations):
             self.iterate(it)
 
+    def capture(self, host, iterations=4):
+        """Capture one whole loop -- restart from the batch's initial poses, then `iterations`
+        refinement iterations (stand-in, pose update, render, compare step: ~14 launches and 2
+        memsets each) -- into ONE CUDA graph; `self.graph.replay()` then costs one launch call
+        from the host, which is what matters once a GPU's share of the batch is small (8 GPUs x 32
+        pairs).  The programmatic dependent launches inside the render and the step are kept
+        as programmatic edges of the graph.
+
+        `iterations` must be even: the renderer's incremental background ping-pongs between two
+        item lists per call, and a replay has to find the previous replay's last frame in the
+        half it was captured to read.  Nothing else may render through this loop's renderer
+        between replays (an eager loop of the same even length is fine)."""
+        if iterations % 2:
+            raise ValueError("capture() needs an even number of iterations (ping-pong item lists)")
+        self.set_batch_poses(host)
+        self.run(iterations)  # warm-up; also establishes the incremental-background state
+        torch.cuda.synchronize(self.device)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            self.set_batch_poses(host)
+            self.run(iterations)
+        self.graph = g
+        self.graph_iterations = iterations
+        return g
+
     # ------------------------------------------------------------------ test phase
     def iterate_test(self, rot_est, trans_est, update_mask="box_rendered"):
         """One TEST-time refinement iteration (deepim/core/tester.py:520-594 +
