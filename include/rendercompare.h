@@ -283,6 +283,19 @@ typedef struct rc_compare_step_args {
   int32_t batch_size, height, width, num_points;
   void *stream;                    /* cudaStream_t */
   void **marks;                    /* host array of RC_STEP_MARKS cudaEvent_t, or NULL */
+  /* Sparse frame (optional; all three zero = dense).  When the caller also drives the
+   * rasteriser, the rendered frame is zero outside the 16x16 tiles the renderer's work list
+   * names, so the step can skip the background: the rendered crop box (zoom_mask.py:40-62) is
+   * reduced over those tiles only and combined with `observed_box`, and the GT flow
+   * (gpu_flow_kernel.cu:32-69, zero wherever depth_src <= 1e-3) is computed on those tiles
+   * and re-zeroed on the tiles the previous frame covered.  Results are identical to the
+   * dense step's. */
+  void *frame_renderer;            /* rc_renderer handle whose LAST rc_render_dev call wrote depth_rendered, or NULL */
+  const int32_t *observed_box;     /* [B,4] x0,x1,y0,y1 of mask_gt_observed > 0.3 (= bbox[:, :4] of a dense
+                                      rc_zoom_factor_dev call; x1 < 0: empty); required with frame_renderer */
+  int32_t flow_tracks_frames;      /* 1: flow/valid still hold THIS step's output for the renderer's previous
+                                      frame (same buffers, one step per render); 0: contents unknown, the
+                                      flow planes are written in full */
 } rc_compare_step_args;
 
 int rc_compare_step_dev(const rc_compare_step_args *args);

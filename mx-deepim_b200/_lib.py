@@ -78,6 +78,9 @@ class rc_compare_step_args(ctypes.Structure):
         ("num_points", c_int32),
         ("stream", c_void_p),
         ("marks", POINTER(c_void_p)),
+        ("frame_renderer", c_void_p),
+        ("observed_box", c_void_p),
+        ("flow_tracks_frames", c_int32),
     ])
 
 

@@ -37,6 +37,30 @@ int launch_zoom_factor(const float *obs, const float *rend, const float *src_pos
                        float *trans_out, int batch_size, int channels, int height, int width,
                        int mode, void *stream);
 
+// zoom.cu: zoom factor from precomputed boxes: the observed box from `observed_box` [B,4], the
+// rendered box from the workspace entries 4..7 (filled by frame.cu's tile pass, reset here).
+int launch_zoom_factor_boxes(const int32_t *observed_box, const float *src_pose, const float *K,
+                             float *zoom_factor, int32_t *bbox, int32_t *workspace,
+                             const float *trans_in, float *trans_out, int batch_size, int height,
+                             int width, void *stream);
+
+// raster.cu: the (tile, pair) items of the renderer's last frame and of the one before.
+// Items are packed pair << 16 | tile row << 8 | tile column over 16x16-pixel tiles.
+struct FrameItems {
+  const int32_t *cur_list, *cur_count;    // tiles the last frame covers (count: device int)
+  const int32_t *prev_list, *prev_count;  // tiles the frame before covered; NULL if there was none
+  const int32_t *tile_count;              // [max_batch][tiles] > 0 <=> the tile is in cur_list
+  int tiles_x, tiles_y, H, W, max_batch;
+};
+int renderer_frame_items(void *handle, FrameItems *out);
+
+// frame.cu: rendered crop box (into workspace entries 4..7) and, with flow != NULL, GT flow on
+// the frame's tiles (+ zeros on the previous frame's stale tiles when zero_prev).
+int launch_frame_tiles(const FrameItems &F, const float *depth_src, const float *depth_tgt,
+                       const float *KT, const float *Kinv, float *flow, float *valid,
+                       int32_t *workspace, int batch_size, int height, int width, bool zero_prev,
+                       void *stream);
+
 // Set by rc_compare_step_dev around launches that may overlap their predecessor in the stream
 // (programmatic dependent launch: the kernel does not consume the predecessor's output).
 inline thread_local bool tl_pdl = false;

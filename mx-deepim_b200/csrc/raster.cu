@@ -94,7 +94,7 @@ struct Renderer {
   const int32_t *prev_list, *prev_heavy;     // the previous call's items = tiles its frame dirtied
   // ---- host-side state (not used by kernels): ping-pong work lists for the incremental background
   int32_t *work_list_b[2], *heavy_count;     // heavy_count [2]
-  int cur, have_prev, last_B;
+  int cur, have_prev, last_B, n_frames;
   const void *last_out[5];
   float last_mean[3];
 };
@@ -1234,12 +1234,40 @@ int rc_render_dev(void *handle, const rc_render_args *a) {
   st = rc::check_launch();
   // host state for the next call's incremental test (the handle is not thread-safe)
   Rh.have_prev = st == RC_OK;
+  Rh.n_frames = st == RC_OK ? (Rh.n_frames < 2 ? Rh.n_frames + 1 : 2) : 0;
   Rh.last_B = B;
   for (int i = 0; i < 5; ++i) Rh.last_out[i] = outs[i];
   for (int i = 0; i < 3; ++i) Rh.last_mean[i] = a->pixel_means[i];
   Rh.cur = cur ^ 1;
   return rc::note_status(st);
 }
+
+}  // extern "C"
+
+namespace rc {
+// The last frame's items for the compare step's sparse passes (frame.cu).  Valid until the
+// next rc_render_dev call on this handle.
+int renderer_frame_items(void *handle, FrameItems *out) {
+  RC_REQUIRE(handle && out, RC_ERR_INVALID_ARG);
+  const Renderer &R = *static_cast<const Renderer *>(handle);
+  RC_REQUIRE(R.have_prev && R.n_frames >= 1, RC_ERR_INVALID_ARG);  // no completed render yet
+  const int last = R.cur ^ 1;  // the half the last call filled
+  out->cur_list = R.work_list_b[last];
+  out->cur_count = R.heavy_count + last;
+  const bool two = R.n_frames >= 2;
+  out->prev_list = two ? R.work_list_b[last ^ 1] : nullptr;
+  out->prev_count = two ? R.heavy_count + (last ^ 1) : nullptr;
+  out->tile_count = R.tile_count;
+  out->tiles_x = R.tiles_x;
+  out->tiles_y = R.tiles_y;
+  out->H = R.H;
+  out->W = R.W;
+  out->max_batch = R.max_batch;
+  return RC_OK;
+}
+}  // namespace rc
+
+extern "C" {
 
 int rc_render_stats(void *handle, int batch_size, void *stream, int64_t *out) {
   RC_REQUIRE(handle && out && batch_size > 0, RC_ERR_INVALID_ARG);

@@ -65,6 +65,30 @@ int rc_compare_step_dev(const rc_compare_step_args *a) {
                                   zt ? a->trans_gt : nullptr, zt ? a->zoom_trans_gt : nullptr, B,
                                   1, H, W, RC_ZF_MASK, a->stream);
   };
+  // sparse frame: the rendered box and the GT flow from the renderer's tile items (frame.cu)
+  const bool sparse = a->frame_renderer != nullptr;
+  rc::FrameItems F;
+  bool flow_tiles = false;  // flow on the tiles only (else the dense kernel writes the planes)
+  if (sparse) {
+    RC_REQUIRE(a->observed_box != nullptr, RC_ERR_INVALID_ARG);
+    if ((st = rc::renderer_frame_items(a->frame_renderer, &F)) != RC_OK) return st;
+    RC_REQUIRE(F.H == H && F.W == W && B <= F.max_batch, RC_ERR_INVALID_ARG);
+    flow_tiles = do_flow && a->flow_tracks_frames != 0 && F.prev_list != nullptr;
+  }
+  auto dense_flow = [&]() -> int {
+    return rc_flow_dev(a->depth_rendered, a->depth_gt_observed, a->KT, a->Kinv, a->flow, a->valid,
+                       B, H, W, a->stream);
+  };
+  auto tiles = [&]() -> int {  // rendered box (+ flow) over the frame's tiles
+    return rc::launch_frame_tiles(F, a->depth_rendered, a->depth_gt_observed, a->KT, a->Kinv,
+                                  flow_tiles ? a->flow : nullptr, flow_tiles ? a->valid : nullptr,
+                                  a->workspace, B, H, W, flow_tiles, a->stream);
+  };
+  auto boxes = [&]() -> int {  // zoom factor (+ ZoomTrans) from the two boxes
+    return rc::launch_zoom_factor_boxes(a->observed_box, a->src_pose, a->K, a->zoom_factor,
+                                        a->bbox, a->workspace, zt ? a->trans_gt : nullptr,
+                                        zt ? a->zoom_trans_gt : nullptr, B, H, W, a->stream);
+  };
   struct PdlScope {  // launches inside the scope may start before their predecessor ends
     explicit PdlScope(bool on) { rc::tl_pdl = on; }
     ~PdlScope() { rc::tl_pdl = false; }
@@ -80,25 +104,39 @@ int rc_compare_step_dev(const rc_compare_step_args *a) {
       PdlScope scope(do_bwd);
       if ((st = loss()) != RC_OK) return st;
     }
-    {
-      PdlScope scope(do_loss || do_bwd);
-      if ((st = bbox()) != RC_OK) return st;
-    }
-    if (do_flow) {
-      PdlScope scope(true);
-      st = rc_flow_dev(a->depth_rendered, a->depth_gt_observed, a->KT, a->Kinv, a->flow, a->valid,
-                       B, H, W, a->stream);
-      if (st != RC_OK) return st;
+    if (!sparse) {
+      {
+        PdlScope scope(do_loss || do_bwd);
+        if ((st = bbox()) != RC_OK) return st;
+      }
+      if (do_flow) {
+        PdlScope scope(true);
+        if ((st = dense_flow()) != RC_OK) return st;
+      }
+    } else {
+      // [dense flow when the planes' contents are unknown] -> tile pass -> zoom factor; the
+      // zoom-factor kernel waits (griddepcontrol.wait) for the tile pass right before it
+      bool first = !(do_loss || do_bwd);
+      if (do_flow && !flow_tiles) {
+        PdlScope scope(!first);
+        if ((st = dense_flow()) != RC_OK) return st;
+        first = false;
+      }
+      {
+        PdlScope scope(!first);
+        if ((st = tiles()) != RC_OK) return st;
+      }
+      {
+        PdlScope scope(true);
+        if ((st = boxes()) != RC_OK) return st;
+      }
     }
   } else {
     if ((st = rc::mark(a->marks, 0, s)) != RC_OK) return st;
-    if (do_flow) {
-      st = rc_flow_dev(a->depth_rendered, a->depth_gt_observed, a->KT, a->Kinv, a->flow,
-                       a->valid, B, H, W, a->stream);
-      if (st != RC_OK) return st;
-    }
+    if (do_flow && !flow_tiles && (st = dense_flow()) != RC_OK) return st;
+    if (sparse && (st = tiles()) != RC_OK) return st;
     if ((st = rc::mark(a->marks, 1, s)) != RC_OK) return st;
-    if ((st = bbox()) != RC_OK) return st;
+    if ((st = sparse ? boxes() : bbox()) != RC_OK) return st;
   }
   if ((st = rc::mark(a->marks, 2, s)) != RC_OK) return st;
   // (3) one resampler launch: 3 masks + 6 image channels + 2 flow + 2 flow-weight planes

@@ -743,6 +743,53 @@ __global__ void zoom_trans_kernel(const float *__restrict__ zf, const float *__r
   }
 }
 
+// Zoom factor when the two boxes are already known: block of 128 pairs per CTA, one thread per
+// pair.  The rendered box comes from the workspace entries 4..7 (frame.cu's tile pass; read
+// with atomicExch, which also re-arms the workspace), the observed box from `observed_box`.
+__global__ void __launch_bounds__(128)
+zoom_factor_boxes_kernel(const int32_t *__restrict__ observed_box, int32_t *__restrict__ ws,
+                         const float *__restrict__ src_pose, const float *__restrict__ K,
+                         float *__restrict__ zoom_factor, int32_t *__restrict__ bbox,
+                         const float *__restrict__ trans_in, float *__restrict__ trans_out, int B,
+                         int H, int W) {
+  pdl_wait();  // the tile pass's atomics
+  pdl_launch_dependents();
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  int32_t *w = ws + b * RC_ZF_WS_STRIDE;
+  int32_t fin[8];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) fin[k] = observed_box[b * 4 + k];
+#pragma unroll
+  for (int k = 4; k < 8; ++k) {
+    const int e = atomicExch(w + k, 0);
+    fin[k] = (k & 1) ? e - 1 : INT_MAX - e;
+  }
+  zoom_factor_finalize(fin, src_pose + b * 12, K, zoom_factor + b * 4,
+                       bbox ? bbox + b * 8 : nullptr, H, W);
+  if (trans_out) {  // fused ZoomTrans forward (zoom_trans.py:30-44)
+    const float wx = zoom_factor[b * 4];
+    trans_out[b * 3 + 0] = __fdiv_rn(trans_in[b * 3 + 0], wx);
+    trans_out[b * 3 + 1] = __fdiv_rn(trans_in[b * 3 + 1], wx);
+    trans_out[b * 3 + 2] = trans_in[b * 3 + 2];
+  }
+}
+
+int launch_zoom_factor_boxes(const int32_t *observed_box, const float *src_pose, const float *K,
+                             float *zoom_factor, int32_t *bbox, int32_t *workspace,
+                             const float *trans_in, float *trans_out, int batch_size, int height,
+                             int width, void *stream) {
+  RC_REQUIRE(batch_size >= 0 && height > 0 && width > 0, RC_ERR_INVALID_ARG);
+  if (batch_size == 0) return note_status(RC_OK);
+  RC_REQUIRE(observed_box && src_pose && K && zoom_factor && workspace, RC_ERR_INVALID_ARG);
+  RC_REQUIRE((trans_in == nullptr) == (trans_out == nullptr), RC_ERR_INVALID_ARG);
+  RC_CUDA_TRY(launch_maybe_pdl(zoom_factor_boxes_kernel, dim3((batch_size + 127) / 128), dim3(128),
+                               0, static_cast<cudaStream_t>(stream), tl_pdl, observed_box,
+                               workspace, src_pose, K, zoom_factor, bbox, trans_in, trans_out,
+                               batch_size, height, width));
+  return note_status(check_launch());
+}
+
 int launch_zoom_factor(const float *obs, const float *rend, const float *src_pose,
                        const float *K, const float *pixel_means, float *zoom_factor,
                        int32_t *bbox, int32_t *workspace, const float *trans_in,

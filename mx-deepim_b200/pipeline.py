@@ -375,9 +375,14 @@ class RefineLoop(object):
 
     def __init__(self, meshes, batch, device, K=synth.K_LINEMOD, pixel_means=synth.PIXEL_MEANS,
                  num_points=synth.NUM_3D_SAMPLE, damping=0.5, predict=None, seed=0,
-                 backward=False, lw_pm=1.0):
+                 backward=False, lw_pm=1.0, sparse=True):
+        """sparse=True: the compare step takes the rendered crop box and the GT flow from the
+        16x16 tiles the renderer reports as covered (rc_compare_step_args.frame_renderer,
+        csrc/frame.cu) instead of streaming the ~90 % background of both planes; results are
+        identical (tests/test_refine_gpu.py)."""
         from .render import DeviceRenderer
 
+        self.sparse = bool(sparse)
         self.B = batch
         self.device = torch.device(device)
         self.K = np.asarray(K, np.float32)
@@ -442,12 +447,28 @@ class RefineLoop(object):
         self.rot_gt.copy_(t(q0))
         self.trans_gt.copy_(t(t0))
         self._pose0 = None
+        if self.sparse:
+            # the observed box is a property of the batch: one dense pass now instead of one per
+            # iteration (obs == rend == mask_gt_observed; entries 0..3 are the "> 0.3" box)
+            zf = torch.empty((self.B, 4), dtype=torch.float32, device=self.device)
+            box8 = torch.empty((self.B, 8), dtype=torch.int32, device=self.device)
+            C.zoom_factor(self.obs["mask_gt_observed"], self.obs["mask_gt_observed"], self.pose[0],
+                          self.K, None, zf, _lib.RC_ZF_MASK, bbox=box8)
+            self.observed_box = box8[:, :4].contiguous()
+        self._flow_tracks = False  # the flow planes do not hold a previous frame's flow yet
         for par in (0, 1):
             x = dict(self.obs)
             x.update(image_rendered=self.image_rendered, depth_rendered=self.depth_rendered,
                      src_pose=self.pose[par], KT=self.KT, rot_est=self.rot_est,
                      trans_est=self.trans_est, trans_gt=self.trans_gt)
             self.bound[par] = self.step.bind(x)
+            self._bind_frame(self.bound[par])
+
+    def _bind_frame(self, a):
+        if self.sparse:
+            a.frame_renderer = self.renderer.handle
+            a.observed_box = self.observed_box.data_ptr()
+            a.flow_tracks_frames = 0
 
     def set_batch_poses(self, host):
         """Restart the loop from the batch's initial source poses (same observed side)."""
@@ -473,7 +494,11 @@ class RefineLoop(object):
                                         "mask": self.mask_rendered}, marks=render_marks,
                                    incremental=True)  # the loop owns these three buffers
         self.cur = nxt
-        self.step.run(None, args=self.bound[nxt], marks=marks)
+        a = self.bound[nxt]
+        if self.sparse:
+            a.flow_tracks_frames = 1 if self._flow_tracks else 0
+        self.step.run(None, args=a, marks=marks)
+        self._flow_tracks = True  # one step per render: the flow planes follow the frames
 
     def run(self, iterations=4):
         for it in range(iterations):
@@ -539,7 +564,10 @@ class RefineLoop(object):
         x = {"image_observed": self.obs["image_observed"], "image_rendered": self.image_rendered,
              "depth_rendered": self.depth_rendered, "mask_observed": mo,
              "src_pose": self.pose[nxt]}
+        # dense step: in the test graph the "observed" box is that of mask_observed, which the
+        # mask policy changes every iteration, so there is no per-batch box to reuse
         self.step.run(None, args=self.step.bind(x, test_phase=True))
+        self._flow_tracks = False  # this frame was rendered without a flow pass
 
     def _scratch_q(self):
         if not hasattr(self, "_sq"):

@@ -112,3 +112,58 @@ def test_refine_loop_graph_replay_equals_eager(cuda_device):
             assert torch.equal(got[k], eager[k]), k
     with pytest.raises(ValueError):
         loop.capture(host, iterations=3)
+
+
+def test_sparse_frame_step_equals_dense_step(cuda_device):
+    """rc_compare_step_args.frame_renderer (csrc/frame.cu): crop box + GT flow taken from the
+    renderer's covered tiles, stale tiles re-zeroed -- every output of every iteration is
+    bit-identical to the dense step's, including across loop restarts (the object jumps back to
+    its initial pose: the largest set of stale tiles) and after a test-phase iteration."""
+    import torch
+
+    from mx_deepim_b200 import pipeline, synth
+
+    rng = np.random.default_rng(13)
+    meshes = [synth.make_mesh(rng, level=3, kind=0), synth.make_mesh(rng, level=2, kind=1)]
+    B = 5
+    loops = [pipeline.RefineLoop(meshes, B, cuda_device, seed=7, backward=True, sparse=sp)
+             for sp in (False, True)]
+    host = pipeline.make_refine_batch(meshes, B, 125, renderer=loops[0].renderer, occlusion=True)
+    for lp in loops:
+        lp.set_batch(host)
+    keys = ("flow", "flow_weights_valid", "zoom_factor", "bbox", "zoom_mask_rendered",
+            "zoom_mask_gt_observed", "zoom_image_rendered", "zoom_flow", "zoom_flow_weights",
+            "zoom_trans_gt", "point_matching_loss_sum", "grad_rot")
+
+    def compare(tag):
+        torch.cuda.synchronize()
+        od, os_ = loops[0].step.outputs(), loops[1].step.outputs()
+        for k in keys:
+            assert torch.equal(od[k], os_[k]), (tag, k)
+        assert torch.equal(loops[0].depth_rendered, loops[1].depth_rendered), tag
+
+    for rep in range(2):
+        for lp in loops:
+            lp.set_batch_poses(host)
+        for it in range(4):
+            for lp in loops:
+                lp.iterate(it)
+            compare((rep, it))
+    assert float(loops[1].step.valid.sum()) > 0
+    # a test-phase iteration renders without a flow pass: the next training step must not trust
+    # the flow planes' history
+    q = torch.tensor([[1.0, 0.02, -0.01, 0.03]] * B, device=cuda_device)
+    t = torch.tensor([[0.01, -0.02, 0.05]] * B, device=cuda_device)
+    for lp in loops:
+        lp.iterate_test(q, t)
+    for it in range(2):
+        for lp in loops:
+            lp.iterate(it)
+        compare(("after_test", it))
+    # with event marks (serialised issue order)
+    from mx_deepim_b200 import _lib
+
+    for lp in loops:
+        marks = [_lib.Event() for _ in range(_lib.RC_STEP_MARKS)]
+        lp.iterate(2, marks=marks)
+    compare("marks")
