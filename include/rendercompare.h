@@ -116,6 +116,8 @@ typedef struct rc_zoom_group {
 
 #define RC_ZOOM_ACCUMULATE 1
 #define RC_ZOOM_SRC_BROADCAST 2
+#define RC_ZOOM_SRC_FRAME_SPARSE 4  /* set by rc_compare_step_dev only: src is zero outside the renderer's
+                                       covered tiles and pre/post map 0 to a constant */
 
 #define RC_PRE_NONE 0
 #define RC_PRE_THRESH02 1   /* tap = tap > 0.2 ? 1 : 0   (zoom_mask.py:40-45)          */
@@ -293,9 +295,17 @@ typedef struct rc_compare_step_args {
   void *frame_renderer;            /* rc_renderer handle whose LAST rc_render_dev call wrote depth_rendered, or NULL */
   const int32_t *observed_box;     /* [B,4] x0,x1,y0,y1 of mask_gt_observed > 0.3 (= bbox[:, :4] of a dense
                                       rc_zoom_factor_dev call; x1 < 0: empty); required with frame_renderer */
-  int32_t flow_tracks_frames;      /* 1: flow/valid still hold THIS step's output for the renderer's previous
-                                      frame (same buffers, one step per render); 0: contents unknown, the
-                                      flow planes are written in full */
+  int32_t outputs_track_frames;    /* 1: flow/valid and the zoomed outputs still hold THIS step's output for
+                                      the renderer's previous frame (same buffers, one step per render);
+                                      0: contents unknown, every plane is written in full */
+  uint8_t *zoom_tile_state;        /* [B, ceil(H/8) * ceil(W/128) * 4] bytes or NULL.  With frame_renderer: one
+                                      flag per 32 x 8 block of resampler outputs = "the rendered-side planes with a
+                                      constant background (zoom_mask_rendered, zoom_flow,
+                                      zoom_flow_weights) hold that background here".  A tile whose source
+                                      window lies in tiles the frame does not cover, and whose flag says
+                                      it already holds the background, is not recomputed for those planes.
+                                      Maintained by the step; ignored (but rewritten) when
+                                      outputs_track_frames == 0 */
 } rc_compare_step_args;
 
 int rc_compare_step_dev(const rc_compare_step_args *args);

@@ -80,7 +80,8 @@ class rc_compare_step_args(ctypes.Structure):
         ("marks", POINTER(c_void_p)),
         ("frame_renderer", c_void_p),
         ("observed_box", c_void_p),
-        ("flow_tracks_frames", c_int32),
+        ("outputs_track_frames", c_int32),
+        ("zoom_tile_state", c_void_p),
     ])
 
 

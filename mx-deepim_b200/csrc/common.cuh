@@ -61,6 +61,19 @@ int launch_frame_tiles(const FrameItems &F, const float *depth_src, const float 
                        int32_t *workspace, int batch_size, int height, int width, bool zero_prev,
                        void *stream);
 
+// zoom.cu: rc_zoom_sample_dev with the compare step's sparse-frame information (or NULL).
+// One state byte per warp of an output tile (128 x 8 pixels, 4 warps of 32 columns):
+// tile_state is [B][ceil(H/8) * ceil(W/128) * 4].
+struct ZoomSparse {
+  const int32_t *tile_count;  // the renderer's per-(pair, 16x16 tile) record counts of the frame
+  uint8_t *tile_state;
+  int tiles_x, tiles_y;
+  bool state_valid;
+};
+int launch_zoom_sample(const float *zoom_factor, int inverse, const rc_zoom_group *groups,
+                       int n_groups, int batch_size, int height, int width,
+                       const ZoomSparse *sparse, void *stream);
+
 // Set by rc_compare_step_dev around launches that may overlap their predecessor in the stream
 // (programmatic dependent launch: the kernel does not consume the predecessor's output).
 inline thread_local bool tl_pdl = false;

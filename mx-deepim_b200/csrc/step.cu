@@ -73,7 +73,7 @@ int rc_compare_step_dev(const rc_compare_step_args *a) {
     RC_REQUIRE(a->observed_box != nullptr, RC_ERR_INVALID_ARG);
     if ((st = rc::renderer_frame_items(a->frame_renderer, &F)) != RC_OK) return st;
     RC_REQUIRE(F.H == H && F.W == W && B <= F.max_batch, RC_ERR_INVALID_ARG);
-    flow_tiles = do_flow && a->flow_tracks_frames != 0 && F.prev_list != nullptr;
+    flow_tiles = do_flow && a->outputs_track_frames != 0 && F.prev_list != nullptr;
   }
   auto dense_flow = [&]() -> int {
     return rc_flow_dev(a->depth_rendered, a->depth_gt_observed, a->KT, a->Kinv, a->flow, a->valid,
@@ -155,17 +155,27 @@ int rc_compare_step_dev(const rc_compare_step_args *a) {
     set(n++, a->mask_observed, a->zoom_mask_observed, 1, RC_PRE_NONE, RC_POST_ROUND, 0);
   if (a->zoom_mask_gt_observed)
     set(n++, a->mask_gt_observed, a->zoom_mask_gt_observed, 1, RC_PRE_NONE, RC_POST_ROUND, 0);
+  // rendered-side planes whose background maps to a constant: skippable per output tile
+  const int sp = (sparse && a->zoom_tile_state) ? RC_ZOOM_SRC_FRAME_SPARSE : 0;
   if (a->zoom_mask_rendered)
-    set(n++, a->depth_rendered, a->zoom_mask_rendered, 1, RC_PRE_THRESH02, RC_POST_ROUND, 0);
+    set(n++, a->depth_rendered, a->zoom_mask_rendered, 1, RC_PRE_THRESH02, RC_POST_ROUND, sp);
   if (a->zoom_image_observed)
     set(n++, a->image_observed, a->zoom_image_observed, 3, RC_PRE_ADD_MEAN, RC_POST_SUB_MEAN, 0);
   if (a->zoom_image_rendered)
     set(n++, a->image_rendered, a->zoom_image_rendered, 3, RC_PRE_ADD_MEAN, RC_POST_SUB_MEAN, 0);
-  if (do_flow && a->zoom_flow) set(n++, a->flow, a->zoom_flow, 2, RC_PRE_NONE, RC_POST_DIV_WX, 0);
+  if (do_flow && a->zoom_flow) set(n++, a->flow, a->zoom_flow, 2, RC_PRE_NONE, RC_POST_DIV_WX, sp);
   if (do_flow && a->zoom_flow_weights)
     set(n++, a->valid, a->zoom_flow_weights, 2, RC_PRE_NONE, RC_POST_ROUND_M045,
-        RC_ZOOM_SRC_BROADCAST);
-  st = rc_zoom_sample_dev(a->zoom_factor, 0, g, n, B, H, W, a->stream);
+        RC_ZOOM_SRC_BROADCAST | sp);
+  rc::ZoomSparse zs;
+  if (sp) {
+    zs.tile_count = F.tile_count;
+    zs.tile_state = a->zoom_tile_state;
+    zs.tiles_x = F.tiles_x;
+    zs.tiles_y = F.tiles_y;
+    zs.state_valid = a->outputs_track_frames != 0;
+  }
+  st = rc::launch_zoom_sample(a->zoom_factor, 0, g, n, B, H, W, sp ? &zs : nullptr, a->stream);
   if (st != RC_OK) return st;
   if ((st = rc::mark(a->marks, 3, s)) != RC_OK) return st;
   if ((st = rc::mark(a->marks, 4, s)) != RC_OK) return st;

@@ -263,6 +263,14 @@ struct ZoomParams {
   int H, W;
   int spot_x0, spot_x1, spot_y0, spot_y1;  // zoom_image_with_factor.py:36-45
   int src_aligned;                          // every source plane 16-byte aligned (cp.async staging)
+  // sparse frame (compare step only; tile_state == NULL: off).  Planes in sparse_mask have
+  // sources that are zero outside the renderer's covered 16x16 tiles (tile_count > 0) and
+  // map zero to a constant; an output tile whose source window touches no covered tile and
+  // whose state byte says it already holds that constant is skipped for those planes.
+  const int32_t *tile_count;  // [B][src_tiles]
+  uint8_t *tile_state;        // [B][gridDim.y * gridDim.x][4 warps]
+  unsigned sparse_mask;
+  int src_tiles_x, src_tiles, state_valid;
 };
 
 // Affine parameters of one sample: (wx, wy, tx, ty) as float32, forward or
@@ -527,19 +535,6 @@ zoom_sample_kernel(const __grid_constant__ ZoomParams P, int smem_floats) {
   const bool full_rows = j_first + ZT_H <= H;
   const size_t col_off = (size_t)j_first * W + i;
 
-  if (threadIdx.x < P.n_planes) {
-    const ZoomPlane &zp = P.planes[threadIdx.x];
-    PlaneCtx c;
-    c.src = zp.src + (long long)b * zp.src_bstride;
-    c.dst = zp.dst + (long long)b * zp.dst_bstride;
-    c.pre_op = zp.pre_op;
-    c.post_op = zp.post_op;
-    c.accumulate = zp.accumulate;
-    c.channel = zp.channel;
-    c.mean = zp.mean;
-    ctx[threadIdx.x] = c;
-  }
-
   float wx, wy, tx, ty, wx_in;
   zoom_affine(P.zoom_factor + b * 4, P.inverse, H, W, wx, wy, tx, ty, wx_in);
   const float stepx = (float)(2.0 / (W - 1)), stepy = (float)(2.0 / (H - 1));
@@ -596,9 +591,51 @@ zoom_sample_kernel(const __grid_constant__ ZoomParams P, int smem_floats) {
   const unsigned step_mask = __reduce_or_sync(0xffffffffu, sm_);
   const bool jump = __reduce_or_sync(0xffffffffu, jm_) != 0u;
   const bool staged = sane && !jump && plane_floats <= smem_floats;
+  // sparse frame, decided per WARP (32 output columns x 8 rows): does the warp's source window
+  // touch no covered tile, and do its outputs already hold the sparse planes' background?
+  // A skipping warp still stages and meets the barriers; it only omits blend, post and store
+  // of the planes in P.sparse_mask.
+  unsigned wskip = 0u;  // planes this warp skips
+  if (P.tile_state != nullptr) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint8_t *st = P.tile_state +
+                  (((size_t)b * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) * (ZT_THREADS / 32) + warp;
+    const int held = *st;  // every lane reads before the vote below, lane 0 writes after it
+    const int xw0 = __shfl_sync(0xffffffffu, x0, 0), xw1 = __shfl_sync(0xffffffffu, x0, 31) + 1;
+    int any = 1;
+    if (sane && !P.inverse) {
+      const int sx0 = max(xw0, 0), sx1 = min(xw1, W - 1);
+      const int sy0 = max(y_lo, 0), sy1 = min(y_lo + wh - 1, H - 1);
+      any = 0;
+      if (sx1 >= sx0 && sy1 >= sy0) {
+        const int tx0 = sx0 >> 4, ntx = (sx1 >> 4) - tx0 + 1, ty0 = sy0 >> 4,
+                  nty = (sy1 >> 4) - ty0 + 1;
+        if (ntx * nty > 32) any = 1;
+        else if (lane < ntx * nty)
+          any = __ldg(P.tile_count + (size_t)b * P.src_tiles + (ty0 + lane / ntx) * P.src_tiles_x +
+                      tx0 + lane % ntx) > 0 ? 1 : 0;
+      }
+    }
+    const bool bg_now = !__any_sync(0xffffffffu, any);
+    if (lane == 0) *st = bg_now ? 1 : 0;
+    if (bg_now && P.state_valid && held) wskip = P.sparse_mask;
+  }
+  const int n_planes = P.n_planes;
+  if (threadIdx.x < P.n_planes) {
+    const ZoomPlane &zp = P.planes[threadIdx.x];
+    PlaneCtx c;
+    c.src = zp.src + (long long)b * zp.src_bstride;
+    c.dst = zp.dst + (long long)b * zp.dst_bstride;
+    c.pre_op = zp.pre_op;
+    c.post_op = zp.post_op;
+    c.accumulate = zp.accumulate;
+    c.channel = zp.channel;
+    c.mean = zp.mean;
+    ctx[threadIdx.x] = c;
+  }
   __syncthreads();  // ctx[] visible
   if (staged) {
-    const int pps = max(1, min(P.n_planes, smem_floats / plane_floats));  // planes per stage
+    const int pps = max(1, min(n_planes, smem_floats / plane_floats));  // planes per stage
     const uint32_t win_s = (uint32_t)__cvta_generic_to_shared(win4);
     const uint32_t pitch = 16u * (uint32_t)nch;
     const uint32_t plane_bytes = 4u * (uint32_t)plane_floats;
@@ -614,8 +651,8 @@ zoom_sample_kernel(const __grid_constant__ ZoomParams P, int smem_floats) {
     uint32_t a_row0 = win_s + 4u * (uint32_t)(x0 - xa) + (uint32_t)(r_first - y_lo) * pitch;
     asm volatile("" : "+r"(a_row0));  // keep the shared-window address in a register
 
-    for (int p0 = 0; p0 < P.n_planes; p0 += pps) {
-      const int np = min(pps, P.n_planes - p0);
+    for (int p0 = 0; p0 < n_planes; p0 += pps) {
+      const int np = min(pps, n_planes - p0);
       if (p0 > 0) __syncthreads();  // consumers of the previous stage are done
       // stage: chunk q = (window row, 4-float column chunk); the same chunk of every plane
       const int nchunks = nch * wh;
@@ -642,6 +679,7 @@ zoom_sample_kernel(const __grid_constant__ ZoomParams P, int smem_floats) {
       __syncthreads();
       uint32_t a_pl = a_row0;
       for (int pl = 0; pl < np; ++pl, a_pl += plane_bytes) {
+        if ((wskip >> (p0 + pl)) & 1u) continue;  // warp-uniform
         const PlaneCtx &c_ = ctx[p0 + pl];
         const int pre_op = c_.pre_op;
         const float mean = c_.mean;
@@ -684,9 +722,10 @@ zoom_sample_kernel(const __grid_constant__ ZoomParams P, int smem_floats) {
   if (!act) return;
   const bool xin0 = (x0 >= 0) && (x0 <= W - 1);
   const bool xin1 = (x0 + 1 >= 0) && (x0 + 1 <= W - 1);
-  for (int pl = 0; pl < P.n_planes; ++pl) {
-    const ZoomPlane &zp = P.planes[pl];
-    const float *__restrict__ s = zp.src + (long long)b * zp.src_bstride;
+  for (int pl = 0; pl < n_planes; ++pl) {
+    if ((wskip >> pl) & 1u) continue;
+    const PlaneCtx &zp = ctx[pl];
+    const float *__restrict__ s = zp.src;
     float out[ZT_H];
 #pragma unroll
     for (int m = 0; m < ZT_H; ++m) {
@@ -702,7 +741,7 @@ zoom_sample_kernel(const __grid_constant__ ZoomParams P, int smem_floats) {
       out[m] = blend(tl, tr, bl, br, rows[m].wt, rows[m].wb, wl, wr);
     }
     post_col(out, zp.post_op, zp.mean, zp.channel, P, wx_in, rwx, wx_ok, i, j_first);
-    float *dst = zp.dst + (long long)b * zp.dst_bstride + (size_t)j_first * W + i;
+    float *dst = zp.dst + (size_t)j_first * W + i;
 #pragma unroll
     for (int m = 0; m < ZT_H; ++m) {
       if (j_first + m < H) {
@@ -855,6 +894,16 @@ int rc_zoom_factor_dev(const float *obs, const float *rend, const float *src_pos
 
 int rc_zoom_sample_dev(const float *zoom_factor, int inverse, const rc_zoom_group *groups,
                        int n_groups, int batch_size, int height, int width, void *stream) {
+  return rc::launch_zoom_sample(zoom_factor, inverse, groups, n_groups, batch_size, height, width,
+                                nullptr, stream);
+}
+
+}  // extern "C"
+
+namespace rc {
+int launch_zoom_sample(const float *zoom_factor, int inverse, const rc_zoom_group *groups,
+                       int n_groups, int batch_size, int height, int width,
+                       const ZoomSparse *sparse, void *stream) {
   RC_REQUIRE(batch_size >= 0 && height > 1 && width > 1, RC_ERR_INVALID_ARG);
   RC_REQUIRE(n_groups >= 0 && n_groups <= RC_ZOOM_MAX_GROUPS, RC_ERR_INVALID_ARG);
   if (batch_size == 0 || n_groups == 0) return rc::note_status(RC_OK);
@@ -862,6 +911,7 @@ int rc_zoom_sample_dev(const float *zoom_factor, int inverse, const rc_zoom_grou
   RC_REQUIRE(width % 4 == 0, RC_ERR_UNALIGNED);
   rc::ZoomParams P;
   P.n_planes = 0;
+  P.sparse_mask = 0u;
   const long long plane = (long long)height * width;
   for (int g = 0; g < n_groups; ++g) {
     const rc_zoom_group &G = groups[g];
@@ -880,6 +930,8 @@ int rc_zoom_sample_dev(const float *zoom_factor, int inverse, const rc_zoom_grou
       z.pre_op = G.pre_op;
       z.post_op = G.post_op;
       z.accumulate = (G.flags & RC_ZOOM_ACCUMULATE) ? 1 : 0;
+      if ((G.flags & RC_ZOOM_SRC_FRAME_SPARSE) && !z.accumulate)
+        P.sparse_mask |= 1u << (P.n_planes - 1);
       z.channel = c;
       z.mean = G.mean[c];
     }
@@ -887,6 +939,16 @@ int rc_zoom_sample_dev(const float *zoom_factor, int inverse, const rc_zoom_grou
   P.src_aligned = 1;
   for (int g = 0; g < n_groups; ++g)
     if (!rc::aligned16(groups[g].src)) P.src_aligned = 0;
+  P.tile_count = nullptr;
+  P.tile_state = nullptr;
+  P.src_tiles_x = P.src_tiles = P.state_valid = 0;
+  if (sparse && sparse->tile_state && sparse->tile_count && P.sparse_mask && !inverse) {
+    P.tile_count = sparse->tile_count;
+    P.tile_state = sparse->tile_state;
+    P.src_tiles_x = sparse->tiles_x;
+    P.src_tiles = sparse->tiles_x * sparse->tiles_y;
+    P.state_valid = sparse->state_valid ? 1 : 0;
+  }
   P.zoom_factor = zoom_factor;
   P.inverse = inverse ? 1 : 0;
   P.H = height;
@@ -920,6 +982,9 @@ int rc_zoom_sample_dev(const float *zoom_factor, int inverse, const rc_zoom_grou
                                 static_cast<cudaStream_t>(stream)>>>(P, kSmemFloats);
   return rc::note_status(rc::check_launch());
 }
+}  // namespace rc
+
+extern "C" {
 
 int rc_zoom_trans_dev(const float *zoom_factor, const float *trans_in, float *trans_out,
                       int batch_size, int inverse, int scale_xy, int accumulate, void *stream) {

@@ -104,6 +104,9 @@ class CompareStep(object):
         self.grad_rot = torch.empty((B, 4), **f) if backward else None
         self.grad_trans = torch.empty((B, 3), **f) if backward else None
         self.grad_zoom_trans = torch.empty((B, 3), **f) if backward else None
+        # one flag per 32x8 block of resampler outputs (sparse frame step, see RefineLoop)
+        self.zoom_tile_state = torch.zeros((B, ((Hh + 7) // 8) * ((Ww + 127) // 128) * 4),
+                                           dtype=torch.uint8, device=self.device)
         self.Kd = C.device_const(self.K, self.device)
         self.graph = None
         # flow, bbox+zoom factor(+ZoomTrans), resampler, pm loss (+ loss bwd, ZoomTrans bwd)
@@ -468,7 +471,8 @@ class RefineLoop(object):
         if self.sparse:
             a.frame_renderer = self.renderer.handle
             a.observed_box = self.observed_box.data_ptr()
-            a.flow_tracks_frames = 0
+            a.zoom_tile_state = self.step.zoom_tile_state.data_ptr()
+            a.outputs_track_frames = 0
 
     def set_batch_poses(self, host):
         """Restart the loop from the batch's initial source poses (same observed side)."""
@@ -496,7 +500,7 @@ class RefineLoop(object):
         self.cur = nxt
         a = self.bound[nxt]
         if self.sparse:
-            a.flow_tracks_frames = 1 if self._flow_tracks else 0
+            a.outputs_track_frames = 1 if self._flow_tracks else 0
         self.step.run(None, args=a, marks=marks)
         self._flow_tracks = True  # one step per render: the flow planes follow the frames
 
