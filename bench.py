@@ -209,12 +209,13 @@ def run_ours(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
 
-    from mx_deepim_b200 import _lib, pipeline, synth
+    from mx_deepim_b200 import _lib, pipeline, shard, synth
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the product has no CPU fallback")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    numa_cores = shard.bind_to_gpu_numa(local_rank) if world > 1 else None
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
@@ -385,7 +386,8 @@ def run_ours(args, rank, world, local_rank):
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "steps": Ke, "loss_checksum": loss_host,
                     "feed": "pipeline.HostFeed: float32 pinned host blobs, 2 device staging sets, "
-                            "upload of batch i+1 overlapped with the step of batch i"},
+                            "upload of batch i+1 overlapped with the step of batch i",
+                    "host_cores_bound": (len(numa_cores) if numa_cores else None)},
             "e2e_packed": {"value": e2e_packed_value, "unit": UNIT, "h2d_bytes_per_step": h2d_p,
                            "d2h_bytes_per_step": d2h, "steps": Ke,
                            "formats": "uint8 BGR HWC images, uint16 mm depth, uint8 masks; decoded on "

@@ -42,3 +42,38 @@ def allreduce_metric(loss_sum: torch.Tensor, count: int):
     if _is_dist():
         dist.all_reduce(t, op=dist.ReduceOp.SUM)
     return float(t[0].item()), float(t[1].item())
+
+
+def bind_to_gpu_numa(device_index: int):
+    """Pin this process to the CPU cores NVML lists as local to GPU `device_index`, so that the
+    pinned staging buffers it allocates afterwards (first touch) sit on the GPU's own NUMA node
+    and the host feed of eight ranks does not cross the socket interconnect.  Best effort:
+    returns the core list, or None when NVML / the affinity call is unavailable."""
+    import os
+
+    try:
+        import pynvml
+
+        pynvml.nvmlInit()
+        try:
+            h = None
+            try:  # NVML enumerates in PCI order; CUDA's index may differ (CUDA_VISIBLE_DEVICES)
+                pr = torch.cuda.get_device_properties(int(device_index))
+                bus = "%08x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+                h = pynvml.nvmlDeviceGetHandleByPciBusId(bus.encode())
+            except Exception:
+                h = None
+            if h is None:
+                h = pynvml.nvmlDeviceGetHandleByIndex(int(device_index))
+            n_words = (os.cpu_count() + 63) // 64
+            words = pynvml.nvmlDeviceGetCpuAffinity(h, n_words)
+        finally:
+            pynvml.nvmlShutdown()
+        cores = [64 * w + b for w, word in enumerate(words) for b in range(64) if (word >> b) & 1]
+        allowed = sorted(set(cores) & set(os.sched_getaffinity(0)))
+        if not allowed:
+            return None
+        os.sched_setaffinity(0, allowed)
+        return allowed
+    except Exception:
+        return None

@@ -54,3 +54,14 @@ def test_gloo_world_size_2():
     assert mx0 == mx1 == 11.0
     assert s0 == s1 == (1.0 + 2.0) + (2.0 + 2.0) and n0 == n1 == 257.0
     assert (seed0, seed1) == (102, 1102)
+
+
+def test_bind_to_gpu_numa_is_best_effort():
+    """No NVML / no GPU here: the helper reports None and leaves the affinity alone."""
+    import os
+
+    from mx_deepim_b200 import shard
+
+    before = os.sched_getaffinity(0)
+    assert shard.bind_to_gpu_numa(0) is None
+    assert os.sched_getaffinity(0) == before
