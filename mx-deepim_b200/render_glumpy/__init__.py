@@ -3,7 +3,7 @@ names, constructor and `render` signatures and return values, backed by the CUDA
 (csrc/raster.cu) instead of glumpy / OpenGL.
 
     render_py.Render_Py                                   render_py.py:48-128
-    render_py_depth.Render_Py                             render_py_depth.py:48-128
+    render_py_depth.Render_Py_depth                       render_py_depth.py:47-128
     render_py_multi.Render_Py                             render_py_multi.py:49-147
     render_py_light.Render_Py_Light                       render_py_light.py:80-213
     render_py_light_multi_program.Render_Py_Light_MultiProgram   render_py_light_multi_program.py:84-240

@@ -26,17 +26,43 @@ Two parts with different provenance:
   by a [2x3] GEMM, x_real = (g+1)*(n-1)/2, zero contribution from taps outside
   [0, n-1], float32 tap weights and a float64-promoted blend.
 
-PARITY UNPINNED for the sampler: the reference ships no golden vectors and no
-asserting test for these operators; the restatement is
-cross-checked against torch.nn.functional.grid_sample(align_corners=True,
-padding_mode="zeros") in tests/test_oracle_zoom.py.
+PINNED for everything the plugins compute in Python / numpy: the reference's
+own operator files run unmodified under a numpy `mxnet` stand-in
+(tests/golden/make_golden_ops.py, mx_stub.py) and every function below
+reproduces their outputs bit-exactly (tests/test_golden_ops_cpu.py).
+PARITY UNPINNED for the two MXNet built-ins (GridGenerator, BilinearSampler):
+the reference ships no golden vectors and no asserting test for them
+(SURVEY.md section 4); the restatement is cross-checked against
+torch.nn.functional.grid_sample(align_corners=True, padding_mode="zeros") in
+tests/test_oracle_cpu.py.
 """
 from __future__ import annotations
 
 import numpy as np
 
+import contextlib
+
 f32 = np.float32
 f64 = np.float64
+
+# Scalar promotion of the reference's mixed np.float32 / Python-scalar expressions:
+#   "legacy" -- numpy 1.x, which the reference was written for: evaluated in float64 (default;
+#               what the product implements);
+#   "nep50"  -- numpy >= 2: stays float32.  Used only to compare with the golden vectors that
+#               tests/golden/make_golden_ops.py produces by running the reference's own plugin
+#               files under this container's numpy 2.x.
+PROMOTION = "legacy"
+
+
+@contextlib.contextmanager
+def promotion(mode):
+    global PROMOTION
+    assert mode in ("legacy", "nep50")
+    old, PROMOTION = PROMOTION, mode
+    try:
+        yield
+    finally:
+        PROMOTION = old
 
 
 # ----------------------------------------------------------------- rounding
@@ -115,6 +141,10 @@ def zoom_factor_from_valid(valid_real, valid_rendered, K, src_pose, height, widt
     wy = crop_height / height
     tx = zoom_c_x / width * 2 - 1
     ty = zoom_c_y / height * 2 - 1
+    if PROMOTION == "nep50" and rbox[1] >= 0:
+        # NEP 50: np.float32 centre with Python ints stays float32 (three float32 roundings)
+        tx = f32(f32(f32(obj_rendered_c_x / f32(width)) * f32(2)) - f32(1))
+        ty = f32(f32(f32(obj_rendered_c_y / f32(height)) * f32(2)) - f32(1))
     zf = np.array([wx, wy, tx, ty], dtype=f64).astype(f32)  # zoom_factor_array[b, i] = ... (:116-119)
     bbox = np.array([obj_real_start_x, obj_real_end_x, obj_real_start_y, obj_real_end_y, *rbox],
                     dtype=np.int64)
@@ -192,6 +222,8 @@ def bilinear_sampler(data, gx, gy):
 
 def inverse_affine(zf, height, width):
     """zoom_flow.py:35-44 / zoom_mask_with_factor.py:43-52 (float64 scalars, numpy 1.x)."""
+    if PROMOTION == "nep50":
+        return _inverse_affine_f32(zf, height, width)
     wx_in, wy_in, tx_in, ty_in = [f64(v) for v in np.asarray(zf, f32)]
     wx = 1 / wx_in
     wy = 1 / wy_in
@@ -202,6 +234,21 @@ def inverse_affine(zf, height, width):
     tx = (width * 0.5 - obj_real_c_x) / crop_width * 2
     ty = (height * 0.5 - obj_real_c_y) / crop_height * 2
     return f32(wx), f32(wy), f32(tx), f32(ty)
+
+
+def _inverse_affine_f32(zf, height, width):
+    """The same expressions with every operation rounded to float32 (NEP 50 promotion)."""
+    wx_in, wy_in, tx_in, ty_in = [f32(v) for v in np.asarray(zf, f32)]
+    w, h = f32(width), f32(height)
+    wx = f32(f32(1) / wx_in)
+    wy = f32(f32(1) / wy_in)
+    crop_width = f32(wx_in * w)
+    crop_height = f32(wy_in * h)
+    obj_real_c_x = f32(f32(f32(tx_in * f32(0.5)) * w) + f32(0.5 * width))
+    obj_real_c_y = f32(f32(f32(ty_in * f32(0.5)) * h) + f32(0.5 * height))
+    tx = f32(f32(f32(f32(width * 0.5) - obj_real_c_x) / crop_width) * f32(2))
+    ty = f32(f32(f32(f32(height * 0.5) - obj_real_c_y) / crop_height) * f32(2))
+    return wx, wy, tx, ty
 
 
 def sample_batch(data, zoom_factor, inverse=False):

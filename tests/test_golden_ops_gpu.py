@@ -1,0 +1,147 @@
+"""The CUDA plugins against golden vectors produced by the REFERENCE'S OWN operator files
+(tests/golden/ops_reference.npz, made by tests/golden/make_golden_ops.py: deepim/operator_py/*.py
+run unmodified under a numpy `mxnet` stand-in whose two MXNet built-ins are the sampler
+restatement).  No oracle call in this file: the committed reference outputs are the checker.
+
+Bars (north_star): zoom factors bit-exact -- wx, wy always; tx, ty wherever the golden run's
+numpy-2 (NEP 50) scalar promotion coincides with the numpy-1.x promotion the product follows
+(recorded per value in the fixture), else within 1.5 ulp(1); resampled values within 1e-4 abs;
+0/1 masks equal on >= 99.999 % of the pixels; Transform3D within 1e-5 m, gradients 2e-4 rel.
+"""
+import os
+
+import numpy as np
+import pytest
+
+import helpers
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+STRIDE = 8
+TOL = 1e-4
+K_FLAT = helpers.K_LM.flatten()
+PM_FLAT = helpers.PIXEL_MEANS.flatten()
+
+
+@pytest.fixture(scope="module")
+def gold():
+    return np.load(os.path.join(GOLD, "ops_reference.npz"))
+
+
+def _custom(dev, **kw):
+    import torch
+
+    from mx_deepim_b200 import operator, operator_py  # noqa: F401
+
+    kw = {k: (torch.from_numpy(np.ascontiguousarray(v)).to(dev)
+              if isinstance(v, np.ndarray) and k not in ("K", "pixel_means", "T_means", "T_stds")
+              else v) for k, v in kw.items()}
+    h = operator.Custom(**kw)
+    torch.cuda.synchronize()
+    return h
+
+
+def bits(gold, key, shape):
+    n = int(np.prod(shape))
+    return np.unpackbits(gold[key + "__bits"])[:n].reshape(shape).astype(np.float32)
+
+
+def check_plane(gold, key, got, tol=TOL):
+    ref = gold[key + "__sample"]
+    assert np.abs(got[..., ::STRIDE, ::STRIDE] - ref).max() <= tol, key
+    s = got.astype(np.float64).sum(axis=(-2, -1))
+    assert np.abs(s - gold[key + "__sum"]).max() <= tol * got.shape[-1] * got.shape[-2], key
+
+
+def check_mask(gold, key, got):
+    assert (got != bits(gold, key, got.shape)).mean() < 1e-5, key
+
+
+def check_zoom_factor(got, ref, legacy_equal):
+    g, r = got.view(np.uint32), ref.view(np.uint32)
+    assert np.array_equal(g[:, :2], r[:, :2])
+    assert np.array_equal(g[legacy_equal], r[legacy_equal])
+    assert np.abs(got.astype(np.float64) - ref.astype(np.float64)).max() <= 1.5 * 2.0 ** -23
+
+
+@pytest.mark.parametrize("tag,batch,seed,empty", [("a", 2, 5, ()), ("b", 4, 6, (1,))])
+def test_zoom_mask_and_image_vs_reference_golden(cuda_device, gold, tag, batch, seed, empty):
+    d = helpers.make_zoom_inputs(batch, seed, empty_rendered=empty)
+    eq = gold["zoom_mask_%s/legacy_equal" % tag]
+    h = _custom(cuda_device, op_type="ZoomMask", mask_observed=d["mask_observed"],
+                mask_gt_observed=d["mask_gt_observed"], mask_rendered=d["mask_rendered"],
+                src_pose=d["src_pose"], K=K_FLAT, height=480, width=640)
+    out = dict(zip(("zoom_mask_observed", "zoom_mask_gt_observed", "zoom_mask_rendered",
+                    "zoom_factor"), [o.cpu().numpy() for o in h.outputs]))
+    check_zoom_factor(out["zoom_factor"], gold["zoom_mask_%s/zoom_factor" % tag], eq)
+    for k in ("zoom_mask_observed", "zoom_mask_gt_observed", "zoom_mask_rendered"):
+        check_mask(gold, "zoom_mask_%s/%s" % (tag, k), out[k])
+    h = _custom(cuda_device, op_type="ZoomImage", image_observed=d["image_observed"],
+                image_rendered=d["image_rendered"], src_pose=d["src_pose"], K=K_FLAT, height=480,
+                width=640, pixel_means=PM_FLAT)
+    o = [x.cpu().numpy() for x in h.outputs]
+    check_zoom_factor(o[2], gold["zoom_image_%s/zoom_factor" % tag], eq)
+    # a 1-ulp tx / ty moves a tap by < 4e-5 px; random texture (|gradient| <= 255 / px) -> 1e-2
+    tol = TOL if eq.all() else 1e-2
+    check_plane(gold, "zoom_image_%s/zoom_image_observed" % tag, o[0], tol)
+    check_plane(gold, "zoom_image_%s/zoom_image_rendered" % tag, o[1], tol)
+
+
+def test_with_factor_family_vs_reference_golden(cuda_device, gold):
+    d = helpers.make_zoom_inputs(2, 5)
+    zf = gold["zoom_mask_a/zoom_factor"]  # fed as data: identical sampling coordinates
+    for hl in (False, True):
+        h = _custom(cuda_device, op_type="ZoomImageWithFactor", zoom_factor=zf,
+                    image_observed=d["image_observed"], image_rendered=d["image_rendered"],
+                    height=480, width=640, pixel_means=PM_FLAT, high_light_center=hl)
+        check_plane(gold, "zoom_image_wf_hl%d/zoom_image_observed" % hl, h.outputs[0].cpu().numpy())
+        check_plane(gold, "zoom_image_wf_hl%d/zoom_image_rendered" % hl, h.outputs[1].cpu().numpy())
+    h = _custom(cuda_device, op_type="ZoomDepth", zoom_factor=zf,
+                depth_observed=d["depth_observed"], depth_rendered=d["depth_rendered"])
+    check_plane(gold, "zoom_depth/zoom_depth_observed", h.outputs[0].cpu().numpy())
+    check_plane(gold, "zoom_depth/zoom_depth_rendered", h.outputs[1].cpu().numpy())
+    h = _custom(cuda_device, op_type="ZoomFlow", zoom_factor=zf, flow=d["flow"],
+                flow_weights=d["flow_weights"], b_inv_zoom=False)
+    zoomed = h.outputs[0].cpu().numpy()
+    check_plane(gold, "zoom_flow/zoom_flow", zoomed, TOL * 4)  # 1e-4 px scaled by 1 / wx <= 4
+    check_mask(gold, "zoom_flow/zoom_flow_weights", h.outputs[1].cpu().numpy())
+    h = _custom(cuda_device, op_type="ZoomMaskWithFactor", zoom_factor=zf,
+                mask=d["depth_rendered"], b_inv_zoom=False)
+    check_mask(gold, "zoom_mask_wf/zoom_mask", h.outputs[0].cpu().numpy())
+
+
+def test_zoom_trans_vs_reference_golden(cuda_device, gold):
+    import torch
+
+    zf = gold["zoom_mask_a/zoom_factor"]
+    td, og = gold["zoom_trans/trans_delta"], gold["zoom_trans/out_grad"]
+    for inv in (False, True):
+        for zg in (False, True):
+            h = _custom(cuda_device, op_type="ZoomTrans", zoom_factor=zf, trans_delta=td,
+                        b_inv_zoom=inv, b_zoom_grad=zg)
+            assert np.array_equal(h.outputs[0].cpu().numpy().view(np.uint32),
+                                  gold["zoom_trans/fwd_inv%d_zg%d" % (inv, zg)].view(np.uint32))
+            gz, gt = h.backward([torch.from_numpy(og).to(cuda_device)])
+            assert float(gz.abs().sum()) == 0.0
+            assert np.array_equal(gt.cpu().numpy().view(np.uint32),
+                                  gold["zoom_trans/bwd_inv%d_zg%d" % (inv, zg)].view(np.uint32))
+
+
+@pytest.mark.parametrize("rot_coord", ["MODEL", "CAMERA", "CAMERA_NEW", "NAIVE"])
+def test_transform3d_vs_reference_golden(cuda_device, gold, rot_coord):
+    import torch
+
+    p = helpers.make_points_inputs(4, 11, num_points=3000, num_keep=2500)
+    og = np.random.default_rng(78).normal(0, 1.0, size=p["points"].shape).astype(np.float32)
+    h = _custom(cuda_device, op_type="Transform3D", point_cloud=p["points"],
+                rotation=p["rotation"], translation=p["translation"], pose_src=p["pose_src"],
+                T_means=np.zeros(3, np.float32), T_stds=np.ones(3, np.float32),
+                rot_coord=rot_coord)
+    ref = gold["transform3d/%s/fwd" % rot_coord]
+    assert np.abs(h.outputs[0].cpu().numpy() - ref).max() < 1e-5
+    grads = h.backward([torch.from_numpy(og).to(cuda_device)])
+    torch.cuda.synchronize()
+    assert float(grads[0].abs().sum()) == 0.0 and float(grads[3].abs().sum()) == 0.0
+    for got, key in ((grads[1], "grad_rotation"), (grads[2], "grad_translation")):
+        r = gold["transform3d/%s/%s" % (rot_coord, key)]
+        assert np.abs(got.cpu().numpy() - r).max() <= 2e-4 * max(1.0, np.abs(r).max()), key
