@@ -47,10 +47,14 @@ def bits(gold, key, shape):
 
 
 def check_plane(gold, key, got, tol=TOL):
+    """`tol` is a scalar or one value per sample of the batch."""
+    tol = np.broadcast_to(np.asarray(tol, np.float64), got.shape[:1])
     ref = gold[key + "__sample"]
-    assert np.abs(got[..., ::STRIDE, ::STRIDE] - ref).max() <= tol, key
+    err = np.abs(got[..., ::STRIDE, ::STRIDE] - ref).reshape(got.shape[0], -1).max(axis=1)
+    assert (err <= tol).all(), (key, err)
     s = got.astype(np.float64).sum(axis=(-2, -1))
-    assert np.abs(s - gold[key + "__sum"]).max() <= tol * got.shape[-1] * got.shape[-2], key
+    serr = np.abs(s - gold[key + "__sum"]).reshape(got.shape[0], -1).max(axis=1)
+    assert (serr <= tol * got.shape[-1] * got.shape[-2]).all(), (key, serr)
 
 
 def check_mask(gold, key, got):
@@ -81,8 +85,10 @@ def test_zoom_mask_and_image_vs_reference_golden(cuda_device, gold, tag, batch, 
                 width=640, pixel_means=PM_FLAT)
     o = [x.cpu().numpy() for x in h.outputs]
     check_zoom_factor(o[2], gold["zoom_image_%s/zoom_factor" % tag], eq)
-    # a 1-ulp tx / ty moves a tap by < 4e-5 px; random texture (|gradient| <= 255 / px) -> 1e-2
-    tol = TOL if eq.all() else 1e-2
+    # pairs whose tx, ty coincide with the golden run's: the 1e-4 bar.  Elsewhere tx / ty differ by
+    # <= 1.5 * 2^-23, i.e. the taps move by <= 5.7e-5 px, and these test images are per-pixel
+    # random noise (|gradient| <= 255 / px): <= 1.5e-2
+    tol = np.where(eq.all(axis=1), TOL, 2e-2)
     check_plane(gold, "zoom_image_%s/zoom_image_observed" % tag, o[0], tol)
     check_plane(gold, "zoom_image_%s/zoom_image_rendered" % tag, o[1], tol)
 
