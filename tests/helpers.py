@@ -181,3 +181,31 @@ def make_eval_inputs(seed, batch=4, num_points=1500):
     d_test[:, :40] = 0
     return dict(pose_est=pose_est, pose_gt=pose_gt, points=points, n_valid=n_valid,
                 d_test=d_test.astype(np.float32), d_gt=d_gt, d_est=d_est)
+
+
+def make_updater_inputs(batch, seed, K=K_LM):
+    """A batch for one pass of batchUpdaterPyMulti.forward: two procedural meshes, src / tgt
+    poses, the observed depth (GL-restatement render at the target pose, 1 mm quantised) and
+    'network predictions' = the ground-truth update damped by 0.5 plus noise."""
+    from mx_deepim_b200 import synth
+    from oracle import pose_np, raster_np
+
+    rng = np.random.default_rng(seed)
+    meshes = [synth.make_mesh(rng, level=3, kind=0, texture_size=128),
+              synth.make_mesh(rng, level=3, kind=2, texture_size=128)]
+    cls = rng.integers(0, len(meshes), size=batch).astype(np.int32)
+    src = np.zeros((batch, 3, 4), np.float32)
+    tgt = np.zeros((batch, 3, 4), np.float32)
+    rot = np.zeros((batch, 4), np.float32)
+    trans = np.zeros((batch, 3), np.float32)
+    depth = np.zeros((batch, 1, H, W), np.float32)
+    for b in range(batch):
+        src[b], tgt[b] = random_pose_pair(rng, K)
+        q, t = pose_np.calc_RT_delta(src[b], tgt[b], np.zeros(3), np.ones(3), "CAMERA", "QUAT")
+        q = np.array([1.0, 0, 0, 0]) + 0.5 * (q - np.array([1.0, 0, 0, 0])) + rng.normal(0, 0.01, 4)
+        rot[b] = q / np.linalg.norm(q)
+        trans[b] = 0.5 * t + rng.normal(0, 0.005, size=3)
+        d = raster_np.render_py(meshes[cls[b]], tgt[b, :, :3], tgt[b, :, 3], K, r_type="mat")[1]
+        depth[b, 0] = np.round(d.astype(np.float64) * 1000.0) / 1000.0
+    return dict(meshes=meshes, class_index=cls, src_pose=src, tgt_pose=tgt, rot_est=rot,
+                trans_est=trans, depth_gt_observed=depth)

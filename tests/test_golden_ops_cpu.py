@@ -220,3 +220,48 @@ def test_renderer_signatures_vs_reference_modules():
             ref = m[key]
             assert got[:len(ref)] == ref, (module, fn_name, got, ref)
             assert all(d is not None for _, d in got[len(ref):]), (module, fn_name)
+
+
+# ------------------------------------------------------------------ batch updater (a22)
+def test_updater_restatement_vs_reference_driver():
+    """oracle/updater_np.updater_forward against the reference's own batchUpdaterPyMulti.forward
+    (tests/golden/make_golden_updater.py: the driver run unmodified with stand-ins for mxnet,
+    gpu_flow and the GL renderer).  The golden run's numpy 2 keeps `2.0 / Nq` of quat2mat in
+    float32 where the restatement follows numpy 1.x (float64): poses agree to float32 rounding,
+    so frames are compared at the north_star bars rather than bit for bit."""
+    from oracle import updater_np
+
+    g = np.load(os.path.join(GOLD, "updater_reference.npz"))
+    inp = helpers.make_updater_inputs(3, 31)
+    pm = helpers.PIXEL_MEANS[[2, 1, 0]]
+    ref = updater_np.updater_forward(inp["meshes"], inp["class_index"], inp["src_pose"],
+                                     inp["tgt_pose"], inp["rot_est"], inp["trans_est"],
+                                     inp["depth_gt_observed"], helpers.K_LM, pm, np.zeros(3),
+                                     np.ones(3))
+    assert list(g["pred_names"]).index("rot_est") == 4  # get_names(): flow preds come first
+    np.testing.assert_allclose(ref["src_pose"], g["src_pose"], rtol=0, atol=3e-7)
+    np.testing.assert_allclose(ref["rot"], g["rot"], rtol=0, atol=2e-6)
+    np.testing.assert_allclose(ref["trans"], g["trans"], rtol=1e-5, atol=2e-6)
+    shape = ref["depth_rendered"].shape
+    n = int(np.prod(shape))
+    fg = np.unpackbits(g["foreground__bits"])[:n].reshape(shape).astype(bool)
+    assert fg.sum() > 3000
+    assert ((ref["depth_rendered"] > 0) == fg).mean() >= 0.9999
+    mask = np.unpackbits(g["mask_rendered__bits"])[:n].reshape(shape)
+    assert (ref["mask_rendered"] == mask).mean() >= 0.9999
+    S = 4
+    d, dg = ref["depth_rendered"][..., ::S, ::S], g["depth_rendered__sample"]
+    both = (d > 0) & (dg > 0)
+    assert (np.abs(d[both] - dg[both]) / dg[both]).max() <= 1e-5
+    im, img = ref["image_rendered"][..., ::S, ::S], g["image_rendered__sample"]
+    b3 = np.broadcast_to(both, im.shape)
+    assert (np.abs(im[b3] - img[b3]) < 1e-3).mean() >= 0.995  # a texel boundary may flip
+    bg = np.broadcast_to(~(d > 0) & ~(dg > 0), im.shape)
+    assert np.array_equal(im[bg], img[bg])  # background = -pixel_means exactly
+    w = np.unpackbits(g["flow_weights__bits"])[:2 * n].reshape(ref["flow_weights"].shape)
+    assert np.array_equal(w[:, 0], w[:, 1])  # np.tile(valid, [1, 2, 1, 1])
+    assert (ref["flow_weights"] == w).mean() >= 0.9999
+    fl, flg = ref["flow"][..., ::S, ::S], g["flow__sample"]
+    v = np.broadcast_to((w[:, :1, ::S, ::S] > 0) & (ref["flow_weights"][:, :1, ::S, ::S] > 0),
+                        fl.shape)
+    assert v.sum() > 100 and np.abs(fl[v] - flg[v]).max() < 2e-3

@@ -6,7 +6,8 @@ restatement).  No oracle call in this file: the committed reference outputs are 
 Bars (north_star): zoom factors bit-exact -- wx, wy always; tx, ty wherever the golden run's
 numpy-2 (NEP 50) scalar promotion coincides with the numpy-1.x promotion the product follows
 (recorded per value in the fixture), else within 1.5 ulp(1); resampled values within 1e-4 abs;
-0/1 masks equal on >= 99.999 % of the pixels; Transform3D within 1e-5 m, gradients 2e-4 rel.
+0/1 masks equal on >= 99.999 % of the pixels; Transform3D within 1e-5 m, gradients 2e-4 rel;
+one refine iteration against the reference driver's own outputs at the rasteriser bars.
 """
 import os
 
@@ -151,3 +152,67 @@ def test_transform3d_vs_reference_golden(cuda_device, gold, rot_coord):
     for got, key in ((grads[1], "grad_rotation"), (grads[2], "grad_translation")):
         r = gold["transform3d/%s/%s" % (rot_coord, key)]
         assert np.abs(got.cpu().numpy() - r).max() <= 2e-4 * max(1.0, np.abs(r).max()), key
+
+
+def test_refine_iteration_vs_reference_driver_golden(cuda_device):
+    """One iteration of the on-device loop (pose update -> raster -> post -> labels -> KT -> GT
+    flow; RefineLoop.iterate) against what the reference's own batchUpdaterPyMulti.forward
+    produced for the same batch and the same 'network predictions'
+    (tests/golden/updater_reference.npz, see make_golden_updater.py for its stand-ins)."""
+    import torch
+
+    from mx_deepim_b200 import pipeline, synth
+    from mx_deepim_b200 import pose as P
+
+    g = np.load(os.path.join(GOLD, "updater_reference.npz"))
+    inp = helpers.make_updater_inputs(3, 31)
+    B = 3
+    rot = torch.from_numpy(inp["rot_est"]).to(cuda_device)
+    trans = torch.from_numpy(inp["trans_est"]).to(cuda_device)
+    holder = {}
+
+    def predict(it, rot_gt, trans_gt):
+        holder["loop"].rot_est.copy_(rot)
+        holder["loop"].trans_est.copy_(trans)
+
+    loop = pipeline.RefineLoop(inp["meshes"], B, cuda_device, K=helpers.K_LM, predict=predict)
+    holder["loop"] = loop
+    rng = np.random.default_rng(0)
+    pts = np.zeros((B, 3, synth.NUM_3D_SAMPLE), np.float32)
+    wts = np.zeros_like(pts)
+    for b in range(B):
+        pts[b], wts[b] = synth.mesh_points(inp["meshes"][inp["class_index"][b]], rng)
+    mask_gt = (inp["depth_gt_observed"] > 0).astype(np.float32)
+    host = dict(class_index=inp["class_index"], src_pose=inp["src_pose"], tgt_pose=inp["tgt_pose"],
+                image_observed=np.zeros((B, 3, 480, 640), np.float32),
+                depth_gt_observed=inp["depth_gt_observed"], mask_gt_observed=mask_gt,
+                mask_observed=mask_gt.copy(), point_cloud_model=pts, point_cloud_weights=wts,
+                point_cloud_observed=pts.copy(), Kinv=P.make_Kinv(helpers.K_LM))
+    loop.set_batch(host)
+    loop.iterate(0)
+    torch.cuda.synchronize()
+    np.testing.assert_allclose(loop.pose[loop.cur].cpu().numpy(), g["src_pose"], rtol=2e-6, atol=3e-7)
+    np.testing.assert_allclose(loop.rot_gt.cpu().numpy(), g["rot"], atol=3e-6)
+    np.testing.assert_allclose(loop.trans_gt.cpu().numpy(), g["trans"], rtol=1e-5, atol=2e-6)
+    depth = loop.depth_rendered.cpu().numpy()
+    n = depth.size
+    fg = np.unpackbits(g["foreground__bits"])[:n].reshape(depth.shape).astype(bool)
+    assert ((depth > 0) == fg).mean() >= 0.999  # north_star: >= 99.9 % mask agreement
+    mask = np.unpackbits(g["mask_rendered__bits"])[:n].reshape(depth.shape)
+    assert (loop.mask_rendered.cpu().numpy() == mask).mean() >= 0.999
+    S = 4
+    d, dg = depth[..., ::S, ::S], g["depth_rendered__sample"]
+    both = (d > 0) & (dg > 0)
+    assert both.sum() > 200
+    assert ((np.abs(d[both] - dg[both]) / dg[both]) <= 1e-5).mean() >= 0.999  # 1e-5 relative
+    im, img = loop.image_rendered.cpu().numpy()[..., ::S, ::S], g["image_rendered__sample"]
+    b3 = np.broadcast_to(both, im.shape)
+    assert (np.abs(im[b3] - img[b3]) < 1e-3).mean() >= 0.995
+    bg = np.broadcast_to(~(d > 0) & ~(dg > 0), im.shape)
+    assert np.array_equal(im[bg], img[bg])
+    w = np.unpackbits(g["flow_weights__bits"])[:2 * n].reshape((B, 2, 480, 640))
+    valid = loop.step.valid.cpu().numpy()
+    assert (valid == w[:, :1]).mean() >= 0.999
+    fl, flg = loop.step.flow.cpu().numpy()[..., ::S, ::S], g["flow__sample"]
+    v = np.broadcast_to((w[:, :1, ::S, ::S] > 0) & (valid[..., ::S, ::S] > 0), fl.shape)
+    assert v.sum() > 100 and np.abs(fl[v] - flg[v]).max() < 2e-3
