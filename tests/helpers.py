@@ -209,3 +209,22 @@ def make_updater_inputs(batch, seed, K=K_LM):
         depth[b, 0] = np.round(d.astype(np.float64) * 1000.0) / 1000.0
     return dict(meshes=meshes, class_index=cls, src_pose=src, tgt_pose=tgt, rot_est=rot,
                 trans_est=trans, depth_gt_observed=depth)
+
+
+def make_prep_inputs(seed):
+    """One frame for the loader / test-time update golden vectors: BGR uint8 image, model points,
+    a pose, a depth map and the rendered / observed masks of a test-time batch."""
+    rng = np.random.default_rng(seed)
+    bgr = rng.integers(0, 256, size=(H, W, 3), dtype=np.uint8)
+    points_obj = np.round(rng.normal(size=(1234, 3)) * 0.05, 6)
+    pose = random_pose_pair(rng)[0]
+    depth = np.zeros((H, W), np.float32)
+    depth[100:300, 200:420] = rng.uniform(0.5, 1.2, size=(200, 220)).astype(np.float32)
+    mask_rendered = np.zeros((H, W), np.float32)
+    mask_rendered[120:310, 180:400] = (rng.random((190, 220)) > 0.3)
+    mask_rendered[120, 180] = mask_rendered[309, 399] = 1
+    mask_observed = np.zeros((H, W), np.float32)
+    mask_observed[90:280, 220:450] = (rng.random((190, 230)) > 0.5)
+    mask_observed[90, 220] = mask_observed[279, 449] = 1
+    return dict(bgr=bgr, pixel_means=np.array([102.9801, 115.9465, 122.7717]), points_obj=points_obj,
+                pose=pose, depth=depth, mask_rendered=mask_rendered, mask_observed=mask_observed)

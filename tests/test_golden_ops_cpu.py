@@ -265,3 +265,27 @@ def test_updater_restatement_vs_reference_driver():
     v = np.broadcast_to((w[:, :1, ::S, ::S] > 0) & (ref["flow_weights"][:, :1, ::S, ::S] > 0),
                         fl.shape)
     assert v.sum() > 100 and np.abs(fl[v] - flg[v]).max() < 2e-3
+
+
+# ------------------------------------------------------------------ loaders / test-time update
+def test_loader_and_test_update_vs_reference_code():
+    """tests/golden/prep_reference.npz (lib/utils/image.py and lib/pair_matching/data_pair.py run
+    unmodified): the oracle's lift of update_data_batch's mask policies and the product's host
+    mirror of get_point_cloud_model (same np.random stream) are bit-identical to it."""
+    from mx_deepim_b200 import prep
+    from oracle import updater_np
+
+    g = np.load(os.path.join(GOLD, "prep_reference.npz"))
+    inp = helpers.make_prep_inputs(21)
+    n = 480 * 640
+    for policy in ("box_rendered", "box_observed", "init"):
+        ref = np.unpackbits(g["update_%s/mask_observed__bits" % policy])[:n].reshape(480, 640)
+        got = updater_np.update_mask_observed(policy, inp["mask_observed"], inp["mask_rendered"])
+        assert np.array_equal(got, ref), policy
+        rend = np.unpackbits(g["update_%s/mask_rendered__bits" % policy])[:n].reshape(480, 640)
+        assert np.array_equal(rend, inp["mask_rendered"])
+    assert np.array_equal(g["update/src_pose"][0], inp["pose"])
+    assert np.array_equal(g["update/depth_rendered"][0, 0], inp["depth"][::4, ::4])
+    np.random.seed(4)
+    ps, pw = prep.get_point_cloud_model(inp["points_obj"], 3000)
+    assert np.array_equal(ps, g["points_sample"]) and np.array_equal(pw, g["points_weights"])

@@ -216,3 +216,33 @@ def test_refine_iteration_vs_reference_driver_golden(cuda_device):
     fl, flg = loop.step.flow.cpu().numpy()[..., ::S, ::S], g["flow__sample"]
     v = np.broadcast_to((w[:, :1, ::S, ::S] > 0) & (valid[..., ::S, ::S] > 0), fl.shape)
     assert v.sum() > 100 and np.abs(fl[v] - flg[v]).max() < 2e-3
+
+
+def test_loader_and_test_update_vs_reference_golden(cuda_device):
+    """Device image transform, observed point cloud and the test-time mask policies against the
+    outputs of the reference's own lib/utils/image.py and data_pair.update_data_batch
+    (tests/golden/prep_reference.npz)."""
+    import torch
+
+    from mx_deepim_b200 import pipeline, prep
+
+    g = np.load(os.path.join(GOLD, "prep_reference.npz"))
+    inp = helpers.make_prep_inputs(21)
+    t = prep.transform(inp["bgr"], inp["pixel_means"])
+    assert t.shape == (1, 3, 480, 640)
+    assert np.array_equal(t[..., ::4, ::4].astype(np.float32), g["transform"])
+    np.testing.assert_allclose(t.astype(np.float64).sum(axis=(-2, -1)), g["transform_sum"], rtol=1e-7)
+    # update_data_batch's image blob = resize (identity at 480x640) + transform of a float frame
+    assert np.array_equal(t[..., ::4, ::4].astype(np.float32), g["update/image_rendered"])
+    pts = torch.from_numpy(g["points_sample"].astype(np.float32)).to(cuda_device)
+    pose = torch.from_numpy(inp["pose"][None]).to(cuda_device)
+    obs = prep.get_point_cloud_observed(pts, pose)
+    torch.cuda.synchronize()
+    np.testing.assert_allclose(obs[0].cpu().numpy(), g["points_observed"], rtol=0, atol=1e-6)
+    n = 480 * 640
+    for policy, src in (("box_rendered", "mask_rendered"), ("box_observed", "mask_observed")):
+        ref = np.unpackbits(g["update_%s/mask_observed__bits" % policy])[:n].reshape(480, 640)
+        m = torch.from_numpy(inp[src][None, None]).to(cuda_device)
+        out, _ = pipeline.mask_box(m)
+        torch.cuda.synchronize()
+        assert np.array_equal(out[0, 0].cpu().numpy(), ref.astype(np.float32)), policy
