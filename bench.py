@@ -400,6 +400,12 @@ def run_ours(args, rank, world, local_rank):
                          "peak_source": peak_src,
                          "kernel_us": kernel_ms * 1e3,
                          "algorithmic_bytes_per_launch": kbytes,
+                         # the same launch on the DRAM counters of the committed capture
+                         "dram_gbs": (traffic / (kernel_ms * 1e-3) / 1e9) if traffic else None,
+                         "dram_frac": (traffic / (kernel_ms * 1e-3) / 1e9 / peak) if traffic else None,
+                         "note": "frac > 1 is possible: SURVEY 8(d) counts every source plane in "
+                                 "full, a zoom-in reads only its crop window (traffic < "
+                                 "algorithmic bytes); the kernel is issue-bound, see DESIGN.md 3",
                          "step_achieved_gbs": step_bytes * K / (ms_max * 1e-3) / 1e9},
             "kernel_us": breakdown,
             "clocks": clocks,

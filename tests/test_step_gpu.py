@@ -155,3 +155,33 @@ def test_host_feed_overlapped_uploads_keep_batches_apart(cuda_device, packed):
     for i in (n - 2, n - 1):
         assert torch.equal(feed.loss[i % 2], snaps[i][0].cpu())
         assert torch.equal(feed.zoom_factor[i % 2], snaps[i][1].cpu())
+
+
+@pytest.mark.parametrize("B,backward", [(16, True), (64, False)])
+def test_compare_step_full_size_batch_permutation_property(cuda_device, B, backward):
+    """Size-independent property at BASELINE.json's batch sizes (configs[1] = 16 pairs, the
+    refine loop's 64): pairs are independent, so permuting the batch must permute EVERY output
+    bit for bit (no cross-pair leakage through shared workspaces, tickets, clusters or tile
+    lists), and a pair's outputs must not depend on its position in the batch."""
+    import torch
+
+    from mx_deepim_b200 import pipeline, synth
+
+    host = synth.make_compare_batch(B, seed=500 + B, occlusion=True)
+    perm = np.random.default_rng(B).permutation(B)
+    host_p = {k: (np.ascontiguousarray(v[perm]) if isinstance(v, np.ndarray) and v.ndim >= 1
+                  and v.shape[0] == B else v) for k, v in host.items()}
+    outs = []
+    for h in (host, host_p):
+        step = pipeline.CompareStep(B, cuda_device, backward=backward, lw_pm=LW_PM)
+        x = step.to_device(h, non_blocking=False)
+        step.run(x)
+        torch.cuda.synchronize()
+        outs.append({k: v.cpu().numpy() for k, v in step.outputs().items() if v is not None})
+        del step, x
+    assert set(outs[0]) == set(outs[1]) and len(outs[0]) >= 10
+    for k, a in outs[0].items():
+        b = outs[1][k]
+        assert a.shape[0] == B, k
+        assert np.array_equal(a[perm].view(np.uint8), b.view(np.uint8)), k
+    assert outs[0]["flow_weights_valid"].sum() > 1000 * B  # the batch is not degenerate
