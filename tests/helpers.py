@@ -1,6 +1,8 @@
 """Seeded synthetic inputs shared by the tests (LINEMOD-shaped, no dataset needed)."""
 from __future__ import annotations
 
+import os
+
 import numpy as np
 
 H, W = 480, 640
@@ -228,3 +230,38 @@ def make_prep_inputs(seed):
     mask_observed[90, 220] = mask_observed[279, 449] = 1
     return dict(bgr=bgr, pixel_means=np.array([102.9801, 115.9465, 122.7717]), points_obj=points_obj,
                 pose=pose, depth=depth, mask_rendered=mask_rendered, mask_observed=mask_observed)
+
+
+def write_pair_files(root, seed, n_pairs=2):
+    """Write `n_pairs` frames in the dataset's on-disk formats under `root` (8-bit BGR colour
+    PNGs, 16-bit depth PNGs in mm, 8-bit label PNGs, -pose.txt with one header row, and one
+    points.xyz) and return the pairdb records the reference's loaders take."""
+    import cv2
+
+    rng = np.random.default_rng(seed)
+    root = str(root)
+    os.makedirs(os.path.join(root, "model"), exist_ok=True)
+    np.savetxt(os.path.join(root, "model", "points.xyz"),
+               np.round(rng.normal(size=(500, 3)) * 0.05, 6))
+    recs = []
+    for i in range(n_pairs):
+        p = lambda s: os.path.join(root, "%06d-%s" % (i, s))  # noqa: E731
+        label = np.zeros((H, W), np.uint8)
+        label[100 + 10 * i:300, 150:400 + 20 * i] = 1 + i
+        label[20:60, 30:90] = 7  # another instance
+        for name in ("color_obs", "color_rend"):
+            cv2.imwrite(p(name + ".png"), rng.integers(0, 256, size=(H, W, 3), dtype=np.uint8))
+        for name in ("depth_obs", "depth_rend"):
+            d = rng.integers(400, 3000, size=(H, W)).astype(np.uint16)
+            d[rng.random((H, W)) < 0.5] = 0
+            cv2.imwrite(p(name + ".png"), d)
+        cv2.imwrite(p("label.png"), label)
+        pose = random_pose_pair(rng)[0]
+        with open(p("pose.txt"), "w") as f:
+            f.write("%d\n" % (1 + i))
+            np.savetxt(f, pose)
+        recs.append({"image_observed": p("color_obs.png"), "image_rendered": p("color_rend.png"),
+                     "depth_observed": p("depth_obs.png"), "depth_gt_observed": p("depth_obs.png"),
+                     "depth_rendered": p("depth_rend.png"), "mask_gt_observed": p("label.png"),
+                     "mask_idx": 1 + i, "pose_observed": p("pose.txt"), "img_flipped": False})
+    return recs

@@ -247,3 +247,31 @@ def test_loader_and_test_update_vs_reference_golden(cuda_device):
         out, _ = pipeline.mask_box(m)
         torch.cuda.synchronize()
         assert np.array_equal(out[0, 0].cpu().numpy(), ref.astype(np.float32)), policy
+
+
+def test_dataset_files_to_device_blobs_vs_reference_loaders(cuda_device, tmp_path):
+    """Files in the dataset's on-disk formats -> dataio.read_pair / stack_pairs (storage dtypes,
+    pinned) -> upload -> device decode, against the float blobs the reference's own loaders made
+    from the same files (tests/golden/dataio_reference.npz): bit-exact."""
+    import torch
+
+    from mx_deepim_b200 import dataio
+
+    g = np.load(os.path.join(GOLD, "dataio_reference.npz"))
+    pairdb = helpers.write_pair_files(tmp_path, 41)
+    batch = dataio.stack_pairs([dataio.read_pair(r) for r in pairdb], pin=True)
+    out = dataio.decode_batch(batch, cuda_device, depth_factor=1000.0,
+                              pixel_means_bgr=[102.9801, 115.9465, 122.7717], mask_inputs=True)
+    torch.cuda.synchronize()
+    S = 4
+    for k in ("image_observed", "image_rendered", "depth_gt_observed", "depth_observed",
+              "depth_rendered"):
+        got = out[k].cpu().numpy()
+        assert got.dtype == np.float32 and got.shape[2:] == (480, 640), k
+        assert np.array_equal(got[..., ::S, ::S], g[k]), k
+    for k in ("depth_gt_observed", "depth_observed", "depth_rendered"):
+        np.testing.assert_allclose(out[k].double().sum(dim=(-2, -1)).cpu().numpy(), g[k + "_sum"],
+                                   rtol=1e-12)
+    m = out["mask_gt_observed"].cpu().numpy()
+    assert m[0].sum() == 200 * 250 and m[1].sum() == 190 * 270  # label == mask_idx, per pair
+    np.testing.assert_array_equal(out["pose_observed"].cpu().numpy(), g["poses"].astype(np.float32))

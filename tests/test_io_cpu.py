@@ -62,3 +62,42 @@ def test_load_texture_is_rgb_top_row_first(tmp_path):
     t = load_texture(str(tmp_path / "t.png"))
     assert t.shape == (4, 6, 3) and t.dtype == np.uint8 and t.flags["C_CONTIGUOUS"]
     assert t[0, 0].tolist() == [255, 0, 0] and t[3, 0].tolist() == [0, 0, 200]
+
+
+def test_dataset_readers_vs_reference_loaders(tmp_path):
+    """mx_deepim_b200/dataio.py readers (storage dtypes, no decode on the host) against the
+    outputs of the reference's own loaders on the same files
+    (tests/golden/make_golden_dataio.py -> dataio_reference.npz)."""
+    import os
+
+    import torch
+
+    from mx_deepim_b200 import dataio
+
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "dataio_reference.npz"))
+    pairdb = helpers.write_pair_files(tmp_path, 41)
+    assert np.array_equal(dataio.load_object_points(str(tmp_path / "model" / "points.xyz")), g["points"])
+    recs = [dataio.read_pair(r) for r in pairdb]
+    assert np.array_equal(np.stack([r["pose_observed"] for r in recs]), g["poses"].astype(np.float32))
+    batch = dataio.stack_pairs(recs)
+    assert batch["image_observed"].dtype == torch.uint8 and batch["image_observed"].shape == (2, 480, 640, 3)
+    assert batch["depth_rendered"].dtype == torch.int16 and batch["mask_gt_observed"].dtype == torch.uint8
+    assert batch["mask_idx"].tolist() == [1, 2]
+    S = 4
+    # the raw values are what the reference decodes: redo its float formulas on the host here
+    raw = batch["depth_rendered"].numpy().view(np.uint16)
+    assert np.array_equal((raw.astype(np.float32) / 1000)[:, None, ::S, ::S], g["depth_rendered"])
+    raw = batch["depth_observed"].numpy().view(np.uint16).astype(np.float32)
+    lab = batch["mask_gt_observed"].numpy()
+    raw *= lab == np.array([1, 2]).reshape(2, 1, 1)  # image.py:244
+    assert np.array_equal((raw / 1000)[:, None, ::S, ::S], g["depth_observed"])
+    im = batch["image_observed"].numpy()
+    means = np.array([102.9801, 115.9465, 122.7717])
+    ref = np.stack([im[:, :, :, 2 - i] - means[2 - i] for i in range(3)], axis=1)  # image.py:717-720
+    assert np.array_equal(ref[..., ::S, ::S].astype(np.float32), g["image_observed"])
+    import pytest
+
+    with pytest.raises(AssertionError):
+        dataio.read_depth(str(tmp_path / "missing.png"))
+    with pytest.raises(RuntimeError):
+        dataio.decode_batch(batch, "cpu")  # no CPU fallback
