@@ -21,10 +21,16 @@ def pose_errors(pose_est, pose_gt, points, K, n_valid=None, want_adi=True, strea
     """pose_est, pose_gt: CUDA float32 [B,3,4]; points: CUDA float32 [B,3,N] or [3,N] (shared);
     K: 3x3; n_valid: CUDA int32 [B] or None.  Returns CUDA float64 [B,5] =
     (add, adi, arp_2d, re_deg, te)."""
+    C.check_tensor("pose_est", pose_est, ndim=3)
     B = int(pose_est.shape[0])
+    C.check_tensor("pose_est", pose_est, shape=(B, 3, 4))
+    C.check_tensor("pose_gt", pose_gt, shape=(B, 3, 4))
     dev = pose_est.device
     shared = points.dim() == 2
     N = int(points.shape[-1])
+    C.check_tensor("points", points, shape=(3, N) if shared else (B, 3, N))
+    if n_valid is not None:
+        C.check_tensor("n_valid", n_valid, dtype=torch.int32, shape=(B,))
     lib = _lib.load()
     out = torch.empty((B, 5), dtype=torch.float64, device=dev)
     ws = torch.empty((B * lib.rc_pose_error_chunks(N) * 3,), dtype=torch.float64, device=dev)
@@ -42,8 +48,13 @@ def pose_errors(pose_est, pose_gt, points, K, n_valid=None, want_adi=True, strea
 def visib_mask(d_test, d_model, delta, visib_gt=None, out=None, stream=None):
     """CUDA float32 tensors of equal shape -> float32 0/1 mask (estimate_visib_mask; with
     visib_gt: estimate_visib_mask_est)."""
+    C.check_tensor("d_test", d_test)
+    C.check_tensor("d_model", d_model, shape=d_test.shape)
+    if visib_gt is not None:
+        C.check_tensor("visib_gt", visib_gt, shape=d_test.shape)
     if out is None:
         out = torch.empty_like(d_test)
+    C.check_tensor("out", out, shape=d_test.shape)
     with torch.cuda.device(d_test.device):
         st = _lib.load().rc_visib_mask_dev(d_test.data_ptr(), d_model.data_ptr(),
                                            visib_gt.data_ptr() if visib_gt is not None else None,
@@ -57,7 +68,15 @@ def flow_epe(flow_pred, flow_gt, visible, bg=None, depth_rendered=None, stream=N
     """flow_pred, flow_gt CUDA float32 [B,2,H,W]; visible [B,1,H,W]; bg [B,1,H,W] or derived
     from depth_rendered (tester.py:712).  Returns CUDA float64 [B,6] = epe_all, num_all,
     epe_viz, num_viz, epe_vizbg, num_vizbg."""
+    C.check_tensor("flow_pred", flow_pred, ndim=4)
     B, _, H, W = flow_pred.shape
+    C.check_tensor("flow_pred", flow_pred, shape=(B, 2, H, W))
+    C.check_tensor("flow_gt", flow_gt, shape=(B, 2, H, W))
+    C.check_tensor("visible", visible, shape=(B, 1, H, W))
+    if bg is not None:
+        C.check_tensor("bg", bg, shape=(B, 1, H, W))
+    if depth_rendered is not None:
+        C.check_tensor("depth_rendered", depth_rendered, shape=(B, 1, H, W))
     dev = flow_pred.device
     lib = _lib.load()
     out = torch.empty((B, 6), dtype=torch.float64, device=dev)

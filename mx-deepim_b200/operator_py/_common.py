@@ -20,15 +20,20 @@ def _req_flag(req):
     raise ValueError("unknown req %r" % (req,))
 
 
-def check_tensor(name, t, ndim=None):
+def check_tensor(name, t, ndim=None, dtype=torch.float32, shape=None):
+    """A tensor crosses into the C ABI as a bare pointer: it has to be a CUDA tensor of the
+    declared dtype and C-contiguous (a transposed or sliced view would be read with the wrong
+    strides, silently)."""
     if not isinstance(t, torch.Tensor) or not t.is_cuda:
         raise TypeError("%s must be a CUDA torch.Tensor (no CPU fallback)" % name)
-    if t.dtype != torch.float32:
-        raise TypeError("%s must be float32, got %s" % (name, t.dtype))
+    if t.dtype != dtype:
+        raise TypeError("%s must be %s, got %s" % (name, dtype, t.dtype))
     if not t.is_contiguous():
         raise ValueError("%s must be contiguous" % name)
     if ndim is not None and t.dim() != ndim:
         raise ValueError("%s must have %d dims, got %d" % (name, ndim, t.dim()))
+    if shape is not None and tuple(t.shape) != tuple(shape):
+        raise ValueError("%s must have shape %s, got %s" % (name, tuple(shape), tuple(t.shape)))
 
 
 class Group(object):

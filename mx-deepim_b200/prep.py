@@ -31,6 +31,20 @@ def _dev(device):
     return torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
 
 
+def _check(name, t, dtype, shape=None):
+    """Every tensor that crosses into the C ABI is passed as a bare pointer: it has to be a
+    CUDA tensor of the declared dtype, C-contiguous (a transposed or sliced view would be read
+    with the wrong strides -- silently), and of the declared shape."""
+    if not isinstance(t, torch.Tensor) or not t.is_cuda:
+        raise TypeError("%s must be a CUDA torch.Tensor (no CPU fallback)" % name)
+    if t.dtype != dtype:
+        raise TypeError("%s must be %s, got %s" % (name, dtype, t.dtype))
+    if not t.is_contiguous():
+        raise ValueError("%s must be contiguous" % name)
+    if shape is not None and tuple(t.shape) != tuple(shape):
+        raise ValueError("%s must have shape %s, got %s" % (name, tuple(shape), tuple(t.shape)))
+
+
 def transform_batch(bgr_u8, pixel_means, out=None, stream=None):
     """bgr_u8: CUDA uint8 [B,H,W,3] (BGR as cv2.imread delivers).  pixel_means: 3 values in
     B,G,R order (config.network.PIXEL_MEANS).  Returns float32 [B,3,H,W] RGB - means."""
@@ -41,6 +55,7 @@ def transform_batch(bgr_u8, pixel_means, out=None, stream=None):
     B, H, W, _ = bgr_u8.shape
     if out is None:
         out = torch.empty((B, 3, H, W), dtype=torch.float32, device=bgr_u8.device)
+    _check("out", out, torch.float32, (B, 3, H, W))
     means = (ctypes.c_double * 3)(*[float(v) for v in np.asarray(pixel_means, np.float64).reshape(-1)[:3]])
     with torch.cuda.device(bgr_u8.device):
         st = _lib.load().rc_prep_image_dev(bgr_u8.data_ptr(), out.data_ptr(), means, B, H, W,
@@ -69,8 +84,12 @@ def decode_depth(raw_u16, depth_factor, mask=None, mask_idx=None, out=None, stre
     B, H, W = raw_u16.shape
     if out is None:
         out = torch.empty((B, 1, H, W), dtype=torch.float32, device=raw_u16.device)
+    _check("out", out, torch.float32, (B, 1, H, W))
     if (mask is None) != (mask_idx is None):
         raise ValueError("mask and mask_idx go together")
+    if mask is not None:
+        _check("mask", mask, torch.uint8, (B, H, W))
+        _check("mask_idx", mask_idx, torch.int32, (B,))
     with torch.cuda.device(raw_u16.device):
         st = _lib.load().rc_prep_depth_dev(
             raw_u16.data_ptr(), mask.data_ptr() if mask is not None else None,
@@ -86,8 +105,11 @@ def decode_mask(mask_u8, mask_idx, out=None, stream=None):
     if mask_u8.dtype != torch.uint8 or mask_u8.dim() != 3:
         raise TypeError("mask_u8 must be a uint8 [B,H,W] tensor")
     B, H, W = mask_u8.shape
+    _check("mask_u8", mask_u8, torch.uint8)
+    _check("mask_idx", mask_idx, torch.int32, (B,))
     if out is None:
         out = torch.empty((B, 1, H, W), dtype=torch.float32, device=mask_u8.device)
+    _check("out", out, torch.float32, (B, 1, H, W))
     with torch.cuda.device(mask_u8.device):
         st = _lib.load().rc_prep_mask_dev(mask_u8.data_ptr(), mask_idx.data_ptr(), out.data_ptr(),
                                           B, H, W, _lib.stream_ptr(stream))
@@ -115,9 +137,14 @@ def get_point_cloud_model(points_obj, num_sample, rng=np.random):
 def get_point_cloud_observed(points_model, pose_observed, out=None, stream=None):
     """image.py:592-596 batched on the device: points_model CUDA float32 [B,3,N], pose_observed
     CUDA float32 [B,3,4] -> [B,3,N]."""
+    _check("points_model", points_model, torch.float32)
+    if points_model.dim() != 3 or points_model.shape[1] != 3:
+        raise ValueError("points_model must be [B,3,N]")
     B, _, N = points_model.shape
+    _check("pose_observed", pose_observed, torch.float32, (B, 3, 4))
     if out is None:
         out = torch.empty_like(points_model)
+    _check("out", out, torch.float32, (B, 3, N))
     with torch.cuda.device(points_model.device):
         st = _lib.load().rc_points_transform_dev(points_model.data_ptr(), pose_observed.data_ptr(),
                                                  out.data_ptr(), B, N, _lib.stream_ptr(stream))
@@ -137,10 +164,15 @@ def calc_flow_batch(depth_src, depth_tgt, transform, K, thresh=3e-3, standard_re
     transform: CUDA float64 [B,3,4] (make_transform per pair); K: 3x3 (host).
     Returns (flow [B,2,H,W] f32, visible [B,1,H,W] f32, x_valid [B,3,capacity] f32 or None,
     counts [B] int32 or None).  No synchronisation."""
+    _check("depth_src", depth_src, torch.float32)
+    if depth_src.dim() != 4 or depth_src.shape[1] != 1:
+        raise ValueError("depth_src must be [B,1,H,W]")
     B, _, H, W = depth_src.shape
     dev = depth_src.device
+    _check("depth_tgt", depth_tgt, torch.float32, (B, 1, H, W))
     if transform.dtype != torch.float64 or tuple(transform.shape) != (B, 3, 4):
         raise TypeError("transform must be float64 [B,3,4]")
+    _check("transform", transform, torch.float64, (B, 3, 4))
     lib = _lib.load()
     flow = torch.empty((B, 2, H, W), dtype=torch.float32, device=dev)
     visible = torch.empty((B, 1, H, W), dtype=torch.float32, device=dev)

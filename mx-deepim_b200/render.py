@@ -26,6 +26,7 @@ import torch
 
 from . import _lib
 from . import pose as P
+from .operator_py import _common as C
 
 
 # ------------------------------------------------------------------- mesh IO
@@ -156,6 +157,14 @@ class DeviceRenderer(object):
                     out[k] = torch.empty((B, H, W), dtype=torch.int32, device=self.device)
             elif k not in out:
                 out[k] = torch.empty(shapes[k], **f)
+        C.check_tensor("cls_idx", cls_idx, dtype=torch.int32, shape=(B,))
+        C.check_tensor("poses", poses, shape=(B, 3, 4))
+        for k, t in (("light_pos", light_pos), ("light_int", light_int)):
+            if t is not None:
+                C.check_tensor(k, t, shape=(B, 3))
+        for k in set(want) | {"depth"}:
+            C.check_tensor(k, out[k], dtype=torch.int32 if k == "tri_id" else torch.float32,
+                           shape=(B, H, W) if k == "tri_id" else shapes[k])
         a = _lib.rc_render_args()
         a.cls_idx, a.poses = cls_idx.data_ptr(), poses.data_ptr()
         a.light_pos = light_pos.data_ptr() if light_pos is not None else None

@@ -235,8 +235,14 @@ def test_loader_and_test_update_vs_reference_golden(cuda_device):
     np.testing.assert_allclose(t.astype(np.float64).sum(axis=(-2, -1)), g["transform_sum"], rtol=1e-6)
     # update_data_batch's image blob = resize (identity at 480x640) + transform of a float frame
     assert np.array_equal(t[..., ::4, ::4].astype(np.float32), g["update/image_rendered"])
-    pts = torch.from_numpy(g["points_sample"].astype(np.float32)).to(cuda_device)
+    # the stored array is the loader's TRANSPOSED view (image.py:586): a non-contiguous tensor
+    # must be refused, not read with the wrong strides
+    strided = torch.from_numpy(g["points_sample"].astype(np.float32)).to(cuda_device)
     pose = torch.from_numpy(inp["pose"][None]).to(cuda_device)
+    if not strided.is_contiguous():
+        with pytest.raises(ValueError):
+            prep.get_point_cloud_observed(strided, pose)
+    pts = torch.from_numpy(np.ascontiguousarray(g["points_sample"], np.float32)).to(cuda_device)
     obs = prep.get_point_cloud_observed(pts, pose)
     torch.cuda.synchronize()
     np.testing.assert_allclose(obs[0].cpu().numpy(), g["points_observed"], rtol=0, atol=1e-6)

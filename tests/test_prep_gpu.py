@@ -208,3 +208,44 @@ def test_calc_flow_device_matches_reference_golden(cuda_device):
         assert np.array_equal(v2, rv)
         assert np.abs(f2 - rf).max() < 1e-4
         np.testing.assert_allclose(x2, rx, rtol=1e-6, atol=1e-7)
+
+
+def test_entry_points_refuse_strided_and_mistyped_tensors(cuda_device):
+    """Tensors cross the C ABI as bare pointers, so the host mirrors must refuse views whose
+    strides the kernels would misread (transposed loader output, channel slices) and wrong
+    dtypes, instead of computing garbage silently."""
+    import torch
+
+    from mx_deepim_b200 import evaluation, flow, prep
+    from mx_deepim_b200.render import DeviceRenderer
+    from mx_deepim_b200 import synth
+
+    dev = cuda_device
+    pts_t = torch.zeros((2, 3000, 3), device=dev).transpose(1, 2)  # [B,3,N] view, not contiguous
+    pose = torch.zeros((2, 3, 4), device=dev)
+    with pytest.raises(ValueError):
+        prep.get_point_cloud_observed(pts_t, pose)
+    with pytest.raises(ValueError):
+        prep.get_point_cloud_observed(pts_t.contiguous(), pose[:1])
+    with pytest.raises(TypeError):
+        prep.get_point_cloud_observed(pts_t.contiguous().double(), pose)
+    depth4 = torch.zeros((2, 2, 480, 640), device=dev)
+    with pytest.raises(ValueError):  # channel slice of a 2-channel tensor
+        prep.calc_flow_batch(depth4[:, :1], depth4[:, 1:], torch.zeros((2, 3, 4), dtype=torch.float64, device=dev),
+                             synth.K_LINEMOD)
+    lab = torch.zeros((2, 480, 640), dtype=torch.uint8, device=dev)
+    with pytest.raises(TypeError):
+        prep.decode_mask(lab, torch.ones(2, dtype=torch.int64, device=dev))
+    with pytest.raises(ValueError):
+        evaluation.visib_mask(depth4[:, 0], depth4[:, 1], 0.015)
+    with pytest.raises(ValueError):
+        evaluation.pose_errors(pose, pose, pts_t, synth.K_LINEMOD)
+    with pytest.raises(ValueError):
+        flow.gpu_flow_dev(depth4[:, :1], depth4[:, 1:], pose, torch.eye(3, device=dev))
+    ren = DeviceRenderer([synth.make_mesh(np.random.default_rng(0), level=1, texture_size=8)],
+                         synth.K_LINEMOD, max_batch=2, device=dev)
+    with pytest.raises(TypeError):
+        ren.render_batch(torch.zeros(2, dtype=torch.int64, device=dev), pose)
+    with pytest.raises(ValueError):
+        ren.render_batch(torch.zeros(2, dtype=torch.int32, device=dev),
+                         torch.zeros((2, 4, 3), device=dev).transpose(1, 2))
