@@ -55,7 +55,9 @@ void _flow(float *flow, float *valid, float *depth_src, float *depth_tgt,
 int rc_last_status(void);
 
 /* Same work, status-returning.  Uses an internal per-device staging arena
- * that grows monotonically (no per-call cudaMalloc/cudaFree). */
+ * that grows monotonically (no per-call cudaMalloc/cudaFree).  Re-entrant like
+ * the reference's `_flow`: concurrent callers on one device are serialised on
+ * the arena, callers on different devices do not interact. */
 int rc_flow_host(float *flow, float *valid, const float *depth_src,
                  const float *depth_tgt, const float *KT, const float *Kinv,
                  int batch_size, int height, int width, int device_id);

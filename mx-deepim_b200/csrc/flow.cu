@@ -15,6 +15,8 @@
 // rounding intrinsic in the association nvcc gives the reference source
 // (FMUL/FFMA/FADD sequence read from its sm_100a SASS), so the
 // result does not depend on this file's optimisation flags.
+#include <mutex>
+
 #include "common.cuh"
 #include "flow_device.cuh"
 
@@ -90,10 +92,15 @@ static int launch_flow(const float *depth_src, const float *depth_tgt, const flo
   return check_launch();
 }
 
-// Grow-only staging arena for the host-pointer entry point (one per device).
+// Grow-only staging arena for the host-pointer entry point (one per device).  The reference's
+// _flow is re-entrant per device (it mallocs and frees per call, gpu_flow_kernel.cu:86-147);
+// the arena is shared, so a per-device mutex is held for the whole host-pointer call: concurrent
+// callers on one device take turns (they would share the PCIe link anyway), callers on
+// different devices do not interact.
 struct Arena {
   void *ptr = nullptr;
   size_t bytes = 0;
+  std::mutex mu;
 };
 static Arena g_arena[64];
 
@@ -136,6 +143,7 @@ int rc_flow_host(float *flow, float *valid, const float *depth_src, const float 
   RC_REQUIRE(device_id >= 0 && device_id < 64, RC_ERR_INVALID_ARG);
   if (batch_size == 0) return rc::note_status(RC_OK);
   RC_REQUIRE(depth_src && depth_tgt && KT && Kinv && flow && valid, RC_ERR_INVALID_ARG);
+  std::lock_guard<std::mutex> guard(rc::g_arena[device_id].mu);
   int cur = -1;
   RC_CUDA_TRY(cudaGetDevice(&cur));  // gpu_flow_kernel.cu:71-80
   if (cur != device_id) RC_CUDA_TRY(cudaSetDevice(device_id));

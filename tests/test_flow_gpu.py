@@ -95,3 +95,36 @@ def test_flow_full_size_properties(cuda_device):
     for rep in range(16):
         assert np.array_equal(valid[rep * 4:(rep + 1) * 4], ref_valid)
         assert np.array_equal(flow[rep * 4:(rep + 1) * 4], ref_flow)
+
+
+def test_host_pointer_flow_is_reentrant(cuda_device):
+    """The reference's `_flow` keeps no state between calls (it mallocs and frees per call), so
+    engine threads may call it concurrently.  The drop-in shares one staging arena per device:
+    four threads hammering gpu_flow with different batch sizes (the arena regrows) must each get
+    exactly the oracle's answer."""
+    import threading
+
+    from mx_deepim_b200 import flow
+
+    fn = flow.gpu_flow_wrapper(cuda_device.index or 0)
+    cases = [helpers.make_flow_inputs(b, 40 + b, occlude=bool(b % 2)) for b in (1, 3, 2, 4)]
+    refs = [flow_np.flow_kernel_cpu(c["depth_src"], c["depth_tgt"], c["KT"], c["Kinv"]) for c in cases]
+    errors = []
+
+    def worker(i):
+        try:
+            c = cases[i]
+            for _ in range(6):
+                f, v = fn(c["depth_src"], c["depth_tgt"], c["KT"], c["Kinv"])
+                if not (np.array_equal(f, refs[i][0]) and np.array_equal(v, refs[i][1])):
+                    errors.append("thread %d: wrong result" % i)
+                    return
+        except Exception as exc:  # noqa: BLE001
+            errors.append("thread %d: %r" % (i, exc))
+
+    threads = [threading.Thread(target=worker, args=(i,)) for i in range(4)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errors, errors
