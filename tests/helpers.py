@@ -265,3 +265,17 @@ def write_pair_files(root, seed, n_pairs=2):
                      "depth_rendered": p("depth_rend.png"), "mask_gt_observed": p("label.png"),
                      "mask_idx": 1 + i, "pose_observed": p("pose.txt"), "img_flipped": False})
     return recs
+
+
+def make_pose_mode_inputs(seed, batch=12):
+    """float32 blobs of the updater's pose block: src / tgt poses and unnormalised quaternion +
+    translation 'predictions'."""
+    rng = np.random.default_rng(seed)
+    src = np.zeros((batch, 3, 4), np.float32)
+    tgt = np.zeros((batch, 3, 4), np.float32)
+    for b in range(batch):
+        src[b], tgt[b] = random_pose_pair(rng)
+    rot = rng.normal(size=(batch, 4)).astype(np.float32)
+    rot[:, 0] = np.abs(rot[:, 0]) + 2.0
+    trans = rng.normal(0, 0.05, size=(batch, 3)).astype(np.float32)
+    return dict(src_pose=src, tgt_pose=tgt, rot_est=rot, trans_est=trans)

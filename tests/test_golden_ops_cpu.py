@@ -289,3 +289,22 @@ def test_loader_and_test_update_vs_reference_code():
     np.random.seed(4)
     ps, pw = prep.get_point_cloud_model(inp["points_obj"], 3000)
     assert np.array_equal(ps, g["points_sample"]) and np.array_equal(pw, g["points_weights"])
+
+
+@pytest.mark.parametrize("mode", ["MODEL", "CAMERA", "CAMERA_NEW"])
+def test_pose_block_modes_vs_reference_rt_transform(mode):
+    """oracle/updater_np.pose_update for every rot_coord mode and non-trivial T_means / T_stds
+    against the reference's own RT_transform / calc_RT_delta / calc_se3
+    (tests/golden/make_golden_pose_modes.py).  The golden run's numpy 2 keeps quat2mat's
+    `2.0 / Nq` in float32 (numpy 1.x: float64), hence float32-rounding tolerances."""
+    from oracle import updater_np
+
+    g = np.load(os.path.join(GOLD, "pose_modes_reference.npz"))
+    inp = helpers.make_pose_mode_inputs(51)
+    means, stds = np.array([0.01, -0.02, 0.05]), np.array([0.5, 0.8, 1.5])
+    pose, rot, trans, KT = updater_np.pose_update(inp["src_pose"], inp["rot_est"], inp["trans_est"],
+                                                  inp["tgt_pose"], helpers.K_LM, means, stds, mode)
+    np.testing.assert_allclose(pose, g[mode + "/pose"], rtol=0, atol=3e-7)
+    np.testing.assert_allclose(rot, g[mode + "/rot"], rtol=0, atol=2e-6)
+    np.testing.assert_allclose(trans, g[mode + "/trans"], rtol=1e-5, atol=2e-6)
+    np.testing.assert_allclose(KT, g[mode + "/KT"], rtol=2e-6, atol=3e-4)

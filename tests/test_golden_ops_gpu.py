@@ -281,3 +281,26 @@ def test_dataset_files_to_device_blobs_vs_reference_loaders(cuda_device, tmp_pat
     m = out["mask_gt_observed"].cpu().numpy()
     assert m[0].sum() == 200 * 250 and m[1].sum() == 190 * 270  # label == mask_idx, per pair
     np.testing.assert_array_equal(out["pose_observed"].cpu().numpy(), g["poses"].astype(np.float32))
+
+
+@pytest.mark.parametrize("mode", ["MODEL", "CAMERA", "CAMERA_NEW"])
+def test_pose_update_modes_vs_reference_golden(cuda_device, mode):
+    """rc_pose_update_dev for every rot_coord mode and non-trivial T_means / T_stds against the
+    reference's own RT_transform / calc_RT_delta / calc_se3 outputs
+    (tests/golden/pose_modes_reference.npz)."""
+    import torch
+
+    from mx_deepim_b200 import pipeline
+
+    g = np.load(os.path.join(GOLD, "pose_modes_reference.npz"))
+    inp = helpers.make_pose_mode_inputs(51)
+    t = lambda a: torch.from_numpy(a).to(cuda_device)  # noqa: E731
+    out = pipeline.pose_update(t(inp["src_pose"]), t(inp["rot_est"]), t(inp["trans_est"]),
+                               t(inp["tgt_pose"]), helpers.K_LM, T_means=(0.01, -0.02, 0.05),
+                               T_stds=(0.5, 0.8, 1.5), rot_coord=mode)
+    torch.cuda.synchronize()
+    pose, rot, trans, KT = [o.cpu().numpy() for o in out]
+    np.testing.assert_allclose(pose, g[mode + "/pose"], rtol=2e-6, atol=3e-7)
+    np.testing.assert_allclose(rot, g[mode + "/rot"], rtol=0, atol=3e-6)
+    np.testing.assert_allclose(trans, g[mode + "/trans"], rtol=1e-5, atol=3e-6)
+    np.testing.assert_allclose(KT, g[mode + "/KT"], rtol=2e-6, atol=3e-4)
