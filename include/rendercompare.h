@@ -57,7 +57,11 @@ int rc_last_status(void);
 /* Same work, status-returning.  Uses an internal per-device staging arena
  * that grows monotonically (no per-call cudaMalloc/cudaFree).  Re-entrant like
  * the reference's `_flow`: concurrent callers on one device are serialised on
- * the arena, callers on different devices do not interact. */
+ * the arena, callers on different devices do not interact.  Batches of two or
+ * more pairs are walked by up to 8 worker threads (env RC_FLOW_HOST_THREADS;
+ * 0 / 1 = plain pageable copies), each with a page-locked slot, a device slot
+ * and a stream, so the host-side staging of the caller's pageable buffers runs
+ * in parallel and overlaps the transfers; the results are the same kernel's. */
 int rc_flow_host(float *flow, float *valid, const float *depth_src,
                  const float *depth_tgt, const float *KT, const float *Kinv,
                  int batch_size, int height, int width, int device_id);
