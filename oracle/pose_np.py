@@ -13,7 +13,7 @@ The reference module itself does not import under numpy >= 2
 (RT_transform.py:246-247 use np.maximum_sctype / np.float).  With a two-line
 shim it does; tests/golden/make_golden.py imports it that way in the build
 container and stores its outputs in tests/golden/pose_*.npz, which pin this
-restatement (tests/test_oracle_pose.py).  Docstring known answers of the
+restatement (tests/test_oracle_cpu.py, tests/test_golden_ops_cpu.py).  Docstring known answers of the
 reference (RT_transform.py:409-414, :478-483) are checked there too.
 """
 from __future__ import annotations

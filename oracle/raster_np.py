@@ -11,7 +11,8 @@ reference's OpenGL renderers.
 
 PARITY UNPINNED (see raster_oracle.c header): no GL on this box, no rendered goldens in the
 reference.  Cross-oracle pin used instead (north_star): the rendered depth must be consistent
-with the flow oracle -- see tests/test_oracle_raster.py.
+with the flow oracle -- see tests/test_oracle_cpu.py::test_raster_oracle_cross_checks; the projection / view matrices are
+pinned against the reference renderer classes themselves (tests/golden/make_golden_render.py).
 """
 from __future__ import annotations
 
