@@ -448,6 +448,21 @@ int rc_prep_depth_dev(const uint16_t *raw, const uint8_t *mask, const int32_t *m
 int rc_prep_mask_dev(const uint8_t *mask, const int32_t *mask_idx, float *out, int batch_size,
                      int height, int width, void *stream);
 
+/* Mask from a decoded depth map (metres): out = depth > thresh ? 1 : (keep_small ? depth : 0).
+ * keep_small = 1 is mask_rendered of get_pair_mask, lib/utils/image.py:487-492
+ * (`depth_rendered[depth_rendered > 0.2] = 1`, smaller values stay); keep_small = 0 is the
+ * binary mask the init policies box from (:335-337, :446-447).  count % 4 == 0, 16-byte
+ * aligned device pointers; in place allowed. */
+int rc_mask_from_depth_dev(const float *depth, float *out, float thresh, int keep_small,
+                           int64_t count, void *stream);
+
+/* mask_dilate, lib/utils/mask_dilate.py:10-58, with the random draws made by the caller:
+ * thickness dev [B,4] int32 = thickness of the four growth blocks in the reference's order
+ * (rows shifted down :22-29, up :30-37, columns shifted right :38-45, left :46-53), 0 where
+ * the drawn `direction` skips the block.  mask / out dev [B,1,H,W] float32, out != mask. */
+int rc_mask_dilate_dev(const float *mask, const int32_t *thickness, float *out, int batch_size,
+                       int height, int width, void *stream);
+
 /* get_point_cloud_observed, lib/utils/image.py:592-596: out = R . X + T per sample
  * (float64 accumulation, float32 store).  points/out dev [B,3,N]; pose dev [B,3,4]. */
 int rc_points_transform_dev(const float *points, const float *pose, float *out, int batch_size,

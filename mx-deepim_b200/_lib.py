@@ -154,6 +154,8 @@ SIGNATURES = {
     "rc_prep_image_dev": (c_int, [_P, _P, POINTER(ctypes.c_double), c_int, c_int, c_int, _P]),
     "rc_prep_depth_dev": (c_int, [_P, _P, _P, _P, c_float, c_int, c_int, c_int, _P]),
     "rc_prep_mask_dev": (c_int, [_P, _P, _P, c_int, c_int, c_int, _P]),
+    "rc_mask_from_depth_dev": (c_int, [_P, _P, c_float, c_int, c_int64, _P]),
+    "rc_mask_dilate_dev": (c_int, [_P, _P, _P, c_int, c_int, c_int, _P]),
     "rc_points_transform_dev": (c_int, [_P, _P, _P, c_int, c_int, _P]),
     "rc_calc_flow_blocks": (c_int, [c_int, c_int]),
     "rc_calc_flow_dev": (c_int, [_P, _P, _P, POINTER(ctypes.c_double), ctypes.c_double, c_int, _P,

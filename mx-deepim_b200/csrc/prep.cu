@@ -174,6 +174,50 @@ prep_mask_kernel(const uint8_t *__restrict__ mask, const int32_t *__restrict__ m
                     (int)((mw >> 16) & 255u) == want ? 1.f : 0.f, (int)(mw >> 24) == want ? 1.f : 0.f));
 }
 
+// Mask from a decoded depth map: mask_rendered of get_pair_mask (lib/utils/image.py:487-492:
+// `depth[depth > 0.2] = 1`, smaller values stay) or the binary test-time init mask (:446-447).
+__global__ void __launch_bounds__(256)
+mask_from_depth_kernel(const float *depth, float *out, float thresh,
+                       int keep_small, long long quads) {
+  const long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= quads) return;
+  const float4 d = reinterpret_cast<const float4 *>(depth)[q];  // plain load: `out` may alias `depth`
+  float4 o;
+  o.x = d.x > thresh ? 1.f : (keep_small ? d.x : 0.f);
+  o.y = d.y > thresh ? 1.f : (keep_small ? d.y : 0.f);
+  o.z = d.z > thresh ? 1.f : (keep_small ? d.z : 0.f);
+  o.w = d.w > thresh ? 1.f : (keep_small ? d.w : 0.f);
+  st_f4(reinterpret_cast<float4 *>(out) + q, o);
+}
+
+// mask_dilate (lib/utils/mask_dilate.py:10-58) with the caller's random draws: t[4] per sample =
+// thickness of the down / up / right / left growth (0 = that block is not taken).  Each block
+// adds 1 where the pixel is 0 and the pixel `t` away in the opposite direction is not, and the
+// result is clamped at 1; a non-zero pixel keeps its value (clamped at 1).
+__global__ void __launch_bounds__(256)
+mask_dilate_kernel(const float *__restrict__ mask, const int32_t *__restrict__ t4,
+                   float *__restrict__ out, int H, int W) {
+  const int b = blockIdx.y;
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= H * W) return;
+  const float *m = mask + (size_t)b * H * W;
+  const int y = p / W, x = p - y * W;
+  const int td = t4[b * 4 + 0], tu = t4[b * 4 + 1], tr = t4[b * 4 + 2], tl = t4[b * 4 + 3];
+  const float v = __ldg(m + p);
+  float o;
+  if (v != 0.f) {
+    o = v > 1.f ? 1.f : v;
+  } else {
+    bool grow = false;
+    if (td > 0 && y >= td) grow |= __ldg(m + p - td * W) != 0.f;
+    if (tu > 0 && y < H - tu) grow |= __ldg(m + p + tu * W) != 0.f;
+    if (tr > 0 && x >= tr) grow |= __ldg(m + p - tr) != 0.f;
+    if (tl > 0 && x < W - tl) grow |= __ldg(m + p + tl) != 0.f;
+    o = grow ? 1.f : 0.f;
+  }
+  out[(size_t)b * H * W + p] = o;
+}
+
 // get_point_cloud_observed (lib/utils/image.py:592-596): R . X + T in float64, stored float32.
 __global__ void __launch_bounds__(256)
 points_transform_kernel(const float *__restrict__ pts, const float *__restrict__ pose,
@@ -396,6 +440,31 @@ int rc_prep_mask_dev(const uint8_t *mask, const int32_t *mask_idx, float *out, i
   const int quads = height * width / 4;
   dim3 grid((quads + 255) / 256, batch_size);
   rc::prep_mask_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(mask, mask_idx, out, quads);
+  return rc::note_status(rc::check_launch());
+}
+
+int rc_mask_from_depth_dev(const float *depth, float *out, float thresh, int keep_small,
+                           int64_t count, void *stream) {
+  RC_REQUIRE(count >= 0, RC_ERR_INVALID_ARG);
+  if (count == 0) return rc::note_status(RC_OK);
+  RC_REQUIRE(depth && out, RC_ERR_INVALID_ARG);
+  RC_REQUIRE(count % 4 == 0 && rc::aligned16(depth) && rc::aligned16(out), RC_ERR_UNALIGNED);
+  const long long quads = count / 4;
+  rc::mask_from_depth_kernel<<<(unsigned)((quads + 255) / 256), 256, 0,
+                               static_cast<cudaStream_t>(stream)>>>(depth, out, thresh,
+                                                                    keep_small ? 1 : 0, quads);
+  return rc::note_status(rc::check_launch());
+}
+
+int rc_mask_dilate_dev(const float *mask, const int32_t *thickness, float *out, int batch_size,
+                       int height, int width, void *stream) {
+  RC_REQUIRE(batch_size >= 0 && height > 0 && width > 0, RC_ERR_INVALID_ARG);
+  if (batch_size == 0) return rc::note_status(RC_OK);
+  RC_REQUIRE(mask && thickness && out && mask != out, RC_ERR_INVALID_ARG);
+  RC_REQUIRE(batch_size <= 65535, RC_ERR_INVALID_ARG);
+  dim3 grid((height * width + 255) / 256, batch_size);
+  rc::mask_dilate_kernel<<<grid, 256, 0, static_cast<cudaStream_t>(stream)>>>(mask, thickness, out,
+                                                                             height, width);
   return rc::note_status(rc::check_launch());
 }
 

@@ -7,6 +7,8 @@ and argument meaning, over CUDA tensors:
     decode_depth(raw, depth_factor, mask, idx)    image.py:200-206, :229-260
     calc_flow(depth_src, pose_src, pose_tgt, K, depth_tgt, thresh, standard_rep)
                                                   /root/reference/lib/pair_matching/flow.py:12-81
+    get_pair_mask(label, idx, depth_rendered, phase, init_mask, dilate)   image.py:272-492
+    mask_dilate(mask, draws) / draw_dilate()      /root/reference/lib/utils/mask_dilate.py:10-58
     get_point_cloud_model(points_obj, num_sample) image.py:559-589
     get_point_cloud_observed(points, pose)        image.py:592-596
 
@@ -115,6 +117,90 @@ def decode_mask(mask_u8, mask_idx, out=None, stream=None):
                                           B, H, W, _lib.stream_ptr(stream))
     _lib.check(st, "rc_prep_mask_dev")
     return out
+
+
+def mask_from_depth(depth, thresh=0.2, keep_small=False, out=None, stream=None):
+    """depth CUDA float32 (metres, any shape, numel % 4 == 0) -> depth > thresh ? 1 :
+    (keep_small ? depth : 0).  keep_small=True is get_pair_mask's mask_rendered
+    (image.py:487-492), False the binary mask the init policies box from (:335-337, :446-447)."""
+    _check("depth", depth, torch.float32)
+    if out is None:
+        out = torch.empty_like(depth)
+    _check("out", out, torch.float32, depth.shape)
+    with torch.cuda.device(depth.device):
+        st = _lib.load().rc_mask_from_depth_dev(depth.data_ptr(), out.data_ptr(), float(thresh),
+                                                1 if keep_small else 0, depth.numel(),
+                                                _lib.stream_ptr(stream))
+    _lib.check(st, "rc_mask_from_depth_dev")
+    return out
+
+
+def draw_dilate(max_thickness=10, rng=np.random):
+    """The random draws of ONE mask_dilate call in the reference's order (mask_dilate.py:19-47):
+    `direction`, then a thickness for every block that direction does not skip.  Returns the
+    four thicknesses (rows down, rows up, columns right, columns left), 0 = block skipped."""
+    direction = rng.randint(10)
+    t = [0, 0, 0, 0]
+    for i, skip in enumerate(([0, 1, 4], [1, 2, 5], [2, 3, 6], [0, 3, 7])):
+        if direction not in skip:
+            t[i] = rng.randint(max_thickness) + 1
+    return t
+
+
+def mask_dilate(mask, thickness, out=None, stream=None):
+    """mask_dilate (lib/utils/mask_dilate.py:10-58) on the device for a batch: mask CUDA float32
+    [B,1,H,W]; thickness [B,4] (draw_dilate per pair; tensor or array-like).  Returns [B,1,H,W]."""
+    _check("mask", mask, torch.float32)
+    if mask.dim() != 4 or mask.shape[1] != 1:
+        raise ValueError("mask must be [B,1,H,W]")
+    B, _, H, W = mask.shape
+    if not isinstance(thickness, torch.Tensor):
+        thickness = torch.from_numpy(np.ascontiguousarray(thickness, np.int32).reshape(B, 4)).to(mask.device)
+    _check("thickness", thickness, torch.int32, (B, 4))
+    if out is None:
+        out = torch.empty_like(mask)
+    _check("out", out, torch.float32, mask.shape)
+    if out.data_ptr() == mask.data_ptr():
+        raise ValueError("out must not alias mask")
+    with torch.cuda.device(mask.device):
+        st = _lib.load().rc_mask_dilate_dev(mask.data_ptr(), thickness.data_ptr(), out.data_ptr(),
+                                            B, H, W, _lib.stream_ptr(stream))
+    _lib.check(st, "rc_mask_dilate_dev")
+    return out
+
+
+def get_pair_mask(label_u8, mask_idx, depth_rendered, phase="train", init_mask=None,
+                  dilate=False, max_thickness=10, rng=np.random, stream=None):
+    """get_pair_mask (lib/utils/image.py:272-492) for a batch on the device, for the policies
+    the shipped configs use: phase "train" with TRAIN.INIT_MASK "box_gt", phase "test" with
+    TEST.INIT_MASK "box_rendered"; `dilate` = *.MASK_DILATE (draws come from `rng` pair by pair,
+    in the reference's order).
+
+    label_u8 CUDA uint8 [B,H,W] + mask_idx int32 [B] (train only, may be None for test);
+    depth_rendered CUDA float32 [B,1,H,W] in metres (prep.decode_depth).
+    Returns (mask_observed, mask_gt_observed, mask_rendered), each float32 [B,1,H,W]; at test
+    time mask_gt_observed IS mask_observed (image.py:480-481)."""
+    from .pipeline import mask_box
+
+    if init_mask is None:
+        init_mask = "box_gt" if phase == "train" else "box_rendered"
+    if phase == "train":
+        if init_mask != "box_gt":
+            raise Exception("Unknown mask type: {}".format(init_mask))  # image.py:343
+        gt = decode_mask(label_u8, mask_idx, stream=stream)
+        obs, _ = mask_box(gt, stream=stream)
+    else:
+        if init_mask != "box_rendered":
+            raise Exception("Unknown init mask type: {}".format(init_mask))  # image.py:467-470
+        binary = mask_from_depth(depth_rendered, 0.2, keep_small=False, stream=stream)
+        obs, _ = mask_box(binary, stream=stream)
+        gt = None
+    if dilate:
+        B = depth_rendered.shape[0]
+        draws = [draw_dilate(max_thickness, rng) for _ in range(B)]
+        obs = mask_dilate(obs, draws, stream=stream)
+    rend = mask_from_depth(depth_rendered, 0.2, keep_small=True, stream=stream)
+    return obs, (obs if gt is None else gt), rend
 
 
 def get_point_cloud_model(points_obj, num_sample, rng=np.random):

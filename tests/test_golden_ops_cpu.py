@@ -308,3 +308,62 @@ def test_pose_block_modes_vs_reference_rt_transform(mode):
     np.testing.assert_allclose(rot, g[mode + "/rot"], rtol=0, atol=2e-6)
     np.testing.assert_allclose(trans, g[mode + "/trans"], rtol=1e-5, atol=2e-6)
     np.testing.assert_allclose(KT, g[mode + "/KT"], rtol=2e-6, atol=3e-4)
+
+
+# ------------------------------------------------------------------ iteration-0 masks
+def _mask_files(tmp_path):
+    import cv2
+
+    pairdb = helpers.write_pair_files(tmp_path, 41)
+    labels = [cv2.imread(r["mask_gt_observed"], cv2.IMREAD_UNCHANGED) for r in pairdb]
+    depths = [cv2.imread(r["depth_rendered"], cv2.IMREAD_UNCHANGED).astype(np.float32) / 1000
+              for r in pairdb]
+    return pairdb, labels, depths
+
+
+def test_mask_preparation_restatement_vs_reference_loader(tmp_path):
+    """oracle/prep_np.py (mask_dilate per pixel with the draws taken out, get_pair_mask for the
+    configs' policies) against the reference's own get_pair_mask / mask_dilate
+    (tests/golden/make_golden_masks.py): bit for bit, including the order of the random draws."""
+    from oracle import prep_np
+
+    g = np.load(os.path.join(GOLD, "masks_reference.npz"))
+    pairdb, labels, depths = _mask_files(tmp_path)
+    n = 2 * 480 * 640
+    for phase, init in (("train", "box_gt"), ("test", "box_rendered")):
+        for dil in (False, True):
+            tag = "%s_%s_dil%d" % (phase, init, dil)
+            np.random.seed(77)
+            obs, gt, rend = [], [], []
+            for rec, lab, d in zip(pairdb, labels, depths):
+                draws = prep_np.draw_dilate(10) if dil else None
+                if phase == "train":
+                    o, m, r = prep_np.pair_masks_train_box_gt(lab, rec["mask_idx"], d, draws)
+                else:
+                    o, m, r = prep_np.pair_masks_test_box_rendered(d, draws)
+                obs.append(o); gt.append(m); rend.append(r)
+            ref_o = np.unpackbits(g[tag + "/mask_observed"])[:n].reshape(2, 480, 640)
+            ref_g = np.unpackbits(g[tag + "/mask_gt_observed"])[:n].reshape(2, 480, 640)
+            assert np.array_equal(np.stack(obs), ref_o), tag
+            assert np.array_equal(np.stack(gt), ref_g), tag
+            assert np.array_equal(np.stack(rend)[:, None, ::4, ::4], g[tag + "/mask_rendered"]), tag
+    rng = np.random.default_rng(9)
+    masks = (rng.random((12, 96, 128)) > 0.97).astype(np.float64)
+    masks[3] *= 0.5
+    masks[4, 10:20, 10:20] = 3.0
+    np.random.seed(5)
+    for m, ref in zip(masks, g["dilate/out"]):
+        assert np.array_equal(prep_np.mask_dilate_from_draws(m, prep_np.draw_dilate(10)), ref)
+
+
+def test_dilate_draws_of_the_product_follow_the_reference_rng_order():
+    """prep.draw_dilate (host logic of the product) consumes np.random exactly like
+    mask_dilate.py:19-47, i.e. like the restatement that is pinned above."""
+    from mx_deepim_b200 import prep
+    from oracle import prep_np
+
+    np.random.seed(123)
+    a = [prep.draw_dilate(10) for _ in range(200)]
+    np.random.seed(123)
+    b = [prep_np.draw_dilate(10) for _ in range(200)]
+    assert a == b and any(0 in t for t in a) and max(max(t) for t in a) == 10

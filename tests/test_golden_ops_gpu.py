@@ -304,3 +304,48 @@ def test_pose_update_modes_vs_reference_golden(cuda_device, mode):
     np.testing.assert_allclose(rot, g[mode + "/rot"], rtol=0, atol=3e-6)
     np.testing.assert_allclose(trans, g[mode + "/trans"], rtol=1e-5, atol=3e-6)
     np.testing.assert_allclose(KT, g[mode + "/KT"], rtol=2e-6, atol=3e-4)
+
+
+def test_mask_preparation_vs_reference_loader_golden(cuda_device, tmp_path):
+    """Iteration-0 masks on the device (prep.get_pair_mask: label decode, bounding rectangle,
+    mask_dilate with the reference's random draws, mask_rendered) against the reference's own
+    get_pair_mask / mask_dilate outputs (tests/golden/masks_reference.npz): bit for bit."""
+    import cv2
+    import torch
+
+    from mx_deepim_b200 import prep
+
+    g = np.load(os.path.join(GOLD, "masks_reference.npz"))
+    pairdb = helpers.write_pair_files(tmp_path, 41)
+    label = np.stack([cv2.imread(r["mask_gt_observed"], cv2.IMREAD_UNCHANGED) for r in pairdb])
+    raw = np.stack([cv2.imread(r["depth_rendered"], cv2.IMREAD_UNCHANGED) for r in pairdb])
+    lab_d = torch.from_numpy(label).to(cuda_device)
+    idx_d = torch.tensor([r["mask_idx"] for r in pairdb], dtype=torch.int32, device=cuda_device)
+    depth = prep.decode_depth(torch.from_numpy(raw.view(np.int16)).to(cuda_device), 1000.0)
+    n = 2 * 480 * 640
+    for phase, init in (("train", "box_gt"), ("test", "box_rendered")):
+        for dil in (False, True):
+            tag = "%s_%s_dil%d" % (phase, init, dil)
+            np.random.seed(77)
+            obs, gt, rend = prep.get_pair_mask(lab_d, idx_d, depth, phase=phase, init_mask=init,
+                                               dilate=dil)
+            torch.cuda.synchronize()
+            ref_o = np.unpackbits(g[tag + "/mask_observed"])[:n].reshape(2, 1, 480, 640)
+            ref_g = np.unpackbits(g[tag + "/mask_gt_observed"])[:n].reshape(2, 1, 480, 640)
+            assert np.array_equal(obs.cpu().numpy(), ref_o.astype(np.float32)), tag
+            assert np.array_equal(gt.cpu().numpy(), ref_g.astype(np.float32)), tag
+            r = rend.cpu().numpy()
+            assert np.array_equal(r[..., ::4, ::4], g[tag + "/mask_rendered"]), tag
+            np.testing.assert_allclose(r.astype(np.float64).sum(axis=(-2, -1)),
+                                       g[tag + "/mask_rendered_sum"], rtol=1e-12)
+    rng = np.random.default_rng(9)
+    masks = (rng.random((12, 96, 128)) > 0.97).astype(np.float64)
+    masks[3] *= 0.5
+    masks[4, 10:20, 10:20] = 3.0
+    np.random.seed(5)
+    draws = [prep.draw_dilate(10) for _ in range(12)]
+    out = prep.mask_dilate(torch.from_numpy(masks[:, None].astype(np.float32)).to(cuda_device), draws)
+    torch.cuda.synchronize()
+    assert np.array_equal(out.cpu().numpy()[:, 0], g["dilate/out"].astype(np.float32))
+    with pytest.raises(Exception):
+        prep.get_pair_mask(lab_d, idx_d, depth, phase="train", init_mask="mask_gt")
