@@ -49,6 +49,9 @@ int rc_device_sm_count(int device_id, int *sm_count);
  * (lib/flow_c/gpu_flow.hpp:1-3): blocking, selects `device_id`, outputs are
  * fully overwritten.  Like the reference it has no return value; unlike the
  * reference a CUDA failure is recorded (rc_last_status) instead of printed. */
+/* The library ALSO exports this function under the reference's own C++ linkage
+ * (`_Z5_flowPfS_S_S_S_S_iiii`, csrc/flow_cxx.cu), which is what lib/flow_c/gpu_flow.pyx:12-16
+ * links against when it is compiled as C++ with the reference's unmodified gpu_flow.hpp. */
 void _flow(float *flow, float *valid, float *depth_src, float *depth_tgt,
            float *KT, float *Kinv, int batch_size, int height, int width,
            int device_id);
@@ -65,6 +68,13 @@ int rc_last_status(void);
 int rc_flow_host(float *flow, float *valid, const float *depth_src,
                  const float *depth_tgt, const float *KT, const float *Kinv,
                  int batch_size, int height, int width, int device_id);
+
+/* Frees the host-pointer path's grow-only staging arena of `device_id` (device buffer,
+ * page-locked slots, worker streams).  The reference's _flow mallocs and frees per call
+ * (gpu_flow_kernel.cu:86-147); ours keeps the buffers between calls, so a long-lived process
+ * that is done with the host-pointer entry points can hand the memory back.  Safe to call
+ * at any time; the next _flow / rc_flow_host call re-creates what it needs. */
+int rc_flow_host_release(int device_id);
 
 /* Device-pointer fast path.  Requires W % 4 == 0 and 16-byte aligned planes. */
 int rc_flow_dev(const float *depth_src, const float *depth_tgt, const float *KT,
@@ -312,6 +322,13 @@ typedef struct rc_compare_step_args {
                                       it already holds the background, is not recomputed for those planes.
                                       Maintained by the step; ignored (but rewritten) when
                                       outputs_track_frames == 0 */
+  const float *loss_src_pose;      /* [B,3,4] or NULL (= src_pose).  The pose the point-matching loss and its
+                                      backward transform the model points with.  In the reference the loss
+                                      belongs to the network pass that PRODUCED rot_est/trans_est, i.e. to the
+                                      pose before the updater applied them (deepIM_flownet.py:446-499 runs in
+                                      the forward on src_pose_i; batch_updater_py_multi.py:211-312 refines the
+                                      pose afterwards), while flow/zoom read the refined pose `src_pose`.  A
+                                      refine loop therefore binds the pre-update pose here. */
 } rc_compare_step_args;
 
 int rc_compare_step_dev(const rc_compare_step_args *args);
@@ -386,6 +403,13 @@ typedef struct rc_render_args {
 } rc_render_args;
 
 int rc_render_dev(void *handle, const rc_render_args *args);
+
+/* Tells the handle that `n_renders` rc_render_dev calls captured into a CUDA graph have just been
+ * REPLAYED (a replay executes the kernels but not the host side of rc_render_dev, which is what
+ * tracks the ping-pong half of the incremental background's item lists).  Only the parity of
+ * `n_renders` matters.  Call it after every replay of a graph that holds an odd number of
+ * renders; harmless otherwise. */
+int rc_renderer_note_replay(void *handle, int n_renders);
 
 /* Counters of the last rc_render_dev call on this handle's workspaces (debug / bench):
  * out[0] = triangle records emitted, out[1] = tile-list entries.  Synchronises the stream. */

@@ -82,6 +82,7 @@ class rc_compare_step_args(ctypes.Structure):
         ("observed_box", c_void_p),
         ("outputs_track_frames", c_int32),
         ("zoom_tile_state", c_void_p),
+        ("loss_src_pose", c_void_p),
     ])
 
 
@@ -115,6 +116,7 @@ SIGNATURES = {
     "rc_device_sm_count": (c_int, [c_int, POINTER(c_int)]),
     "_flow": (None, [_P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int]),
     "rc_flow_host": (c_int, [_P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int]),
+    "rc_flow_host_release": (c_int, [c_int]),
     "rc_flow_dev": (c_int, [_P, _P, _P, _P, _P, _P, c_int, c_int, c_int, _P]),
     "rc_zoom_factor_dev": (c_int, [_P, _P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int,
                                    c_int, _P]),
@@ -138,6 +140,7 @@ SIGNATURES = {
                                    POINTER(c_void_p)]),
     "rc_renderer_destroy": (c_int, [c_void_p]),
     "rc_render_dev": (c_int, [c_void_p, POINTER(rc_render_args)]),
+    "rc_renderer_note_replay": (c_int, [_P, c_int]),
     "rc_render_stats": (c_int, [c_void_p, c_int, c_void_p, POINTER(c_int64)]),
     "rc_pose_update_dev": (c_int, [_P, _P, _P, _P, _P, POINTER(c_float), POINTER(c_float), c_int,
                                    _P, _P, _P, _P, c_int, _P]),

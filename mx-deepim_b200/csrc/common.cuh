@@ -14,6 +14,8 @@ namespace rc {
 // Recorded by every failing CUDA call so that rc_last_cuda_error() can report it.
 void set_cuda_error(cudaError_t e);
 int note_status(int status);
+// status.cu: SM count of `device` (< 0 = current device), cached per device.
+int device_sm_count(int device = -1);
 
 #define RC_CUDA_TRY(expr)                         \
   do {                                            \

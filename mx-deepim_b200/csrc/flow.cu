@@ -54,6 +54,10 @@ flow_kernel_v4(const float *__restrict__ depth_src, const float *__restrict__ de
   st_f4(reinterpret_cast<float4 *>(f) + q, o0);
   st_f4(reinterpret_cast<float4 *>(f + plane) + q, o1);
   st_f4(reinterpret_cast<float4 *>(valid + b * plane) + q, ov);
+  // possibly launched programmatically behind a grid it never reads (rc_compare_step_dev):
+  // waiting after the work makes this grid's completion imply the predecessor's, which is what
+  // the normal launch behind it (the resampler) relies on
+  pdl_wait();
 }
 
 // Scalar variant for widths that are not a multiple of four (host entry only).
@@ -291,6 +295,26 @@ int rc_flow_host(float *flow, float *valid, const float *depth_src, const float 
   RC_CUDA_TRY(cudaMemcpyAsync(flow, d_flow, 2 * plane, cudaMemcpyDeviceToHost, s));
   RC_CUDA_TRY(cudaMemcpyAsync(valid, d_valid, plane, cudaMemcpyDeviceToHost, s));
   RC_CUDA_TRY(cudaStreamSynchronize(s));
+  return rc::note_status(RC_OK);
+}
+
+int rc_flow_host_release(int device_id) {
+  RC_REQUIRE(device_id >= 0 && device_id < 64, RC_ERR_INVALID_ARG);
+  rc::Arena &a = rc::g_arena[device_id];
+  std::lock_guard<std::mutex> guard(a.mu);
+  if (!a.ptr && !a.pin && !a.have_streams) return rc::note_status(RC_OK);
+  int cur = -1;
+  RC_CUDA_TRY(cudaGetDevice(&cur));
+  if (cur != device_id) RC_CUDA_TRY(cudaSetDevice(device_id));
+  if (a.have_streams) {
+    for (int i = 0; i < rc::kHostWorkers; ++i) (void)cudaStreamDestroy(a.streams[i]);
+    a.have_streams = false;
+  }
+  if (a.ptr) (void)cudaFree(a.ptr);
+  if (a.pin) (void)cudaFreeHost(a.pin);
+  a.ptr = a.pin = nullptr;
+  a.bytes = a.pin_bytes = 0;
+  if (cur != device_id) RC_CUDA_TRY(cudaSetDevice(cur));
   return rc::note_status(RC_OK);
 }
 

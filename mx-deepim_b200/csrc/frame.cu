@@ -106,6 +106,7 @@ frame_tiles_kernel(FrameItems F, const float *__restrict__ depth_src,
       atomicMax(w + 7, y1 + 1);
     }
   }
+  pdl_wait();  // completion of this grid implies completion of the grid it was launched behind
 }
 
 int launch_frame_tiles(const FrameItems &F, const float *depth_src, const float *depth_tgt,
@@ -122,13 +123,7 @@ int launch_frame_tiles(const FrameItems &F, const float *depth_src, const float 
     RC_REQUIRE(aligned16(flow) && aligned16(valid), RC_ERR_UNALIGNED);
     RC_REQUIRE(!zero_prev || (F.prev_list && F.prev_count), RC_ERR_INVALID_ARG);
   }
-  static int sm_count = 0;
-  if (sm_count == 0) {
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess ||
-        cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
-      sm_count = 148;
-  }
+  const int sm_count = device_sm_count();
   // the item counts live on the device: a fixed grid of a few blocks per SM strides over them
   long long blocks = ((long long)batch_size * F.tiles_x * F.tiles_y + FT_ITEMS_PER_BLOCK - 1) /
                      FT_ITEMS_PER_BLOCK;

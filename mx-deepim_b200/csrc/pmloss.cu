@@ -174,6 +174,9 @@ __device__ __forceinline__ bool cluster_sum(const double (&mine)[NV], double *ta
   }
   cg::cluster_group cluster = cg::this_cluster();
   const unsigned rank = cluster.block_rank();
+  // distributed shared memory of another CTA may only be touched once that CTA is known to
+  // have started: all CTAs of the cluster meet here first
+  cluster.sync();
   if (threadIdx.x == 0) {
     double *dst = cluster.map_shared_rank(table, 0);
 #pragma unroll
@@ -249,6 +252,10 @@ pm_fwd_kernel(const float *__restrict__ points, const float *__restrict__ obs,
   double part[1] = {acc}, mine[1], tot[1];
   block_sum_n<1>(part, red, mine);
   if (cluster_sum<1, CL>(mine, table, tot) && loss_sum) loss_sum[b] = (float)tot[0];
+  // launched programmatically behind another grid and never reads it: wait HERE, after the
+  // work, so that this grid's completion implies the predecessor's (a later normal launch
+  // that waits for this one has then transitively waited for everything before it)
+  pdl_wait();
 }
 
 // quat2mat_backward, transform3d.py:256-327 (float64 tail, float32 result).
@@ -358,7 +365,9 @@ pm_bwd_kernel(const float *__restrict__ out_grad, const float *__restrict__ poin
 #pragma unroll
   for (int k = 0; k < 9; ++k) part[3 + k] = gr[k];
   block_sum_n<12>(part, red, mine);  // one pass: twelve sums between two barriers
-  if (!cluster_sum<12, CL>(mine, table, sums)) return;
+  const bool lead = cluster_sum<12, CL>(mine, table, sums);
+  pdl_wait();  // see pm_fwd_kernel: this grid's completion must imply its predecessor's
+  if (!lead) return;
   // values the reference holds as float32 NDArrays
   float Df[3], Gf[9];
 #pragma unroll

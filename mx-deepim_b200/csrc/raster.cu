@@ -1107,6 +1107,13 @@ int rc_renderer_destroy(void *handle) {
   return rc::note_status(RC_OK);
 }
 
+int rc_renderer_note_replay(void *handle, int n_renders) {
+  RC_REQUIRE(handle != nullptr && n_renders >= 0, RC_ERR_INVALID_ARG);
+  rc::Renderer &Rh = *static_cast<rc::Renderer *>(handle);
+  Rh.cur ^= (n_renders & 1);
+  return rc::note_status(RC_OK);
+}
+
 int rc_render_dev(void *handle, const rc_render_args *a) {
   RC_REQUIRE(handle && a, RC_ERR_INVALID_ARG);
   rc::Renderer &Rh = *static_cast<rc::Renderer *>(handle);  // the handle (host state lives here)
@@ -1155,10 +1162,9 @@ int rc_render_dev(void *handle, const rc_render_args *a) {
     return RC_OK;
   };
   int st;
-  static int sm_count = 0, cover_per_sm = 0, resolve_per_sm = 0;
-  if (sm_count == 0) {
-    if (cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, R.device) != cudaSuccess)
-      sm_count = 148;
+  const int sm_count = rc::device_sm_count(R.device);
+  static int cover_per_sm = 0, resolve_per_sm = 0;  // per kernel, not per device
+  if (cover_per_sm == 0) {
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&cover_per_sm, rc::raster_cover_kernel,
                                                       rc::RT_CV_THREADS, 0) != cudaSuccess ||
         cover_per_sm < 1)

@@ -9,6 +9,21 @@ int note_status(int status) {
   g_last_status = status;
   return status;
 }
+
+// SM count of `device` (< 0: the calling thread's current device), cached PER DEVICE: the
+// reference drives several GPUs from one process (batch_updater_py_multi.py:176), so a
+// process-wide cache filled by whichever device called first would size grids for the wrong part.
+int device_sm_count(int device) {
+  constexpr int kMaxDev = 64;
+  static int cache[kMaxDev];  // 0 = unknown; benign race (every writer stores the same value)
+  if (device < 0 && cudaGetDevice(&device) != cudaSuccess) return 148;
+  if (device >= 0 && device < kMaxDev && cache[device] > 0) return cache[device];
+  int v = 0;
+  if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, device) != cudaSuccess || v <= 0)
+    return 148;
+  if (device >= 0 && device < kMaxDev) cache[device] = v;
+  return v;
+}
 }  // namespace rc
 
 extern "C" {

@@ -41,17 +41,19 @@ int rc_compare_step_dev(const rc_compare_step_args *a) {
   // test phase (deepIM_flownet.py:778-838): no GT flow, no loss -- flow == NULL skips both the
   // flow kernel and the flow planes of the resampler
   const bool do_flow = a->flow != nullptr && a->valid != nullptr;
+  // the loss belongs to the pass that produced rot_est / trans_est: pre-update pose if given
+  const float *loss_pose = a->loss_src_pose ? a->loss_src_pose : a->src_pose;
   // overlap unless the caller wants per-kernel marks of the overlapped kernels
   const bool serial = a->marks && (a->marks[0] || a->marks[1] || a->marks[4] || a->marks[5]);
   auto loss = [&]() -> int {
     return rc_pm_loss_fwd_dev(a->point_cloud_model, a->point_cloud_observed,
-                              a->point_cloud_weights, a->rot_est, a->trans_est, a->src_pose,
+                              a->point_cloud_weights, a->rot_est, a->trans_est, loss_pose,
                               a->T_means, a->T_stds, a->rot_coord, a->loss_type, a->norm_term,
                               a->sl1_scalar, nullptr, a->loss_map, a->loss_sum, B, N, a->stream);
   };
   auto loss_bwd = [&]() -> int {
     return rc_pm_loss_bwd_dev(a->point_cloud_model, a->point_cloud_observed,
-                              a->point_cloud_weights, a->rot_est, a->trans_est, a->src_pose,
+                              a->point_cloud_weights, a->rot_est, a->trans_est, loss_pose,
                               a->T_means, a->T_stds, a->rot_coord, a->loss_type, a->norm_term,
                               a->sl1_scalar, a->grad_scale, a->grad_rot, a->grad_trans, B, N,
                               a->stream);

@@ -240,6 +240,7 @@ zoom_bbox_kernel(const float *__restrict__ obs, const float *__restrict__ rend,
       trans_out[b * 3 + 2] = trans_in[b * 3 + 2];
     }
   }
+  pdl_wait();  // completion of this grid implies completion of the grid it was launched behind
 }
 
 // ---------------------------------------------------------------- sampler
@@ -848,13 +849,7 @@ int launch_zoom_factor(const float *obs, const float *rend, const float *src_pos
   // blocks per sample than it takes to give every thread four quads (the loop batches 4 loads
   // per plane).  All blocks being resident at once also means griddepcontrol.launch_dependents
   // releases the next kernel immediately.
-  static int sm_count = 0;
-  if (sm_count == 0) {
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess ||
-        cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
-      sm_count = 148;
-  }
+  const int sm_count = device_sm_count();
   const int max_bps = (quads + 256 * 4 - 1) / (256 * 4);
   int bps = (sm_count * (channels == 1 ? 2 : 1)) / batch_size;
   // large batches fill the GPU several times over anyway: four blocks per sample keep the last

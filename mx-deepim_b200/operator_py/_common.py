@@ -105,9 +105,12 @@ def device_const(values, device):
 _WS_CACHE = {}
 
 
-def _workspace(batch, device):
-    """Zeroed bbox workspace; the kernel leaves it zeroed, so one buffer per (device, B)."""
-    key = (str(device), int(batch))
+def _workspace(batch, device, stream_handle):
+    """Zeroed bbox workspace.  The kernel leaves it zeroed, so the buffer is reused -- but only
+    by launches that are ordered behind each other: one buffer per (device, B, stream).  Two
+    CustomOps with the same batch on different engine streams therefore never share one
+    (they would race on the atomics and on the ticket counter)."""
+    key = (str(device), int(batch), int(stream_handle))
     ws = _WS_CACHE.get(key)
     if ws is None:
         ws = torch.zeros((batch, _lib.RC_ZF_WS_INTS), dtype=torch.int32, device=device)
@@ -126,14 +129,19 @@ def zoom_factor(obs, rend, src_pose, K, pixel_means, zoom_factor_out, mode, bbox
     dev = obs.device
     Kd = device_const(K, dev)
     pm = device_const(pixel_means, dev) if pixel_means is not None else None
-    ws = _workspace(B, dev)
     lib = _lib.load()
     with torch.cuda.device(dev):
+        sp = _lib.stream_ptr(stream)
+        ws = _workspace(B, dev, sp)
         st = lib.rc_zoom_factor_dev(obs.data_ptr(), rend.data_ptr(), src_pose.data_ptr(),
                                     Kd.data_ptr(), pm.data_ptr() if pm is not None else None,
                                     zoom_factor_out.data_ptr(),
                                     bbox.data_ptr() if bbox is not None else None, ws.data_ptr(),
-                                    B, C, H, W, mode, _lib.stream_ptr(stream))
+                                    B, C, H, W, mode, sp)
+        if st != _lib.RC_OK:
+            # a failed / aborted launch may leave partial boxes or a ticket behind: drop the
+            # buffer so that the next call starts from a freshly zeroed one
+            _WS_CACHE.pop((str(dev), int(B), int(sp)), None)
     _lib.check(st, "rc_zoom_factor_dev")
 
 

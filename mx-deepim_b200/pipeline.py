@@ -150,6 +150,10 @@ class CompareStep(object):
                 raise ValueError("%s is on %s, step is on %s" % (k, t.device, self.device))
             setattr(a, k, t.data_ptr())
         a.K = self.Kd.data_ptr()
+        lsp = x.get("loss_src_pose")
+        if lsp is not None and not test_phase:
+            C.check_tensor("loss_src_pose", lsp)
+            a.loss_src_pose = lsp.data_ptr()
         if test_phase:
             a.mask_gt_observed = x["mask_observed"].data_ptr()
         skip = ("flow", "valid", "zoom_flow", "zoom_flow_weights", "zoom_trans_gt", "loss_map",
@@ -190,7 +194,8 @@ class CompareStep(object):
         `marks`: optional list of RC_STEP_MARKS _lib.Event (or None entries) recorded around
         the kernels.  `args`: a struct from bind(x) to skip re-binding."""
         a = self.bind(x) if args is None else args
-        a.stream = _lib.stream_ptr(stream)
+        with torch.cuda.device(self.device):  # the CURRENT stream of the step's device
+            a.stream = _lib.stream_ptr(stream)
         if marks is not None:
             arr = (ctypes.c_void_p * _lib.RC_STEP_MARKS)()
             for i, m in enumerate(marks):
@@ -415,6 +420,7 @@ class RefineLoop(object):
         self.cur = 0
         self.bound = [None, None]
         self.obs = None
+        self.graph = None
         # stand-in + pose update + 8 render kernels (clear, vertex, setup, clip, scan, fill, cover,
         # resolve) + step
         self.launches_per_iteration = 1 + 1 + 8 + self.step.launches_per_step
@@ -434,6 +440,7 @@ class RefineLoop(object):
         depth_gt_observed, mask_observed, mask_gt_observed, src_pose, tgt_pose, class_index,
         point_cloud_model / weights / observed, Kinv."""
         t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(self.device)
+        self.graph = None  # a captured loop holds raw pointers into the previous batch's tensors
         self.obs = {k: t(host[k]) for k in ("image_observed", "depth_gt_observed", "mask_observed",
                                             "mask_gt_observed", "tgt_pose", "point_cloud_model",
                                             "point_cloud_weights", "point_cloud_observed", "Kinv")}
@@ -461,9 +468,12 @@ class RefineLoop(object):
         self._flow_tracks = False  # the flow planes do not hold a previous frame's flow yet
         for par in (0, 1):
             x = dict(self.obs)
+            # flow / zoom read the refined pose pose[par]; the loss (and its backward) belongs to
+            # the pass that produced rot_est / trans_est, i.e. to the pose BEFORE the update
+            # (deepIM_flownet.py:446-499 vs batch_updater_py_multi.py:211-312)
             x.update(image_rendered=self.image_rendered, depth_rendered=self.depth_rendered,
-                     src_pose=self.pose[par], KT=self.KT, rot_est=self.rot_est,
-                     trans_est=self.trans_est, trans_gt=self.trans_gt)
+                     src_pose=self.pose[par], loss_src_pose=self.pose[1 - par], KT=self.KT,
+                     rot_est=self.rot_est, trans_est=self.trans_est, trans_gt=self.trans_gt)
             self.bound[par] = self.step.bind(x)
             self._bind_frame(self.bound[par])
 
@@ -474,7 +484,7 @@ class RefineLoop(object):
             a.zoom_tile_state = self.step.zoom_tile_state.data_ptr()
             a.outputs_track_frames = 0
 
-    def set_batch_poses(self, host):
+    def set_batch_poses(self, host=None):
         """Restart the loop from the batch's initial source poses (same observed side)."""
         if getattr(self, "_pose0", None) is None:
             t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(self.device)
@@ -490,6 +500,10 @@ class RefineLoop(object):
         """One refinement iteration on the current stream (no synchronisation)."""
         self.predict(it, self.rot_gt, self.trans_gt)
         nxt = 1 - self.cur
+        if self.renderer.serial != getattr(self, "_my_serial", -1):
+            # somebody else rendered through this renderer since our last frame: its item lists no
+            # longer describe what the flow planes / zoomed outputs hold -> one dense step
+            self._flow_tracks = False
         pose_update(self.pose[self.cur], self.rot_est, self.trans_est, self.obs["tgt_pose"], self.K,
                     out=(self.pose[nxt], self.rot_gt, self.trans_gt, self.KT))
         self.renderer.render_batch(self.cls, self.pose[nxt], pixel_means=self.render_means,
@@ -497,6 +511,7 @@ class RefineLoop(object):
                                    out={"depth": self.depth_rendered, "image": self.image_rendered,
                                         "mask": self.mask_rendered}, marks=render_marks,
                                    incremental=True)  # the loop owns these three buffers
+        self._my_serial = self.renderer.serial
         self.cur = nxt
         a = self.bound[nxt]
         if self.sparse:
@@ -508,30 +523,63 @@ class RefineLoop(object):
         for it in range(iterations):
             self.iterate(it)
 
-    def capture(self, host, iterations=4):
+    def check_status(self):
+        """Synchronise and raise if any render of this loop overflowed the rasteriser's tile
+        lists (DeviceRenderer.check_status).  The loop itself never synchronises; call this at
+        the end of a loop / epoch, before trusting its outputs."""
+        self.renderer.check_status()
+
+    def capture(self, host=None, iterations=4):
         """Capture one whole loop -- restart from the batch's initial poses, then `iterations`
         refinement iterations (stand-in, pose update, render, compare step: ~14 launches and 2
-        memsets each) -- into ONE CUDA graph; `self.graph.replay()` then costs one launch call
-        from the host, which is what matters once a GPU's share of the batch is small (8 GPUs x 32
+        memsets each) -- into a CUDA graph; `self.replay()` then costs one launch call from the
+        host, which is what matters once a GPU's share of the batch is small (8 GPUs x 32
         pairs).  The programmatic dependent launches inside the render and the step are kept
         as programmatic edges of the graph.
 
-        `iterations` must be even: the renderer's incremental background ping-pongs between two
-        item lists per call, and a replay has to find the previous replay's last frame in the
-        half it was captured to read.  Nothing else may render through this loop's renderer
-        between replays (an eager loop of the same even length is fine)."""
-        if iterations % 2:
-            raise ValueError("capture() needs an even number of iterations (ping-pong item lists)")
+        The renderer's incremental background ping-pongs between two item lists per render, and
+        a replay has to find the previous loop's last frame in the half it was captured to read.
+        An even `iterations` returns to the same half, so one graph serves every replay; for an
+        odd count TWO graphs are captured (one per starting half) and replay() alternates
+        between them.  replay() also notices when anybody rendered through this loop's renderer
+        since the last replay (DeviceRenderer.serial) -- the captured pointers would then read
+        another frame's item list -- and re-captures instead of replaying stale state."""
+        if iterations < 1:
+            raise ValueError("capture() needs at least one iteration")
+        if host is None and getattr(self, "_pose0", None) is None:
+            raise ValueError("capture() needs the batch (set_batch_poses has not run yet)")
         self.set_batch_poses(host)
         self.run(iterations)  # warm-up; also establishes the incremental-background state
         torch.cuda.synchronize(self.device)
-        g = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(g):
-            self.set_batch_poses(host)
-            self.run(iterations)
-        self.graph = g
+        self.graphs = []
+        for _ in range(1 if iterations % 2 == 0 else 2):
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self.set_batch_poses(host)
+                self.run(iterations)
+            self.graphs.append(g)
+            # capturing ran the HOST side of every render (the handle's ping-pong parity moved)
+            # but not the kernels: execute the loop once so that device and host agree again
+            g.replay()
+        self._graph_turn = 0
+        self.graph = self.graphs[0]
         self.graph_iterations = iterations
-        return g
+        self._graph_serial = self.renderer.serial
+        return self.graph
+
+    def replay(self):
+        """Replay the captured loop (capture() first).  Safe against an eager render through the
+        same renderer in between (re-captures) and for odd iteration counts (alternates)."""
+        if getattr(self, "graph", None) is None:
+            raise RuntimeError("RefineLoop.replay(): no captured loop (capture() first, and again "
+                               "after set_batch)")
+        if self.renderer.serial != self._graph_serial:
+            self.capture(None, self.graph_iterations)
+        g = self.graphs[self._graph_turn % len(self.graphs)]
+        self._graph_turn += 1
+        g.replay()
+        if self.graph_iterations % 2:
+            self.renderer.note_replay(self.graph_iterations)
 
     # ------------------------------------------------------------------ test phase
     def iterate_test(self, rot_est, trans_est, update_mask="box_rendered"):
@@ -563,6 +611,7 @@ class RefineLoop(object):
                                    want=("depth", "image", "mask"),
                                    out={"depth": self.depth_rendered, "image": self.image_rendered,
                                         "mask": self.mask_rendered}, incremental=True)
+        self._my_serial = self.renderer.serial
         self.cur = nxt
         mo = self.mask_observed_test if update_mask == "box_rendered" else self.obs["mask_observed"]
         x = {"image_observed": self.obs["image_observed"], "image_rendered": self.image_rendered,

@@ -127,6 +127,9 @@ class DeviceRenderer(object):
                                     self.device.index or 0, ctypes.byref(self.handle))
         _lib.check(st, "rc_renderer_create")
         self.status = torch.zeros((1,), dtype=torch.int32, device=self.device)
+        # host-issued rc_render_dev calls on this handle (CUDA-graph replays do not count): lets
+        # an owner of captured graphs notice that somebody else rendered in between
+        self.serial = 0
 
     def __del__(self):
         try:
@@ -191,8 +194,29 @@ class DeviceRenderer(object):
             a.marks = ctypes.cast(arr, ctypes.POINTER(ctypes.c_void_p))
         with torch.cuda.device(self.device):
             st = _lib.load().rc_render_dev(self.handle, ctypes.byref(a))
+        self.serial += 1
         _lib.check(st, "rc_render_dev")
         return out
+
+    def note_replay(self, n_renders):
+        """A CUDA graph holding `n_renders` captured render_batch calls was just replayed
+        (rc_renderer_note_replay keeps the handle's ping-pong parity in step)."""
+        _lib.check(_lib.load().rc_renderer_note_replay(self.handle, int(n_renders)),
+                   "rc_renderer_note_replay")
+
+    def check_status(self, reset=True):
+        """Raise if any render since the last check overflowed its tile lists (raster_scan_kernel
+        sets the device flag; the fill / cover passes then clamp and DROP triangles, so depth,
+        mask and everything derived from them would be wrong).  Synchronises the device: call it
+        where the caller synchronises anyway (Render_Py.render does), at the end of an
+        asynchronous loop (RefineLoop.check_status) or once per bench."""
+        flag = int(self.status.item())
+        if flag:
+            if reset:
+                self.status.zero_()
+            raise _lib.RenderCompareError(
+                "rc_render_dev: tile-list capacity exceeded (RC_ERR_CAPACITY): a pair's triangles "
+                "cover more tile entries than 8 * max_triangles + 16 * tiles; the frame is incomplete")
 
     def stats(self, batch):
         out = (ctypes.c_int64 * 2)()
@@ -207,7 +231,7 @@ class DeviceRenderer(object):
         pose[0, :, :3], pose[0, :, 3] = R, np.asarray(t).reshape(3)
         o = self.render_batch(cls, torch.from_numpy(pose).to(self.device), K=K,
                               want=("depth", "bgr"), **kw)
-        torch.cuda.synchronize(self.device)
+        self.check_status()  # synchronises; a dropped triangle must not reach the caller silently
         return o["bgr"][0].cpu().numpy(), o["depth"][0, 0].cpu().numpy()
 
 

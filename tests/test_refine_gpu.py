@@ -55,16 +55,22 @@ def test_refine_loop_matches_updater_oracle(cuda_device):
         zm = zoom_np.zoom_mask_forward(host["mask_observed"], host["mask_gt_observed"], depth, pose,
                                        synth.K_LINEMOD)
         assert np.array_equal(loop.step.zoom_factor.cpu().numpy(), zm[3])
+        # the loss belongs to the pass that produced (rot_est, trans_est): it transforms the
+        # model points with the pose BEFORE the update (deepIM_flownet.py:446-499 runs in the
+        # network forward on src_pose_i; batch_updater_py_multi.py:211-312 refines afterwards)
         _, _, sums = transform3d_np.pm_loss_forward(
             host["point_cloud_model"], host["point_cloud_observed"], host["point_cloud_weights"],
-            rot_est, trans_est, pose, means, stds)
+            rot_est, trans_est, prev_pose, means, stds)
         np.testing.assert_allclose(loop.step.loss_sum.cpu().numpy(), sums, rtol=1e-4)
         losses.append(float(sums.sum()))
         prev_pose = pose
-    # the damped ground-truth update converges: the poses approach the targets
+    # the damped ground-truth update converges: the poses approach the targets and the
+    # point-matching loss of every pass is smaller than the one before
     err0 = np.abs(host["src_pose"] - host["tgt_pose"]).max()
     err3 = np.abs(prev_pose - host["tgt_pose"]).max()
     assert err3 < 0.5 * err0
+    assert losses[0] > losses[1] > losses[2] > 0, losses
+    loop.check_status()  # no tile-list overflow in any render of the loop
 
 
 def test_refine_loop_graph_replay_equals_eager(cuda_device):
@@ -110,8 +116,72 @@ def test_refine_loop_graph_replay_equals_eager(cuda_device):
         got = snap()
         for k in eager:
             assert torch.equal(got[k], eager[k]), k
-    with pytest.raises(ValueError):
-        loop.capture(host, iterations=3)
+
+
+@pytest.mark.parametrize("iters", [3, 4])
+def test_refine_loop_replay_is_safe(cuda_device, iters):
+    """RefineLoop.replay(): an ODD iteration count (the renderer's ping-pong item lists do not
+    return to the same half: two graphs, alternated) and a foreign render through the same
+    renderer between replays (the captured pointers would read another frame's item list:
+    re-capture) both give the eager loop's results bit for bit, and an eager loop after an odd
+    number of replays still does."""
+    import torch
+
+    from mx_deepim_b200 import pipeline, synth
+
+    rng = np.random.default_rng(21)
+    meshes = [synth.make_mesh(rng, level=3, kind=1), synth.make_mesh(rng, level=3, kind=0)]
+    B = 4
+    loop = pipeline.RefineLoop(meshes, B, cuda_device, seed=9, backward=True)
+    host = pipeline.make_refine_batch(meshes, B, 321, renderer=loop.renderer, occlusion=True)
+    loop.set_batch(host)
+
+    def snap():
+        torch.cuda.synchronize()
+        out = {"depth": loop.depth_rendered.clone(), "image": loop.image_rendered.clone(),
+               "mask": loop.mask_rendered.clone(), "pose": loop.pose[loop.cur].clone()}
+        for k, v in loop.step.outputs().items():
+            if v is not None:
+                out[k] = v.clone()
+        return out
+
+    def same(a, b, tag):
+        for k in a:
+            x, y = a[k], b[k]
+            if x.dtype == torch.float32:
+                x, y = x.view(torch.int32), y.view(torch.int32)
+            assert torch.equal(x, y), (tag, k)
+
+    loop.set_batch_poses(host)
+    loop.run(iters)
+    eager = snap()
+    assert float(eager["mask"].sum()) > 0
+    s = torch.cuda.Stream(device=cuda_device)
+    with torch.cuda.stream(s):
+        loop.capture(host, iterations=iters)
+        assert len(loop.graphs) == (1 if iters % 2 == 0 else 2)
+        for rep in range(5):
+            loop.replay()
+            same(eager, snap(), ("replay", rep))
+        # eager loop right after an odd number of replays: host and device parity must agree
+        loop.set_batch_poses(host)
+        loop.run(iters)
+        same(eager, snap(), "eager-after-replays")
+        loop.replay()  # the eager renders moved renderer.serial: this re-captures
+        same(eager, snap(), "replay-after-eager")
+        # a second user of the renderer between replays (another pose, other output buffers)
+        other = loop.renderer.render_batch(loop.cls, loop.obs["tgt_pose"], want=("depth",))
+        assert float(other["depth"].sum()) > 0
+        loop.replay()
+        same(eager, snap(), "replay-after-foreign-render")
+        loop.replay()
+        same(eager, snap(), "replay-after-foreign-render-2")
+    loop.check_status()
+    # a new batch drops the captured graphs (they hold raw pointers into the old one)
+    loop.set_batch(host)
+    assert loop.graph is None
+    with pytest.raises(RuntimeError):
+        loop.replay()
 
 
 def test_sparse_frame_step_equals_dense_step(cuda_device):
