@@ -428,6 +428,14 @@ int rc_pose_update_dev(const float *src_pose, const float *rot_est, const float 
                        const float *T_stds, int rot_coord, float *refined_pose, float *rot_res,
                        float *trans_res, float *KT, int batch_size, void *stream);
 
+/* calc_RT_delta(pose_src, pose_tgt, T_means, T_stds, rot_coord, rot_type="QUAT")
+ * (lib/pair_matching/RT_transform.py:16-48) batched on the device: the regression labels of
+ * iteration 0, which the reference's loaders compute per pair on the host.  src_pose, tgt_pose
+ * [B,3,4]; rot_res [B,4] (w,x,y,z, w >= 0); trans_res [B,3]. */
+int rc_pose_delta_dev(const float *src_pose, const float *tgt_pose, const float *T_means,
+                      const float *T_stds, int rot_coord, float *rot_res, float *trans_res,
+                      int batch_size, void *stream);
+
 /* Synthetic-workload utility (not a reference interface): the network stand-in of SURVEY.md 8(d)
  * for refine loops without the CNN -- rot_est = normalise((1-a) * identity + a * rot_gt + noise_q),
  * trans_est = a * trans_gt + noise_t; all arrays device float32 ([B,4] / [B,3]). */

@@ -144,6 +144,7 @@ SIGNATURES = {
     "rc_render_stats": (c_int, [c_void_p, c_int, c_void_p, POINTER(c_int64)]),
     "rc_pose_update_dev": (c_int, [_P, _P, _P, _P, _P, POINTER(c_float), POINTER(c_float), c_int,
                                    _P, _P, _P, _P, c_int, _P]),
+    "rc_pose_delta_dev": (c_int, [_P, _P, POINTER(c_float), POINTER(c_float), c_int, _P, _P, c_int, _P]),
     "rc_standin_predict_dev": (c_int, [_P, _P, _P, _P, c_float, _P, _P, c_int, _P]),
     "rc_pm_loss_bwd_dev": (c_int, [_P, _P, _P, _P, _P, _P, POINTER(c_float), POINTER(c_float),
                                    c_int, c_int, c_float, c_float, c_float, _P, _P, c_int, c_int,

@@ -100,6 +100,17 @@ static inline cudaError_t launch_maybe_pdl(void (*kern)(KArgs...), dim3 grid, di
 }
 #endif
 
+// Event mark on `s`.  While `s` is being captured into a CUDA graph a plain cudaEventRecord would
+// only create a dependency edge; cudaEventRecordExternal makes it a real event-record NODE, so
+// that every replay of the graph re-records the event and cudaEventElapsedTime works on it --
+// this is how bench.py times kernels inside a replayed refine loop.
+static inline cudaError_t record_mark(cudaEvent_t e, cudaStream_t s) {
+  cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(s, &cs) == cudaSuccess && cs == cudaStreamCaptureStatusActive)
+    return cudaEventRecordWithFlags(e, s, cudaEventRecordExternal);
+  return cudaEventRecord(e, s);
+}
+
 static inline bool aligned16(const void *p) {
   return (reinterpret_cast<uintptr_t>(p) & 15u) == 0;
 }

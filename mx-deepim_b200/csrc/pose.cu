@@ -255,6 +255,47 @@ __global__ void pose_update_kernel(const float *__restrict__ src_pose, const flo
     }
 }
 
+// calc_RT_delta(pose_src, pose_tgt, T_means, T_stds, rot_coord, "QUAT") alone
+// (RT_transform.py:16-48): the regression labels of ITERATION 0, which the reference's loader
+// computes on the host per pair (lib/dataset/*: calc_RT_delta on the stored float32 poses).
+__global__ void pose_delta_kernel(const float *__restrict__ src_pose,
+                                  const float *__restrict__ tgt_pose, PoseUpdateParams pp,
+                                  float *__restrict__ rot_res, float *__restrict__ trans_res, int B) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  double Rn[9], Tr[3], Rt[9], Tt[3];
+  for (int i = 0; i < 3; ++i) {
+    for (int j = 0; j < 3; ++j) {
+      Rn[i * 3 + j] = src_pose[b * 12 + i * 4 + j];
+      Rt[i * 3 + j] = tgt_pose[b * 12 + i * 4 + j];
+    }
+    Tr[i] = src_pose[b * 12 + i * 4 + 3];
+    Tt[i] = tgt_pose[b * 12 + i * 4 + 3];
+  }
+  double Rdel[9];  // R_inv_transform, :72-79
+  for (int i = 0; i < 3; ++i)
+    for (int j = 0; j < 3; ++j) {
+      double a = 0.0;
+      for (int k = 0; k < 3; ++k)
+        a += (pp.rot_coord == RC_ROT_MODEL) ? Rn[k * 3 + i] * Rt[k * 3 + j] : Rt[i * 3 + k] * Rn[j * 3 + k];
+      Rdel[i * 3 + j] = a;
+    }
+  double q[4];
+  mat2quat(Rdel, q);
+  double tdl[3];  // T_inv_transform, :113-132
+  if (pp.rot_coord == RC_ROT_CAMERA_NEW) {
+    tdl[0] = (Tt[0] - Tr[0]) / Tr[2];
+    tdl[1] = (Tt[1] - Tr[1]) / Tr[2];
+  } else {
+    tdl[0] = Tt[0] / Tt[2] - Tr[0] / Tr[2];
+    tdl[1] = Tt[1] / Tt[2] - Tr[1] / Tr[2];
+  }
+  tdl[2] = log(Tr[2] / Tt[2]);
+  for (int i = 0; i < 4; ++i) rot_res[b * 4 + i] = (float)q[i];
+  for (int i = 0; i < 3; ++i)
+    trans_res[b * 3 + i] = (float)((tdl[i] - (double)pp.means[i]) / (double)pp.stds[i]);
+}
+
 // Stand-in for the FlowNet heads in synthetic refine loops ("predicted (q, t) =
 // calc_RT_delta(src, tgt) damped by 0.5 + N(0, small)").  The CNN is out of scope; this keeps the
 // stand-in at one launch so that it does not weigh on the measured loop.
@@ -298,6 +339,25 @@ int rc_pose_update_dev(const float *src_pose, const float *rot_est, const float 
   rc::pose_update_kernel<<<(batch_size + 63) / 64, 64, 0, static_cast<cudaStream_t>(stream)>>>(
       src_pose, rot_est, trans_est, tgt_pose, K, pp, refined_pose, rot_res, trans_res, KT,
       batch_size);
+  return rc::note_status(rc::check_launch());
+}
+
+int rc_pose_delta_dev(const float *src_pose, const float *tgt_pose, const float *T_means,
+                      const float *T_stds, int rot_coord, float *rot_res, float *trans_res,
+                      int batch_size, void *stream) {
+  RC_REQUIRE(batch_size >= 0, RC_ERR_INVALID_ARG);
+  RC_REQUIRE(rot_coord == RC_ROT_MODEL || rot_coord == RC_ROT_CAMERA || rot_coord == RC_ROT_CAMERA_NEW,
+             RC_ERR_INVALID_ARG);
+  if (batch_size == 0) return rc::note_status(RC_OK);
+  RC_REQUIRE(src_pose && tgt_pose && rot_res && trans_res, RC_ERR_INVALID_ARG);
+  rc::PoseUpdateParams pp;
+  for (int i = 0; i < 3; ++i) {
+    pp.means[i] = T_means ? T_means[i] : 0.f;
+    pp.stds[i] = T_stds ? T_stds[i] : 1.f;
+  }
+  pp.rot_coord = rot_coord;
+  rc::pose_delta_kernel<<<(batch_size + 63) / 64, 64, 0, static_cast<cudaStream_t>(stream)>>>(
+      src_pose, tgt_pose, pp, rot_res, trans_res, batch_size);
   return rc::note_status(rc::check_launch());
 }
 

@@ -1158,7 +1158,7 @@ int rc_render_dev(void *handle, const rc_render_args *a) {
   O.mode = a->mode;
   auto mark = [&](int i) -> int {
     if (a->marks && a->marks[i])
-      RC_CUDA_TRY(cudaEventRecord(static_cast<cudaEvent_t>(a->marks[i]), s));
+      RC_CUDA_TRY(rc::record_mark(static_cast<cudaEvent_t>(a->marks[i]), s));
     return RC_OK;
   };
   int st;

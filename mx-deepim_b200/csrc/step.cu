@@ -21,7 +21,7 @@
 
 namespace rc {
 static inline int mark(void **marks, int i, cudaStream_t s) {
-  if (marks && marks[i]) RC_CUDA_TRY(cudaEventRecord(static_cast<cudaEvent_t>(marks[i]), s));
+  if (marks && marks[i]) RC_CUDA_TRY(record_mark(static_cast<cudaEvent_t>(marks[i]), s));
   return RC_OK;
 }
 }  // namespace rc
@@ -209,7 +209,7 @@ int rc_event_destroy(void *event) {
 
 int rc_event_record(void *event, void *stream) {
   RC_REQUIRE(event != nullptr, RC_ERR_INVALID_ARG);
-  RC_CUDA_TRY(cudaEventRecord(static_cast<cudaEvent_t>(event), static_cast<cudaStream_t>(stream)));
+  RC_CUDA_TRY(rc::record_mark(static_cast<cudaEvent_t>(event), static_cast<cudaStream_t>(stream)));
   return rc::note_status(RC_OK);
 }
 

@@ -367,6 +367,26 @@ def pose_update(src_pose, rot_est, trans_est, tgt_pose, K, T_means=(0, 0, 0), T_
     return out
 
 
+def pose_delta(src_pose, tgt_pose, T_means=(0, 0, 0), T_stds=(1, 1, 1), rot_coord="CAMERA",
+               out=None, stream=None):
+    """Batched calc_RT_delta(src, tgt, rot_type="QUAT") (RT_transform.py:16-48) on device: the
+    iteration-0 regression labels.  Returns (rot [B,4], trans [B,3])."""
+    C.check_tensor("src_pose", src_pose)
+    C.check_tensor("tgt_pose", tgt_pose)
+    B = src_pose.shape[0]
+    dev = src_pose.device
+    if out is None:
+        f = dict(dtype=torch.float32, device=dev)
+        out = (torch.empty((B, 4), **f), torch.empty((B, 3), **f))
+    with torch.cuda.device(dev):
+        st = _lib.load().rc_pose_delta_dev(
+            src_pose.data_ptr(), tgt_pose.data_ptr(), _lib.f3(T_means), _lib.f3(T_stds),
+            _lib.ROT_COORD[rot_coord.lower()], out[0].data_ptr(), out[1].data_ptr(), B,
+            _lib.stream_ptr(stream))
+    _lib.check(st, "rc_pose_delta_dev")
+    return out
+
+
 class RefineLoop(object):
     """On-device replacement of the refine loop's data path
     (/root/reference/deepim/core/module.py:1205-1213 calling
@@ -411,6 +431,26 @@ class RefineLoop(object):
         self.mask_rendered = torch.empty((B, 1, synth.H, synth.W), **f)
         self.rot_est = torch.empty((B, 4), **f)
         self.trans_est = torch.empty((B, 3), **f)
+        # the batch's observed side lives in PERSISTENT tensors (set_batch copies into them), so
+        # bound argument structs and captured graphs stay valid from batch to batch
+        Hh, Ww, N = synth.H, synth.W, num_points
+        self.obs = {"image_observed": torch.zeros((B, 3, Hh, Ww), **f),
+                    "depth_gt_observed": torch.zeros((B, 1, Hh, Ww), **f),
+                    "mask_observed": torch.zeros((B, 1, Hh, Ww), **f),
+                    "mask_gt_observed": torch.zeros((B, 1, Hh, Ww), **f),
+                    "tgt_pose": torch.zeros((B, 3, 4), **f),
+                    "point_cloud_model": torch.zeros((B, 3, N), **f),
+                    "point_cloud_weights": torch.zeros((B, 3, N), **f),
+                    "point_cloud_observed": torch.zeros((B, 3, N), **f),
+                    "Kinv": torch.zeros((3, 3), **f)}
+        self.cls = torch.zeros((B,), dtype=torch.int32, device=self.device)
+        self.pose0 = torch.zeros((B, 3, 4), **f)   # the batch's initial source poses
+        self.rot0 = torch.zeros((B, 4), **f)       # iteration-0 labels (calc_RT_delta(src, tgt))
+        self.trans0 = torch.zeros((B, 3), **f)
+        self.observed_box = torch.zeros((B, 4), dtype=torch.int32, device=self.device)
+        self._zf_scratch = torch.empty((B, 4), **f)
+        self._box8 = torch.empty((B, 8), dtype=torch.int32, device=self.device)
+        self._have_batch = False
         self.damping = float(damping)
         self.predict = predict if predict is not None else self._damped_gt
         g = torch.Generator(device="cpu").manual_seed(int(seed))
@@ -418,9 +458,19 @@ class RefineLoop(object):
         self.noise_t = (0.005 * torch.randn((8, B, 3), generator=g)).to(self.device)
         self.identity_q = torch.tensor([1.0, 0.0, 0.0, 0.0], **f)
         self.cur = 0
-        self.bound = [None, None]
-        self.obs = None
         self.graph = None
+        self._flow_tracks = False
+        self.bound = [None, None]
+        for par in (0, 1):
+            x = dict(self.obs)
+            # flow / zoom read the refined pose pose[par]; the loss (and its backward) belongs to
+            # the pass that produced rot_est / trans_est, i.e. to the pose BEFORE the update
+            # (deepIM_flownet.py:446-499 vs batch_updater_py_multi.py:211-312)
+            x.update(image_rendered=self.image_rendered, depth_rendered=self.depth_rendered,
+                     src_pose=self.pose[par], loss_src_pose=self.pose[1 - par], KT=self.KT,
+                     rot_est=self.rot_est, trans_est=self.trans_est, trans_gt=self.trans_gt)
+            self.bound[par] = self.step.bind(x)
+            self._bind_frame(self.bound[par])
         # stand-in + pose update + 8 render kernels (clear, vertex, setup, clip, scan, fill, cover,
         # resolve) + step
         self.launches_per_iteration = 1 + 1 + 8 + self.step.launches_per_step
@@ -438,44 +488,30 @@ class RefineLoop(object):
     def set_batch(self, host):
         """Observed side of the batch + initial poses.  `host`: numpy dict with image_observed,
         depth_gt_observed, mask_observed, mask_gt_observed, src_pose, tgt_pose, class_index,
-        point_cloud_model / weights / observed, Kinv."""
-        t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(self.device)
-        self.graph = None  # a captured loop holds raw pointers into the previous batch's tensors
-        self.obs = {k: t(host[k]) for k in ("image_observed", "depth_gt_observed", "mask_observed",
-                                            "mask_gt_observed", "tgt_pose", "point_cloud_model",
-                                            "point_cloud_weights", "point_cloud_observed", "Kinv")}
-        self.cls = t(np.asarray(host["class_index"], np.int32))
-        self.pose[0].copy_(t(host["src_pose"]))
-        self.cur = 0
-        from . import pose as P
+        point_cloud_model / weights / observed, Kinv (float32 blobs as the reference's loader
+        hands them over).  Copies into the loop's persistent tensors; captured graphs stay valid."""
+        t = lambda a: torch.from_numpy(np.ascontiguousarray(a))
+        for k in self.obs:
+            self.obs[k].copy_(t(host[k]))
+        self.cls.copy_(t(np.asarray(host["class_index"], np.int32)))
+        self.pose0.copy_(t(host["src_pose"]))
+        self.finish_batch()
 
-        q0 = np.zeros((self.B, 4), np.float32)
-        t0 = np.zeros((self.B, 3), np.float32)
-        for b in range(self.B):
-            q0[b], t0[b] = P.calc_RT_delta(host["src_pose"][b], host["tgt_pose"][b], np.zeros(3),
-                                           np.ones(3), "CAMERA")
-        self.rot_gt.copy_(t(q0))
-        self.trans_gt.copy_(t(t0))
-        self._pose0 = None
+    def finish_batch(self, stream=None):
+        """After the observed side, `cls` and `pose0` have been written (set_batch, or a host
+        feed's on-device decode): iteration-0 labels, the observed crop box, loop restart.
+        No synchronisation."""
+        # iteration-0 regression labels: calc_RT_delta(src, tgt) (the loader's job in the reference)
+        pose_delta(self.pose0, self.obs["tgt_pose"], out=(self.rot0, self.trans0), stream=stream)
         if self.sparse:
             # the observed box is a property of the batch: one dense pass now instead of one per
             # iteration (obs == rend == mask_gt_observed; entries 0..3 are the "> 0.3" box)
-            zf = torch.empty((self.B, 4), dtype=torch.float32, device=self.device)
-            box8 = torch.empty((self.B, 8), dtype=torch.int32, device=self.device)
-            C.zoom_factor(self.obs["mask_gt_observed"], self.obs["mask_gt_observed"], self.pose[0],
-                          self.K, None, zf, _lib.RC_ZF_MASK, bbox=box8)
-            self.observed_box = box8[:, :4].contiguous()
-        self._flow_tracks = False  # the flow planes do not hold a previous frame's flow yet
-        for par in (0, 1):
-            x = dict(self.obs)
-            # flow / zoom read the refined pose pose[par]; the loss (and its backward) belongs to
-            # the pass that produced rot_est / trans_est, i.e. to the pose BEFORE the update
-            # (deepIM_flownet.py:446-499 vs batch_updater_py_multi.py:211-312)
-            x.update(image_rendered=self.image_rendered, depth_rendered=self.depth_rendered,
-                     src_pose=self.pose[par], loss_src_pose=self.pose[1 - par], KT=self.KT,
-                     rot_est=self.rot_est, trans_est=self.trans_est, trans_gt=self.trans_gt)
-            self.bound[par] = self.step.bind(x)
-            self._bind_frame(self.bound[par])
+            C.zoom_factor(self.obs["mask_gt_observed"], self.obs["mask_gt_observed"], self.pose0,
+                          self.K, None, self._zf_scratch, _lib.RC_ZF_MASK, bbox=self._box8,
+                          stream=stream)
+            self.observed_box.copy_(self._box8[:, :4])
+        self._have_batch = True
+        self.set_batch_poses()
 
     def _bind_frame(self, a):
         if self.sparse:
@@ -485,15 +521,13 @@ class RefineLoop(object):
             a.outputs_track_frames = 0
 
     def set_batch_poses(self, host=None):
-        """Restart the loop from the batch's initial source poses (same observed side)."""
-        if getattr(self, "_pose0", None) is None:
-            t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(self.device)
-            self._pose0 = t(host["src_pose"])
-            self._rot0 = self.rot_gt.clone()
-            self._trans0 = self.trans_gt.clone()
-        self.pose[0].copy_(self._pose0)
-        self.rot_gt.copy_(self._rot0)
-        self.trans_gt.copy_(self._trans0)
+        """Restart the loop from the batch's initial source poses (same observed side).
+        `host` is accepted for compatibility and ignored: the poses are the ones set_batch got."""
+        if not self._have_batch:
+            raise RuntimeError("RefineLoop: set_batch() first")
+        self.pose[0].copy_(self.pose0)
+        self.rot_gt.copy_(self.rot0)
+        self.trans_gt.copy_(self.trans0)
         self.cur = 0
 
     def iterate(self, it, marks=None, render_marks=None):
@@ -519,9 +553,10 @@ class RefineLoop(object):
         self.step.run(None, args=a, marks=marks)
         self._flow_tracks = True  # one step per render: the flow planes follow the frames
 
-    def run(self, iterations=4):
+    def run(self, iterations=4, marks=None):
+        """`marks`: optional per-iteration lists of RC_STEP_MARKS events (see CompareStep.run)."""
         for it in range(iterations):
-            self.iterate(it)
+            self.iterate(it, marks=marks[it] if marks is not None else None)
 
     def check_status(self):
         """Synchronise and raise if any render of this loop overflowed the rasteriser's tile
@@ -529,7 +564,7 @@ class RefineLoop(object):
         the end of a loop / epoch, before trusting its outputs."""
         self.renderer.check_status()
 
-    def capture(self, host=None, iterations=4):
+    def capture(self, host=None, iterations=4, marks=None):
         """Capture one whole loop -- restart from the batch's initial poses, then `iterations`
         refinement iterations (stand-in, pose update, render, compare step: ~14 launches and 2
         memsets each) -- into a CUDA graph; `self.replay()` then costs one launch call from the
@@ -546,8 +581,6 @@ class RefineLoop(object):
         another frame's item list -- and re-captures instead of replaying stale state."""
         if iterations < 1:
             raise ValueError("capture() needs at least one iteration")
-        if host is None and getattr(self, "_pose0", None) is None:
-            raise ValueError("capture() needs the batch (set_batch_poses has not run yet)")
         self.set_batch_poses(host)
         self.run(iterations)  # warm-up; also establishes the incremental-background state
         torch.cuda.synchronize(self.device)
@@ -556,7 +589,9 @@ class RefineLoop(object):
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g):
                 self.set_batch_poses(host)
-                self.run(iterations)
+                # marks: event-record NODES inside the graph (rc::record_mark), re-recorded by
+                # every replay -- kernel timing inside a replayed loop
+                self.run(iterations, marks=marks)
             self.graphs.append(g)
             # capturing ran the HOST side of every render (the handle's ping-pong parity moved)
             # but not the kernels: execute the loop once so that device and host agree again
@@ -564,6 +599,7 @@ class RefineLoop(object):
         self._graph_turn = 0
         self.graph = self.graphs[0]
         self.graph_iterations = iterations
+        self._graph_marks = marks
         self._graph_serial = self.renderer.serial
         return self.graph
 
@@ -574,7 +610,7 @@ class RefineLoop(object):
             raise RuntimeError("RefineLoop.replay(): no captured loop (capture() first, and again "
                                "after set_batch)")
         if self.renderer.serial != self._graph_serial:
-            self.capture(None, self.graph_iterations)
+            self.capture(None, self.graph_iterations, marks=self._graph_marks)
         g = self.graphs[self._graph_turn % len(self.graphs)]
         self._graph_turn += 1
         g.replay()
@@ -633,10 +669,134 @@ class RefineLoop(object):
         return self._st
 
 
+LOOP_PACKED_KEYS = ("image_observed", "depth_gt_observed", "mask_gt_observed", "mask_observed")
+LOOP_SMALL_KEYS = ("src_pose", "tgt_pose", "class_index", "mask_idx", "point_cloud_model",
+                   "point_cloud_weights")
+
+
+def pack_refine_batch(host, depth_factor=1000.0, pixel_means_bgr=None, pin=True):
+    """A RefineLoop batch (float32 blobs, make_refine_batch / the reference's DataBatch) in the
+    dataset's STORAGE formats, as the files decode to before the reference's loaders touch them
+    (lib/utils/image.py:186-305): colour uint8 [B,H,W,3] BGR, depth 16-bit in 1/depth_factor m
+    (int16 view of the uint16 data), label image uint8 [B,H,W] + mask_idx, mask_observed uint8.
+    The point cloud is the sampled MODEL cloud only; the observed cloud (R_gt X + t_gt,
+    image.py:592-596) is computed on the device.  Returns CPU tensors (page-locked if `pin`)."""
+    means = np.asarray(synth.PIXEL_MEANS if pixel_means_bgr is None else pixel_means_bgr,
+                       np.float64).reshape(-1)
+    means_rgb = means[::-1].reshape(1, 3, 1, 1)
+    rgb = np.clip(np.rint(host["image_observed"].astype(np.float64) + means_rgb), 0, 255).astype(np.uint8)
+    out = {"image_observed": np.ascontiguousarray(rgb[:, ::-1].transpose(0, 2, 3, 1)),
+           "depth_gt_observed": np.ascontiguousarray(
+               np.rint(host["depth_gt_observed"][:, 0].astype(np.float64) * depth_factor)
+               .astype(np.uint16).view(np.int16)),
+           "mask_gt_observed": np.ascontiguousarray(host["mask_gt_observed"][:, 0].astype(np.uint8)),
+           "mask_observed": np.ascontiguousarray(host["mask_observed"][:, 0].astype(np.uint8)),
+           "mask_idx": np.ones((host["src_pose"].shape[0],), np.int32),
+           "src_pose": np.ascontiguousarray(host["src_pose"], np.float32),
+           "tgt_pose": np.ascontiguousarray(host["tgt_pose"], np.float32),
+           "class_index": np.ascontiguousarray(host["class_index"], np.int32),
+           "point_cloud_model": np.ascontiguousarray(host["point_cloud_model"], np.float32),
+           "point_cloud_weights": np.ascontiguousarray(host["point_cloud_weights"], np.float32)}
+    res = {}
+    for k, v in out.items():
+        t = torch.from_numpy(v)
+        res[k] = t.pin_memory() if pin else t
+    return res
+
+
+class LoopFeed(object):
+    """End-to-end driver of a RefineLoop from HOST batches in the dataset's storage formats
+    (pack_refine_batch): per batch
+
+        H2D (copy stream, page-locked source; overlaps the previous batch's loop)
+        -> on-device decode into the loop's persistent float32 blobs (prep.py: image.transform,
+           DEPTH_FACTOR, label == idx, R_gt X + t_gt) -> iteration-0 labels + observed crop box
+        -> `iterations` refinement iterations (one CUDA-graph replay)
+        -> D2H of the refined poses and the last iteration's point-matching loss sums.
+
+    The observed side is uploaded ONCE per loop and the rendered side never crosses PCIe (the
+    device renders it) -- the reference re-uploads every float32 blob each iteration
+    (batch_updater_py_multi.py:357-365, 12.4 MB per pair).  `depth` raw staging sets on the
+    device; results of submit() number n are in pose_out[n % depth] / loss_out[n % depth]
+    (page-locked) once done[n % depth] has completed."""
+
+    def __init__(self, loop, example, iterations=4, depth_factor=1000.0, pixel_means_bgr=None,
+                 depth=2, use_graph=True):
+        from . import prep
+
+        self.prep = prep
+        self.loop, self.iterations, self.depth = loop, int(iterations), int(depth)
+        self.depth_factor = float(depth_factor)
+        self.means_bgr = np.asarray(
+            synth.PIXEL_MEANS if pixel_means_bgr is None else pixel_means_bgr, np.float64).reshape(-1)
+        dev, B = loop.device, loop.B
+        for k in LOOP_PACKED_KEYS + LOOP_SMALL_KEYS:
+            if example[k].shape[0] != B:
+                raise ValueError("%s: batch %d, loop was built for %d" % (k, example[k].shape[0], B))
+        self.raw = [{k: torch.empty_like(example[k], device=dev)
+                     for k in LOOP_PACKED_KEYS + LOOP_SMALL_KEYS} for _ in range(self.depth)]
+        self.copy_stream = torch.cuda.Stream(device=dev)
+        self.uploaded = [torch.cuda.Event() for _ in range(self.depth)]
+        self.done = [torch.cuda.Event() for _ in range(self.depth)]
+        self.pose_out = torch.empty((self.depth, B, 3, 4), dtype=torch.float32).pin_memory()
+        self.loss_out = torch.empty((self.depth, B), dtype=torch.float32).pin_memory()
+        self.n = 0
+        self.use_graph = bool(use_graph)
+        self.h2d_bytes = int(sum(example[k].numel() * example[k].element_size()
+                                 for k in LOOP_PACKED_KEYS + LOOP_SMALL_KEYS))
+        self.d2h_bytes = int(B * 12 * 4 + B * 4)
+        self.decode_launches = 8  # image, depth, 2 masks, points, labels, observed box, box copy
+
+    def _decode(self, raw):
+        p, lp = self.prep, self.loop
+        o = lp.obs
+        p.transform_batch(raw["image_observed"], self.means_bgr, out=o["image_observed"])
+        p.decode_depth(raw["depth_gt_observed"], self.depth_factor, out=o["depth_gt_observed"])
+        p.decode_mask(raw["mask_gt_observed"], raw["mask_idx"], out=o["mask_gt_observed"])
+        p.decode_mask(raw["mask_observed"], raw["mask_idx"], out=o["mask_observed"])
+        o["tgt_pose"].copy_(raw["tgt_pose"], non_blocking=True)
+        o["point_cloud_model"].copy_(raw["point_cloud_model"], non_blocking=True)
+        o["point_cloud_weights"].copy_(raw["point_cloud_weights"], non_blocking=True)
+        p.get_point_cloud_observed(o["point_cloud_model"], o["tgt_pose"],
+                                   out=o["point_cloud_observed"])
+        lp.cls.copy_(raw["class_index"], non_blocking=True)
+        lp.pose0.copy_(raw["src_pose"], non_blocking=True)
+        lp.finish_batch()
+
+    def submit(self, host):
+        """Enqueue one batch (dict of page-locked CPU tensors from pack_refine_batch).  Returns
+        the slot index; no host synchronisation."""
+        i = self.n % self.depth
+        lp = self.loop
+        compute = torch.cuda.current_stream(lp.device)
+        raw = self.raw[i]
+        with torch.cuda.stream(self.copy_stream):
+            if self.n >= self.depth:  # the slot's previous batch has been decoded and consumed
+                self.copy_stream.wait_event(self.done[i])
+            for k in LOOP_PACKED_KEYS + LOOP_SMALL_KEYS:
+                raw[k].copy_(host[k], non_blocking=True)
+            self.uploaded[i].record(self.copy_stream)
+        compute.wait_event(self.uploaded[i])
+        self._decode(raw)
+        if self.use_graph:
+            if lp.graph is None or getattr(lp, "graph_iterations", None) != self.iterations:
+                lp.capture(None, self.iterations)  # first batch: runs the loop eagerly + captures
+            lp.replay()
+        else:
+            lp.run(self.iterations)
+        self.pose_out[i].copy_(lp.pose[lp.cur], non_blocking=True)
+        self.loss_out[i].copy_(lp.step.loss_sum, non_blocking=True)
+        self.done[i].record(compute)
+        self.n += 1
+        return i
+
+
 def make_refine_batch(meshes, batch, seed, K=synth.K_LINEMOD, num_points=synth.NUM_3D_SAMPLE,
-                      renderer=None, occlusion=False):
+                      renderer=None, occlusion=False, render_fn=None):
     """Synthetic observed side for RefineLoop: target renders come from `renderer`
-    (a DeviceRenderer; the product's own rasteriser) so that no oracle is involved."""
+    (a DeviceRenderer; the product's own rasteriser) so that no oracle is involved.
+    `render_fn(cls [B] int32, tgt [B,3,4], pixel_means) -> (depth [B,1,H,W], image [B,3,H,W])`
+    replaces the renderer where there is no GPU (the CPU arm of bench.py passes its own)."""
     rng = np.random.default_rng(seed)
     B = batch
     cls = rng.integers(0, len(meshes), size=B).astype(np.int32)
@@ -649,13 +809,25 @@ def make_refine_batch(meshes, batch, seed, K=synth.K_LINEMOD, num_points=synth.N
         src[b], tgt[b] = synth.random_pose_pair(rng, K)
         pts[b], wts[b] = synth.mesh_points(meshes[cls[b]], rng, num_points)
         obs[b] = tgt[b, :, :3].astype(np.float64) @ pts[b].astype(np.float64) + tgt[b, :, 3:].astype(np.float64)
-    dev = renderer.device
     pm = synth.PIXEL_MEANS[[2, 1, 0]]
-    out = renderer.render_batch(torch.from_numpy(cls).to(dev), torch.from_numpy(tgt).to(dev),
-                                pixel_means=pm, want=("depth", "image"))
-    torch.cuda.synchronize(dev)
-    depth = out["depth"].cpu().numpy()
-    image = out["image"].cpu().numpy()
+    if render_fn is not None:
+        depth, image = render_fn(cls, tgt, pm)
+        depth = np.ascontiguousarray(depth, np.float32)
+        image = np.ascontiguousarray(image, np.float32)
+    else:
+        dev = renderer.device
+        depth = np.empty((B, 1, synth.H, synth.W), np.float32)
+        image = np.empty((B, 3, synth.H, synth.W), np.float32)
+        chunk = max(1, min(B, renderer.max_batch))
+        for lo in range(0, B, chunk):
+            hi = min(B, lo + chunk)
+            out = renderer.render_batch(torch.from_numpy(cls[lo:hi]).to(dev),
+                                        torch.from_numpy(tgt[lo:hi]).to(dev),
+                                        pixel_means=pm, want=("depth", "image"))
+            torch.cuda.synchronize(dev)
+            renderer.check_status()
+            depth[lo:hi] = out["depth"].cpu().numpy()
+            image[lo:hi] = out["image"].cpu().numpy()
     depth = (np.round(depth.astype(np.float64) * 1000.0) / 1000.0).astype(np.float32)  # 1 mm PNG
     # mask_gt_observed is the object's LABEL mask (label == cls_idx, lib/dataset/LM6D_REFINE.py),
     # so a nearer occluder removes pixels from it but never adds any; depth_gt_observed is the

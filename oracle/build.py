@@ -44,14 +44,15 @@ def build_oracle(force=False):
 def build_ref(force=False):
     """Compile the reference's own CUDA flow kernel for sm_100a (no source is copied)."""
     src = os.path.join(REFERENCE_FLOW_DIR, "gpu_flow_kernel.cu")
+    shim = os.path.join(HERE, "ref_flow_shim.cu")  # #includes `src` in place + a device-pointer launch
     if not os.path.exists(src):
         return REF_LIB if os.path.exists(REF_LIB) else None
-    if not force and os.path.exists(REF_LIB):
+    if not force and _newer(REF_LIB, [shim, src]):
         return REF_LIB
     nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
     os.makedirs(REF_DIR, exist_ok=True)
-    cmd = [nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-Xcompiler", "-fPIC",
-           "-shared", "-I", REFERENCE_FLOW_DIR, "-o", REF_LIB, src]
+    cmd = [nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-Xcompiler",
+           "-fPIC", "-shared", "-I", REFERENCE_FLOW_DIR, "-o", REF_LIB, shim]
     subprocess.check_call(cmd)
     return REF_LIB
 

@@ -132,3 +132,19 @@ def reference_kernel_gpu(depth_src, depth_tgt, KT, Kinv, device_id=0):
     _ref(flow.ctypes.data, valid.ctypes.data, depth_src.ctypes.data, depth_tgt.ctypes.data,
          KT.ctypes.data, Kinv.ctypes.data, B, H, W, int(device_id))
     return flow, valid
+
+
+def reference_kernel_dev(depth_src, depth_tgt, KT, Kinv, flow, valid, stream=0):
+    """Launch the reference's unmodified `flow_kernel` (gpu_flow_kernel.cu:32-69, its own launch
+    configuration :129-130) on DEVICE buffers -- arguments are raw device addresses (ints) of
+    float32 arrays [B,1,H,W] x2, [B,3,4], [3,3], [B,2,H,W], [B,1,H,W] given as (ptr, shape) by the
+    caller: kernel-only baseline G0.  No synchronisation."""
+    lib = ctypes.CDLL(_build.REF_LIB)
+    fn = lib.ref_flow_kernel_dev
+    fn.restype = ctypes.c_int
+    fn.argtypes = [ctypes.c_void_p] * 6 + [ctypes.c_int] * 3 + [ctypes.c_void_p]
+    (ps, shape) = depth_src
+    B, _, H, W = shape
+    rc = fn(ps, depth_tgt, KT, Kinv, flow, valid, B, H, W, stream)
+    if rc != 0:
+        raise RuntimeError("ref_flow_kernel_dev: CUDA error %d" % rc)

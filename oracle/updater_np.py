@@ -57,7 +57,7 @@ def pose_update(src_pose, rot_est, trans_est, tgt_pose, K, T_means, T_stds, rot_
 
 def updater_forward(meshes, class_index, src_pose, tgt_pose, rot_est, trans_est, depth_gt_observed,
                     K, pixel_means_bgr_order, T_means, T_stds, rot_coord="CAMERA", zNear=0.25,
-                    zFar=6.0):
+                    zFar=6.0, flow_threads=0):
     """The update_package of batch_updater_py_multi.py:322-356 (LINEMOD branch)."""
     B = src_pose.shape[0]
     H, W = depth_gt_observed.shape[2:]
@@ -76,7 +76,8 @@ def updater_forward(meshes, class_index, src_pose, tgt_pose, rot_est, trans_est,
     mask[depth > 0.2] = 1
     Kinv = np.array(np.linalg.inv(np.asarray(K, np.float64)))
     flow, valid = flow_np.flow_kernel_cpu(depth.astype(np.float32), depth_gt_observed.astype(np.float32),
-                                          KT.astype(np.float32), Kinv.astype(np.float32))
+                                          KT.astype(np.float32), Kinv.astype(np.float32),
+                                          num_threads=flow_threads)
     return {"image_rendered": image.astype(np.float32), "depth_rendered": depth.astype(np.float32),
             "src_pose": refined.astype(np.float32), "rot": rot_res.astype(np.float32),
             "trans": trans_res.astype(np.float32), "flow": flow,

@@ -26,7 +26,16 @@ def test_reference_arm_json_line():
     assert d["value"] > 0 and d["gpu_launches"] == 0
     assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] >= 1
     assert d["e2e"]["value"] == d["value"] and d["e2e"]["h2d_bytes_per_step"] == 0
-    assert d["config"]["workload"].startswith("cfg2")
+    # default workload = the full refine loop the metric is quoted on (BASELINE.json configs[4])
+    assert d["config"]["workload"].startswith("cfg5")
+    assert "rasteriser" in d["cpu_baseline"]["sample"]
+
+
+def test_reference_arm_cfg2():
+    p = _run("--impl", "reference", "--config", "2", "--steps", "1", "--warmup", "1")
+    assert p.returncode == 0, p.stderr[-2000:]
+    d = json.loads([l for l in p.stdout.splitlines() if l.startswith("{")][0])
+    assert d["config"]["workload"].startswith("cfg2") and d["value"] > 0
 
 
 def test_reference_arm_other_ranks_exit_quietly():

@@ -177,11 +177,23 @@ def test_refine_loop_replay_is_safe(cuda_device, iters):
         loop.replay()
         same(eager, snap(), "replay-after-foreign-render-2")
     loop.check_status()
-    # a new batch drops the captured graphs (they hold raw pointers into the old one)
-    loop.set_batch(host)
-    assert loop.graph is None
-    with pytest.raises(RuntimeError):
+    # a NEW batch: set_batch copies into the loop's persistent tensors, so the captured graphs
+    # (raw pointers) stay valid and replay the new batch
+    host2 = pipeline.make_refine_batch(meshes, B, 654, renderer=loop.renderer)
+    loop.set_batch(host2)
+    loop.run(iters)
+    eager2 = snap()
+    assert not torch.equal(eager2["pose"], eager["pose"])
+    with torch.cuda.stream(s):
         loop.replay()
+        same(eager2, snap(), "replay-new-batch")
+        loop.replay()
+        same(eager2, snap(), "replay-new-batch-2")
+    fresh = pipeline.RefineLoop(meshes, B, cuda_device, seed=9)
+    with pytest.raises(RuntimeError):
+        fresh.replay()
+    with pytest.raises(RuntimeError):
+        fresh.set_batch_poses()
 
 
 def test_sparse_frame_step_equals_dense_step(cuda_device):
