@@ -220,6 +220,34 @@ def bilinear_sampler(data, gx, gy):
     return (((t1 + t2) + t3) + t4).astype(f32)
 
 
+def sample_affine_f64(data, wx, wy, tx, ty):
+    """The SAME formulas as grid_generator_affine + bilinear_sampler, every operation in float64:
+    the semantic twin of the float32 restatement (which has to follow MXNet's float32 rounding).
+    tests/test_oracle_cpu.py pins it to torch.nn.functional.grid_sample(align_corners=True,
+    padding_mode="zeros") in float64 to 1e-9, i.e. the SEMANTICS (normalised grid, pixel mapping,
+    floor / weight / zero-tap rules) are pinned independently of the float32 arithmetic."""
+    data = np.asarray(data, dtype=f64)
+    C, H, W = data.shape
+    xn = np.arange(W, dtype=f64) * (2.0 / (W - 1)) - 1.0
+    yn = np.arange(H, dtype=f64) * (2.0 / (H - 1)) - 1.0
+    gx = np.broadcast_to((f64(wx) * xn + f64(tx))[None, :], (H, W))
+    gy = np.broadcast_to((f64(wy) * yn + f64(ty))[:, None], (H, W))
+    x_real = (gx + 1.0) * (W - 1) / 2.0
+    y_real = (gy + 1.0) * (H - 1) / 2.0
+    x0f, y0f = np.floor(x_real), np.floor(y_real)
+    x0, y0 = x0f.astype(np.int64), y0f.astype(np.int64)
+    wyt = 1.0 - (y_real - y0f)
+    wxl = 1.0 - (x_real - x0f)
+
+    def tap(yy, xx):
+        ok = (xx >= 0) & (xx <= W - 1) & (yy >= 0) & (yy <= H - 1)
+        v = data[:, np.clip(yy, 0, H - 1), np.clip(xx, 0, W - 1)]
+        return np.where(ok[None], v, 0.0)
+
+    return (tap(y0, x0) * wyt * wxl + tap(y0, x0 + 1) * wyt * (1.0 - wxl) +
+            tap(y0 + 1, x0) * (1.0 - wyt) * wxl + tap(y0 + 1, x0 + 1) * (1.0 - wyt) * (1.0 - wxl))
+
+
 def inverse_affine(zf, height, width):
     """zoom_flow.py:35-44 / zoom_mask_with_factor.py:43-52 (float64 scalars, numpy 1.x)."""
     if PROMOTION == "nep50":

@@ -230,3 +230,54 @@ def test_zoom_other_frame_sizes(cuda_device, height, width):
                 image_rendered=img_r, height=height, width=width, pixel_means=pm.flatten())
     out = [o.cpu().numpy() for o in h.outputs]
     assert np.abs(out[0] - ref_o).max() <= TOL and np.abs(out[1] - ref_r).max() <= TOL
+
+
+# ---------------------------------------------------------------- independent sampler pin
+PIN_CASES = [(0.32, 0.32, 0.05, -0.1), (0.11, 0.11, -0.4, 0.3), (1.7, 1.7, 0.3, -0.2),
+             (0.4, 0.4, 0.85, -0.9), (0.999, 0.999, 0.0, 0.0), (0.25, 0.25, 0.2, 0.1)]
+
+
+@pytest.mark.parametrize("inverse", [False, True])
+def test_zoom_sample_kernel_vs_torch_grid_sample(cuda_device, inverse):
+    """rc_zoom_sample_dev against an INDEPENDENT implementation of the same operator pair:
+    torch.nn.functional.affine_grid + grid_sample (align_corners=True, zeros padding) on the
+    GPU, in float64 (the semantics pinned in tests/test_oracle_cpu.py) -- a checker only, never a
+    product dependency.  Bars = the float32 coordinate-rounding bounds measured for the float32
+    restatement (tests/test_oracle_cpu.py, x2 margin): the kernel must be as close to the exact
+    operator as MXNet's own float32 arithmetic is.  Smooth field and image-range noise; zoom-in,
+    zoom-out, off-image windows, inverse zoom (zoom_flow.py:35-44).  And against the float32
+    restatement itself at the north_star bar (1e-4 abs)."""
+    import torch
+    import torch.nn.functional as F
+
+    from mx_deepim_b200.operator_py import _common as C
+
+    B = len(PIN_CASES)
+    rng = np.random.default_rng(321)
+    smooth = np.fromfunction(lambda b, c, y, x: np.sin(x / 37.0) + np.cos(y / 23.0) + c + 0 * b,
+                             (B, 2, 480, 640)).astype(np.float32)
+    noise = rng.uniform(-255, 255, size=(B, 2, 480, 640)).astype(np.float32)
+    zf = np.array(PIN_CASES, np.float32)
+    zf_d = _t(zf, cuda_device)
+    if inverse:
+        aff = np.array([[float(v) for v in zoom_np.inverse_affine(z, 480, 640)] for z in zf], np.float64)
+    else:
+        aff = zf.astype(np.float64)
+    theta = torch.tensor([[[a[0], 0.0, a[2]], [0.0, a[1], a[3]]] for a in aff], dtype=torch.float64,
+                         device=cuda_device)
+    for name, data, bar in (("smooth", smooth, 4.2e-4), ("noise", noise, 0.13)):
+        src = _t(data, cuda_device)
+        dst = torch.empty_like(src)
+        C.zoom_sample(zf_d, [C.Group(src, dst)], 480, 640, inverse=inverse)
+        torch.cuda.synchronize()
+        grid = F.affine_grid(theta, [B, 2, 480, 640], align_corners=True)
+        ref = F.grid_sample(src.double(), grid, mode="bilinear", padding_mode="zeros",
+                            align_corners=True)
+        err = (dst.double() - ref).abs().amax(dim=(1, 2, 3)).cpu().numpy()
+        assert err.max() <= bar, (name, inverse, err)
+        if name == "smooth" and not inverse:
+            assert err[[0, 1, 5]].max() <= 4e-6, err  # zoom-in inside the image: the production case
+        # and the float32 restatement (MXNet's arithmetic) at the north_star bar
+        mine = zoom_np.sample_batch(data, zf, inverse=inverse)
+        d = np.abs(dst.cpu().numpy() - mine)
+        assert d.max() <= (1e-4 if name == "noise" else 2e-6), (name, inverse, d.max())
