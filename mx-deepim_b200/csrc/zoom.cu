@@ -22,6 +22,7 @@
 // window is smaller than the output tile, so the taps are L1/L2 hits) and
 // issues one 128-bit store.  Write traffic dominates: 52 B/px out of 60.
 #include <limits.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 
@@ -254,6 +255,7 @@ struct ZoomPlane {
   int accumulate;
   int channel;  // channel index inside its group (for the centre spot)
   float mean;
+  int dup_second;  // version 2: same source and operations as the previous plane (computed once)
 };
 
 struct ZoomParams {
@@ -272,6 +274,13 @@ struct ZoomParams {
   uint8_t *tile_state;        // [B][gridDim.y * gridDim.x][4 warps]
   unsigned sparse_mask;
   int src_tiles_x, src_tiles, state_valid;
+  // zoom_sample2_kernel: runs of consecutive planes with the same pre / post operation, no
+  // accumulation and the same sparse flag (<= 3 planes each); dup: the run is ONE computed plane
+  // whose result also goes to the next plane's destination (RC_ZOOM_SRC_BROADCAST pairs)
+  struct Bundle {
+    uint8_t first, n, dup, pad_;
+  } bundles[RC_ZOOM_MAX_PLANES];
+  int n_bundles;
 };
 
 // Affine parameters of one sample: (wx, wy, tx, ty) as float32, forward or
@@ -753,6 +762,504 @@ zoom_sample_kernel(const __grid_constant__ ZoomParams P, int smem_floats) {
   }
 }
 
+// ===================================================================== resampler, version 2
+//
+// zoom_sample2_kernel: the same operator pair, organised so that the instruction stream per
+// output value is a handful of instructions instead of ~29 (ncu of version 1: 5.8e7 warp
+// instructions for 6.4e7 outputs, SM-issue bound at 73 %, DRAM at 50 %).
+//
+//  * ONE WARP owns a 32-column x 16-row output tile; the four warps of a block share the staged
+//    source window (one barrier pair per stage) and nothing else.
+//  * The blend is separable and is evaluated in two phases that use two DIFFERENT lane
+//    mappings, exchanged through a 4 KB per-warp shared-memory tile:
+//      A (lane = output column): for every source row the tile touches (16 wy + 2 of them when
+//        zooming in) the horizontal blend h = l * wl + r * wr of that row at this column.  The
+//        taps come from the block's source window, staged in shared memory by 16-byte cp.async
+//        exactly as in version 1 (as many planes per stage as fit; out-of-image chunks are
+//        zero-filled by the copy itself), so a tap is an LDS with a 32-bit address and an
+//        immediate offset.  (Measured alternative, dropped: taps straight from global memory
+//        through the read-only path -- 64-bit address arithmetic per load tripled phase A's
+//        instruction count and the loads' latency was exposed: 107 us instead of 70.)  The
+//        planes' pre-operation is applied to the taps;
+//      B (lane = 4 adjacent columns x one of 4 rows): out = ht * wt + hb * wb for FOUR columns at
+//        once: two 128-bit shared loads, the sm_100 packed-fp32 pipe (fma.rn.f32x2: same IEEE
+//        results as four scalar operations, half the issue slots), the plane's post-operation,
+//        one 128-bit store.  A warp-wide store instruction writes four 128-byte row segments.
+//  * Everything that depends on the tile only (row coordinates, weights, addresses) is computed
+//    once per tile and reused by all 13 planes; planes are processed in runs of up to three with
+//    the same pre / post operation (template instantiations: no per-value switches).
+//  * Same sampling coordinates, weights, tap selection and blend association as version 1
+//    ((l*wl + r*wr) per source row, then ht*wt + hb*wb), i.e. bit-identical outputs for float
+//    planes; rounded 0/1 planes after RC_PRE_THRESH02 use the comparison v >= 0.5 (identical to
+//    roundf for v in [0, 1.5)).
+//  * Tiles that are not zoom-in shaped (the 16 rows touch more source rows than the exchange tile
+//    holds) are split into 8- or 4-row chunks; beyond that (|scale| > ~3) and for degenerate
+//    factors every thread gathers its own four outputs.
+constexpr int Z2_TR = 16;     // output rows per warp tile
+constexpr int Z2_WARPS = 4;   // warps per block: the block covers 128 x 16 outputs
+constexpr int Z2_SLOTS = 16;  // rows of 32 floats in a warp's exchange tile (2 KB)
+
+__device__ __forceinline__ unsigned long long pack2(float lo, float hi) {
+  unsigned long long r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpack2(unsigned long long v, float &lo, float &hi) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ unsigned long long mul2(unsigned long long a, unsigned long long b) {
+  unsigned long long r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ unsigned long long fma2(unsigned long long a, unsigned long long b,
+                                                   unsigned long long c) {
+  unsigned long long r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+__device__ __forceinline__ unsigned long long add2(unsigned long long a, unsigned long long b) {
+  unsigned long long r;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+// Shared loads that the compiler may SCHEDULE (hoist above independent stores, interleave the
+// passes): not volatile -- a volatile asm keeps its order relative to every other volatile asm,
+// which would serialise "load, wait, compute, store" pass after pass.  Ordering against the
+// writers of the shared tile comes from `tok`: an otherwise unused operand that is re-defined by
+// an opaque statement after every barrier (z2_fence), so a load can move neither above the
+// barrier that publishes its data nor below the stores that consume it.
+__device__ __forceinline__ float4 lds_f4_t(uint32_t addr, int tok) {
+  float4 v;
+  asm("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4]; // %5"
+      : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+      : "r"(addr), "r"(tok));
+  return v;
+}
+__device__ __forceinline__ float lds_f1_t(uint32_t addr, int tok) {
+  float v;
+  asm("ld.shared.f32 %0, [%1]; // %2" : "=f"(v) : "r"(addr), "r"(tok));
+  return v;
+}
+__device__ __forceinline__ void z2_fence(int &tok) { asm volatile("" : "+r"(tok)::"memory"); }
+__device__ __forceinline__ void sts_f1(uint32_t addr, float v) {
+  asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+}
+__device__ __forceinline__ float ldg_nc(const float *p) {
+  float v;
+  asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(v) : "l"(p));
+  return v;
+}
+
+// Phase A of ONE plane: window rows 0 .. wh-1 of the staged plane (this lane's left tap of row 0
+// at shared address `a`, rows `pitch` bytes apart) -> exchange rows 0 .. wh-1 (`st` = this lane's
+// slot in exchange row 0).  EDGE: the window reaches outside the image, where the staged taps are
+// zero and must stay zero under an additive pre-operation (the sampler zero-pads the
+// PRE-PROCESSED image); okl / okr / y_lo / H describe which taps those are.
+template <int PRE, bool EDGE>
+__device__ __forceinline__ void z2_phase_a(uint32_t a, uint32_t pitch, uint32_t st, float wl, float wr,
+                                           float mean, int wh, bool okl, bool okr, int y_lo, int H,
+                                           int tok) {
+#pragma unroll 4
+  for (int r = 0; r < wh; ++r) {
+    float tl = lds_f1_t(a, tok);
+    float tr = lds_f1_t(a + 4u, tok);
+    if (PRE == RC_PRE_THRESH02) {
+      tl = tl > 0.2f ? 1.f : 0.f;
+      tr = tr > 0.2f ? 1.f : 0.f;
+    } else if (PRE == RC_PRE_ADD_MEAN) {
+      if (EDGE) {
+        const int ys = y_lo + r;
+        const bool rok = (ys >= 0 && ys <= H - 1);
+        tl = (rok && okl) ? __fadd_rn(tl, mean) : 0.f;
+        tr = (rok && okr) ? __fadd_rn(tr, mean) : 0.f;
+      } else {
+        tl = __fadd_rn(tl, mean);
+        tr = __fadd_rn(tr, mean);
+      }
+    }
+    sts_f1(st, __fmaf_rn(tr, wr, __fmul_rn(tl, wl)));
+    a += pitch;
+    st += 128u;
+  }
+}
+
+// Post-operation on four adjacent outputs (columns i .. i+3 of row j) of one plane.
+template <int POST>
+__device__ __forceinline__ void z2_post(float (&o)[4], float mean, int channel, const ZoomParams &P,
+                                        float wx_in, float rwx, bool wx_ok, int i, int j,
+                                        bool binary01) {
+  if (POST == RC_POST_ROUND) {
+    if (binary01) {  // taps are exactly 0 / 1: 0 <= v < 1.5, roundf(v) == (v >= 0.5)
+#pragma unroll
+      for (int k = 0; k < 4; ++k) o[k] = o[k] >= 0.5f ? 1.f : 0.f;
+    } else {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) o[k] = round_away(o[k]);
+    }
+  } else if (POST == RC_POST_ROUND_M045) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) o[k] = round_away(__fsub_rn(o[k], 0.45f));
+  } else if (POST == RC_POST_DIV_WX) {
+    if (wx_ok) {
+      // Markstein: q = a * rb, two FMA refinements -> the correctly rounded quotient whenever
+      // nothing over/underflows; a non-finite or overflowing case surfaces as NaN / a huge value
+      // and is redone with the IEEE division.  Packed: 5 instructions per pair.
+      const unsigned long long b2 = pack2(-wx_in, -wx_in), r2 = pack2(rwx, rwx);
+      const unsigned long long a01 = pack2(o[0], o[1]), a23 = pack2(o[2], o[3]);
+      unsigned long long q01 = mul2(a01, r2), q23 = mul2(a23, r2);
+      unsigned long long e01 = fma2(b2, q01, a01), e23 = fma2(b2, q23, a23);
+      q01 = fma2(e01, r2, q01);
+      q23 = fma2(e23, r2, q23);
+      e01 = fma2(b2, q01, a01);
+      e23 = fma2(b2, q23, a23);
+      q01 = fma2(e01, r2, q01);
+      q23 = fma2(e23, r2, q23);
+      float q[4];
+      unpack2(q01, q[0], q[1]);
+      unpack2(q23, q[2], q[3]);
+      const float chk = fmaxf(fmaxf(fabsf(q[0]), fabsf(q[1])), fmaxf(fabsf(q[2]), fabsf(q[3])));
+      const float sum = __fadd_rn(__fadd_rn(q[0], q[1]), __fadd_rn(q[2], q[3]));
+      if (!(chk <= 1e30f) || sum != sum) {  // rare: redo exactly
+#pragma unroll
+        for (int k = 0; k < 4; ++k) q[k] = __fdiv_rn(o[k], wx_in);
+      }
+#pragma unroll
+      for (int k = 0; k < 4; ++k) o[k] = q[k];
+    } else {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) o[k] = __fdiv_rn(o[k], wx_in);
+    }
+  } else if (POST == RC_POST_MUL_WX) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) o[k] = __fmul_rn(o[k], wx_in);
+  } else if (POST == RC_POST_SUB_MEAN) {
+    const unsigned long long m2 = pack2(-mean, -mean);  // v - m == v + (-m), same rounding
+    unpack2(add2(pack2(o[0], o[1]), m2), o[0], o[1]);
+    unpack2(add2(pack2(o[2], o[3]), m2), o[2], o[3]);
+  } else if (POST == RC_POST_SPOT_SUB_MEAN) {
+    const bool yin = (channel == 0) && (j >= P.spot_y0) && (j < P.spot_y1);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float spot = (yin && (i + k) >= P.spot_x0 && (i + k) < P.spot_x1) ? 255.f : 0.f;
+      o[k] = __fsub_rn(fmaxf(o[k], spot), mean);
+    }
+  }
+}
+
+// Phase B of ONE plane: the four passes (rows j0 + 4 ps + q) of this thread's four columns.
+//   ba[ps]   shared address of this thread's quad in the exchange row of pass ps's UPPER source
+//            row (the lower one is the next exchange row)
+//   FULL     the tile lies inside the image: no per-row / per-column store predicates
+//   DUP      the result also goes to dst2 (RC_ZOOM_SRC_BROADCAST pairs)
+template <int POST, int WC, bool FULL, bool DUP>
+__device__ __forceinline__ void z2_phase_b(const ZoomParams &P, const uint32_t (&ba)[4],
+                                           const float (&wt)[4], const float (&wb)[4], float *dst,
+                                           float *dst2, float mean, int channel, bool binary01,
+                                           int b, bool col_ok, int tok) {
+  const int W = WC ? WC : P.W;
+  float wx_in = 1.f, rwx = 1.f;
+  bool wx_ok = false;
+  if (POST == RC_POST_DIV_WX || POST == RC_POST_MUL_WX) {
+    // the sample's own factor (zoom_flow.py:62-66); reloaded here (two of thirteen planes) rather
+    // than carried in registers through the plane loop
+    wx_in = __ldg(P.zoom_factor + b * 4);
+    rwx = __frcp_rn(wx_in);
+    const float awx = fabsf(wx_in);
+    wx_ok = (awx > 1e-15f) && (awx < 1e15f) && ((__float_as_uint(wx_in) & 0x7fffffu) != 0x7fffffu);
+  }
+  // output coordinates of this thread's quad (needed by the centre spot and the edge predicates)
+  const int lane = threadIdx.x & 31;
+  const int i = blockIdx.x * (Z2_WARPS * 32) + (threadIdx.x & ~31) + 4 * (lane & 7);
+  const int jq = blockIdx.y * Z2_TR + (lane >> 3);
+#pragma unroll
+  for (int ps = 0; ps < 4; ++ps) {
+    const int j = jq + 4 * ps;
+    const unsigned long long wt2 = pack2(wt[ps], wt[ps]), wb2 = pack2(wb[ps], wb[ps]);
+    const float4 ht = lds_f4_t(ba[ps], tok);
+    const float4 hb = lds_f4_t(ba[ps] + 128u, tok);
+    float o[4];
+    unpack2(fma2(pack2(hb.x, hb.y), wb2, mul2(pack2(ht.x, ht.y), wt2)), o[0], o[1]);
+    unpack2(fma2(pack2(hb.z, hb.w), wb2, mul2(pack2(ht.z, ht.w), wt2)), o[2], o[3]);
+    z2_post<POST>(o, mean, channel, P, wx_in, rwx, wx_ok, i, j, binary01);
+    if (FULL || (col_ok && j < P.H)) {
+      const float4 v = make_float4(o[0], o[1], o[2], o[3]);
+      st_f4(reinterpret_cast<float4 *>(dst + 4 * ps * W), v);
+      if (DUP) st_f4(reinterpret_cast<float4 *>(dst2 + 4 * ps * W), v);
+    }
+  }
+}
+
+// Fallback for tiles that are not zoom-in shaped (the 16 rows touch more source rows than the
+// exchange tile holds: scale > ~0.9, inverse zooms), unaligned sources and degenerate factors:
+// every thread gathers its own outputs tap by tap, any pre / post operation.  Kept out of line:
+// it must not cost the fast path registers.
+__device__ __noinline__ void z2_gather_tile(const ZoomParams &P, int first, bool dup, int b, int i,
+                                            int j0, int q) {
+  const int H = P.H, W = P.W;
+  float wx, wy, tx, ty, wx_in;
+  zoom_affine(P.zoom_factor + b * 4, P.inverse, H, W, wx, wy, tx, ty, wx_in);
+  const float stepx = (float)(2.0 / (W - 1)), stepy = (float)(2.0 / (H - 1));
+  const float nxm1 = (float)(W - 1), nym1 = (float)(H - 1);
+  const float rwx = __frcp_rn(wx_in);
+  if (i >= W) return;
+  const ZoomPlane &zp = P.planes[first];
+  const float *src = zp.src + (long long)b * zp.src_bstride;
+  for (int ps = 0; ps < 4; ++ps) {
+    const int j = j0 + 4 * ps + q;
+    if (j >= H) continue;
+    const RowCoord rc = row_coord(j, stepy, wy, ty, nym1);
+    const int y0 = rc.y0;
+    const bool yin0 = (y0 >= 0) && (y0 <= H - 1), yin1 = (y0 + 1 >= 0) && (y0 + 1 <= H - 1);
+    float o[4];
+    for (int k = 0; k < 4; ++k) {
+      const float xr = src_coord(i + k, stepx, wx, tx, nxm1);
+      const float xf = floorf(xr);
+      const int x0 = (fabsf(xf) < 1e8f) ? (int)xf : -(1 << 30);
+      const float wl = __fsub_rn(1.0f, __fsub_rn(xr, xf)), wr = __fsub_rn(1.0f, wl);
+      const bool xin0 = (x0 >= 0) && (x0 <= W - 1), xin1 = (x0 + 1 >= 0) && (x0 + 1 <= W - 1);
+      const float *r0 = src + (long long)y0 * W + x0;
+      const float tl = (yin0 && xin0) ? pre(ldg_nc(r0), zp.pre_op, zp.mean) : 0.f;
+      const float tr = (yin0 && xin1) ? pre(ldg_nc(r0 + 1), zp.pre_op, zp.mean) : 0.f;
+      const float bl = (yin1 && xin0) ? pre(ldg_nc(r0 + W), zp.pre_op, zp.mean) : 0.f;
+      const float br = (yin1 && xin1) ? pre(ldg_nc(r0 + W + 1), zp.pre_op, zp.mean) : 0.f;
+      const float ht = __fmaf_rn(tr, wr, __fmul_rn(tl, wl));
+      const float hb = __fmaf_rn(br, wr, __fmul_rn(bl, wl));
+      o[k] = __fmaf_rn(hb, rc.wb, __fmul_rn(ht, rc.wt));
+    }
+    switch (zp.post_op) {
+      case RC_POST_ROUND: z2_post<RC_POST_ROUND>(o, zp.mean, zp.channel, P, wx_in, rwx, false, i, j, false); break;
+      case RC_POST_ROUND_M045: z2_post<RC_POST_ROUND_M045>(o, zp.mean, zp.channel, P, wx_in, rwx, false, i, j, false); break;
+      case RC_POST_DIV_WX: z2_post<RC_POST_DIV_WX>(o, zp.mean, zp.channel, P, wx_in, rwx, false, i, j, false); break;
+      case RC_POST_MUL_WX: z2_post<RC_POST_MUL_WX>(o, zp.mean, zp.channel, P, wx_in, rwx, false, i, j, false); break;
+      case RC_POST_SUB_MEAN: z2_post<RC_POST_SUB_MEAN>(o, zp.mean, zp.channel, P, wx_in, rwx, false, i, j, false); break;
+      case RC_POST_SPOT_SUB_MEAN: z2_post<RC_POST_SPOT_SUB_MEAN>(o, zp.mean, zp.channel, P, wx_in, rwx, false, i, j, false); break;
+      default: break;
+    }
+    const float4 v = make_float4(o[0], o[1], o[2], o[3]);
+    const long long off = (long long)j * W + i;
+    st_f4(reinterpret_cast<float4 *>(zp.dst + (long long)b * zp.dst_bstride + off), v);
+    if (dup) {
+      const ZoomPlane &z2 = P.planes[first + 1];
+      st_f4(reinterpret_cast<float4 *>(z2.dst + (long long)b * z2.dst_bstride + off), v);
+    }
+  }
+}
+
+// grid = (ceil(W/128), ceil(H/16), B); block = 128 (4 warps); 8 KB static exchange tiles +
+// `smem_floats` * 4 bytes of dynamic staging.
+template <int WC>
+__global__ void __launch_bounds__(Z2_WARPS * 32, 7)
+zoom_sample2_kernel(const __grid_constant__ ZoomParams P, int smem_floats) {
+  extern __shared__ float4 win4[];
+  __shared__ __align__(16) float xch[Z2_WARPS][Z2_SLOTS][32];
+  const int H = P.H, W = WC ? WC : P.W;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int b = blockIdx.z;
+  const int ib = blockIdx.x * (Z2_WARPS * 32);  // first column of the block
+  const int i0 = ib + warp * 32, j0c = blockIdx.y * Z2_TR;
+  const bool warp_in = i0 < W;  // a warp right of the image only helps staging and meets barriers
+
+  // ---- state carried through the plane loop (kept small on purpose: a spilled value costs a
+  // local-memory round trip per plane on the critical path)
+  uint32_t tap;          // shared address of this lane's left tap in window row 0 of staged plane 0
+  uint32_t pitch;        // bytes between window rows
+  uint32_t st_lane;      // this lane's slot in row 0 of the warp's exchange tile (phase A)
+  float wl, wr;          // phase A column weights
+  uint32_t ba[4];        // phase B: exchange address of the upper source row, per pass
+  float rwt[4], rwb[4];  // phase B: row weights, per pass
+  int y_first, wh_all, x_a;
+  bool edge, okl, okr, staged;
+  {
+    float wx, wy, tx, ty, wx_in;
+    zoom_affine(P.zoom_factor + b * 4, P.inverse, H, W, wx, wy, tx, ty, wx_in);
+    const float stepx = (float)(2.0 / (W - 1)), stepy = (float)(2.0 / (H - 1));
+    const float nxm1 = (float)(W - 1), nym1 = (float)(H - 1);
+    // phase A: this lane's column
+    const float xr = src_coord(min(i0 + lane, W - 1), stepx, wx, tx, nxm1);
+    const float xf = floorf(xr);
+    const int x0 = (fabsf(xf) < 1e6f) ? (int)xf : -(1 << 20);
+    wl = __fsub_rn(1.0f, __fsub_rn(xr, xf));
+    wr = __fsub_rn(1.0f, wl);
+    okl = (x0 >= 0) && (x0 <= W - 1);
+    okr = (x0 + 1 >= 0) && (x0 + 1 <= W - 1);
+    // the block's source window (block-uniform): columns of outputs ib .. ib+127, rows of the tile
+    const float fx_lo = floorf(src_coord(ib, stepx, wx, tx, nxm1));
+    const float fx_hi = floorf(src_coord(min(ib + Z2_WARPS * 32, W) - 1, stepx, wx, tx, nxm1));
+    const float fy_lo = floorf(src_coord(j0c, stepy, wy, ty, nym1));
+    const float fy_hi = floorf(src_coord(min(j0c + Z2_TR, H) - 1, stepy, wy, ty, nym1));
+    const bool regular = (wx > 0.f) && (wy > 0.f) && (fy_hi >= fy_lo) && (fx_hi >= fx_lo) &&
+                         (fabsf(fy_lo) < 1e6f) && (fabsf(fy_hi) < 1e6f) && (fabsf(fx_lo) < 1e6f) &&
+                         (fabsf(fx_hi) < 1e6f) && (fy_hi - fy_lo + 2.0f <= (float)Z2_SLOTS) &&
+                         P.src_aligned;
+    y_first = regular ? (int)fy_lo : 0;
+    wh_all = regular ? (int)(fy_hi - fy_lo) + 2 : 2;
+    x_a = regular ? ((int)fx_lo & ~3) : 0;  // floor to a multiple of 4 (also for negative values)
+    const int nch = regular ? ((((int)fx_hi + 1 - x_a) >> 2) + 1) : 1;
+    pitch = 16u * (uint32_t)nch;
+    // every decision below that involves a barrier must be block-uniform: the window and the zoom
+    // factor are, but make it explicit -- vote
+    const bool reg_all = __syncthreads_and(regular ? 1 : 0) != 0;
+    staged = reg_all && nch * 4 * wh_all <= smem_floats;
+    // any tap of the WARP's tile outside the image?
+    const bool edge_ = !okl || !okr || y_first < 0 || y_first + wh_all > H;
+    edge = __any_sync(0xffffffffu, edge_);
+    const uint32_t hbase = (uint32_t)__cvta_generic_to_shared(&xch[warp][0][0]);
+    st_lane = hbase + 4u * (uint32_t)lane;
+    tap = (uint32_t)__cvta_generic_to_shared(win4) + 4u * (uint32_t)(x0 - x_a);
+    // phase B: this lane's rows (one per pass); exchange addresses are valid for staged tiles,
+    // where the row's upper source row lies in [y_first, y_first + wh_all - 2]
+#pragma unroll
+    for (int ps = 0; ps < 4; ++ps) {
+      const RowCoord rc = row_coord(min(j0c + 4 * ps + (lane >> 3), H - 1), stepy, wy, ty, nym1);
+      ba[ps] = hbase + 128u * (uint32_t)(rc.y0 - y_first) + 16u * (uint32_t)(lane & 7);
+      rwt[ps] = rc.wt;
+      rwb[ps] = rc.wb;
+    }
+  }
+  const int i_tile = i0 + 4 * (lane & 7);
+  // W % 4 == 0: a quad is inside or outside as a whole; with the compile-time width a multiple of
+  // the block's 128 columns every warp and quad is inside
+  const bool col_ok = (WC && WC % (Z2_WARPS * 32) == 0) ? true : (warp_in && i_tile < W);
+  // warp-uniform "no store predicates needed" (the vote is executed by every lane: no short-circuit)
+  const bool all_cols = __all_sync(0xffffffffu, col_ok);
+  const bool full = all_cols && (j0c + Z2_TR <= H);
+
+  // sparse frame, per warp tile (see version 1): skip the sparse planes where the source window
+  // touches no covered tile and the outputs already hold the background
+  unsigned wskip = 0u;
+  const bool warp_in_u = __any_sync(0xffffffffu, warp_in);
+  if (P.tile_state != nullptr && warp_in_u) {
+    uint8_t *st = P.tile_state +
+                  (((size_t)b * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) * Z2_WARPS + warp;
+    // (votes make the values provably warp-uniform, so the skip mask can live in a uniform register)
+    const bool held = __any_sync(0xffffffffu, *st != 0);
+    const int x0 = x_a + (int)((tap - (uint32_t)__cvta_generic_to_shared(win4)) >> 2);
+    const int xw0 = __shfl_sync(0xffffffffu, x0, 0), xw1 = __shfl_sync(0xffffffffu, x0, 31) + 1;
+    int any = 1;
+    if (staged && !P.inverse) {
+      const int sx0 = max(xw0, 0), sx1 = min(xw1, W - 1);
+      const int sy0 = max(y_first, 0), sy1 = min(y_first + wh_all - 1, H - 1);
+      any = 0;
+      if (sx1 >= sx0 && sy1 >= sy0) {
+        const int tx0 = sx0 >> 4, ntx = (sx1 >> 4) - tx0 + 1, ty0 = sy0 >> 4,
+                  nty = (sy1 >> 4) - ty0 + 1;
+        if (ntx * nty > 32) any = 1;
+        else if (lane < ntx * nty)
+          any = __ldg(P.tile_count + (size_t)b * P.src_tiles + (ty0 + lane / ntx) * P.src_tiles_x +
+                      tx0 + lane % ntx) > 0 ? 1 : 0;
+      }
+    }
+    const bool bg_now = !__any_sync(0xffffffffu, any);
+    __syncwarp();
+    if (lane == 0) *st = bg_now ? 1 : 0;
+    if (bg_now && P.state_valid && held) wskip = P.sparse_mask;
+  }
+  if (!warp_in_u) wskip = 0xffffffffu;
+
+  if (!staged) {
+    // not zoom-in shaped / degenerate / unaligned: every thread gathers its own outputs
+    if (warp_in)
+      for (int pl = 0; pl < P.n_planes; ++pl) {
+        if (P.planes[pl].dup_second) continue;
+        const bool dup = pl + 1 < P.n_planes && P.planes[pl + 1].dup_second;
+        z2_gather_tile(P, pl, dup, b, i_tile, j0c, lane >> 3);
+      }
+    return;
+  }
+  int p0 = 0, p1 = 0;  // planes [p0, p1) are staged; slot = plane - p0
+  int tok = 0;         // ordering token of the schedulable shared loads (lds_f*_t)
+  for (int pl = 0; pl < P.n_planes; ++pl) {
+    const ZoomPlane &zp = P.planes[pl];
+    if (zp.dup_second) continue;  // written together with the plane before it
+    const uint32_t plane_bytes = pitch * (uint32_t)wh_all;
+    if (pl >= p1) {  // block-uniform: stage the next planes
+      if (p1 > 0) __syncthreads();  // every consumer of the previous stage is done
+      p0 = pl;
+      p1 = min(P.n_planes, p0 + smem_floats / (int)(plane_bytes >> 2));
+      const int nch = (int)(pitch >> 4);
+      const int nchunks = nch * wh_all;
+      const float inv_nch = __frcp_rn((float)nch);
+      const uint32_t win_s = (uint32_t)__cvta_generic_to_shared(win4);
+      for (int qq = threadIdx.x; qq < nchunks; qq += Z2_WARPS * 32) {
+        int r = __float2int_rz(__fmul_rn((float)qq + 0.5f, inv_nch));
+        int c = qq - r * nch;
+        if (c < 0) {
+          c += nch;
+          --r;
+        } else if (c >= nch) {
+          c -= nch;
+          ++r;
+        }
+        const int ys = y_first + r, xs = x_a + 4 * c;
+        const bool inb = (xs >= 0) && (xs + 3 <= W - 1) && (ys >= 0) && (ys <= H - 1);
+        const int goff = inb ? ys * W + xs : 0;
+        const int bytes = inb ? 16 : 0;
+        uint32_t sa = win_s + 16u * (uint32_t)qq;
+        for (int k = p0; k < p1; ++k, sa += plane_bytes) {
+          const ZoomPlane &zk = P.planes[k];
+          if (zk.dup_second) continue;
+          cp_async_16(sa, zk.src + (long long)b * zk.src_bstride + goff, bytes);
+        }
+      }
+      cp_async_wait_all();
+      __syncthreads();
+      z2_fence(tok);
+    }
+    if ((wskip >> pl) & 1u) continue;  // warp-uniform
+    // shared address of this lane's first tap of the plane
+    uint32_t a_pl = tap + (uint32_t)(pl - p0) * plane_bytes;
+    // The phase bodies below are separate template instantiations inlined into this loop; the
+    // tile constants are made opaque once per iteration so that the compiler does not hoist
+    // every instantiation's derived values (packed weight pairs, addresses) out of the loop.
+    asm volatile("" : "+r"(st_lane), "+r"(a_pl));
+#pragma unroll
+    for (int ps = 0; ps < 4; ++ps) asm volatile("" : "+r"(ba[ps]), "+f"(rwt[ps]), "+f"(rwb[ps]));
+    const int pre_op = zp.pre_op, post_op = zp.post_op;
+    const float mean = zp.mean;
+    if (pre_op == RC_PRE_ADD_MEAN) {
+      if (edge) z2_phase_a<RC_PRE_ADD_MEAN, true>(a_pl, pitch, st_lane, wl, wr, mean, wh_all, okl, okr, y_first, H, tok);
+      else z2_phase_a<RC_PRE_ADD_MEAN, false>(a_pl, pitch, st_lane, wl, wr, mean, wh_all, okl, okr, y_first, H, tok);
+    } else if (pre_op == RC_PRE_THRESH02) {
+      z2_phase_a<RC_PRE_THRESH02, false>(a_pl, pitch, st_lane, wl, wr, mean, wh_all, okl, okr, y_first, H, tok);
+    } else {
+      z2_phase_a<RC_PRE_NONE, false>(a_pl, pitch, st_lane, wl, wr, mean, wh_all, okl, okr, y_first, H, tok);
+    }
+    __syncwarp();
+    z2_fence(tok);
+    // row of pass 0, this thread's columns (recomputed per plane: cheaper than a register held
+    // across the loop)
+    const int tile_off = (blockIdx.y * Z2_TR + ((threadIdx.x & 31) >> 3)) * W +
+                         blockIdx.x * (Z2_WARPS * 32) + (threadIdx.x & ~31) + 4 * (threadIdx.x & 7);
+    float *dst = zp.dst + (long long)b * zp.dst_bstride + tile_off;
+    const bool dup = pl + 1 < P.n_planes && P.planes[pl + 1].dup_second;
+    float *dst2 = dup ? P.planes[pl + 1].dst + (long long)b * P.planes[pl + 1].dst_bstride + tile_off
+                      : nullptr;
+    const bool bin = pre_op == RC_PRE_THRESH02;
+#define Z2_B2(POST_, FULL_, DUP_) \
+  z2_phase_b<POST_, WC, FULL_, DUP_>(P, ba, rwt, rwb, dst, dst2, mean, zp.channel, bin, b, col_ok, tok)
+#define Z2_B(POST_)                           \
+  do {                                        \
+    if (dup) Z2_B2(POST_, false, true);       \
+    else if (full) Z2_B2(POST_, true, false); \
+    else Z2_B2(POST_, false, false);          \
+  } while (0)
+    switch (post_op) {
+      case RC_POST_ROUND: Z2_B(RC_POST_ROUND); break;
+      case RC_POST_ROUND_M045: Z2_B(RC_POST_ROUND_M045); break;
+      case RC_POST_DIV_WX: Z2_B(RC_POST_DIV_WX); break;
+      case RC_POST_MUL_WX: Z2_B(RC_POST_MUL_WX); break;
+      case RC_POST_SUB_MEAN: Z2_B(RC_POST_SUB_MEAN); break;
+      case RC_POST_SPOT_SUB_MEAN: Z2_B(RC_POST_SPOT_SUB_MEAN); break;
+      default: Z2_B(RC_POST_NONE); break;
+    }
+#undef Z2_B
+#undef Z2_B2
+    __syncwarp();  // the exchange tile is rewritten by the next plane
+    z2_fence(tok);
+  }
+}
+
 // ------------------------------------------------------------- ZoomTrans
 // zoom_trans.py:30-44 (forward) and :57-73 (backward); float32 scalar ops.
 __global__ void zoom_trans_kernel(const float *__restrict__ zf, const float *__restrict__ in,
@@ -906,6 +1413,7 @@ int launch_zoom_sample(const float *zoom_factor, int inverse, const rc_zoom_grou
   RC_REQUIRE(width % 4 == 0, RC_ERR_UNALIGNED);
   rc::ZoomParams P;
   P.n_planes = 0;
+  P.n_bundles = 0;
   P.sparse_mask = 0u;
   const long long plane = (long long)height * width;
   for (int g = 0; g < n_groups; ++g) {
@@ -929,6 +1437,7 @@ int launch_zoom_sample(const float *zoom_factor, int inverse, const rc_zoom_grou
         P.sparse_mask |= 1u << (P.n_planes - 1);
       z.channel = c;
       z.mean = G.mean[c];
+      z.dup_second = 0;
     }
   }
   P.src_aligned = 1;
@@ -967,8 +1476,88 @@ int launch_zoom_sample(const float *zoom_factor, int inverse, const rc_zoom_grou
                                      kSmemFloats * (int)sizeof(float)));
     attr_set = true;
   }
-  dim3 grid((width + rc::ZT_W - 1) / rc::ZT_W, (height + rc::ZT_H - 1) / rc::ZT_H, batch_size);
   RC_REQUIRE(batch_size <= 65535, RC_ERR_INVALID_ARG);
+  // ---- version 2 (zoom_sample2_kernel) whenever every plane is a plain write of one of the
+  // operation pairs it is instantiated for; RC_ZOOM_V1=1 forces version 1 (A/B measurements)
+  {
+    static int force_v1 = -1;
+    if (force_v1 < 0) {
+      const char *e = getenv("RC_ZOOM_V1");
+      force_v1 = (e && e[0] == '1') ? 1 : 0;
+    }
+    bool v2 = !force_v1;
+    for (int pl = 0; pl < P.n_planes && v2; ++pl) {
+      const rc::ZoomPlane &z = P.planes[pl];
+      if (z.accumulate) v2 = false;
+      const bool ok_pair =
+          (z.pre_op == RC_PRE_ADD_MEAN &&
+           (z.post_op == RC_POST_SUB_MEAN || z.post_op == RC_POST_SPOT_SUB_MEAN)) ||
+          (z.pre_op == RC_PRE_THRESH02 && z.post_op == RC_POST_ROUND) ||
+          (z.pre_op == RC_PRE_NONE &&
+           (z.post_op == RC_POST_NONE || z.post_op == RC_POST_ROUND || z.post_op == RC_POST_ROUND_M045 ||
+            z.post_op == RC_POST_DIV_WX || z.post_op == RC_POST_MUL_WX));
+      if (!ok_pair) v2 = false;
+      // phase B writes 128-bit quads: destination planes 16-byte aligned (checked above per group)
+    }
+    if (v2) {
+      P.n_bundles = 0;
+      int pl = 0;
+      while (pl < P.n_planes) {
+        rc::ZoomParams::Bundle &bd = P.bundles[P.n_bundles++];
+        bd.first = (uint8_t)pl;
+        bd.n = 1;
+        bd.dup = 0;
+        bd.pad_ = 0;
+        const rc::ZoomPlane &z0 = P.planes[pl];
+        const unsigned sp0 = (P.sparse_mask >> pl) & 1u;
+        // a broadcast pair: the next plane resamples the SAME source with the same operations
+        if (pl + 1 < P.n_planes) {
+          rc::ZoomPlane &z1 = P.planes[pl + 1];
+          if (z1.src == z0.src && z1.src_bstride == z0.src_bstride && z1.pre_op == z0.pre_op &&
+              z1.post_op == z0.post_op && z1.mean == z0.mean &&
+              z0.post_op != RC_POST_SPOT_SUB_MEAN && ((P.sparse_mask >> (pl + 1)) & 1u) == sp0) {
+            bd.dup = 1;
+            z1.dup_second = 1;
+            pl += 2;
+            continue;
+          }
+        }
+        int n = 1;
+        while (n < 3 && pl + n < P.n_planes) {
+          const rc::ZoomPlane &z1 = P.planes[pl + n];
+          if (z1.pre_op != z0.pre_op || z1.post_op != z0.post_op ||
+              ((P.sparse_mask >> (pl + n)) & 1u) != sp0 || z1.src == P.planes[pl + n - 1].src)
+            break;
+          ++n;
+        }
+        bd.n = (uint8_t)n;
+        pl += n;
+      }
+      // staging: 22 KB per block (all 13 planes of the default step in one stage up to zoom
+      // factors ~0.37: window (128 wx + 8) x (16 wy + 3) floats per plane) + 8 KB exchange tiles:
+      // seven blocks per SM
+      constexpr int kStageFloats = 5632;
+      static bool attr2_set = false;
+      if (!attr2_set) {
+        RC_CUDA_TRY(cudaFuncSetAttribute(rc::zoom_sample2_kernel<640>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         kStageFloats * (int)sizeof(float)));
+        RC_CUDA_TRY(cudaFuncSetAttribute(rc::zoom_sample2_kernel<0>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         kStageFloats * (int)sizeof(float)));
+        attr2_set = true;
+      }
+      dim3 grid2((width + 127) / 128, (height + rc::Z2_TR - 1) / rc::Z2_TR, batch_size);
+      if (width == 640)
+        rc::zoom_sample2_kernel<640><<<grid2, rc::Z2_WARPS * 32, kStageFloats * sizeof(float),
+                                       static_cast<cudaStream_t>(stream)>>>(P, kStageFloats);
+      else
+        rc::zoom_sample2_kernel<0><<<grid2, rc::Z2_WARPS * 32, kStageFloats * sizeof(float),
+                                     static_cast<cudaStream_t>(stream)>>>(P, kStageFloats);
+      return rc::note_status(rc::check_launch());
+    }
+  }
+  dim3 grid((width + rc::ZT_W - 1) / rc::ZT_W, (height + rc::ZT_H - 1) / rc::ZT_H, batch_size);
   if (width == 640)
     rc::zoom_sample_kernel<640><<<grid, rc::ZT_THREADS, kSmemFloats * sizeof(float),
                                   static_cast<cudaStream_t>(stream)>>>(P, kSmemFloats);

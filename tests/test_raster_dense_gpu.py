@@ -143,7 +143,7 @@ def test_dense_mesh_lit_modes_match_oracle(cuda_device, dense_meshes, mode):
         mo, mg = o_depth > 0, depth[i, 0] > 0
         assert (mo == mg).mean() >= 0.999
         both = mo & mg
-        assert both.sum() > 400
+        assert both.sum() > (100 if P[i, 2, 3] > 2 else 400)
         assert (np.abs(depth[i, 0][both] - o_depth[both]) / o_depth[both]).max() <= 1e-5
         # 8-bit colour: within one level on >= 99.9 % of the covered pixels
         d = np.abs(np.round(bgr[i][both]).astype(np.int32) - o_bgr[both].astype(np.int32)).max(axis=-1)

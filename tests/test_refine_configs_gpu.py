@@ -109,8 +109,12 @@ def test_refine_loop_at_baseline_shape(cuda_device, cfg):
         np.testing.assert_allclose(_take(loop.step.loss_sum, idx), sums, rtol=1e-4)
         if sh["backward"]:
             g_rot, g_tr = transform3d_np.pm_loss_backward(*args, 1.0 / synth.NUM_3D_SAMPLE)
-            np.testing.assert_allclose(_take(loop.step.grad_rot, idx), g_rot, rtol=5e-4, atol=1e-6)
-            np.testing.assert_allclose(_take(loop.step.grad_trans, idx), g_tr, rtol=5e-4, atol=1e-6)
+            # L1 loss: d|x|/dx = sign(x) flips for a point whose residual is within float32 rounding
+            # of zero, which moves a gradient component by 2 w / (N norm) of that point: absolute
+            # slack of 1e-3 of the row's largest component on top of the relative bar
+            for got, want in ((_take(loop.step.grad_rot, idx), g_rot), (_take(loop.step.grad_trans, idx), g_tr)):
+                slack = 1e-3 * np.abs(want).max(axis=1, keepdims=True) + 1e-6
+                assert (np.abs(got - want) <= 5e-4 * np.abs(want) + slack).all(), (cfg, it)
     loop.check_status()
     # the poses converged towards the targets under the damped-GT stand-in
     err0 = np.abs(host["src_pose"] - host["tgt_pose"]).max(axis=(1, 2))
