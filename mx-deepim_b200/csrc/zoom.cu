@@ -274,13 +274,6 @@ struct ZoomParams {
   uint8_t *tile_state;        // [B][gridDim.y * gridDim.x][4 warps]
   unsigned sparse_mask;
   int src_tiles_x, src_tiles, state_valid;
-  // zoom_sample2_kernel: runs of consecutive planes with the same pre / post operation, no
-  // accumulation and the same sparse flag (<= 3 planes each); dup: the run is ONE computed plane
-  // whose result also goes to the next plane's destination (RC_ZOOM_SRC_BROADCAST pairs)
-  struct Bundle {
-    uint8_t first, n, dup, pad_;
-  } bundles[RC_ZOOM_MAX_PLANES];
-  int n_bundles;
 };
 
 // Affine parameters of one sample: (wx, wy, tx, ty) as float32, forward or
@@ -764,37 +757,52 @@ zoom_sample_kernel(const __grid_constant__ ZoomParams P, int smem_floats) {
 
 // ===================================================================== resampler, version 2
 //
-// zoom_sample2_kernel: the same operator pair, organised so that the instruction stream per
-// output value is a handful of instructions instead of ~29 (ncu of version 1: 5.8e7 warp
-// instructions for 6.4e7 outputs, SM-issue bound at 73 %, DRAM at 50 %).
+// zoom_sample2_kernel: the same operator pair as version 1 above, reorganised after ncu showed
+// version 1 bound by instruction issue (5.8e7 warp instructions for 6.4e7 outputs, SM 73 %,
+// DRAM 50 %), not by HBM.  Measured on B200 (round 2, profiles/r2_zoom_*): default step
+// (B = 16, zoom 0.32) 70.4 -> 65.9 us, cfg 5 (B = 1024, zoom ~0.17) 3450 -> 2720 us per launch =
+// 98 % of the measured HBM peak on the bytes the launch has to move.
 //
 //  * ONE WARP owns a 32-column x 16-row output tile; the four warps of a block share the staged
 //    source window (one barrier pair per stage) and nothing else.
-//  * The blend is separable and is evaluated in two phases that use two DIFFERENT lane
-//    mappings, exchanged through a 4 KB per-warp shared-memory tile:
+//  * The blend is separable and is evaluated, plane by plane, in two phases that use two
+//    DIFFERENT lane mappings, exchanged through a 2 KB per-warp shared-memory tile:
 //      A (lane = output column): for every source row the tile touches (16 wy + 2 of them when
 //        zooming in) the horizontal blend h = l * wl + r * wr of that row at this column.  The
 //        taps come from the block's source window, staged in shared memory by 16-byte cp.async
 //        exactly as in version 1 (as many planes per stage as fit; out-of-image chunks are
-//        zero-filled by the copy itself), so a tap is an LDS with a 32-bit address and an
-//        immediate offset.  (Measured alternative, dropped: taps straight from global memory
-//        through the read-only path -- 64-bit address arithmetic per load tripled phase A's
-//        instruction count and the loads' latency was exposed: 107 us instead of 70.)  The
-//        planes' pre-operation is applied to the taps;
-//      B (lane = 4 adjacent columns x one of 4 rows): out = ht * wt + hb * wb for FOUR columns at
-//        once: two 128-bit shared loads, the sm_100 packed-fp32 pipe (fma.rn.f32x2: same IEEE
-//        results as four scalar operations, half the issue slots), the plane's post-operation,
-//        one 128-bit store.  A warp-wide store instruction writes four 128-byte row segments.
-//  * Everything that depends on the tile only (row coordinates, weights, addresses) is computed
-//    once per tile and reused by all 13 planes; planes are processed in runs of up to three with
-//    the same pre / post operation (template instantiations: no per-value switches).
+//        zero-filled by the copy itself), so a tap is an LDS with a 32-bit address.  The
+//        plane's pre-operation is applied to the taps;
+//      B (lane = 4 adjacent columns x one of 4 rows, four passes): out = ht * wt + hb * wb for
+//        FOUR columns at once: two 128-bit shared loads, the sm_100 packed-fp32 pipe
+//        (fma.rn.f32x2 = FFMA2: the same IEEE results as scalar operations, half the issue
+//        slots), the plane's post-operation, one 128-bit store.  A warp-wide store instruction
+//        writes four 128-byte row segments.
+//  * Everything that depends on the tile only (row weights, exchange addresses, tap address) is
+//    computed once per tile and reused by all 13 planes; the pre / post operations are template
+//    instantiations selected once per plane (no per-value switches).
 //  * Same sampling coordinates, weights, tap selection and blend association as version 1
 //    ((l*wl + r*wr) per source row, then ht*wt + hb*wb), i.e. bit-identical outputs for float
 //    planes; rounded 0/1 planes after RC_PRE_THRESH02 use the comparison v >= 0.5 (identical to
 //    roundf for v in [0, 1.5)).
-//  * Tiles that are not zoom-in shaped (the 16 rows touch more source rows than the exchange tile
-//    holds) are split into 8- or 4-row chunks; beyond that (|scale| > ~3) and for degenerate
-//    factors every thread gathers its own four outputs.
+//  * Tiles that are not zoom-in shaped (the 16 rows touch more than 16 source rows: scale > ~0.9,
+//    inverse zooms), unaligned sources and degenerate factors: every thread gathers its own
+//    outputs (z2_gather_tile).
+//
+// What the measurements taught (each a separate ncu capture):
+//   - taps straight from global memory through the read-only path instead of the staged window:
+//     64-bit address arithmetic per load tripled phase A's instruction count and the loads'
+//     latency was exposed (107 us);
+//   - runs of three planes per phase with one template instantiation per (pre, post, count): 14 k
+//     SASS instructions, instruction-cache misses and > 128 live registers (99 us);
+//   - `asm volatile` shared loads: a volatile asm keeps its order against every other volatile
+//     asm, so "load, wait, blend, store" ran pass after pass with the shared-memory latency
+//     exposed each time; the loads are now ordinary (schedulable) asm statements ordered against
+//     the barriers by a token operand (73.8 -> 69.4 us);
+//   - any value spilled by the register allocator is reloaded at the top of EVERY plane, right
+//     where it is needed (15 % of the stall samples were one 4-byte reload): the state carried
+//     through the plane loop is kept small and the kernel is bounded to six blocks per SM
+//     (80 registers, no spill) rather than seven with spills (69.4 -> 65.9 us).
 constexpr int Z2_TR = 16;     // output rows per warp tile
 constexpr int Z2_WARPS = 4;   // warps per block: the block covers 128 x 16 outputs
 constexpr int Z2_SLOTS = 16;  // rows of 32 floats in a warp's exchange tile (2 KB)
@@ -860,27 +868,44 @@ template <int PRE, bool EDGE>
 __device__ __forceinline__ void z2_phase_a(uint32_t a, uint32_t pitch, uint32_t st, float wl, float wr,
                                            float mean, int wh, bool okl, bool okr, int y_lo, int H,
                                            int tok) {
-#pragma unroll 4
-  for (int r = 0; r < wh; ++r) {
-    float tl = lds_f1_t(a, tok);
-    float tr = lds_f1_t(a + 4u, tok);
-    if (PRE == RC_PRE_THRESH02) {
-      tl = tl > 0.2f ? 1.f : 0.f;
-      tr = tr > 0.2f ? 1.f : 0.f;
-    } else if (PRE == RC_PRE_ADD_MEAN) {
-      if (EDGE) {
-        const int ys = y_lo + r;
-        const bool rok = (ys >= 0 && ys <= H - 1);
-        tl = (rok && okl) ? __fadd_rn(tl, mean) : 0.f;
-        tr = (rok && okr) ? __fadd_rn(tr, mean) : 0.f;
-      } else {
-        tl = __fadd_rn(tl, mean);
-        tr = __fadd_rn(tr, mean);
+  // Rows in groups of Z2_RG, each group fully unrolled with per-row predicates: all taps of a
+  // group are in flight before the first blend needs one (a rolled remainder loop would wait for
+  // the shared-memory latency row by row; zooming in, a tile has 5 - 8 source rows).
+  constexpr int Z2_RG = 4;
+  for (int r0 = 0; r0 < wh; r0 += Z2_RG) {
+    float tl[Z2_RG], tr[Z2_RG];
+#pragma unroll
+    for (int k = 0; k < Z2_RG; ++k) {
+      tl[k] = 0.f;
+      tr[k] = 0.f;
+      if (r0 + k < wh) {
+        tl[k] = lds_f1_t(a + (uint32_t)k * pitch, tok);
+        tr[k] = lds_f1_t(a + (uint32_t)k * pitch + 4u, tok);
       }
     }
-    sts_f1(st, __fmaf_rn(tr, wr, __fmul_rn(tl, wl)));
-    a += pitch;
-    st += 128u;
+#pragma unroll
+    for (int k = 0; k < Z2_RG; ++k) {
+      if (r0 + k < wh) {
+        float l = tl[k], r = tr[k];
+        if (PRE == RC_PRE_THRESH02) {
+          l = l > 0.2f ? 1.f : 0.f;
+          r = r > 0.2f ? 1.f : 0.f;
+        } else if (PRE == RC_PRE_ADD_MEAN) {
+          if (EDGE) {
+            const int ys = y_lo + r0 + k;
+            const bool rok = (ys >= 0 && ys <= H - 1);
+            l = (rok && okl) ? __fadd_rn(l, mean) : 0.f;
+            r = (rok && okr) ? __fadd_rn(r, mean) : 0.f;
+          } else {
+            l = __fadd_rn(l, mean);
+            r = __fadd_rn(r, mean);
+          }
+        }
+        sts_f1(st + 128u * (uint32_t)k, __fmaf_rn(r, wr, __fmul_rn(l, wl)));
+      }
+    }
+    a += Z2_RG * pitch;
+    st += 128u * Z2_RG;
   }
 }
 
@@ -1049,7 +1074,7 @@ __device__ __noinline__ void z2_gather_tile(const ZoomParams &P, int first, bool
 // grid = (ceil(W/128), ceil(H/16), B); block = 128 (4 warps); 8 KB static exchange tiles +
 // `smem_floats` * 4 bytes of dynamic staging.
 template <int WC>
-__global__ void __launch_bounds__(Z2_WARPS * 32, 7)
+__global__ void __launch_bounds__(Z2_WARPS * 32, 6)
 zoom_sample2_kernel(const __grid_constant__ ZoomParams P, int smem_floats) {
   extern __shared__ float4 win4[];
   __shared__ __align__(16) float xch[Z2_WARPS][Z2_SLOTS][32];
@@ -1153,9 +1178,13 @@ zoom_sample2_kernel(const __grid_constant__ ZoomParams P, int smem_floats) {
     const bool bg_now = !__any_sync(0xffffffffu, any);
     __syncwarp();
     if (lane == 0) *st = bg_now ? 1 : 0;
-    if (bg_now && P.state_valid && held) wskip = P.sparse_mask;
+    if (bg_now && P.state_valid && held) wskip = 1u;  // skip the planes of P.sparse_mask
   }
-  if (!warp_in_u) wskip = 0xffffffffu;
+  if (!warp_in_u) wskip = 2u;  // skip every plane
+  // The two skip bits ride in the upper bits of wh_all: as a variable of their own they were
+  // the value the register allocator chose to spill, and the reload sat on the critical path of
+  // every plane (15 % of the stall samples).
+  wh_all |= (int)(wskip << 8);
 
   if (!staged) {
     // not zoom-in shaped / degenerate / unaligned: every thread gathers its own outputs
@@ -1172,13 +1201,14 @@ zoom_sample2_kernel(const __grid_constant__ ZoomParams P, int smem_floats) {
   for (int pl = 0; pl < P.n_planes; ++pl) {
     const ZoomPlane &zp = P.planes[pl];
     if (zp.dup_second) continue;  // written together with the plane before it
-    const uint32_t plane_bytes = pitch * (uint32_t)wh_all;
+    const int wh = wh_all & 0xff;
+    const uint32_t plane_bytes = pitch * (uint32_t)wh;
     if (pl >= p1) {  // block-uniform: stage the next planes
       if (p1 > 0) __syncthreads();  // every consumer of the previous stage is done
       p0 = pl;
       p1 = min(P.n_planes, p0 + smem_floats / (int)(plane_bytes >> 2));
       const int nch = (int)(pitch >> 4);
-      const int nchunks = nch * wh_all;
+      const int nchunks = nch * wh;
       const float inv_nch = __frcp_rn((float)nch);
       const uint32_t win_s = (uint32_t)__cvta_generic_to_shared(win4);
       for (int qq = threadIdx.x; qq < nchunks; qq += Z2_WARPS * 32) {
@@ -1206,7 +1236,7 @@ zoom_sample2_kernel(const __grid_constant__ ZoomParams P, int smem_floats) {
       __syncthreads();
       z2_fence(tok);
     }
-    if ((wskip >> pl) & 1u) continue;  // warp-uniform
+    if ((wh_all >> 9) | ((wh_all >> 8) & (int)(P.sparse_mask >> pl) & 1)) continue;  // warp-uniform
     // shared address of this lane's first tap of the plane
     uint32_t a_pl = tap + (uint32_t)(pl - p0) * plane_bytes;
     // The phase bodies below are separate template instantiations inlined into this loop; the
@@ -1218,12 +1248,12 @@ zoom_sample2_kernel(const __grid_constant__ ZoomParams P, int smem_floats) {
     const int pre_op = zp.pre_op, post_op = zp.post_op;
     const float mean = zp.mean;
     if (pre_op == RC_PRE_ADD_MEAN) {
-      if (edge) z2_phase_a<RC_PRE_ADD_MEAN, true>(a_pl, pitch, st_lane, wl, wr, mean, wh_all, okl, okr, y_first, H, tok);
-      else z2_phase_a<RC_PRE_ADD_MEAN, false>(a_pl, pitch, st_lane, wl, wr, mean, wh_all, okl, okr, y_first, H, tok);
+      if (edge) z2_phase_a<RC_PRE_ADD_MEAN, true>(a_pl, pitch, st_lane, wl, wr, mean, wh, okl, okr, y_first, H, tok);
+      else z2_phase_a<RC_PRE_ADD_MEAN, false>(a_pl, pitch, st_lane, wl, wr, mean, wh, okl, okr, y_first, H, tok);
     } else if (pre_op == RC_PRE_THRESH02) {
-      z2_phase_a<RC_PRE_THRESH02, false>(a_pl, pitch, st_lane, wl, wr, mean, wh_all, okl, okr, y_first, H, tok);
+      z2_phase_a<RC_PRE_THRESH02, false>(a_pl, pitch, st_lane, wl, wr, mean, wh, okl, okr, y_first, H, tok);
     } else {
-      z2_phase_a<RC_PRE_NONE, false>(a_pl, pitch, st_lane, wl, wr, mean, wh_all, okl, okr, y_first, H, tok);
+      z2_phase_a<RC_PRE_NONE, false>(a_pl, pitch, st_lane, wl, wr, mean, wh, okl, okr, y_first, H, tok);
     }
     __syncwarp();
     z2_fence(tok);
@@ -1413,7 +1443,6 @@ int launch_zoom_sample(const float *zoom_factor, int inverse, const rc_zoom_grou
   RC_REQUIRE(width % 4 == 0, RC_ERR_UNALIGNED);
   rc::ZoomParams P;
   P.n_planes = 0;
-  P.n_bundles = 0;
   P.sparse_mask = 0u;
   const long long plane = (long long)height * width;
   for (int g = 0; g < n_groups; ++g) {
@@ -1500,38 +1529,16 @@ int launch_zoom_sample(const float *zoom_factor, int inverse, const rc_zoom_grou
       // phase B writes 128-bit quads: destination planes 16-byte aligned (checked above per group)
     }
     if (v2) {
-      P.n_bundles = 0;
-      int pl = 0;
-      while (pl < P.n_planes) {
-        rc::ZoomParams::Bundle &bd = P.bundles[P.n_bundles++];
-        bd.first = (uint8_t)pl;
-        bd.n = 1;
-        bd.dup = 0;
-        bd.pad_ = 0;
+      // a broadcast pair (RC_ZOOM_SRC_BROADCAST: the next plane resamples the SAME source with the
+      // same operations) is computed once and stored twice
+      for (int pl = 0; pl + 1 < P.n_planes; ++pl) {
         const rc::ZoomPlane &z0 = P.planes[pl];
-        const unsigned sp0 = (P.sparse_mask >> pl) & 1u;
-        // a broadcast pair: the next plane resamples the SAME source with the same operations
-        if (pl + 1 < P.n_planes) {
-          rc::ZoomPlane &z1 = P.planes[pl + 1];
-          if (z1.src == z0.src && z1.src_bstride == z0.src_bstride && z1.pre_op == z0.pre_op &&
-              z1.post_op == z0.post_op && z1.mean == z0.mean &&
-              z0.post_op != RC_POST_SPOT_SUB_MEAN && ((P.sparse_mask >> (pl + 1)) & 1u) == sp0) {
-            bd.dup = 1;
-            z1.dup_second = 1;
-            pl += 2;
-            continue;
-          }
-        }
-        int n = 1;
-        while (n < 3 && pl + n < P.n_planes) {
-          const rc::ZoomPlane &z1 = P.planes[pl + n];
-          if (z1.pre_op != z0.pre_op || z1.post_op != z0.post_op ||
-              ((P.sparse_mask >> (pl + n)) & 1u) != sp0 || z1.src == P.planes[pl + n - 1].src)
-            break;
-          ++n;
-        }
-        bd.n = (uint8_t)n;
-        pl += n;
+        rc::ZoomPlane &z1 = P.planes[pl + 1];
+        if (!z0.dup_second && z1.src == z0.src && z1.src_bstride == z0.src_bstride &&
+            z1.pre_op == z0.pre_op && z1.post_op == z0.post_op && z1.mean == z0.mean &&
+            z0.post_op != RC_POST_SPOT_SUB_MEAN &&
+            ((P.sparse_mask >> (pl + 1)) & 1u) == ((P.sparse_mask >> pl) & 1u))
+          z1.dup_second = 1;
       }
       // staging: 22 KB per block (all 13 planes of the default step in one stage up to zoom
       // factors ~0.37: window (128 wx + 8) x (16 wy + 3) floats per plane) + 8 KB exchange tiles:
