@@ -501,6 +501,8 @@ def run_loop(args, rank, world, local_rank):
         if world > 1:
             dist.barrier()
 
+    if args.pairs_total:  # experiment knob (e.g. one GPU's share of an 8-GPU run); not the metric
+        cfg = dict(cfg, total=args.pairs_total, name=cfg["name"] + " [--pairs-total %d]" % args.pairs_total)
     if cfg["total"] is not None:
         lo, hi = shard.partition(cfg["total"], world, rank)
         B = hi - lo
@@ -658,8 +660,8 @@ def run_loop(args, rank, world, local_rank):
         zf = loop.step.zoom_factor.cpu().numpy()
         win = np.clip(zf[:, 0], 0, 1) * np.clip(zf[:, 1], 0, 1)  # crop area / frame area
         comp = float(52 * px * B + 48 * px * float(win.sum()))   # 12 distinct source planes
-        grid = ((synth.W + 127) // 128) * ((synth.H + 7) // 8) * B
-        traffic, traffic_src = _traffic("zoom_sample_kernel", grid)
+        grid = ((synth.W + 127) // 128) * ((synth.H + 15) // 16) * B  # zoom_sample2_kernel: 128 x 16 tiles
+        traffic, traffic_src = _traffic("zoom_sample2_kernel", grid)
         render_s = sum(kern[n] for n in r_names) * 1e-6
         ntri = sum(loop.renderer.n_triangles[c] for c in host["class_index"])
         fg = float((loop.depth_rendered > 0).sum().item())
@@ -687,7 +689,7 @@ def run_loop(args, rank, world, local_rank):
                     "limiter": "host->device copy: %.1f GB/s aggregate over %d rank(s)" % (h2d_gbs, world),
                     "host_cores_bound": (len(numa_cores) if numa_cores else None)},
             "gpu_launches": loop.launches_per_iteration * steps_timed,
-            "roofline": {"bound": "hbm", "kernel": "zoom_sample_kernel", "achieved": achieved,
+            "roofline": {"bound": "hbm", "kernel": "zoom_sample2_kernel", "achieved": achieved,
                          "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                          "kernel_us": kernel_us,
@@ -866,8 +868,8 @@ def run_step(args, rank, world, local_rank):
         zf = step.zoom_factor.cpu().numpy()
         win = np.clip(zf[:, 0], 0, 1) * np.clip(zf[:, 1], 0, 1)
         comp = float(52 * px * B + 48 * px * float(win.sum()))
-        grid = ((synth.W + 127) // 128) * ((synth.H + 7) // 8) * B
-        traffic, traffic_src = _traffic("zoom_sample_kernel", grid)
+        grid = ((synth.W + 127) // 128) * ((synth.H + 15) // 16) * B  # zoom_sample2_kernel: 128 x 16 tiles
+        traffic, traffic_src = _traffic("zoom_sample2_kernel", grid)
         step_bytes = pipeline.algorithmic_bytes_per_pair(synth.H, synth.W, synth.NUM_3D_SAMPLE) * B
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K,
@@ -888,7 +890,7 @@ def run_step(args, rank, world, local_rank):
                         "d2h_bytes_per_step": ffeed.d2h_bytes,
                         "feed": "float32 blobs as the reference's DataBatch holds them (12.4 MB per pair)"},
             "gpu_launches": step.launches_per_step * K * repeats,
-            "roofline": {"bound": "hbm", "kernel": "zoom_sample_kernel", "achieved": achieved,
+            "roofline": {"bound": "hbm", "kernel": "zoom_sample2_kernel", "achieved": achieved,
                          "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                          "kernel_us": kernel_ms * 1e3,
@@ -921,6 +923,8 @@ def main():
                          "replaying one CUDA graph per loop")
     ap.add_argument("--min-seconds", type=float, default=1.0,
                     help="repeat the K-step block until this much GPU time is inside one event pair")
+    ap.add_argument("--pairs-total", type=int, default=0,
+                    help="experiments only: override the config's total number of pairs")
     ap.add_argument("--config", type=int, default=DEFAULT_CONFIG, choices=sorted(CONFIGS),
                     help="BASELINE.json config (5 = default: the full refine loop the metric is "
                          "quoted on; 2 = compare step only)")

@@ -170,11 +170,13 @@ def main():
         traffic = json.load(open(tpath)) if os.path.exists(tpath) else {}
         for d in F:
             name = re.sub(r"<.*", "", d["kernel"])
-            traffic[name] = {
+            rec = {
                 "bytes_per_launch": g(d, "dram__bytes_read.sum") + g(d, "dram__bytes_write.sum"),
                 "read": g(d, "dram__bytes_read.sum"), "write": g(d, "dram__bytes_write.sum"),
                 "grid": g(d, "launch__grid_size"),
                 "source": "profiles/%s_ncu_full.csv (ncu --set full, one launch)" % tag}
+            traffic[name] = rec  # latest capture of the kernel, whatever its launch shape
+            traffic["%s@%d" % (name, int(rec["grid"]))] = rec  # ... and per launch shape
         with open(tpath, "w") as fh:
             json.dump(traffic, fh, indent=1, sort_keys=True)
     with open(os.path.join(PROF, "%s_summary.md" % tag), "w") as fh:

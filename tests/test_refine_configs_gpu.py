@@ -109,12 +109,17 @@ def test_refine_loop_at_baseline_shape(cuda_device, cfg):
         np.testing.assert_allclose(_take(loop.step.loss_sum, idx), sums, rtol=1e-4)
         if sh["backward"]:
             g_rot, g_tr = transform3d_np.pm_loss_backward(*args, 1.0 / synth.NUM_3D_SAMPLE)
-            # L1 loss: d|x|/dx = sign(x) flips for a point whose residual is within float32 rounding
-            # of zero, which moves a gradient component by 2 w / (N norm) of that point: absolute
-            # slack of 1e-3 of the row's largest component on top of the relative bar
+            # L1 loss: d|x|/dx = sign(x) FLIPS for a coordinate whose residual is within float32
+            # rounding of zero, and every flip moves a gradient component by up to
+            # 2 * grad_scale / norm * |d est / d parameter| -- as the poses converge (iteration 2, 3)
+            # more and more residuals sit there.  Count them in the oracle and allow that much.
+            est = transform3d_np.forward(args[0], rot_est, trans_est, prev, ZERO, ONE)
+            x = (est - args[1]) / np.float32(0.1)
+            near = ((np.abs(x) < 2e-5) & (args[2] > 0)).reshape(N_SAMPLE, -1).sum(axis=1, keepdims=True)
+            flip = 2.0 * (1.0 / synth.NUM_3D_SAMPLE) / 0.1 * 4.0
             for got, want in ((_take(loop.step.grad_rot, idx), g_rot), (_take(loop.step.grad_trans, idx), g_tr)):
-                slack = 1e-3 * np.abs(want).max(axis=1, keepdims=True) + 1e-6
-                assert (np.abs(got - want) <= 5e-4 * np.abs(want) + slack).all(), (cfg, it)
+                slack = near * flip + 1e-3 * np.abs(want).max(axis=1, keepdims=True) + 1e-6
+                assert (np.abs(got - want) <= 5e-4 * np.abs(want) + slack).all(), (cfg, it, near.ravel())
     loop.check_status()
     # the poses converged towards the targets under the damped-GT stand-in
     err0 = np.abs(host["src_pose"] - host["tgt_pose"]).max(axis=(1, 2))
