@@ -623,7 +623,7 @@ def run_loop(args, rank, world, local_rank):
     torch.cuda.synchronize()
     flat_r = [m for l in rm for m in l]
     flat_s = [m for l in sm for m in l]
-    r_names = ["raster_clear_vertex_setup_clip", "raster_scan", "raster_fill", "raster_cover_resolve"]
+    r_names = ["raster_clear_vertex_setup", "raster_scan_clip", "raster_fill", "raster_cover_resolve"]
     kern = {n: sum(m[j].elapsed_ms(m[j + 1]) for m in flat_r) / len(flat_r) * 1e3
             for j, n in enumerate(r_names)}
     s_names = {"frame_tiles_flow": (0, 1), "zoom_factor_boxes": (1, 2), "zoom_sample": (2, 3),
@@ -709,6 +709,7 @@ def run_loop(args, rank, world, local_rank):
                            "covered_px_per_s": fg / render_s if render_s > 0 else None,
                            "algorithmic_gbs": (20 * px * B) / render_s / 1e9 if render_s > 0 else None,
                            "records": stats["records"], "tile_entries": stats["tile_entries"],
+                           "micro_direct": stats["direct"],
                            "covered_px_per_pair": fg / B},
             "kernel_us_serialised": kern,
             "loss_checksum": loss_checksum,

@@ -147,7 +147,7 @@ typedef struct rc_zoom_group {
 #define RC_POST_SUB_MEAN 5       /* v - mean[c]               (zoom_image_with_factor.py:71-72) */
 #define RC_POST_SPOT_SUB_MEAN 6  /* max(v, centre spot) - mean[c]  (:36-45,:67-70)      */
 
-#define RC_ZOOM_MAX_GROUPS 8
+#define RC_ZOOM_MAX_GROUPS 12
 #define RC_ZOOM_MAX_PLANES 16
 
 /* Bilinear resampling of up to RC_ZOOM_MAX_PLANES planes that share one
@@ -329,7 +329,23 @@ typedef struct rc_compare_step_args {
                                       the forward on src_pose_i; batch_updater_py_multi.py:211-312 refines the
                                       pose afterwards), while flow/zoom read the refined pose `src_pose`.  A
                                       refine loop therefore binds the pre-update pose here. */
+  /* INPUT_DEPTH graphs (deepIM_flownet.py:669-681, test graph :827-835): ZoomDepth of the two depth
+   * maps with the step's zoom factor (zoom_depth.py:24-50), as two more planes of the same
+   * resampler launch.  All three NULL = the shipped configs (INPUT_DEPTH: False). */
+  const float *depth_observed;     /* [B,1,H,W] or NULL */
+  float *zoom_depth_observed;      /* [B,1,H,W] or NULL */
+  float *zoom_depth_rendered;      /* [B,1,H,W] or NULL (source: depth_rendered) */
+  int32_t phases;                  /* 0 = the whole step in one call; else a mask of RC_STEP_PHASE_*: the
+                                      caller issues the phases itself, e.g. the loss phase on a second
+                                      stream beside the rasteriser (it reads poses and points only) and
+                                      the ZoomTrans backward beside the resampler.  Ordering between the
+                                      phases is then the caller's: FRAME before SAMPLE and ZT_BWD, LOSS
+                                      before ZT_BWD */
 } rc_compare_step_args;
+#define RC_STEP_PHASE_LOSS 1    /* Transform3D + point-matching loss (+ backward)             */
+#define RC_STEP_PHASE_FRAME 2   /* GT flow, crop boxes, zoom factor (+ ZoomTrans forward)     */
+#define RC_STEP_PHASE_SAMPLE 4  /* the resampler launch                                       */
+#define RC_STEP_PHASE_ZT_BWD 8  /* invZoomTrans.backward of grad_trans                        */
 
 int rc_compare_step_dev(const rc_compare_step_args *args);
 
@@ -412,7 +428,9 @@ int rc_render_dev(void *handle, const rc_render_args *args);
 int rc_renderer_note_replay(void *handle, int n_renders);
 
 /* Counters of the last rc_render_dev call on this handle's workspaces (debug / bench):
- * out[0] = triangle records emitted, out[1] = tile-list entries.  Synchronises the stream. */
+ * out[0] = triangles that survived culling, out[1] = tile-list entries, out[2] = how many of
+ * out[0] were micro-triangles merged straight into the z-winner blocks (no record, no list
+ * entry).  `out` holds 3 values.  Synchronises the stream. */
 int rc_render_stats(void *handle, int batch_size, void *stream, int64_t *out);
 
 /* ------------------------------------------------------ pose update (host driver math)
@@ -442,6 +460,17 @@ int rc_pose_delta_dev(const float *src_pose, const float *tgt_pose, const float 
 int rc_standin_predict_dev(const float *rot_gt, const float *trans_gt, const float *noise_q,
                            const float *noise_t, float damping, float *rot_est, float *trans_est,
                            int batch_size, void *stream);
+
+/* The same stand-in at the head of rc_pose_update_dev's kernel (one launch instead of two on the
+ * refine loop's chain of dependent launches): rot_est / trans_est are WRITTEN (the loss and the
+ * caller read them) and then used as the update.  rot_gt / trans_gt may alias rot_res /
+ * trans_res (labels in, new labels out).  Not a reference interface. */
+int rc_pose_update_standin_dev(const float *src_pose, const float *rot_gt, const float *trans_gt,
+                               const float *noise_q, const float *noise_t, float damping,
+                               float *rot_est, float *trans_est, const float *tgt_pose,
+                               const float *K, const float *T_means, const float *T_stds,
+                               int rot_coord, float *refined_pose, float *rot_res,
+                               float *trans_res, float *KT, int batch_size, void *stream);
 
 /* ------------------------------------------------ test-time mask policies (8(f) rank 1)
  * The "box_rendered" / "box_observed" branches of update_data_batch,

@@ -23,7 +23,7 @@ RC_PRE_NONE, RC_PRE_THRESH02, RC_PRE_ADD_MEAN = 0, 1, 2
 RC_ROT_MODEL, RC_ROT_CAMERA, RC_ROT_CAMERA_NEW, RC_ROT_NAIVE = range(4)
 RC_PM_L1, RC_PM_L2, RC_PM_SMOOTH_L1 = range(3)
 RC_ZOOM_ACCUMULATE, RC_ZOOM_SRC_BROADCAST = 1, 2
-RC_ZOOM_MAX_GROUPS = 8
+RC_ZOOM_MAX_GROUPS = 12
 RC_ZOOM_MAX_PLANES = 16
 RC_ZF_WS_INTS = 10
 RC_BOX_WS_INTS = 5
@@ -50,6 +50,7 @@ class rc_zoom_group(ctypes.Structure):
 
 
 RC_STEP_MARKS = 6
+RC_STEP_PHASE_LOSS, RC_STEP_PHASE_FRAME, RC_STEP_PHASE_SAMPLE, RC_STEP_PHASE_ZT_BWD = 1, 2, 4, 8
 _STEP_IN = ("image_observed", "image_rendered", "depth_gt_observed", "depth_rendered",
             "mask_observed", "mask_gt_observed", "src_pose", "KT", "Kinv", "K",
             "point_cloud_model", "point_cloud_weights", "point_cloud_observed", "rot_est",
@@ -83,6 +84,10 @@ class rc_compare_step_args(ctypes.Structure):
         ("outputs_track_frames", c_int32),
         ("zoom_tile_state", c_void_p),
         ("loss_src_pose", c_void_p),
+        ("depth_observed", c_void_p),
+        ("zoom_depth_observed", c_void_p),
+        ("zoom_depth_rendered", c_void_p),
+        ("phases", c_int32),
     ])
 
 
@@ -146,6 +151,9 @@ SIGNATURES = {
                                    _P, _P, _P, _P, c_int, _P]),
     "rc_pose_delta_dev": (c_int, [_P, _P, POINTER(c_float), POINTER(c_float), c_int, _P, _P, c_int, _P]),
     "rc_standin_predict_dev": (c_int, [_P, _P, _P, _P, c_float, _P, _P, c_int, _P]),
+    "rc_pose_update_standin_dev": (c_int, [_P, _P, _P, _P, _P, c_float, _P, _P, _P, _P,
+                                           POINTER(c_float), POINTER(c_float), c_int, _P, _P, _P,
+                                           _P, c_int, _P]),
     "rc_pm_loss_bwd_dev": (c_int, [_P, _P, _P, _P, _P, _P, POINTER(c_float), POINTER(c_float),
                                    c_int, c_int, c_float, c_float, c_float, _P, _P, c_int, c_int,
                                    _P]),

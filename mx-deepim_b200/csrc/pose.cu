@@ -132,17 +132,49 @@ struct PoseUpdateParams {
   int rot_coord;
 };
 
-__global__ void pose_update_kernel(const float *__restrict__ src_pose, const float *__restrict__ rot_est,
-                                   const float *__restrict__ trans_est,
+// Stand-in for the FlowNet heads in synthetic refine loops (SURVEY.md 8(d): "predicted (q, t) =
+// calc_RT_delta(src, tgt) damped by 0.5 + N(0, small)").  The CNN is out of scope; the stand-in
+// must not weigh on the measured loop, so it either runs as one small launch
+// (rc_standin_predict_dev) or rides at the head of the pose update (rc_pose_update_standin_dev),
+// which takes it off the loop's chain of dependent launches altogether.
+struct Standin {
+  const float *rot_gt, *trans_gt, *noise_q, *noise_t;  // rot_gt == NULL: no stand-in
+  float *rot_est, *trans_est;                          // written for the loss (and the tests)
+  float damping;
+};
+
+__device__ __forceinline__ void standin_predict(const Standin &sp, int b, float *q, float *t) {
+  float n2 = 0.f;
+  for (int i = 0; i < 4; ++i) {
+    q[i] = __fadd_rn(__fmaf_rn(sp.damping, sp.rot_gt[b * 4 + i],
+                               __fmul_rn(1.f - sp.damping, i == 0 ? 1.f : 0.f)),
+                     sp.noise_q[b * 4 + i]);
+    n2 = __fmaf_rn(q[i], q[i], n2);
+  }
+  const float inv = __fdiv_rn(1.f, sqrtf(n2));  // L2Normalization upstream of the pose update
+  for (int i = 0; i < 4; ++i) q[i] = __fmul_rn(q[i], inv);
+  for (int i = 0; i < 3; ++i)
+    t[i] = __fmaf_rn(sp.damping, sp.trans_gt[b * 3 + i], sp.noise_t[b * 3 + i]);
+}
+
+__global__ void pose_update_kernel(const float *__restrict__ src_pose, const float *rot_est,
+                                   const float *trans_est,
                                    const float *__restrict__ tgt_pose, const float *__restrict__ K,
-                                   PoseUpdateParams pp, float *__restrict__ refined_pose,
-                                   float *__restrict__ rot_res, float *__restrict__ trans_res,
+                                   PoseUpdateParams pp, Standin sp, float *__restrict__ refined_pose,
+                                   float *rot_res, float *trans_res,
                                    float *__restrict__ KT, int B) {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= B) return;
   // ---- RT_transform (RT_transform.py:135-161): quat = r / ||r|| in float32, quat2mat float64
-  float r[4];
-  for (int i = 0; i < 4; ++i) r[i] = rot_est[b * 4 + i];
+  float r[4], te[3];
+  if (sp.rot_gt) {  // the stand-in's prediction from the current labels (may alias rot_res)
+    standin_predict(sp, b, r, te);
+    for (int i = 0; i < 4; ++i) sp.rot_est[b * 4 + i] = r[i];
+    for (int i = 0; i < 3; ++i) sp.trans_est[b * 3 + i] = te[i];
+  } else {
+    for (int i = 0; i < 4; ++i) r[i] = rot_est[b * 4 + i];
+    for (int i = 0; i < 3; ++i) te[i] = trans_est[b * 3 + i];
+  }
   const float nr = sqrtf(__fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(r[0], r[0]), __fmul_rn(r[1], r[1])),
                                              __fmul_rn(r[2], r[2])),
                                    __fmul_rn(r[3], r[3])));
@@ -176,7 +208,7 @@ __global__ void pose_update_kernel(const float *__restrict__ src_pose, const flo
   // T_transform, :82-103, float32 arithmetic on float32 operands
   float td1[3];
   for (int i = 0; i < 3; ++i)
-    td1[i] = __fadd_rn(__fmul_rn(trans_est[b * 3 + i], pp.stds[i]), pp.means[i]);
+    td1[i] = __fadd_rn(__fmul_rn(te[i], pp.stds[i]), pp.means[i]);
   const float Tsf[3] = {(float)Ts[0], (float)Ts[1], (float)Ts[2]};
   const float z2 = __fdiv_rn(Tsf[2], expf(td1[2]));
   float Tn[3];
@@ -296,23 +328,13 @@ __global__ void pose_delta_kernel(const float *__restrict__ src_pose,
     trans_res[b * 3 + i] = (float)((tdl[i] - (double)pp.means[i]) / (double)pp.stds[i]);
 }
 
-// Stand-in for the FlowNet heads in synthetic refine loops (SURVEY.md 8(d): "predicted (q, t) =
-// calc_RT_delta(src, tgt) damped by 0.5 + N(0, small)").  The CNN is out of scope; this keeps the
-// stand-in at one launch so that it does not weigh on the measured loop.
-__global__ void standin_predict_kernel(const float *__restrict__ rot_gt, const float *__restrict__ trans_gt,
-                                       const float *__restrict__ noise_q, const float *__restrict__ noise_t,
-                                       float damping, float *__restrict__ rot_est,
-                                       float *__restrict__ trans_est, int B) {
+__global__ void standin_predict_kernel(Standin sp, int B) {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= B) return;
-  float q[4], n2 = 0.f;
-  for (int i = 0; i < 4; ++i) {
-    q[i] = (1.f - damping) * (i == 0 ? 1.f : 0.f) + damping * rot_gt[b * 4 + i] + noise_q[b * 4 + i];
-    n2 += q[i] * q[i];
-  }
-  const float inv = 1.f / sqrtf(n2);  // L2Normalization upstream of the pose update
-  for (int i = 0; i < 4; ++i) rot_est[b * 4 + i] = q[i] * inv;
-  for (int i = 0; i < 3; ++i) trans_est[b * 3 + i] = damping * trans_gt[b * 3 + i] + noise_t[b * 3 + i];
+  float q[4], t[3];
+  standin_predict(sp, b, q, t);
+  for (int i = 0; i < 4; ++i) sp.rot_est[b * 4 + i] = q[i];
+  for (int i = 0; i < 3; ++i) sp.trans_est[b * 3 + i] = t[i];
 }
 
 }  // namespace rc
@@ -336,8 +358,35 @@ int rc_pose_update_dev(const float *src_pose, const float *rot_est, const float 
     pp.stds[i] = T_stds ? T_stds[i] : 1.f;
   }
   pp.rot_coord = rot_coord;
+  rc::Standin none = {};
   rc::pose_update_kernel<<<(batch_size + 63) / 64, 64, 0, static_cast<cudaStream_t>(stream)>>>(
-      src_pose, rot_est, trans_est, tgt_pose, K, pp, refined_pose, rot_res, trans_res, KT,
+      src_pose, rot_est, trans_est, tgt_pose, K, pp, none, refined_pose, rot_res, trans_res, KT,
+      batch_size);
+  return rc::note_status(rc::check_launch());
+}
+
+int rc_pose_update_standin_dev(const float *src_pose, const float *rot_gt, const float *trans_gt,
+                               const float *noise_q, const float *noise_t, float damping,
+                               float *rot_est, float *trans_est, const float *tgt_pose,
+                               const float *K, const float *T_means, const float *T_stds,
+                               int rot_coord, float *refined_pose, float *rot_res,
+                               float *trans_res, float *KT, int batch_size, void *stream) {
+  RC_REQUIRE(batch_size >= 0, RC_ERR_INVALID_ARG);
+  RC_REQUIRE(rot_coord == RC_ROT_MODEL || rot_coord == RC_ROT_CAMERA || rot_coord == RC_ROT_CAMERA_NEW,
+             RC_ERR_INVALID_ARG);
+  if (batch_size == 0) return rc::note_status(RC_OK);
+  RC_REQUIRE(src_pose && rot_gt && trans_gt && noise_q && noise_t && rot_est && trans_est &&
+                 tgt_pose && K && refined_pose && rot_res && trans_res && KT,
+             RC_ERR_INVALID_ARG);
+  rc::PoseUpdateParams pp;
+  for (int i = 0; i < 3; ++i) {
+    pp.means[i] = T_means ? T_means[i] : 0.f;
+    pp.stds[i] = T_stds ? T_stds[i] : 1.f;
+  }
+  pp.rot_coord = rot_coord;
+  rc::Standin sp = {rot_gt, trans_gt, noise_q, noise_t, rot_est, trans_est, damping};
+  rc::pose_update_kernel<<<(batch_size + 63) / 64, 64, 0, static_cast<cudaStream_t>(stream)>>>(
+      src_pose, rot_est, trans_est, tgt_pose, K, pp, sp, refined_pose, rot_res, trans_res, KT,
       batch_size);
   return rc::note_status(rc::check_launch());
 }
@@ -367,8 +416,9 @@ int rc_standin_predict_dev(const float *rot_gt, const float *trans_gt, const flo
   RC_REQUIRE(batch_size >= 0, RC_ERR_INVALID_ARG);
   if (batch_size == 0) return rc::note_status(RC_OK);
   RC_REQUIRE(rot_gt && trans_gt && noise_q && noise_t && rot_est && trans_est, RC_ERR_INVALID_ARG);
+  rc::Standin sp = {rot_gt, trans_gt, noise_q, noise_t, rot_est, trans_est, damping};
   rc::standin_predict_kernel<<<(batch_size + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(
-      rot_gt, trans_gt, noise_q, noise_t, damping, rot_est, trans_est, batch_size);
+      sp, batch_size);
   return rc::note_status(rc::check_launch());
 }
 

@@ -6,27 +6,34 @@
 // and the post-render block
 //   /root/reference/lib/pair_matching/batch_updater_py_multi.py:279-320.
 //
-// B200 design (one render call = a memset + 7 launches for a whole batch, any mix of meshes;
-// launch order: clear, setup, clip, scan, fill, cover, resolve):
+// B200 design (one render call = 7 launches for a whole batch, any mix of meshes, no memset;
+// launch order: clear, vertex, setup, scan, fill, cover, resolve):
 //   clear   : the background (depth 0, mask 0, image 0 - mean ...) in row order with 128-bit
 //             stores -- the whole frame, or in incremental mode (a caller that owns its frame
 //             buffers) only the tiles the previous frame covered.  Launched first; it releases
 //             its dependents at once and the passes below run beside it (programmatic dependent
 //             launches, each waiting for its predecessor only); only resolve waits for it.
-//   setup   : one thread per (triangle, pair): pose transform in float64, pinhole projection,
-//             snap to 1/256 px, edge orientation, GL window depth, culling (incl. micro-
-//             triangles that contain no pixel centre); writes a 64-byte record + its pixel box
-//             and counts the 16x16 tiles it overlaps with warp-aggregated atomics
-//             (__match_any_sync on the tile id).  Triangles straddling the near plane go to a
-//             list for the (usually idle) clip kernel.
-//   scan    : exclusive scan of the per-tile counts (one block per pair) + the list of non-empty
-//             (tile, pair) items.
+//   vertex  : one thread per (vertex, pair): pose transform in float64, pinhole projection, snap
+//             to 1/256 px, GL window depth; also zeroes this call's counters.
+//   setup   : one thread per (triangle, pair): edge orientation, culling (incl. micro-triangles
+//             that contain no pixel centre).  A MICRO-TRIANGLE (pixel box <= 3x3: most of a dense
+//             mesh) that does contain pixel centres is finished here: its fragments go straight
+//             into the pair's dense z-winner blocks with a 64-bit atomicMin (RED in L2) on the
+//             packed (bits(window depth) << 32 | slot) key and its tile gets a mark -- no record,
+//             no tile-list entry, no coverage work.  Larger triangles get a 64-byte record + a
+//             packed tile box, and the 16x16 tiles they overlap are counted with warp-aggregated
+//             atomics (__match_any_sync on the tile id).  Triangles straddling the near plane go
+//             to a list that the scan blocks clip (usually empty).
+//   scan    : near-plane clipping of the pair's straddlers, exclusive scan of the per-tile counts
+//             (one block per pair), the list of non-empty (tile, pair) items (list or mark) and
+//             the list of items that have a tile list.
 //   fill    : tile lists (record indices), again warp-aggregated, one thread per triangle.
-//   cover   : per non-empty tile, atomicMin of a packed (bits(window depth) << 32 | record) key
-//             into a shared-memory z-buffer; large triangles are tested cooperatively, one pixel
-//             per thread; the winners go to a 2 KB block per item.
-//   resolve : one thread per pixel of the non-empty tiles: perspective-correct attributes,
-//             nearest texel, optional Lambert term, fused BGR->RGB / CHW / -mean and mask.
+//   cover   : per item with a tile list, atomicMin of the packed key into a shared-memory
+//             z-buffer; large triangles are tested cooperatively, one pixel per thread; the
+//             winners are merged into the dense z-winner blocks.
+//   resolve : one thread per pixel of the non-empty tiles: reads the winner and puts the empty
+//             key back, perspective-correct attributes from the projected vertices, nearest
+//             texel, optional Lambert term, fused BGR->RGB / CHW / -mean and mask.
 // Every pixel of the frame ends up written by exactly one of clear / resolve; the mesh is read
 // once per pair.
 //
@@ -50,6 +57,7 @@ constexpr int RT_THREADS = 256;
 constexpr int RT_SUB = 8;            // sub-pixel bits (GL-style 1/256 px snapping)
 static_assert((1 << RT_TW_SHIFT) == RT_TW && RT_TW % 4 == 0, "tile width");
 static_assert(RT_THREADS % (RT_PIX / 4) == 0, "whole tiles per background pass");
+static_assert(RT_TH == RT_TW, "one shift for tile rows and columns");
 
 struct __align__(16) TriRec {  // 64 bytes = four 128-bit loads
   int x0, y0, x1, y1;    // fixed-point vertices, oriented so that the area is positive
@@ -70,6 +78,9 @@ struct __align__(16) VtxS {
 constexpr int RT_VF_VALID = 1;  // in front of the camera and |u|, |v| < 1e6 px
 constexpr int RT_VF_NEAR = 2;   // z >= znear (inside the near plane)
 constexpr unsigned RT_TBOX_NONE = 0xffu;  // packed tile box with tx0 = 255 > tx1 = 0: no record
+// tx0 = 254 > tx1 = 0: a micro-triangle that went straight to the z-winner blocks (no record, no
+// tile-list entry); only rc_render_stats tells it from RT_TBOX_NONE
+constexpr unsigned RT_TBOX_DIRECT = 0xfeu;
 
 struct Renderer {
   int device, H, W, max_batch, n_meshes, max_tris, tiles_x, tiles_y, list_cap;
@@ -86,9 +97,11 @@ struct Renderer {
   int32_t *clip_list;                        // [max_batch * max_tris] b * max_tris + t of near-plane straddlers
   uint2 *clip_box;                           // [max_batch * max_tris] tile boxes of the two pieces of clip_list[i]
   int32_t *tile_count, *tile_start, *tile_fill;  // [max_batch][n_tiles (+1)]
+  int32_t *tile_touch;                       // [B][n_tiles] this call's "a micro-triangle wrote here" marks (behind tile_count)
+  int32_t *bin_list;                         // [max_batch * n_tiles] the items that also have a tile list (coverage pass)
   int32_t *tile_list;                        // [max_batch][list_cap]
   int32_t *work_count;                       // [RT_WC_INTS] header (see RT_WC_*), then tile_count
-  unsigned long long *zwin;                  // [max_batch * n_tiles][RT_PIX] winning keys of the non-empty items
+  unsigned long long *zwin;                  // [max_batch][n_tiles][RT_PIX] winning keys; all ~0 between frames (resolve resets what it reads)
   int32_t *work_list;                        // [max_batch * n_tiles] packed non-empty (tile, pair) items (this call's half)
   int32_t *heavy;                            // [1] their number (this call's half)
   const int32_t *prev_list, *prev_heavy;     // the previous call's items = tiles its frame dirtied
@@ -101,7 +114,8 @@ struct Renderer {
 
 // work_count header
 constexpr int RT_WC_CLIP = 3;      // clip-list length (setup)
-constexpr int RT_WC_TICKET_H = 4;  // next non-empty item (coverage)
+constexpr int RT_WC_TICKET_H = 4;  // next binned item (coverage)
+constexpr int RT_WC_BINNED = 5;    // number of items with a tile list (scan)
 constexpr int RT_WC_INTS = 8;
 
 // work item: pair << 16 | tile row << 8 | tile column
@@ -151,12 +165,28 @@ __device__ __forceinline__ int project_vertex(double x, double y, double z, cons
   return flag | RT_VF_VALID;
 }
 
-// Screen-space record of one triangle from its three projected vertices.  Culls (bb_max = -1)
-// what cannot produce a fragment: degenerate, off-screen, or -- for boxes of at most 3x3 pixels --
-// no pixel centre inside under the very rule the raster kernel applies (integer edge functions +
-// top-left tie bias).  Everything stays in registers: no dynamically indexed arrays.
-__device__ __forceinline__ void make_record(const VtxS &va, const VtxS &vb, const VtxS &vc, int W,
-                                            int H, int tri, bool clipped, RecQ &r) {
+// Where the micro-triangles of one pair go: straight into the pair's dense z-winner blocks.
+struct DirectZ {
+  unsigned long long *zwin;  // [n_tiles][RT_PIX] of this pair
+  int32_t *touch;            // [n_tiles] marks of this pair
+  int tiles_x;
+};
+
+constexpr int RT_REC_NONE = 0;    // nothing to draw
+constexpr int RT_REC_BINNED = 1;  // r holds a record for the tile lists
+constexpr int RT_REC_DIRECT = 2;  // fragments already merged into the z-winner blocks
+
+// Screen-space record of one triangle from its three projected vertices.  Culls what cannot
+// produce a fragment: degenerate, off-screen, or -- for boxes of at most 3x3 pixels -- no pixel
+// centre inside under the very rule the coverage kernel applies (integer edge functions + top-left
+// tie bias).  With `dz` the fragments of such a micro-triangle (the bulk of a dense mesh: a
+// 20k-triangle model covers ~6k pixels) are depth-tested at once with a 64-bit atomicMin on the
+// same (bits(window depth) << 32 | slot) key the coverage kernel uses, so they need no record,
+// no tile-list entry and no coverage pass: the key order decides the winner, whoever writes it.
+// Everything stays in registers: no dynamically indexed arrays.
+__device__ __forceinline__ int make_record(const VtxS &va, const VtxS &vb, const VtxS &vc, int W,
+                                           int H, int tri, bool clipped, RecQ &r,
+                                           const DirectZ *dz = nullptr) {
   r.bb_max = -1;
   r.bb_min = 0;
   const int X0 = va.X, Y0 = va.Y;
@@ -164,7 +194,7 @@ __device__ __forceinline__ void make_record(const VtxS &va, const VtxS &vb, cons
   const double zw0 = va.zw;
   double zw1 = vb.zw, zw2 = vc.zw;
   const long long area = edge_fn(X0, Y0, X1, Y1, X2, Y2);
-  if (area == 0) return;
+  if (area == 0) return RT_REC_NONE;
   const bool sw = area < 0;
   if (sw) {  // orient so that the area is positive: record vertices (0, 2, 1)
     int t = X1; X1 = X2; X2 = t;
@@ -179,21 +209,21 @@ __device__ __forceinline__ void make_record(const VtxS &va, const VtxS &vb, cons
   if (py0 < 0) py0 = 0;
   if (px1 > W - 1) px1 = W - 1;
   if (py1 > H - 1) py1 = H - 1;
-  if (px0 > px1 || py0 > py1) return;
+  if (px0 > px1 || py0 > py1) return RT_REC_NONE;
   if (px1 - px0 <= 2 && py1 - py0 <= 2 && maxx - minx < 1024 && maxy - miny < 1024) {
-    // micro-triangle: test the (at most nine) pixel centres now; most sub-pixel triangles of a
-    // dense mesh contain none and never reach the tile lists.  Relative to the box corner every
+    // micro-triangle: test the (at most nine) pixel centres now.  Relative to the box corner every
     // coordinate is below 2^11 in magnitude, so the edge functions fit 32 bits (same values as
     // the 64-bit ones the coverage pass evaluates: the test is exact, not conservative).
     const int qx = px0 << RT_SUB, qy = py0 << RT_SUB;
     const int x0 = X0 - qx, y0 = Y0 - qy, x1 = X1 - qx, y1 = Y1 - qy, x2 = X2 - qx, y2 = Y2 - qy;
     const int dx0 = x2 - x1, dy0 = y2 - y1, dx1 = x0 - x2, dy1 = y0 - y2, dx2 = x1 - x0,
               dy2 = y1 - y0;
+    const int t1 = tie_bias(dx1, dy1), t2 = tie_bias(dx2, dy2);
     // edge functions at the corner (0, 0), then stepped: +256 in x adds -dy * 256, in y dx * 256
     const int a0i = dy0 * x1 - dx0 * y1 + tie_bias(dx0, dy0);
-    const int a1i = dy1 * x2 - dx1 * y2 + tie_bias(dx1, dy1);
-    const int a2i = dy2 * x0 - dx2 * y0 + tie_bias(dx2, dy2);
-    bool any = false;
+    const int a1i = dy1 * x2 - dx1 * y2 + t1;
+    const int a2i = dy2 * x0 - dx2 * y0 + t2;
+    unsigned cov = 0;  // bit 3 j + i: pixel centre (px0 + i, py0 + j) is inside
     const int ny = py1 - py0, nx = px1 - px0;
     int a0 = a0i, a1 = a1i, a2 = a2i;  // edge values at the start of the pixel row
 #pragma unroll
@@ -201,7 +231,7 @@ __device__ __forceinline__ void make_record(const VtxS &va, const VtxS &vb, cons
       int b0 = a0, b1 = a1, b2 = a2;
 #pragma unroll
       for (int i = 0; i < 3; ++i) {
-        any = any || (j <= ny && i <= nx && ((b0 | b1 | b2) >= 0));
+        if (j <= ny && i <= nx && ((b0 | b1 | b2) >= 0)) cov |= 1u << (3 * j + i);
         b0 -= dy0 << RT_SUB;
         b1 -= dy1 << RT_SUB;
         b2 -= dy2 << RT_SUB;
@@ -210,7 +240,34 @@ __device__ __forceinline__ void make_record(const VtxS &va, const VtxS &vb, cons
       a1 += dx1 << RT_SUB;
       a2 += dx2 << RT_SUB;
     }
-    if (!any) return;
+    if (!cov) return RT_REC_NONE;
+    if (dz) {
+      // window depth exactly as the coverage pass forms it: one division per triangle, then
+      // d = float(zwa + w1 * dzb + w2 * dzc) with the unbiased edge values (this file is
+      // compiled with -fmad=false, so the association is the written one in both places)
+      const double inv_area = 1.0 / (double)(sw ? -area : area);
+      const double dzb = (zw1 - zw0) * inv_area, dzc = (zw2 - zw0) * inv_area;
+      const int w1c = a1i - t1, w2c = a2i - t2;  // w1, w2 at the box corner
+      const unsigned slot = 2u * (unsigned)tri;
+      while (cov) {
+        const int bit = __ffs(cov) - 1;
+        cov &= cov - 1;
+        const int j = bit / 3, i = bit - 3 * j;
+        const int w1 = w1c + j * (dx1 << RT_SUB) - i * (dy1 << RT_SUB);
+        const int w2 = w2c + j * (dx2 << RT_SUB) - i * (dy2 << RT_SUB);
+        const float d = (float)(zw0 + (double)w1 * dzb + (double)w2 * dzc);
+        if (d >= 0.0f && d <= 1.0f) {  // depth clipping of the fragment (far plane)
+          const int x = px0 + i, y = py0 + j;
+          const int tile = (y >> RT_TW_SHIFT) * dz->tiles_x + (x >> RT_TW_SHIFT);
+          const unsigned long long key = ((unsigned long long)__float_as_uint(d) << 32) | slot;
+          atomicMin(dz->zwin + (size_t)tile * RT_PIX + ((y & (RT_TH - 1)) << RT_TW_SHIFT) +
+                        (x & (RT_TW - 1)),
+                    key);
+          dz->touch[tile] = 1;
+        }
+      }
+      return RT_REC_DIRECT;
+    }
   }
   r.bb_min = (int)((py0 << 16) | px0);
   r.bb_max = (int)((py1 << 16) | px1);
@@ -220,6 +277,7 @@ __device__ __forceinline__ void make_record(const VtxS &va, const VtxS &vb, cons
   r.q2 = make_int4(r.bb_max, 0, __double2loint(zw0), __double2hiint(zw0));
   r.q3 = make_int4(__double2loint(zw1), __double2hiint(zw1), __double2loint(zw2),
                    __double2hiint(zw2));
+  return RT_REC_BINNED;
 }
 
 __device__ __forceinline__ void store_record(TriRec *dst, const RecQ &r) {
@@ -329,10 +387,20 @@ __device__ __forceinline__ uint2 clip_and_emit(const double *Pc /* [3][3] */, co
 // corners per vertex).  grid = (ceil(max_verts / 256), B); block = 256.
 __global__ void __launch_bounds__(256)
 raster_vertex_kernel(Renderer R, const int32_t *__restrict__ cls_idx,
-                     const float *__restrict__ poses, Cam cam) {
+                     const float *__restrict__ poses, Cam cam, int n_tiles) {
   pdl_launch_dependents();  // setup waits (griddepcontrol.wait) for this grid's end
   const int b = blockIdx.y;
   const int v = blockIdx.x * blockDim.x + threadIdx.x;
+  // this call's counters start from zero (was two memset nodes in front of the render): the
+  // pair's tile counts and marks, the header and this half's item count.  Their last readers
+  // (the previous frame's consumers) finished before the background pass in front of this
+  // kernel could start, and their first writer (setup) waits for this whole grid.
+  for (int i = v; i < n_tiles; i += gridDim.x * blockDim.x) {
+    R.tile_count[(size_t)b * n_tiles + i] = 0;
+    R.tile_touch[(size_t)b * n_tiles + i] = 0;
+  }
+  if (b == 0 && v < RT_WC_INTS) R.work_count[v] = 0;
+  if (b == 0 && v == RT_WC_INTS) *R.heavy = 0;
   const int mesh = __ldg(cls_idx + b);
   const int v_off = __ldg(R.mesh_vert_off + mesh);
   if (v >= __ldg(R.mesh_vert_off + mesh + 1) - v_off) return;
@@ -373,6 +441,10 @@ raster_setup_kernel(Renderer R, const int32_t *__restrict__ cls_idx, int n_tiles
   uint32_t *tbox = R.tbox + (size_t)b * R.max_tris;
   int32_t *count = R.tile_count + (size_t)b * n_tiles;
   const VtxS *vtx = R.vtx + (size_t)b * R.max_verts - v_off;  // indexed by the global vertex id
+  DirectZ dz;
+  dz.zwin = R.zwin + (size_t)b * n_tiles * RT_PIX;
+  dz.touch = R.tile_touch + (size_t)b * n_tiles;
+  dz.tiles_x = R.tiles_x;
 
   int idx[RT_SETUP_PER][3];
 #pragma unroll
@@ -403,10 +475,12 @@ raster_setup_kernel(Renderer R, const int32_t *__restrict__ cls_idx, int n_tiles
           vb.X = pv[k][1].x >> 2; vb.Y = pv[k][1].y; vb.zw = __hiloint2double(pv[k][1].w, pv[k][1].z);
           vc.X = pv[k][2].x >> 2; vc.Y = pv[k][2].y; vc.zw = __hiloint2double(pv[k][2].w, pv[k][2].z);
           RecQ r;
-          make_record(va, vb, vc, R.W, R.H, t, false, r);
-          if (r.bb_max >= 0) {
+          const int kind = make_record(va, vb, vc, R.W, R.H, t, false, r, &dz);
+          if (kind == RT_REC_BINNED) {
             store_record(recs + 2 * t, r);
             tb[k] = tile_box(r.bb_min, r.bb_max);
+          } else if (kind == RT_REC_DIRECT) {
+            tb[k] = RT_TBOX_DIRECT;
           }
         }
       } else if (f_or & RT_VF_NEAR) {
@@ -424,17 +498,18 @@ raster_setup_kernel(Renderer R, const int32_t *__restrict__ cls_idx, int n_tiles
     for_each_tile(tb[k], R.tiles_x, [&](int key) { tile_atomic(count, key, false); });
 }
 
-// grid-stride over the triangles raster_setup_kernel found straddling the near plane (usually
-// none): clip, emit up to two records into the triangle's slots, count their tiles.
-__global__ void __launch_bounds__(128)
-raster_clip_kernel(Renderer R, const int32_t *__restrict__ cls_idx,
-                   const float *__restrict__ poses, Cam cam, int n_tiles) {
-  pdl_wait();  // setup's clip list and counters
-  pdl_launch_dependents();
-  const int n = R.work_count[RT_WC_CLIP];
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+// The triangles raster_setup_kernel found straddling the near plane (usually none), done by the
+// pair's scan block in front of its scan (was a launch of its own: one more dependent kernel on
+// the chain of every render for a list that is almost always empty).  Every block walks the
+// whole clip list and keeps the entries of its own pair: clip, emit up to two records into the
+// triangle's slots, count their tiles.
+__device__ __noinline__ void clip_pair(const Renderer &R, const int32_t *__restrict__ cls_idx,
+                                       const float *__restrict__ poses, const Cam &cam, int n_tiles,
+                                       int b, int n) {
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
     const int item = R.clip_list[i];
-    const int b = item / R.max_tris, t = item - b * R.max_tris;
+    if (item / R.max_tris != b) continue;
+    const int t = item - b * R.max_tris;
     const int t_off = __ldg(R.mesh_tri_off + __ldg(cls_idx + b));
     const float *pose = poses + b * 12;
     double Pc[9];
@@ -483,43 +558,64 @@ __device__ __forceinline__ int block_excl_scan(int v, int *smem /* [8] */, int &
   return base + inc - v;
 }
 
-// grid = B; block = 256.  Exclusive scan of tile_count -> tile_start, clears tile_fill, and
-// appends the pair's non-empty tiles to the work list (one atomic per pair; the order inside a
-// pair is the tile order).
+// grid = B; block = 256.  Near-plane clipping of the pair's straddlers (if any), then the
+// exclusive scan of tile_count -> tile_start; clears tile_fill; appends the pair's non-empty
+// tiles -- a tile list OR a micro-triangle mark -- to the work list (resolve, the next frame's
+// incremental background, the compare step's sparse passes) and those with a tile list to the
+// coverage pass's list (one atomic per pair and list; the order inside a pair is the tile
+// order).  Leaves tile_count > 0 exactly for the tiles on the work list.
 __global__ void __launch_bounds__(256)
-raster_scan_kernel(Renderer R, int n_tiles, int32_t *__restrict__ status) {
+raster_scan_kernel(Renderer R, const int32_t *__restrict__ cls_idx,
+                   const float *__restrict__ poses, Cam cam, int n_tiles,
+                   int32_t *__restrict__ status) {
   pdl_wait();
   pdl_launch_dependents();
   const int b = blockIdx.x;
-  const int32_t *count = R.tile_count + (size_t)b * n_tiles;
+  const int n_clip = R.work_count[RT_WC_CLIP];
+  if (n_clip > 0) {  // block-uniform
+    clip_pair(R, cls_idx, poses, cam, n_tiles, b, n_clip);
+    __syncthreads();
+  }
+  int32_t *count = R.tile_count + (size_t)b * n_tiles;
+  const int32_t *touch = R.tile_touch + (size_t)b * n_tiles;
   int32_t *start = R.tile_start + (size_t)b * (n_tiles + 1);
   int32_t *fill = R.tile_fill + (size_t)b * n_tiles;
   __shared__ int part[8];
-  __shared__ int s_base;
+  __shared__ int s_base, s_base_bin;
   const int per = (n_tiles + 255) / 256;
   const int lo = min((int)threadIdx.x * per, n_tiles), hi = min(lo + per, n_tiles);
-  int s = 0, ne = 0;
+  int s = 0, ne = 0, nb = 0;
   for (int i = lo; i < hi; ++i) {
     const int c = count[i];
     s += c;
-    ne += c > 0;
+    nb += c > 0;
+    ne += (c > 0) | (touch[i] != 0);
   }
-  int total, total_ne;
+  int total, total_ne, total_nb;
   int acc = block_excl_scan(s, part, total);
-  int ne_off = block_excl_scan(ne, part, total_ne);
+  const int ne_off = block_excl_scan(ne, part, total_ne);
+  const int nb_off = block_excl_scan(nb, part, total_nb);
   if (threadIdx.x == 0) {
     start[n_tiles] = total;
     if (total > R.list_cap && status) atomicExch(status, 1);
     s_base = atomicAdd(R.heavy, total_ne);
+    s_base_bin = total_nb ? atomicAdd(R.work_count + RT_WC_BINNED, total_nb) : 0;
   }
   __syncthreads();
-  int front = s_base + ne_off;
+  int front = s_base + ne_off, front_bin = s_base_bin + nb_off;
   for (int i = lo; i < hi; ++i) {
     start[i] = acc;
     const int c = count[i];
     acc += c;
     fill[i] = 0;
-    if (c > 0) R.work_list[front++] = pack_work(b, i / R.tiles_x, i % R.tiles_x);
+    const int item = pack_work(b, i / R.tiles_x, i % R.tiles_x);
+    if (c > 0) {
+      R.bin_list[front_bin++] = item;
+      R.work_list[front++] = item;
+    } else if (touch[i] != 0) {
+      R.work_list[front++] = item;
+      count[i] = 1;  // "on the work list" for the sparse passes of the compare step
+    }
   }
 }
 
@@ -588,36 +684,78 @@ struct Shaded {
   float c[3];  // R, G, B in 0..255 as the reference's readback delivers them
 };
 
-// Colour of pixel (x, y) on triangle `tri` of `mesh` under `pose`: perspective-correct
-// attributes from the ray / triangle intersection in camera space (identical to 1/w
-// interpolation of the varyings), texture2D NEAREST + CLAMP_TO_EDGE on the flipped upload
-// (render_py_multi.py:75-77), optional Lambert term (render_py_light_modelnet_multi.py:50-74).
-__device__ Shaded shade_pixel(const Renderer &R, const RasterOut &O, const Cam &cam, int mesh,
-                              const TriRec &rec, const float *__restrict__ pose, int b, int x, int y) {
-  const int tri = rec.tri & RT_TRI_MASK;
-  const int t_off = __ldg(R.mesh_tri_off + mesh);
-  int vi[3];
+// The winning triangle of a pixel as resolve needs it: oriented snapped vertices (record order),
+// flags, mesh vertex ids.  Rebuilt from the projected vertices of this call for every triangle
+// that was not near-clipped (micro-triangles have no record at all); clipped pieces come from
+// their record.
+struct WinTri {
+  int x0, y0, x1, y1, x2, y2;
+  int tri;    // triangle index | RT_FLAG_*
+  int vi[3];  // global vertex ids of the SOURCE triangle
+};
+
+__device__ __forceinline__ void load_winner(const Renderer &R, int b, int mesh, unsigned slot,
+                                            WinTri &w) {
+  const int t = (int)(slot >> 1);
+  const int t_off = __ldg(R.mesh_tri_off + mesh), v_off = __ldg(R.mesh_vert_off + mesh);
+#pragma unroll
+  for (int i = 0; i < 3; ++i) w.vi[i] = __ldg(R.tris + (size_t)(t_off + t) * 3 + i);
+  const VtxS *vtx = R.vtx + (size_t)b * R.max_verts - v_off;
+  const int4 p0 = *reinterpret_cast<const int4 *>(vtx + w.vi[0]);
+  const int4 p1 = *reinterpret_cast<const int4 *>(vtx + w.vi[1]);
+  const int4 p2 = *reinterpret_cast<const int4 *>(vtx + w.vi[2]);
+  if ((p0.x & p1.x & p2.x & (RT_VF_NEAR | RT_VF_VALID)) == (RT_VF_NEAR | RT_VF_VALID)) {
+    w.x0 = p0.x >> 2; w.y0 = p0.y;
+    w.x1 = p1.x >> 2; w.y1 = p1.y;
+    w.x2 = p2.x >> 2; w.y2 = p2.y;
+    w.tri = t;
+    if (edge_fn(w.x0, w.y0, w.x1, w.y1, w.x2, w.y2) < 0) {  // make_record's orientation
+      int q = w.x1; w.x1 = w.x2; w.x2 = q;
+      q = w.y1; w.y1 = w.y2; w.y2 = q;
+      w.tri |= RT_FLAG_SWAPPED;
+    }
+  } else {  // a piece of a near-clipped triangle: its vertices are not mesh vertices
+    const int4 *rp = reinterpret_cast<const int4 *>(R.recs + (size_t)b * 2 * R.max_tris + slot);
+    const int4 q0 = __ldg(rp), q1 = __ldg(rp + 1);
+    w.x0 = q0.x; w.y0 = q0.y; w.x1 = q0.z; w.y1 = q0.w;
+    w.x2 = q1.x; w.y2 = q1.y;
+    w.tri = q1.z;
+  }
+}
+
+// Colour of pixel (x, y) on the winning triangle under `pose`: perspective-correct
+// attributes (1/w interpolation of the varyings), texture2D NEAREST + CLAMP_TO_EDGE on the
+// flipped upload (render_py_multi.py:75-77), optional Lambert term
+// (render_py_light_modelnet_multi.py:50-74).  LIT = false is the textured renderer: only the
+// camera-space z of the three vertices is needed (9 float64 products instead of 27).
+template <bool LIT>
+__device__ __forceinline__ Shaded shade_pixel(const Renderer &R, const RasterOut &O, const Cam &cam,
+                                              int mesh, const WinTri &w,
+                                              const float *__restrict__ pose, int b, int x, int y) {
   double Pc[3][3];
+  const bool clipped = (w.tri & RT_FLAG_CLIPPED) != 0;
 #pragma unroll
   for (int i = 0; i < 3; ++i) {
-    vi[i] = __ldg(R.tris + (size_t)(t_off + tri) * 3 + i);
-    const double px = (double)__ldg(R.verts + (size_t)vi[i] * 3 + 0);
-    const double py = (double)__ldg(R.verts + (size_t)vi[i] * 3 + 1);
-    const double pz = (double)__ldg(R.verts + (size_t)vi[i] * 3 + 2);
+    const double px = (double)__ldg(R.verts + (size_t)w.vi[i] * 3 + 0);
+    const double py = (double)__ldg(R.verts + (size_t)w.vi[i] * 3 + 1);
+    const double pz = (double)__ldg(R.verts + (size_t)w.vi[i] * 3 + 2);
 #pragma unroll
     for (int r = 0; r < 3; ++r)
-      Pc[i][r] = (double)pose[r * 4 + 0] * px + (double)pose[r * 4 + 1] * py +
-                 (double)pose[r * 4 + 2] * pz + (double)pose[r * 4 + 3];
+      if (LIT || r == 2 || clipped)
+        Pc[i][r] = (double)pose[r * 4 + 0] * px + (double)pose[r * 4 + 1] * py +
+                   (double)pose[r * 4 + 2] * pz + (double)pose[r * 4 + 3];
+      else
+        Pc[i][r] = 0.0;
   }
   double b1 = 1.0 / 3.0, b2 = 1.0 / 3.0;
-  if (!(rec.tri & RT_FLAG_CLIPPED)) {
+  if (!clipped) {
     // GL-style: screen-space barycentrics from the SNAPPED vertices (integer edge functions),
     // made perspective-correct with 1/w of the vertices.
     const int px = x << RT_SUB, py = y << RT_SUB;
-    const long long w0 = edge_fn(rec.x1, rec.y1, rec.x2, rec.y2, px, py);
-    const long long w1 = edge_fn(rec.x2, rec.y2, rec.x0, rec.y0, px, py);
-    const long long w2 = edge_fn(rec.x0, rec.y0, rec.x1, rec.y1, px, py);
-    const bool sw = (rec.tri & RT_FLAG_SWAPPED) != 0;
+    const long long w0 = edge_fn(w.x1, w.y1, w.x2, w.y2, px, py);
+    const long long w1 = edge_fn(w.x2, w.y2, w.x0, w.y0, px, py);
+    const long long w2 = edge_fn(w.x0, w.y0, w.x1, w.y1, px, py);
+    const bool sw = (w.tri & RT_FLAG_SWAPPED) != 0;
     const double zb = sw ? Pc[2][2] : Pc[1][2], zc = sw ? Pc[1][2] : Pc[2][2];
     // q_i = l_i / z_i up to the common factor 1 / area, which cancels in q_i / sum(q)
     const double q0 = (double)w0 * (1.0 / Pc[0][2]);
@@ -647,10 +785,10 @@ __device__ Shaded shade_pixel(const Renderer &R, const RasterOut &O, const Cam &
   const int has = __ldg(R.mesh_has + mesh);
   double tu = 0.0, tvv = 0.0;
   if (has & 1) {
-    tu = b0 * __ldg(R.uv + (size_t)vi[0] * 2) + b1 * __ldg(R.uv + (size_t)vi[1] * 2) +
-         b2 * __ldg(R.uv + (size_t)vi[2] * 2);
-    tvv = b0 * __ldg(R.uv + (size_t)vi[0] * 2 + 1) + b1 * __ldg(R.uv + (size_t)vi[1] * 2 + 1) +
-          b2 * __ldg(R.uv + (size_t)vi[2] * 2 + 1);
+    tu = b0 * __ldg(R.uv + (size_t)w.vi[0] * 2) + b1 * __ldg(R.uv + (size_t)w.vi[1] * 2) +
+         b2 * __ldg(R.uv + (size_t)w.vi[2] * 2);
+    tvv = b0 * __ldg(R.uv + (size_t)w.vi[0] * 2 + 1) + b1 * __ldg(R.uv + (size_t)w.vi[1] * 2 + 1) +
+          b2 * __ldg(R.uv + (size_t)w.vi[2] * 2 + 1);
   }
   const int Ht = __ldg(R.tex_hw + mesh * 2), Wt = __ldg(R.tex_hw + mesh * 2 + 1);
   int tx = (int)floor(tu * Wt), ty = (int)floor(tvv * Ht);
@@ -658,7 +796,7 @@ __device__ Shaded shade_pixel(const Renderer &R, const RasterOut &O, const Cam &
   ty = min(max(ty, 0), Ht - 1);
   const uint8_t *tex = R.tex + __ldg(R.tex_off + mesh) + ((size_t)(Ht - 1 - ty) * Wt + tx) * 3;
   Shaded s;
-  if (O.mode == RC_RENDER_TEXTURED) {
+  if (!LIT) {
 #pragma unroll
     for (int c = 0; c < 3; ++c) s.c[c] = ((float)__ldg(tex + c) / 255.0f) * 255.0f;  // :136-137
     return s;
@@ -668,9 +806,9 @@ __device__ Shaded shade_pixel(const Renderer &R, const RasterOut &O, const Cam &
     double no[3];
 #pragma unroll
     for (int k = 0; k < 3; ++k)
-      no[k] = b0 * __ldg(R.normals + (size_t)vi[0] * 3 + k) +
-              b1 * __ldg(R.normals + (size_t)vi[1] * 3 + k) +
-              b2 * __ldg(R.normals + (size_t)vi[2] * 3 + k);
+      no[k] = b0 * __ldg(R.normals + (size_t)w.vi[0] * 3 + k) +
+              b1 * __ldg(R.normals + (size_t)w.vi[1] * 3 + k) +
+              b2 * __ldg(R.normals + (size_t)w.vi[2] * 3 + k);
 #pragma unroll
     for (int r = 0; r < 3; ++r)
       n[r] = (double)pose[r * 4 + 0] * no[0] + (double)pose[r * 4 + 1] * no[1] +
@@ -793,7 +931,7 @@ raster_cover_kernel(Renderer R, int n_tiles) {
   __shared__ int s_big[RT_BIG_CAP];
   __shared__ int s_nbig;
   pdl_wait();
-  const int n_heavy = *R.heavy;
+  const int n_heavy = R.work_count[RT_WC_BINNED];
   if (threadIdx.x == 0) s_unit[0] = atomicAdd(R.work_count + RT_WC_TICKET_H, 1);
   __syncthreads();
   for (int par = 0;; par ^= 1) {
@@ -803,7 +941,7 @@ raster_cover_kernel(Renderer R, int n_tiles) {
       s_unit[par ^ 1] = atomicAdd(R.work_count + RT_WC_TICKET_H, 1);
       s_nbig = 0;
     }
-    const int work = R.work_list[unit];
+    const int work = R.bin_list[unit];
     const int b = work >> 16;
     const int tx0 = (work & 0xff) * RT_TW, ty0 = ((work >> 8) & 0xff) * RT_TH;
     const int tile = ((work >> 8) & 0xff) * R.tiles_x + (work & 0xff);
@@ -903,37 +1041,50 @@ raster_cover_kernel(Renderer R, int n_tiles) {
         }
       }
     }
-    unsigned long long *zw = R.zwin + (size_t)unit * RT_PIX;
+    // merge into the pair's dense z-winner blocks, where setup's micro-triangles already are
+    // (same keys, same order: the minimum is the winner whoever wrote it)
+    unsigned long long *zw = R.zwin + ((size_t)b * n_tiles + tile) * RT_PIX;
 #pragma unroll
-    for (int k = 0; k < RT_PIX / RT_CV_THREADS; ++k) zw[threadIdx.x + k * RT_CV_THREADS] = best[k];
+    for (int k = 0; k < RT_PIX / RT_CV_THREADS; ++k)
+      if (best[k] != ~0ull) atomicMin(zw + threadIdx.x + k * RT_CV_THREADS, best[k]);
     __syncthreads();  // z-buffer and queue reused by the next item; next ticket visible
   }
 }
 
-// 4c.  Grid-stride over the non-empty items, one thread per pixel, no shared memory.
+// 4c.  Grid-stride over the non-empty items, one thread per pixel, no shared memory.  Reads the
+// pixel's winning key from the pair's dense z-winner blocks and puts the "empty" key back, so
+// the blocks are all-empty again when the render ends (no clearing pass, no per-frame memset of
+// 2 KB per tile).
+template <bool LIT>
 __global__ void __launch_bounds__(RT_THREADS, 3)
 raster_resolve_kernel(Renderer R, const int32_t *__restrict__ cls_idx,
                       const float *__restrict__ poses, Cam cam, RasterOut O) {
   const int W = R.W, H = R.H;
   const int n_heavy = *R.heavy;
+  const int n_tiles = R.tiles_x * R.tiles_y;
   const size_t plane = (size_t)H * W;
   for (int unit = blockIdx.x; unit < n_heavy; unit += gridDim.x) {
     const int work = __ldg(R.work_list + unit);
     const int b = work >> 16;
+    const int tile = ((work >> 8) & 0xff) * R.tiles_x + (work & 0xff);
     const int x = (work & 0xff) * RT_TW + (threadIdx.x & (RT_TW - 1));
     const int y = ((work >> 8) & 0xff) * RT_TH + (threadIdx.x >> RT_TW_SHIFT);
     if (x >= W || y >= H) continue;
-    const unsigned long long key = R.zwin[(size_t)unit * RT_PIX + threadIdx.x];
+    unsigned long long *zp = R.zwin + ((size_t)b * n_tiles + tile) * RT_PIX + threadIdx.x;
+    const unsigned long long key = *zp;
     float dz = 0.f, cr = 0.f, cg = 0.f, cb = 0.f;
     int tid = -1;
     if (key != ~0ull) {
+      *zp = ~0ull;
       // readback linearisation, render_py_multi.py:139-145, float32 like numpy
       const float d = __uint_as_float((unsigned)(key >> 32));
       dz = (d == 1.0f) ? 0.f : O.lin_c0 / (O.lin_c1 - O.lin_c2 * (2.0f * d - 1.0f));
-      const TriRec rec = R.recs[(size_t)b * 2 * R.max_tris + (unsigned)key];
-      tid = rec.tri & RT_TRI_MASK;
+      tid = (int)((unsigned)key >> 1);
       if (O.image_chw || O.bgr_hwc) {
-        const Shaded s = shade_pixel(R, O, cam, __ldg(cls_idx + b), rec, poses + b * 12, b, x, y);
+        const int mesh = __ldg(cls_idx + b);
+        WinTri w;
+        load_winner(R, b, mesh, (unsigned)key, w);
+        const Shaded s = shade_pixel<LIT>(R, O, cam, mesh, w, poses + b * 12, b, x, y);
         cr = s.c[0];
         cg = s.c[1];
         cb = s.c[2];
@@ -975,7 +1126,7 @@ static void renderer_free(Renderer *r) {
   void *ptrs[] = {r->verts, r->uv, r->normals, r->tris, r->mesh_tri_off, r->mesh_vert_off, r->vtx,
                   r->mesh_has, r->tex,
                   r->tex_off, r->tex_hw, r->recs, r->tbox, r->clip_list, r->clip_box, r->zwin, r->work_count, r->tile_start, r->tile_fill,
-                  r->tile_list, r->work_list_b[0], r->work_list_b[1], r->heavy_count};
+                  r->tile_list, r->work_list_b[0], r->work_list_b[1], r->heavy_count, r->bin_list};
   for (void *p : ptrs)
     if (p) cudaFree(p);
   delete r;
@@ -1079,12 +1230,21 @@ int rc_renderer_create(const rc_mesh_desc *meshes, int n_meshes, int height, int
   RC_TRY(rc::dev_alloc(&r->tbox, (size_t)max_batch * max_tris));
   RC_TRY(rc::dev_alloc(&r->clip_list, (size_t)max_batch * max_tris));
   RC_TRY(rc::dev_alloc(&r->clip_box, (size_t)max_batch * max_tris));
-  RC_TRY(rc::dev_alloc(&r->work_count, (size_t)max_batch * n_tiles + rc::RT_WC_INTS));  // [header | tile counts]
+  // [header | tile counts of the call's B pairs | micro-triangle marks of the same pairs]
+  RC_TRY(rc::dev_alloc(&r->work_count, (size_t)2 * max_batch * n_tiles + rc::RT_WC_INTS));
   r->tile_count = r->work_count + rc::RT_WC_INTS;
+  RC_TRY(rc::dev_alloc(&r->bin_list, (size_t)max_batch * n_tiles));
   RC_TRY(rc::dev_alloc(&r->work_list_b[0], (size_t)max_batch * n_tiles));
   RC_TRY(rc::dev_alloc(&r->work_list_b[1], (size_t)max_batch * n_tiles));
   RC_TRY(rc::dev_alloc(&r->heavy_count, 2));
   RC_TRY(rc::dev_alloc(&r->zwin, (size_t)max_batch * n_tiles * rc::RT_PIX));
+  // all-empty; every render leaves it so (resolve puts the empty key back where it read a winner)
+  if (cudaMemset(r->zwin, 0xff, (size_t)max_batch * n_tiles * rc::RT_PIX * sizeof(unsigned long long)) !=
+          cudaSuccess ||
+      cudaMemset(r->heavy_count, 0, 2 * sizeof(int32_t)) != cudaSuccess) {
+    rc::renderer_free(r);
+    return rc::note_status(RC_ERR_CUDA);
+  }
   RC_TRY(rc::dev_alloc(&r->tile_start, (size_t)max_batch * (n_tiles + 1)));
   RC_TRY(rc::dev_alloc(&r->tile_fill, (size_t)max_batch * n_tiles));
   RC_TRY(rc::dev_alloc(&r->tile_list, (size_t)max_batch * r->list_cap));
@@ -1098,6 +1258,12 @@ int rc_renderer_create(const rc_mesh_desc *meshes, int n_meshes, int height, int
   RC_UP(r->tex, htex)
   RC_UP(r->tex_off, htoff) RC_UP(r->tex_hw, hhw)
 #undef RC_UP
+  // the memsets / copies above ran on the legacy default stream; the renders will come on the
+  // caller's (possibly non-blocking) streams
+  if (cudaDeviceSynchronize() != cudaSuccess) {
+    rc::renderer_free(r);
+    return rc::note_status(RC_ERR_CUDA);
+  }
   *handle = r;
   return rc::note_status(RC_OK);
 }
@@ -1169,7 +1335,8 @@ int rc_render_dev(void *handle, const rc_render_args *a) {
                                                       rc::RT_CV_THREADS, 0) != cudaSuccess ||
         cover_per_sm < 1)
       cover_per_sm = 4;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resolve_per_sm, rc::raster_resolve_kernel,
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resolve_per_sm,
+                                                      rc::raster_resolve_kernel<true>,
                                                       rc::RT_THREADS, 0) != cudaSuccess ||
         resolve_per_sm < 1)
       resolve_per_sm = 2;
@@ -1193,9 +1360,8 @@ int rc_render_dev(void *handle, const rc_render_args *a) {
   for (int i = 0; i < 3 && same; ++i) same = Rh.last_mean[i] == a->pixel_means[i];
   const bool incremental = a->incremental != 0 && same;
   Rh.have_prev = 0;  // until this call's launches are all issued
-  RC_CUDA_TRY(cudaMemsetAsync(R.work_count, 0,
-                              sizeof(int32_t) * ((size_t)B * n_tiles + rc::RT_WC_INTS), s));
-  RC_CUDA_TRY(cudaMemsetAsync(R.heavy, 0, sizeof(int32_t), s));
+  // (no memsets: the vertex pass zeroes this call's counters)
+  R.tile_touch = R.tile_count + (size_t)B * n_tiles;
   // 4a background first: a few CTAs per SM saturate the HBM write path and leave room beside them
   static int clear_ctas = 0;
   if (clear_ctas == 0) {
@@ -1209,16 +1375,14 @@ int rc_render_dev(void *handle, const rc_render_args *a) {
     rc::raster_clear_kernel<<<sm_count * clear_ctas, 256, 0, s>>>(R, O, B);
   dim3 gv((R.max_verts + 255) / 256, B);
   RC_CUDA_TRY(rc::launch_maybe_pdl(rc::raster_vertex_kernel, gv, dim3(256), 0, s, chain, R,
-                                   a->cls_idx, a->poses, cam));
+                                   a->cls_idx, a->poses, cam, n_tiles));
   const int per_block = 256 * rc::RT_SETUP_PER;
   dim3 gs((R.max_tris + per_block - 1) / per_block, B);
   RC_CUDA_TRY(rc::launch_maybe_pdl(rc::raster_setup_kernel, gs, dim3(256), 0, s, chain, R,
                                    a->cls_idx, n_tiles));
-  RC_CUDA_TRY(rc::launch_maybe_pdl(rc::raster_clip_kernel, dim3(32), dim3(128), 0, s, chain, R,
-                                   a->cls_idx, a->poses, cam, n_tiles));
   if ((st = mark(1)) != RC_OK) return st;
   RC_CUDA_TRY(rc::launch_maybe_pdl(rc::raster_scan_kernel, dim3(B), dim3(256), 0, s, chain, R,
-                                   n_tiles, a->status));
+                                   a->cls_idx, a->poses, cam, n_tiles, a->status));
   if ((st = mark(2)) != RC_OK) return st;
   dim3 gf((R.max_tris + 255) / 256, B);
   RC_CUDA_TRY(rc::launch_maybe_pdl(rc::raster_fill_kernel, gf, dim3(256), 0, s, chain, R,
@@ -1234,7 +1398,10 @@ int rc_render_dev(void *handle, const rc_render_args *a) {
   {
     long long g = (long long)sm_count * resolve_per_sm * 2;
     if (g > n_total) g = n_total;
-    rc::raster_resolve_kernel<<<(int)g, rc::RT_THREADS, 0, s>>>(R, a->cls_idx, a->poses, cam, O);
+    if (a->mode == RC_RENDER_TEXTURED)
+      rc::raster_resolve_kernel<false><<<(int)g, rc::RT_THREADS, 0, s>>>(R, a->cls_idx, a->poses, cam, O);
+    else
+      rc::raster_resolve_kernel<true><<<(int)g, rc::RT_THREADS, 0, s>>>(R, a->cls_idx, a->poses, cam, O);
   }
   if ((st = mark(4)) != RC_OK) return st;
   st = rc::check_launch();
@@ -1295,11 +1462,17 @@ int rc_render_stats(void *handle, int batch_size, void *stream, int64_t *out) {
   for (int b = 0; b < batch_size; ++b) entries += st[(size_t)b * (n_tiles + 1) + n_tiles];
   // live records (slots of absent triangles count only when the mesh has max_tris triangles:
   // stale boxes beyond a smaller mesh's triangles are never read by the passes)
-  for (size_t i = 0; i < bb.size(); ++i) recs += bb[i] != rc::RT_TBOX_NONE;
+  // (micro-triangles that went straight to the z-winner blocks count as records: out[2] = how many)
+  int64_t direct = 0;
+  for (size_t i = 0; i < bb.size(); ++i) {
+    recs += bb[i] != rc::RT_TBOX_NONE;
+    direct += bb[i] == rc::RT_TBOX_DIRECT;
+  }
   for (size_t i = 0; i < cb.size(); ++i)
     recs += (cb[i].x != rc::RT_TBOX_NONE) + (cb[i].y != rc::RT_TBOX_NONE);
   out[0] = recs;
   out[1] = entries;
+  out[2] = direct;
   return rc::note_status(RC_OK);
 }
 

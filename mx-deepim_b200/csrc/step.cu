@@ -35,9 +35,15 @@ int rc_compare_step_dev(const rc_compare_step_args *a) {
   if (B == 0) return rc::note_status(RC_OK);
   cudaStream_t s = static_cast<cudaStream_t>(a->stream);
   int st;
-  const bool do_loss = N > 0 && a->loss_sum;
+  // phases: 0 = everything in this call; else only the named parts (the caller orders them,
+  // e.g. the loss on a second stream beside the rasteriser: it reads poses and points only)
+  RC_REQUIRE(a->phases >= 0 && a->phases < 16, RC_ERR_INVALID_ARG);
+  const int ph = a->phases ? a->phases : 15;
+  const bool ph_loss = (ph & RC_STEP_PHASE_LOSS) != 0, ph_frame = (ph & RC_STEP_PHASE_FRAME) != 0,
+             ph_sample = (ph & RC_STEP_PHASE_SAMPLE) != 0, ph_ztb = (ph & RC_STEP_PHASE_ZT_BWD) != 0;
+  const bool do_loss = ph_loss && N > 0 && a->loss_sum;
   // training backward (cfg 5): d loss / d (rot_est, trans_est) with MakeLoss's grad_scale
-  const bool do_bwd = N > 0 && a->grad_rot && a->grad_trans;
+  const bool do_bwd = ph_loss && N > 0 && a->grad_rot && a->grad_trans;
   // test phase (deepIM_flownet.py:778-838): no GT flow, no loss -- flow == NULL skips both the
   // flow kernel and the flow planes of the resampler
   const bool do_flow = a->flow != nullptr && a->valid != nullptr;
@@ -71,7 +77,7 @@ int rc_compare_step_dev(const rc_compare_step_args *a) {
   const bool sparse = a->frame_renderer != nullptr;
   rc::FrameItems F;
   bool flow_tiles = false;  // flow on the tiles only (else the dense kernel writes the planes)
-  if (sparse) {
+  if (sparse && (ph_frame || ph_sample)) {
     RC_REQUIRE(a->observed_box != nullptr, RC_ERR_INVALID_ARG);
     if ((st = rc::renderer_frame_items(a->frame_renderer, &F)) != RC_OK) return st;
     RC_REQUIRE(F.H == H && F.W == W && B <= F.max_batch, RC_ERR_INVALID_ARG);
@@ -106,7 +112,9 @@ int rc_compare_step_dev(const rc_compare_step_args *a) {
       PdlScope scope(do_bwd);
       if ((st = loss()) != RC_OK) return st;
     }
-    if (!sparse) {
+    if (!ph_frame) {
+      // (the caller issues the frame phase)
+    } else if (!sparse) {
       {
         PdlScope scope(do_loss || do_bwd);
         if ((st = bbox()) != RC_OK) return st;
@@ -135,14 +143,15 @@ int rc_compare_step_dev(const rc_compare_step_args *a) {
     }
   } else {
     if ((st = rc::mark(a->marks, 0, s)) != RC_OK) return st;
-    if (do_flow && !flow_tiles && (st = dense_flow()) != RC_OK) return st;
-    if (sparse && (st = tiles()) != RC_OK) return st;
+    if (ph_frame && do_flow && !flow_tiles && (st = dense_flow()) != RC_OK) return st;
+    if (ph_frame && sparse && (st = tiles()) != RC_OK) return st;
     if ((st = rc::mark(a->marks, 1, s)) != RC_OK) return st;
-    if ((st = sparse ? boxes() : bbox()) != RC_OK) return st;
+    if (ph_frame && (st = sparse ? boxes() : bbox()) != RC_OK) return st;
   }
   if ((st = rc::mark(a->marks, 2, s)) != RC_OK) return st;
+  if (ph_sample) {
   // (3) one resampler launch: 3 masks + 6 image channels + 2 flow + 2 flow-weight planes
-  rc_zoom_group g[7];
+  rc_zoom_group g[9];
   auto set = [&](int i, const float *src, float *dst, int ch, int pre, int post, int flags) {
     g[i].src = src;
     g[i].dst = dst;
@@ -169,6 +178,11 @@ int rc_compare_step_dev(const rc_compare_step_args *a) {
   if (do_flow && a->zoom_flow_weights)
     set(n++, a->valid, a->zoom_flow_weights, 2, RC_PRE_NONE, RC_POST_ROUND_M045,
         RC_ZOOM_SRC_BROADCAST | sp);
+  // INPUT_DEPTH (deepIM_flownet.py:669-681): ZoomDepth's two planes ride in the same launch
+  if (a->depth_observed && a->zoom_depth_observed)
+    set(n++, a->depth_observed, a->zoom_depth_observed, 1, RC_PRE_NONE, RC_POST_NONE, 0);
+  if (a->zoom_depth_rendered)
+    set(n++, a->depth_rendered, a->zoom_depth_rendered, 1, RC_PRE_NONE, RC_POST_NONE, sp);
   rc::ZoomSparse zs;
   if (sp) {
     zs.tile_count = F.tile_count;
@@ -179,13 +193,14 @@ int rc_compare_step_dev(const rc_compare_step_args *a) {
   }
   st = rc::launch_zoom_sample(a->zoom_factor, 0, g, n, B, H, W, sp ? &zs : nullptr, a->stream);
   if (st != RC_OK) return st;
+  }  // ph_sample
   if ((st = rc::mark(a->marks, 3, s)) != RC_OK) return st;
   if ((st = rc::mark(a->marks, 4, s)) != RC_OK) return st;
   // Transform3D + point-matching loss (already issued when overlapped)
   if (serial && do_loss && (st = loss()) != RC_OK) return st;
   if (serial && do_bwd && (st = loss_bwd()) != RC_OK) return st;
   // invZoomTrans.backward (zoom_trans.py:50-76): needs this step's zoom factor
-  if (do_bwd && a->grad_zoom_trans) {
+  if (ph_ztb && N > 0 && a->grad_rot && a->grad_trans && a->grad_zoom_trans) {
     st = rc_zoom_trans_dev(a->zoom_factor, a->grad_trans, a->grad_zoom_trans, B, 1,
                            a->zoom_grad ? 1 : 0, 0, a->stream);
     if (st != RC_OK) return st;

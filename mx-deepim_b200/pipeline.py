@@ -65,8 +65,12 @@ class CompareStep(object):
                  num_points=synth.NUM_3D_SAMPLE, K=synth.K_LINEMOD, pixel_means=synth.PIXEL_MEANS,
                  T_means=(0, 0, 0), T_stds=(1, 1, 1), rot_coord="CAMERA", loss_type="L1",
                  norm_term=synth.NORMALIZE_3D_POINT, want_loss_map=True, backward=False,
-                 lw_pm=1.0, zoom_grad=False):
-        """backward=True adds the training backward leg to every step: d loss / d rot_est,
+                 lw_pm=1.0, zoom_grad=False, input_depth=False):
+        """input_depth=True (cfg.network.INPUT_DEPTH, deepIM_flownet.py:669-681 / :827-835): the
+        step also zooms `depth_observed` and `depth_rendered` (ZoomDepth) as two more planes of
+        its one resampler launch; bind() then needs x["depth_observed"].
+
+        backward=True adds the training backward leg to every step: d loss / d rot_est,
         d loss / d trans_est (Transform3D.backward under MakeLoss(grad_scale=LW_PM/N),
         transform3d.py:120-327, deepIM_flownet.py:493-498) and the gradient the network's
         zoomed translation head receives (invZoomTrans.backward, zoom_trans.py:50-76,
@@ -96,6 +100,9 @@ class CompareStep(object):
         self.zoom_flow = torch.empty((B, 2, Hh, Ww), **f)
         self.zoom_flow_weights = torch.empty((B, 2, Hh, Ww), **f)
         self.zoom_trans_gt = torch.empty((B, 3), **f)
+        self.input_depth = bool(input_depth)
+        self.zoom_depth_observed = torch.empty((B, 1, Hh, Ww), **f) if input_depth else None
+        self.zoom_depth_rendered = torch.empty((B, 1, Hh, Ww), **f) if input_depth else None
         self.loss_map = torch.empty((B, 3, N), **f) if want_loss_map else None
         self.loss_sum = torch.empty((B,), **f)
         self.backward = bool(backward)
@@ -156,6 +163,14 @@ class CompareStep(object):
             a.loss_src_pose = lsp.data_ptr()
         if test_phase:
             a.mask_gt_observed = x["mask_observed"].data_ptr()
+        if self.input_depth:
+            t = x["depth_observed"]
+            C.check_tensor("depth_observed", t)
+            if t.device != self.device:
+                raise ValueError("depth_observed is on %s, step is on %s" % (t.device, self.device))
+            a.depth_observed = t.data_ptr()
+            a.zoom_depth_observed = self.zoom_depth_observed.data_ptr()
+            a.zoom_depth_rendered = self.zoom_depth_rendered.data_ptr()
         skip = ("flow", "valid", "zoom_flow", "zoom_flow_weights", "zoom_trans_gt", "loss_map",
                 "loss_sum", "zoom_mask_gt_observed", "grad_rot", "grad_trans",
                 "grad_zoom_trans") if test_phase else ()
@@ -230,6 +245,8 @@ class CompareStep(object):
             "point_matching_loss": self.loss_map, "point_matching_loss_sum": self.loss_sum,
             "grad_rot": self.grad_rot, "grad_trans": self.grad_trans,
             "grad_zoom_trans": self.grad_zoom_trans,
+            "zoom_depth_observed": self.zoom_depth_observed,
+            "zoom_depth_rendered": self.zoom_depth_rendered,
         }
 
 
@@ -403,8 +420,15 @@ class RefineLoop(object):
 
     def __init__(self, meshes, batch, device, K=synth.K_LINEMOD, pixel_means=synth.PIXEL_MEANS,
                  num_points=synth.NUM_3D_SAMPLE, damping=0.5, predict=None, seed=0,
-                 backward=False, lw_pm=1.0, sparse=True):
-        """sparse=True: the compare step takes the rendered crop box and the GT flow from the
+                 backward=False, lw_pm=1.0, sparse=True, side_stream=True):
+        """side_stream=True: the point-matching loss (+ backward) of an iteration is issued on a
+        second stream right after the pose update -- it reads poses and points only, so it runs
+        beside the rasteriser's latency-bound passes instead of in front of the compare step --
+        and the ZoomTrans backward beside the resampler (rc_compare_step_args.phases).  The
+        iteration joins the side stream before it ends; inside a captured loop the fork / join
+        become edges of the graph.  Results are identical (same kernels, same inputs).
+
+        sparse=True: the compare step takes the rendered crop box and the GT flow from the
         16x16 tiles the renderer reports as covered (rc_compare_step_args.frame_renderer,
         csrc/frame.cu) instead of streaming the ~90 % background of both planes; results are
         identical (tests/test_refine_gpu.py)."""
@@ -452,7 +476,9 @@ class RefineLoop(object):
         self._box8 = torch.empty((B, 8), dtype=torch.int32, device=self.device)
         self._have_batch = False
         self.damping = float(damping)
-        self.predict = predict if predict is not None else self._damped_gt
+        self.predict = predict  # None: the damped-GT stand-in, fused into the pose update's launch
+        self.side = torch.cuda.Stream(device=self.device) if side_stream else None
+        self._ev_fork, self._ev_zf, self._ev_join = (torch.cuda.Event() for _ in range(3))
         g = torch.Generator(device="cpu").manual_seed(int(seed))
         self.noise_q = (0.01 * torch.randn((8, B, 4), generator=g)).to(self.device)
         self.noise_t = (0.005 * torch.randn((8, B, 3), generator=g)).to(self.device)
@@ -471,19 +497,9 @@ class RefineLoop(object):
                      rot_est=self.rot_est, trans_est=self.trans_est, trans_gt=self.trans_gt)
             self.bound[par] = self.step.bind(x)
             self._bind_frame(self.bound[par])
-        # stand-in + pose update + 8 render kernels (clear, vertex, setup, clip, scan, fill, cover,
-        # resolve) + step
-        self.launches_per_iteration = 1 + 1 + 8 + self.step.launches_per_step
-
-    def _damped_gt(self, it, rot_gt, trans_gt):
-        """Stand-in for the FlowNet heads: move `damping` of the way to the target, plus noise
-        (one launch: rc_standin_predict_dev)."""
-        with torch.cuda.device(self.device):
-            st = _lib.load().rc_standin_predict_dev(
-                rot_gt.data_ptr(), trans_gt.data_ptr(), self.noise_q[it % 8].data_ptr(),
-                self.noise_t[it % 8].data_ptr(), self.damping, self.rot_est.data_ptr(),
-                self.trans_est.data_ptr(), self.B, _lib.stream_ptr(None))
-        _lib.check(st, "rc_standin_predict_dev")
+        # pose update (+ fused stand-in) + 7 render kernels (clear, vertex, setup, scan, fill,
+        # cover, resolve) + step
+        self.launches_per_iteration = (1 if predict is None else 2) + 7 + self.step.launches_per_step
 
     def set_batch(self, host):
         """Observed side of the batch + initial poses.  `host`: numpy dict with image_observed,
@@ -530,16 +546,45 @@ class RefineLoop(object):
         self.trans_gt.copy_(self.trans0)
         self.cur = 0
 
+    def _pose_update(self, it, nxt):
+        """pose[cur] (+ prediction) -> pose[nxt], new labels, KT; with the default stand-in the
+        prediction is made at the head of the same launch."""
+        out = (self.pose[nxt], self.rot_gt, self.trans_gt, self.KT)
+        if self.predict is not None:
+            self.predict(it, self.rot_gt, self.trans_gt)
+            pose_update(self.pose[self.cur], self.rot_est, self.trans_est, self.obs["tgt_pose"],
+                        self.K, out=out)
+            return
+        with torch.cuda.device(self.device):
+            st = _lib.load().rc_pose_update_standin_dev(
+                self.pose[self.cur].data_ptr(), self.rot_gt.data_ptr(), self.trans_gt.data_ptr(),
+                self.noise_q[it % 8].data_ptr(), self.noise_t[it % 8].data_ptr(), self.damping,
+                self.rot_est.data_ptr(), self.trans_est.data_ptr(), self.obs["tgt_pose"].data_ptr(),
+                C.device_const(self.K, self.device).data_ptr(), _lib.f3((0, 0, 0)),
+                _lib.f3((1, 1, 1)), _lib.ROT_COORD["camera"], out[0].data_ptr(),
+                out[1].data_ptr(), out[2].data_ptr(), out[3].data_ptr(), self.B,
+                _lib.stream_ptr(None))
+        _lib.check(st, "rc_pose_update_standin_dev")
+
     def iterate(self, it, marks=None, render_marks=None):
-        """One refinement iteration on the current stream (no synchronisation)."""
-        self.predict(it, self.rot_gt, self.trans_gt)
+        """One refinement iteration on the current stream (no host synchronisation)."""
         nxt = 1 - self.cur
         if self.renderer.serial != getattr(self, "_my_serial", -1):
             # somebody else rendered through this renderer since our last frame: its item lists no
             # longer describe what the flow planes / zoomed outputs hold -> one dense step
             self._flow_tracks = False
-        pose_update(self.pose[self.cur], self.rot_est, self.trans_est, self.obs["tgt_pose"], self.K,
-                    out=(self.pose[nxt], self.rot_gt, self.trans_gt, self.KT))
+        self._pose_update(it, nxt)
+        a = self.bound[nxt]
+        # the flow / bbox / loss marks serialise the step (clean per-kernel times): one call, one
+        # stream; the resampler's marks (2, 3) do not and go with the SAMPLE phase
+        serial = marks is not None and any(marks[i] is not None for i in (0, 1, 4, 5))
+        split = self.side is not None and not serial and bool(a.loss_sum or a.grad_rot)
+        if split:
+            main = torch.cuda.current_stream(self.device)
+            self._ev_fork.record(main)
+            self.side.wait_event(self._ev_fork)
+            a.phases = _lib.RC_STEP_PHASE_LOSS
+            self.step.run(None, args=a, stream=self.side)
         self.renderer.render_batch(self.cls, self.pose[nxt], pixel_means=self.render_means,
                                    want=("depth", "image", "mask"),
                                    out={"depth": self.depth_rendered, "image": self.image_rendered,
@@ -547,10 +592,23 @@ class RefineLoop(object):
                                    incremental=True)  # the loop owns these three buffers
         self._my_serial = self.renderer.serial
         self.cur = nxt
-        a = self.bound[nxt]
         if self.sparse:
             a.outputs_track_frames = 1 if self._flow_tracks else 0
-        self.step.run(None, args=a, marks=marks)
+        if split:
+            a.phases = _lib.RC_STEP_PHASE_FRAME
+            self.step.run(None, args=a)
+            self._ev_zf.record(main)
+            a.phases = _lib.RC_STEP_PHASE_SAMPLE
+            self.step.run(None, args=a, marks=marks)
+            self.side.wait_event(self._ev_zf)
+            a.phases = _lib.RC_STEP_PHASE_ZT_BWD
+            self.step.run(None, args=a, stream=self.side)
+            self._ev_join.record(self.side)
+            main.wait_event(self._ev_join)
+            a.phases = 0
+        else:
+            a.phases = 0
+            self.step.run(None, args=a, marks=marks)
         self._flow_tracks = True  # one step per render: the flow planes follow the frames
 
     def run(self, iterations=4, marks=None):

@@ -219,11 +219,11 @@ class DeviceRenderer(object):
                 "cover more tile entries than 8 * max_triangles + 16 * tiles; the frame is incomplete")
 
     def stats(self, batch):
-        out = (ctypes.c_int64 * 2)()
+        out = (ctypes.c_int64 * 3)()
         with torch.cuda.device(self.device):
             _lib.check(_lib.load().rc_render_stats(self.handle, batch, _lib.stream_ptr(), out),
                        "rc_render_stats")
-        return {"records": int(out[0]), "tile_entries": int(out[1])}
+        return {"records": int(out[0]), "tile_entries": int(out[1]), "direct": int(out[2])}
 
     def _one(self, idx, R, t, K, **kw):
         cls = torch.tensor([int(idx)], dtype=torch.int32, device=self.device)

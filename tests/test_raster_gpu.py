@@ -99,7 +99,8 @@ def test_render_batch_fused_post(cuda_device):
         assert np.array_equal(image[i], ref_img.astype(np.float32))
         assert np.array_equal(mask[i, 0], (depth[i, 0] > 0.2).astype(np.float32))
     st = r.dev.stats(7)
-    assert st["records"] > 0 and st["tile_entries"] >= st["records"]
+    # micro-triangles go straight to the z-winner blocks: neither record nor tile-list entry
+    assert st["records"] > 0 and st["tile_entries"] >= st["records"] - st["direct"] >= 0
 
 
 def test_near_plane_clipping_and_offscreen(cuda_device):

@@ -254,3 +254,30 @@ def test_sparse_frame_step_equals_dense_step(cuda_device):
         marks = [_lib.Event() for _ in range(_lib.RC_STEP_MARKS)]
         lp.iterate(2, marks=marks)
     compare("marks")
+
+
+def test_refine_loop_side_stream_equals_single_stream(cuda_device):
+    """The loss on a second stream beside the rasteriser (and the ZoomTrans backward beside the
+    resampler) changes the schedule, not one bit of any output."""
+    import torch
+
+    from mx_deepim_b200 import pipeline, synth
+
+    rng = np.random.default_rng(14)
+    meshes = [synth.make_mesh(rng, level=3, kind=1), synth.make_mesh(rng, level=2, kind=0)]
+    B = 5
+    outs = []
+    for side in (False, True):
+        loop = pipeline.RefineLoop(meshes, B, cuda_device, seed=8, backward=True, side_stream=side)
+        host = pipeline.make_refine_batch(meshes, B, 126, renderer=loop.renderer)
+        loop.set_batch(host)
+        loop.run(3)
+        torch.cuda.synchronize()
+        loop.check_status()
+        outs.append({"depth": loop.depth_rendered.clone(), "pose": loop.pose[loop.cur].clone(),
+                     "loss": loop.step.loss_sum.clone(), "zf": loop.step.zoom_factor.clone(),
+                     "zimg": loop.step.zoom_image_rendered.clone(),
+                     "zflow": loop.step.zoom_flow.clone(), "g_rot": loop.step.grad_rot.clone(),
+                     "g_zt": loop.step.grad_zoom_trans.clone(), "rot_est": loop.rot_est.clone()})
+    for k in outs[0]:
+        assert torch.equal(outs[0][k], outs[1][k]), k

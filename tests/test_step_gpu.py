@@ -185,3 +185,67 @@ def test_compare_step_full_size_batch_permutation_property(cuda_device, B, backw
         assert a.shape[0] == B, k
         assert np.array_equal(a[perm].view(np.uint8), b.view(np.uint8)), k
     assert outs[0]["flow_weights_valid"].sum() > 1000 * B  # the batch is not degenerate
+
+
+def test_compare_step_input_depth_planes(cuda_device):
+    """cfg.network.INPUT_DEPTH (deepIM_flownet.py:669-681): ZoomDepth's two planes ride in the
+    step's one resampler launch (rc_compare_step_args.depth_observed / zoom_depth_*) and equal
+    the ZoomDepth oracle; every other output is unchanged."""
+    import torch
+
+    from mx_deepim_b200 import pipeline, synth
+
+    B = 3
+    host = synth.make_compare_batch(B, seed=81, occlusion=True)
+    step = pipeline.CompareStep(B, cuda_device, input_depth=True)
+    x = step.to_device(host, non_blocking=False)
+    x["depth_observed"] = x["depth_gt_observed"]
+    step.run(x)
+    torch.cuda.synchronize()
+    out = {k: (v.cpu().numpy() if v is not None else None) for k, v in step.outputs().items()}
+    ref = _oracle(host, synth)
+    _check(out, ref, False)
+    zo, zr = zoom_np.zoom_depth_forward(ref["zm"][3], host["depth_gt_observed"], host["depth_rendered"])
+    assert np.abs(out["zoom_depth_observed"] - zo).max() <= 1e-4
+    assert np.abs(out["zoom_depth_rendered"] - zr).max() <= 1e-4
+
+
+def test_compare_step_phases_equal_one_call(cuda_device):
+    """rc_compare_step_args.phases: the loss on a second stream, frame -> sample on the first,
+    the ZoomTrans backward behind both -- bit-identical to the single call."""
+    import torch
+
+    from mx_deepim_b200 import _lib, pipeline, synth
+
+    B = 4
+    host = synth.make_compare_batch(B, seed=82)
+    one = pipeline.CompareStep(B, cuda_device, backward=True, lw_pm=LW_PM, zoom_grad=True)
+    x = one.to_device(host, non_blocking=False)
+    one.run(x)
+    torch.cuda.synchronize()
+    want = {k: v.clone() for k, v in one.outputs().items() if v is not None}
+    two = pipeline.CompareStep(B, cuda_device, backward=True, lw_pm=LW_PM, zoom_grad=True)
+    a = two.bind(x)
+    main, side = torch.cuda.current_stream(), torch.cuda.Stream(device=cuda_device)
+    fork, zf, join = torch.cuda.Event(), torch.cuda.Event(), torch.cuda.Event()
+    fork.record(main)
+    side.wait_event(fork)
+    a.phases = _lib.RC_STEP_PHASE_LOSS
+    two.run(None, args=a, stream=side)
+    a.phases = _lib.RC_STEP_PHASE_FRAME
+    two.run(None, args=a)
+    zf.record(main)
+    a.phases = _lib.RC_STEP_PHASE_SAMPLE
+    two.run(None, args=a)
+    side.wait_event(zf)
+    a.phases = _lib.RC_STEP_PHASE_ZT_BWD
+    two.run(None, args=a, stream=side)
+    join.record(side)
+    main.wait_event(join)
+    torch.cuda.synchronize()
+    for k, v in two.outputs().items():
+        if v is not None:
+            assert torch.equal(v, want[k]), k
+    a.phases = 16
+    with pytest.raises(Exception):
+        two.run(None, args=a)
