@@ -125,23 +125,57 @@ def test_refine_loop_at_baseline_shape(cuda_device, cfg):
     err0 = np.abs(host["src_pose"] - host["tgt_pose"]).max(axis=(1, 2))
     err4 = np.abs(loop.pose[loop.cur].cpu().numpy() - host["tgt_pose"]).max(axis=(1, 2))
     assert np.median(err4) < 0.35 * np.median(err0)
+    def direct_grads():
+        """rc_pm_loss_bwd_dev called directly on the loop's final (rot_est, trans_est, pre-update
+        pose): what the fused step's backward leg must hold, whichever stream / graph ran it."""
+        from mx_deepim_b200 import _lib
+
+        stp, o = loop.step, loop.obs
+        gr, gt = torch.empty_like(stp.grad_rot), torch.empty_like(stp.grad_trans)
+        rc = _lib.load().rc_pm_loss_bwd_dev(
+            o["point_cloud_model"].data_ptr(), o["point_cloud_observed"].data_ptr(),
+            o["point_cloud_weights"].data_ptr(), loop.rot_est.data_ptr(), loop.trans_est.data_ptr(),
+            loop.pose[1 - loop.cur].data_ptr(), _lib.f3((0, 0, 0)), _lib.f3((1, 1, 1)),
+            stp.rot_coord, stp.loss_type, stp.norm_term, 1.0, stp.grad_scale, gr.data_ptr(),
+            gt.data_ptr(), B, stp.N, _lib.stream_ptr(None))
+        assert rc == 0
+        torch.cuda.synchronize()
+        return gr, gt
+
+    if sh["backward"]:
+        gr, gt = direct_grads()
+        assert torch.equal(gr, loop.step.grad_rot) and torch.equal(gt, loop.step.grad_trans), "eager"
     # ---- the same loop as a CUDA-graph replay: bit-identical final state
     eager = {"pose": loop.pose[loop.cur].clone(), "depth": loop.depth_rendered.clone(),
-             "image": loop.image_rendered.clone()}
+             "image": loop.image_rendered.clone(), "rot_est": loop.rot_est.clone(),
+             "trans_est": loop.trans_est.clone(), "pose_prev": loop.pose[1 - loop.cur].clone()}
     for k, v in loop.step.outputs().items():
         if v is not None:
             eager[k] = v.clone()
+    # the snapshot's clones run on the default stream; the stream below does not wait for it by
+    # itself, and the captured loop's first launches overwrite what is still being cloned
+    torch.cuda.synchronize()
     s = torch.cuda.Stream(device=cuda_device)
     with torch.cuda.stream(s):
         loop.capture(None, iters)
         for rep in range(2):
             loop.replay()
             s.synchronize()
-            got = {"pose": loop.pose[loop.cur], "depth": loop.depth_rendered, "image": loop.image_rendered}
+            if sh["backward"]:
+                gr, gt = direct_grads()
+                assert torch.equal(gr, loop.step.grad_rot) and torch.equal(gt, loop.step.grad_trans), rep
+            got = {"pose": loop.pose[loop.cur], "depth": loop.depth_rendered, "image": loop.image_rendered,
+                   "rot_est": loop.rot_est, "trans_est": loop.trans_est,
+                   "pose_prev": loop.pose[1 - loop.cur]}
             got.update({k: v for k, v in loop.step.outputs().items() if v is not None})
             for k in eager:
                 x, y = eager[k], got[k]
                 if x.dtype == torch.float32:
                     x, y = x.view(torch.int32), y.view(torch.int32)
-                assert torch.equal(x, y), (cfg, rep, k)
+                if not torch.equal(x, y):
+                    bad = (x != y).reshape(x.shape[0], -1).any(dim=1)
+                    rows = bad.nonzero().flatten()
+                    raise AssertionError((cfg, rep, k, "pairs that differ: %d of %d, first %s"
+                                          % (int(bad.sum()), x.shape[0], rows[:8].tolist()),
+                                          eager[k][rows[:2]].tolist(), got[k][rows[:2]].tolist()))
     loop.check_status()
