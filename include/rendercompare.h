@@ -115,6 +115,23 @@ int rc_zoom_factor_dev(const float *obs, const float *rend, const float *src_pos
                        int32_t *bbox, int32_t *workspace, int batch_size,
                        int channels, int height, int width, int mode, void *stream);
 
+/* The same kernel for callers that cannot allocate device memory (CUDA graph capture, tight
+ * serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Arguments and results as rc_zoom_factor_dev, minus
+ * `workspace`: the scratch is a static device array inside the library
+ * (RC_ZF_NOALLOC_MAX_BATCH x RC_ZF_WS_INTS int32 = 160 KB per GPU, held until the process exits),
+ * cleared by a stream-ordered memset in front of every launch.  Calls no cudaMalloc / cudaFree /
+ * allocating routine.  batch_size > RC_ZF_NOALLOC_MAX_BATCH returns RC_ERR_CAPACITY ("capacity
+ * exceeded") and launches nothing.  Every call on a device shares the array: calls that overlap
+ * on the GPU (different streams without an ordering between them) RACE -- order them, or use
+ * rc_zoom_factor_dev with one workspace per stream. */
+#define RC_ZF_NOALLOC_MAX_BATCH 4096
+int rc_zoom_factor_noalloc_dev(const float *obs, const float *rend, const float *src_pose,
+                               const float *K, const float *pixel_means, float *zoom_factor,
+                               int32_t *bbox, int batch_size, int channels, int height, int width,
+                               int mode, void *stream);
+int rc_zoom_factor_noalloc_max_batch(void); /* = RC_ZF_NOALLOC_MAX_BATCH */
+
 /* One resampled plane family.  `src`/`dst` point at [B,channels,H,W] tensors;
  * every channel of the family gets the same pre/post operation.            */
 typedef struct rc_zoom_group {

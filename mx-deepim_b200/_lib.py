@@ -15,6 +15,7 @@ PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(PKG_DIR, "librendercompare.so")
 
 RC_OK = 0
+RC_ERR_INVALID_ARG, RC_ERR_CUDA, RC_ERR_UNALIGNED, RC_ERR_CAPACITY = 1, 2, 3, 4
 # enums mirrored from include/rendercompare.h
 RC_ZF_MASK, RC_ZF_IMAGE = 0, 1
 RC_PRE_NONE, RC_PRE_THRESH02, RC_PRE_ADD_MEAN = 0, 1, 2
@@ -125,6 +126,9 @@ SIGNATURES = {
     "rc_flow_dev": (c_int, [_P, _P, _P, _P, _P, _P, c_int, c_int, c_int, _P]),
     "rc_zoom_factor_dev": (c_int, [_P, _P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int,
                                    c_int, _P]),
+    "rc_zoom_factor_noalloc_dev": (c_int, [_P, _P, _P, _P, _P, _P, _P, c_int, c_int, c_int, c_int,
+                                           c_int, _P]),
+    "rc_zoom_factor_noalloc_max_batch": (c_int, []),
     "rc_zoom_sample_dev": (c_int, [_P, c_int, POINTER(rc_zoom_group), c_int, c_int, c_int, c_int,
                                    _P]),
     "rc_zoom_trans_dev": (c_int, [_P, _P, _P, c_int, c_int, c_int, c_int, _P]),
