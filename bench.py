@@ -307,7 +307,7 @@ class CpuReference(object):
                 meshes = [synth.make_mesh(rng, level=cfg["level"]) for _ in range(cfg["meshes"])]
             if host is None:
                 host = pipeline.make_refine_batch(meshes, self.pairs, BASE_SEED + config,
-                                                  occlusion=cfg["occlusion"],
+                                                  occlusion=cfg["occlusion"], mask_policy="box_gt",
                                                   render_fn=_oracle_render_fn(meshes))
             else:
                 self.pairs = min(self.pairs, host["src_pose"].shape[0])
@@ -517,7 +517,8 @@ def run_loop(args, rank, world, local_rank):
         sampler.start()
     loop = pipeline.RefineLoop(meshes, B, dev, seed=rank, backward=cfg["backward"])
     host = pipeline.make_refine_batch(meshes, B, shard.rank_seed(BASE_SEED + args.config, rank),
-                                      renderer=loop.renderer, occlusion=cfg["occlusion"])
+                                      renderer=loop.renderer, occlusion=cfg["occlusion"],
+                                      mask_policy="box_gt")
     loop.set_batch(host)
     K = max(ITERS, ((args.steps + ITERS - 1) // ITERS) * ITERS)  # whole loops
     n_loops = K // ITERS
@@ -581,7 +582,7 @@ def run_loop(args, rank, world, local_rank):
     loss_checksum = float(loop.step.loss_sum.double().sum().item())
 
     # ------------------------------------------------ end-to-end arm (`e2e`): host buffers
-    packed = pipeline.pack_refine_batch(host)
+    packed = pipeline.pack_refine_batch(host, mask_policy="box_gt")
     packed2 = {k: v.flip(0).contiguous().pin_memory() for k, v in packed.items()}  # a second host batch
     feed = pipeline.LoopFeed(loop, packed, iterations=ITERS, use_graph=not args.no_graph)
     sets = [packed, packed2]
@@ -682,7 +683,9 @@ def run_loop(args, rank, world, local_rank):
                     "loops": Le, "steps": Le * ITERS, "pose_checksum": pose_checksum,
                     "h2d_gbs_all_ranks": h2d_gbs,
                     "feed": "pipeline.LoopFeed: observed side in storage formats (u8 BGR image, u16 mm "
-                            "depth, u8 label + mask, model points, poses) from page-locked host memory, "
+                            "depth, u8 label, model points, poses; mask_observed = TRAIN.INIT_MASK box_gt "
+                            "derived from the label on the device, as the reference's loader derives it on "
+                            "the host) from page-locked host memory, "
                             "uploaded ONCE per 4-iteration loop on a copy stream (overlaps the previous "
                             "loop), decoded on device; the rendered side never crosses PCIe; D2H of "
                             "refined poses + loss sums per loop",

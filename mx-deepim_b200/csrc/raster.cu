@@ -43,6 +43,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
 #include <vector>
 
 #include "common.cuh"
@@ -99,6 +100,7 @@ struct Renderer {
   int32_t *tile_count, *tile_start, *tile_fill;  // [max_batch][n_tiles (+1)]
   int32_t *tile_touch;                       // [B][n_tiles] this call's "a micro-triangle wrote here" marks (behind tile_count)
   int32_t *bin_list;                         // [max_batch * n_tiles] the items that also have a tile list (coverage pass)
+  int32_t *bin_tri, *bin_n;                  // [max_batch][max_tris], [max_batch]: the pair's triangles that got a record (fill pass)
   int32_t *tile_list;                        // [max_batch][list_cap]
   int32_t *work_count;                       // [RT_WC_INTS] header (see RT_WC_*), then tile_count
   unsigned long long *zwin;                  // [max_batch][n_tiles][RT_PIX] winning keys; all ~0 between frames (resolve resets what it reads)
@@ -401,6 +403,7 @@ raster_vertex_kernel(Renderer R, const int32_t *__restrict__ cls_idx,
   }
   if (b == 0 && v < RT_WC_INTS) R.work_count[v] = 0;
   if (b == 0 && v == RT_WC_INTS) *R.heavy = 0;
+  if (v == 0) R.bin_n[b] = 0;
   const int mesh = __ldg(cls_idx + b);
   const int v_off = __ldg(R.mesh_vert_off + mesh);
   if (v >= __ldg(R.mesh_vert_off + mesh + 1) - v_off) return;
@@ -491,6 +494,17 @@ raster_setup_kernel(Renderer R, const int32_t *__restrict__ cls_idx, int n_tiles
       }
     }
     if (t < R.max_tris) tbox[t] = tb[k];
+    // the few triangles with a record (a dense mesh: ~3 %) go on the pair's list for the fill
+    // pass, one atomic per warp
+    const bool binned = tb[k] != RT_TBOX_NONE && tb[k] != RT_TBOX_DIRECT;
+    const unsigned bal = __ballot_sync(0xffffffffu, binned);
+    if (bal) {
+      const int lane = threadIdx.x & 31, leader = __ffs(bal) - 1;
+      int base = 0;
+      if (lane == leader) base = atomicAdd(R.bin_n + b, __popc(bal));
+      base = __shfl_sync(0xffffffffu, base, leader);
+      if (binned) R.bin_tri[(size_t)b * R.max_tris + base + __popc(bal & ((1u << lane) - 1u))] = t;
+    }
   }
   // count the tiles each record overlaps (warp-aggregated)
 #pragma unroll
@@ -620,29 +634,37 @@ raster_scan_kernel(Renderer R, const int32_t *__restrict__ cls_idx,
 }
 
 // ------------------------------------------------------------------- 3. fill
-// grid = (ceil(max_tris / 256), B); one thread per triangle: reads its packed tile box (4 bytes)
-// and places record slot 2t; the pieces of near-clipped triangles (slots 2t, 2t + 1 of the few
-// triangles on the clip list) are placed from the clip list by the first threads of the grid.
+// grid = (a few, B); block = 256, striding over the pair's list of triangles that have a record
+// (written by setup): reads the triangle's packed tile box (4 bytes) and places record slot 2t;
+// the pieces of near-clipped triangles (slots 2t, 2t + 1 of the few triangles on the clip list)
+// are placed from the clip list by the first threads of the grid.
 __global__ void __launch_bounds__(256)
 raster_fill_kernel(Renderer R, const int32_t *__restrict__ cls_idx, int n_tiles) {
   pdl_wait();
   pdl_launch_dependents();
   const int b = blockIdx.y;
-  const int t = blockIdx.x * blockDim.x + threadIdx.x;
-  const int mesh = __ldg(cls_idx + b);
-  const int n_tri = __ldg(R.mesh_tri_off + mesh + 1) - __ldg(R.mesh_tri_off + mesh);
   const int32_t *start = R.tile_start + (size_t)b * (n_tiles + 1);
   int32_t *fill = R.tile_fill + (size_t)b * n_tiles;
   int32_t *list = R.tile_list + (size_t)b * R.list_cap;
-  unsigned tb = RT_TBOX_NONE;
-  if (t < n_tri) tb = __ldg(R.tbox + (size_t)b * R.max_tris + t);
-  for_each_tile(tb, R.tiles_x, [&](int key) {
-    const int slot = tile_atomic(fill, key, true);
-    if (key >= 0) {
-      const int pos = start[key] + slot;
-      if (pos < R.list_cap) list[pos] = 2 * t;
+  const int n_bin = R.bin_n[b];
+  const int32_t *bin = R.bin_tri + (size_t)b * R.max_tris;
+  // whole warps run every trip (for_each_tile / tile_atomic use full-mask warp primitives)
+  for (int base = blockIdx.x * blockDim.x; base < n_bin; base += gridDim.x * blockDim.x) {
+    const int i = base + threadIdx.x;
+    int t = 0;
+    unsigned tb = RT_TBOX_NONE;
+    if (i < n_bin) {
+      t = bin[i];
+      tb = R.tbox[(size_t)b * R.max_tris + t];
     }
-  });
+    for_each_tile(tb, R.tiles_x, [&](int key) {
+      const int slot = tile_atomic(fill, key, true);
+      if (key >= 0) {
+        const int pos = start[key] + slot;
+        if (pos < R.list_cap) list[pos] = 2 * t;
+      }
+    });
+  }
   const int n_clip = R.work_count[RT_WC_CLIP];
   const int gid = (blockIdx.y * gridDim.x + blockIdx.x) * blockDim.x + threadIdx.x;
   if (gid < n_clip) {
@@ -1126,7 +1148,7 @@ static void renderer_free(Renderer *r) {
   void *ptrs[] = {r->verts, r->uv, r->normals, r->tris, r->mesh_tri_off, r->mesh_vert_off, r->vtx,
                   r->mesh_has, r->tex,
                   r->tex_off, r->tex_hw, r->recs, r->tbox, r->clip_list, r->clip_box, r->zwin, r->work_count, r->tile_start, r->tile_fill,
-                  r->tile_list, r->work_list_b[0], r->work_list_b[1], r->heavy_count, r->bin_list};
+                  r->tile_list, r->work_list_b[0], r->work_list_b[1], r->heavy_count, r->bin_list, r->bin_tri, r->bin_n};
   for (void *p : ptrs)
     if (p) cudaFree(p);
   delete r;
@@ -1234,6 +1256,8 @@ int rc_renderer_create(const rc_mesh_desc *meshes, int n_meshes, int height, int
   RC_TRY(rc::dev_alloc(&r->work_count, (size_t)2 * max_batch * n_tiles + rc::RT_WC_INTS));
   r->tile_count = r->work_count + rc::RT_WC_INTS;
   RC_TRY(rc::dev_alloc(&r->bin_list, (size_t)max_batch * n_tiles));
+  RC_TRY(rc::dev_alloc(&r->bin_tri, (size_t)max_batch * max_tris));
+  RC_TRY(rc::dev_alloc(&r->bin_n, (size_t)max_batch));
   RC_TRY(rc::dev_alloc(&r->work_list_b[0], (size_t)max_batch * n_tiles));
   RC_TRY(rc::dev_alloc(&r->work_list_b[1], (size_t)max_batch * n_tiles));
   RC_TRY(rc::dev_alloc(&r->heavy_count, 2));
@@ -1384,7 +1408,7 @@ int rc_render_dev(void *handle, const rc_render_args *a) {
   RC_CUDA_TRY(rc::launch_maybe_pdl(rc::raster_scan_kernel, dim3(B), dim3(256), 0, s, chain, R,
                                    a->cls_idx, a->poses, cam, n_tiles, a->status));
   if ((st = mark(2)) != RC_OK) return st;
-  dim3 gf((R.max_tris + 255) / 256, B);
+  dim3 gf((unsigned)std::min(8, (R.max_tris + 255) / 256), B);
   RC_CUDA_TRY(rc::launch_maybe_pdl(rc::raster_fill_kernel, gf, dim3(256), 0, s, chain, R,
                                    a->cls_idx, n_tiles));
   if ((st = mark(3)) != RC_OK) return st;

@@ -732,13 +732,20 @@ LOOP_SMALL_KEYS = ("src_pose", "tgt_pose", "class_index", "mask_idx", "point_clo
                    "point_cloud_weights")
 
 
-def pack_refine_batch(host, depth_factor=1000.0, pixel_means_bgr=None, pin=True):
+def pack_refine_batch(host, depth_factor=1000.0, pixel_means_bgr=None, pin=True,
+                      mask_policy="upload"):
     """A RefineLoop batch (float32 blobs, make_refine_batch / the reference's DataBatch) in the
     dataset's STORAGE formats, as the files decode to before the reference's loaders touch them
     (lib/utils/image.py:186-305): colour uint8 [B,H,W,3] BGR, depth 16-bit in 1/depth_factor m
     (int16 view of the uint16 data), label image uint8 [B,H,W] + mask_idx, mask_observed uint8.
     The point cloud is the sampled MODEL cloud only; the observed cloud (R_gt X + t_gt,
-    image.py:592-596) is computed on the device.  Returns CPU tensors (page-locked if `pin`)."""
+    image.py:592-596) is computed on the device.  mask_policy "box_gt" (TRAIN.INIT_MASK of the
+    shipped configs, image.py:330-343): mask_observed is the bounding rectangle of the label
+    mask, which the reference's loader derives from the label file -- it is then not part of
+    the packed batch at all and LoopFeed derives it on the device (rc_mask_box_dev).
+    Returns CPU tensors (page-locked if `pin`)."""
+    if mask_policy not in ("upload", "box_gt"):
+        raise ValueError("mask_policy: 'upload' or 'box_gt'")
     means = np.asarray(synth.PIXEL_MEANS if pixel_means_bgr is None else pixel_means_bgr,
                        np.float64).reshape(-1)
     means_rgb = means[::-1].reshape(1, 3, 1, 1)
@@ -755,6 +762,8 @@ def pack_refine_batch(host, depth_factor=1000.0, pixel_means_bgr=None, pin=True)
            "class_index": np.ascontiguousarray(host["class_index"], np.int32),
            "point_cloud_model": np.ascontiguousarray(host["point_cloud_model"], np.float32),
            "point_cloud_weights": np.ascontiguousarray(host["point_cloud_weights"], np.float32)}
+    if mask_policy == "box_gt":
+        del out["mask_observed"]
     res = {}
     for k, v in out.items():
         t = torch.from_numpy(v)
@@ -780,6 +789,9 @@ class LoopFeed(object):
 
     def __init__(self, loop, example, iterations=4, depth_factor=1000.0, pixel_means_bgr=None,
                  depth=2, use_graph=True):
+        """`example`: one packed batch (pack_refine_batch).  If it carries no "mask_observed"
+        (mask_policy "box_gt") the observed mask is derived on the device from the label mask,
+        as the reference's loader derives it on the host (lib/utils/image.py:330-343)."""
         from . import prep
 
         self.prep = prep
@@ -788,11 +800,17 @@ class LoopFeed(object):
         self.means_bgr = np.asarray(
             synth.PIXEL_MEANS if pixel_means_bgr is None else pixel_means_bgr, np.float64).reshape(-1)
         dev, B = loop.device, loop.B
-        for k in LOOP_PACKED_KEYS + LOOP_SMALL_KEYS:
+        self.box_gt = "mask_observed" not in example
+        self.keys = tuple(k for k in LOOP_PACKED_KEYS + LOOP_SMALL_KEYS
+                          if not (self.box_gt and k == "mask_observed"))
+        if self.box_gt:
+            self._box_ws = torch.zeros((B, _lib.RC_BOX_WS_INTS), dtype=torch.int32, device=dev)
+            self._box_bbox = torch.empty((B, 4), dtype=torch.int32, device=dev)
+        for k in self.keys:
             if example[k].shape[0] != B:
                 raise ValueError("%s: batch %d, loop was built for %d" % (k, example[k].shape[0], B))
-        self.raw = [{k: torch.empty_like(example[k], device=dev)
-                     for k in LOOP_PACKED_KEYS + LOOP_SMALL_KEYS} for _ in range(self.depth)]
+        self.raw = [{k: torch.empty_like(example[k], device=dev) for k in self.keys}
+                    for _ in range(self.depth)]
         self.copy_stream = torch.cuda.Stream(device=dev)
         self.uploaded = [torch.cuda.Event() for _ in range(self.depth)]
         self.done = [torch.cuda.Event() for _ in range(self.depth)]
@@ -801,7 +819,7 @@ class LoopFeed(object):
         self.n = 0
         self.use_graph = bool(use_graph)
         self.h2d_bytes = int(sum(example[k].numel() * example[k].element_size()
-                                 for k in LOOP_PACKED_KEYS + LOOP_SMALL_KEYS))
+                                 for k in self.keys))
         self.d2h_bytes = int(B * 12 * 4 + B * 4)
         self.decode_launches = 8  # image, depth, 2 masks, points, labels, observed box, box copy
 
@@ -811,7 +829,11 @@ class LoopFeed(object):
         p.transform_batch(raw["image_observed"], self.means_bgr, out=o["image_observed"])
         p.decode_depth(raw["depth_gt_observed"], self.depth_factor, out=o["depth_gt_observed"])
         p.decode_mask(raw["mask_gt_observed"], raw["mask_idx"], out=o["mask_gt_observed"])
-        p.decode_mask(raw["mask_observed"], raw["mask_idx"], out=o["mask_observed"])
+        if self.box_gt:
+            mask_box(o["mask_gt_observed"], out=o["mask_observed"], bbox=self._box_bbox,
+                     workspace=self._box_ws)
+        else:
+            p.decode_mask(raw["mask_observed"], raw["mask_idx"], out=o["mask_observed"])
         o["tgt_pose"].copy_(raw["tgt_pose"], non_blocking=True)
         o["point_cloud_model"].copy_(raw["point_cloud_model"], non_blocking=True)
         o["point_cloud_weights"].copy_(raw["point_cloud_weights"], non_blocking=True)
@@ -831,7 +853,7 @@ class LoopFeed(object):
         with torch.cuda.stream(self.copy_stream):
             if self.n >= self.depth:  # the slot's previous batch has been decoded and consumed
                 self.copy_stream.wait_event(self.done[i])
-            for k in LOOP_PACKED_KEYS + LOOP_SMALL_KEYS:
+            for k in self.keys:
                 raw[k].copy_(host[k], non_blocking=True)
             self.uploaded[i].record(self.copy_stream)
         compute.wait_event(self.uploaded[i])
@@ -850,7 +872,7 @@ class LoopFeed(object):
 
 
 def make_refine_batch(meshes, batch, seed, K=synth.K_LINEMOD, num_points=synth.NUM_3D_SAMPLE,
-                      renderer=None, occlusion=False, render_fn=None):
+                      renderer=None, occlusion=False, render_fn=None, mask_policy="hole"):
     """Synthetic observed side for RefineLoop: target renders come from `renderer`
     (a DeviceRenderer; the product's own rasteriser) so that no oracle is involved.
     `render_fn(cls [B] int32, tgt [B,3,4], pixel_means) -> (depth [B,1,H,W], image [B,3,H,W])`
@@ -898,10 +920,22 @@ def make_refine_batch(meshes, batch, seed, K=synth.K_LINEMOD, num_points=synth.N
             mask_gt[b, 0, y0:y0 + 80, x0:x0 + 80] = 0
     bg = rng.uniform(1, 255, size=image.shape).astype(np.float32) - pm.reshape(1, 3, 1, 1)
     image = np.where(mask_gt[:, :1] > 0, image, bg).astype(np.float32)
-    mask_obs = mask_gt.copy()
-    for b in range(B):
-        y0, x0 = rng.integers(0, synth.H - 40), rng.integers(0, synth.W - 40)
-        mask_obs[b, 0, y0:y0 + 40, x0:x0 + 40] = 0
+    # mask_policy "hole": the label mask with a 40x40 hole (a mask that differs from the label);
+    # "box_gt": TRAIN.INIT_MASK of the shipped configs -- the label mask's bounding rectangle with
+    # the reference's exclusive slice end (lib/utils/image.py:330-343)
+    if mask_policy == "box_gt":
+        mask_obs = np.zeros_like(mask_gt)
+        for b in range(B):
+            ys, xs = np.nonzero(mask_gt[b, 0])
+            if len(ys):
+                mask_obs[b, 0, ys.min():ys.max(), xs.min():xs.max()] = 1
+    elif mask_policy == "hole":
+        mask_obs = mask_gt.copy()
+        for b in range(B):
+            y0, x0 = rng.integers(0, synth.H - 40), rng.integers(0, synth.W - 40)
+            mask_obs[b, 0, y0:y0 + 40, x0:x0 + 40] = 0
+    else:
+        raise ValueError("mask_policy: 'hole' or 'box_gt'")
     from . import pose as P
 
     return {"class_index": cls, "src_pose": src, "tgt_pose": tgt, "image_observed": image,

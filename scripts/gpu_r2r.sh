@@ -1,0 +1,41 @@
+#!/bin/bash
+# Round-2 iteration: selected parity tests, default bench (cfg5), per-GPU shares of the 8-GPU
+# strong-scaling runs, ncu launch list of the default bench.
+# Usage: bash scripts/gpu_r2r.sh <tag> [pytest -k expression | all | none]
+TAG=${1:-r}
+OUT=gpurun_out
+mkdir -p $OUT
+K=${2:-all}
+if [ "$K" = "all" ]; then
+timeout 900 python -m pytest tests -m gpu -q --timeout 300 > $OUT/pytest_$TAG.log 2>&1; echo "rc=$?" >> $OUT/pytest_$TAG.log
+elif [ "$K" != "none" ]; then
+timeout 900 python -m pytest tests -m gpu -q --timeout 300 -k "$K" > $OUT/pytest_$TAG.log 2>&1; echo "rc=$?" >> $OUT/pytest_$TAG.log
+fi
+timeout 400 python bench.py --steps 20 --warmup 4 --no-cpu-baseline > $OUT/bench_$TAG.json 2> $OUT/bench_$TAG.err; echo "rc=$?" >> $OUT/bench_$TAG.err
+timeout 300 python bench.py --pairs-total 128 --steps 20 --warmup 4 --no-cpu-baseline > $OUT/bench_b128_$TAG.json 2> $OUT/bench_b128_$TAG.err
+timeout 300 python bench.py --config 4 --steps 20 --warmup 4 --no-cpu-baseline > $OUT/bench_cfg4_$TAG.json 2> $OUT/bench_cfg4_$TAG.err
+timeout 300 python bench.py --config 4 --pairs-total 32 --steps 20 --warmup 4 --no-cpu-baseline > $OUT/bench_cfg4_b32_$TAG.json 2> $OUT/bench_cfg4_b32_$TAG.err
+CMD="python bench.py --steps 4 --warmup 4 --no-cpu-baseline --no-graph --min-seconds 0.01"
+timeout 200 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $OUT/launches_$TAG.csv $CMD > $OUT/ncu_l_$TAG.log 2>&1
+[ -f $OUT/pytest_$TAG.log ] && tail -4 $OUT/pytest_$TAG.log
+python - <<PY
+import json, csv, collections
+for f in ("$TAG","b128_$TAG","cfg4_$TAG","cfg4_b32_$TAG"):
+    try:
+        d=json.load(open("$OUT/bench_%s.json"%f)); print(f, "value %.0f ms/step %.4f e2e %.0f zoom_us %.1f frac_comp %.3f traffic %s"%(d["value"], d["ms_per_step"], d["e2e"]["value"], d["roofline"]["kernel_us"], d["roofline"]["frac_compulsory"], d["roofline"]["traffic"])); print("   ", {k: round(v,1) for k,v in d.get("kernel_us_serialised").items()}); print("   ", d.get("rasteriser"))
+    except Exception as e: print(f, "failed", e)
+try:
+    rows=[r for r in csv.reader(open("$OUT/launches_$TAG.csv")) if len(r)>5]
+    hdr=rows[0]; ki=hdr.index("Kernel Name"); vi=hdr.index("Metric Value"); ui=hdr.index("Metric Unit")
+    agg=collections.defaultdict(list)
+    for r in rows[1:]:
+        try: v=float(r[vi].replace(",",""))
+        except: continue
+        if r[ui]=="ns": v/=1e3
+        elif r[ui]=="ms": v*=1e3
+        agg[r[ki].split("(")[0]].append(v)
+    tot=sum(sum(v) for v in agg.values())
+    for k,v in sorted(agg.items(), key=lambda kv:-sum(kv[1])):
+        print("%-40s n=%3d mean %8.1f us  share %5.1f%%"%(k[:40],len(v),sum(v)/len(v),100*sum(v)/tot))
+except Exception as e: print("launch list failed", e)
+PY

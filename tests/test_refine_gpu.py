@@ -281,3 +281,57 @@ def test_refine_loop_side_stream_equals_single_stream(cuda_device):
                      "g_zt": loop.step.grad_zoom_trans.clone(), "rot_est": loop.rot_est.clone()})
     for k in outs[0]:
         assert torch.equal(outs[0][k], outs[1][k]), k
+
+
+@pytest.mark.parametrize("policy", ["upload", "box_gt"])
+def test_loop_feed_from_storage_formats_equals_float_blobs(cuda_device, policy):
+    """pipeline.LoopFeed: batches in the dataset's storage formats (u8 BGR, u16 mm depth, u8
+    label / mask) from page-locked host memory, decoded on the device, one graph replay per
+    loop, refined poses + loss sums back to the host -- equal to the same loop fed with the
+    float32 blobs (set_batch).  policy "box_gt": mask_observed is NOT uploaded but derived on the
+    device from the label mask (TRAIN.INIT_MASK box_gt, lib/utils/image.py:330-343)."""
+    import torch
+
+    from mx_deepim_b200 import pipeline, synth
+
+    rng = np.random.default_rng(15)
+    meshes = [synth.make_mesh(rng, level=3, kind=1), synth.make_mesh(rng, level=2, kind=0)]
+    B, iters = 4, 4
+    mp = "box_gt" if policy == "box_gt" else "hole"
+    loop = pipeline.RefineLoop(meshes, B, cuda_device, seed=3, backward=True)
+    hosts = [pipeline.make_refine_batch(meshes, B, 500 + i, renderer=loop.renderer, mask_policy=mp,
+                                        occlusion=(i == 1)) for i in range(3)]
+    want = []
+    for h in hosts:
+        # the storage formats hold the image rounded to 8 bits: round the float blob the same way
+        # so that both paths see the same observed image
+        pm = synth.PIXEL_MEANS[[2, 1, 0]].reshape(1, 3, 1, 1)
+        h["image_observed"] = (np.clip(np.rint(h["image_observed"].astype(np.float64) + pm), 0, 255)
+                               - pm).astype(np.float32)
+        loop.set_batch(h)
+        loop.run(iters)
+        torch.cuda.synchronize()
+        want.append({"pose": loop.pose[loop.cur].cpu().numpy().copy(),
+                     "loss": loop.step.loss_sum.cpu().numpy().copy(),
+                     "mask_observed": loop.obs["mask_observed"].cpu().numpy().copy(),
+                     "zimg": loop.step.zoom_image_observed.cpu().numpy().copy(),
+                     "zmask": loop.step.zoom_mask_observed.cpu().numpy().copy()})
+    packed = [pipeline.pack_refine_batch(h, mask_policy=policy) for h in hosts]
+    assert ("mask_observed" in packed[0]) == (policy == "upload")
+    feed = pipeline.LoopFeed(loop, packed[0], iterations=iters)
+    if policy == "box_gt":
+        assert feed.h2d_bytes == pipeline.LoopFeed(loop, pipeline.pack_refine_batch(hosts[0]),
+                                                   iterations=iters).h2d_bytes - B * synth.H * synth.W
+    s = torch.cuda.Stream(device=cuda_device)
+    with torch.cuda.stream(s):
+        for rnd in range(2):  # twice through the two staging slots
+            for i, pk in enumerate(packed):
+                slot = feed.submit(pk)
+                feed.done[slot].synchronize()
+                np.testing.assert_array_equal(feed.pose_out[slot].numpy(), want[i]["pose"])
+                np.testing.assert_array_equal(feed.loss_out[slot].numpy(), want[i]["loss"])
+                s.synchronize()
+                assert np.array_equal(loop.obs["mask_observed"].cpu().numpy(), want[i]["mask_observed"])
+                assert np.array_equal(loop.step.zoom_mask_observed.cpu().numpy(), want[i]["zmask"])
+                assert np.array_equal(loop.step.zoom_image_observed.cpu().numpy(), want[i]["zimg"])
+    loop.check_status()
