@@ -90,6 +90,7 @@ struct Renderer {
   int32_t *mesh_vert_off;                    // [M+1] first vertex of each mesh in the concatenated arrays
   int max_verts;
   VtxS *vtx;                                 // [max_batch][max_verts] projected vertices of this call
+  double *viz;                               // [max_batch][max_verts] their 1 / camera-space z (perspective-correct attributes)
   uint8_t *tex;
   int64_t *tex_off;
   int32_t *tex_hw;                           // [M,2]
@@ -149,7 +150,9 @@ struct RecQ {  // a TriRec as the four 128-bit words it is stored and loaded as
 
 // Camera-space point -> VtxS.  One reciprocal per vertex (the perspective divide as hardware does
 // it); FP64 runs at half rate on sm_100 and a division is ~30 instructions, so they are counted.
-__device__ __forceinline__ int project_vertex(double x, double y, double z, const Cam &cam, VtxS &o) {
+__device__ __forceinline__ int project_vertex(double x, double y, double z, const Cam &cam, VtxS &o,
+                                              double *iz_out = nullptr) {
+  if (iz_out) *iz_out = 0.0;
   o.X = 0;
   o.Y = 0;
   o.zw = 0.0;
@@ -159,6 +162,7 @@ __device__ __forceinline__ int project_vertex(double x, double y, double z, cons
   const double pa = (cam.zfar + cam.znear) / (cam.zfar - cam.znear);
   const double pb = (2.0 * cam.zfar * cam.znear) / (cam.zfar - cam.znear);
   const double iz = 1.0 / z;
+  if (iz_out) *iz_out = iz;
   const double u = cam.fx * x * iz + cam.cx, v = cam.fy * y * iz + cam.cy;
   if (!(fabs(u) < 1e6 && fabs(v) < 1e6)) return flag;
   o.X = __double2int_rn(u * 256.0);  // < 2^28 in magnitude
@@ -417,9 +421,11 @@ raster_vertex_kernel(Renderer R, const int32_t *__restrict__ cls_idx,
     Pc[r] = (double)__ldg(pose + r * 4 + 0) * x + (double)__ldg(pose + r * 4 + 1) * y +
             (double)__ldg(pose + r * 4 + 2) * z + (double)__ldg(pose + r * 4 + 3);
   VtxS o;
-  const int flag = project_vertex(Pc[0], Pc[1], Pc[2], cam, o);
+  double iz;
+  const int flag = project_vertex(Pc[0], Pc[1], Pc[2], cam, o, &iz);
   *reinterpret_cast<int4 *>(R.vtx + (size_t)b * R.max_verts + v) =
       make_int4((o.X << 2) | flag, o.Y, __double2loint(o.zw), __double2hiint(o.zw));
+  R.viz[(size_t)b * R.max_verts + v] = iz;  // resolve: 1/w of the varyings, the very same double
 }
 
 // 1. setup.  grid = (ceil(max_tris / (256 * RT_SETUP_PER)), B); block = 256 (whole warps always
@@ -714,6 +720,7 @@ struct WinTri {
   int x0, y0, x1, y1, x2, y2;
   int tri;    // triangle index | RT_FLAG_*
   int vi[3];  // global vertex ids of the SOURCE triangle
+  double iz[3];  // 1 / camera-space z of the source vertices (valid unless RT_FLAG_CLIPPED)
 };
 
 __device__ __forceinline__ void load_winner(const Renderer &R, int b, int mesh, unsigned slot,
@@ -731,6 +738,9 @@ __device__ __forceinline__ void load_winner(const Renderer &R, int b, int mesh, 
     w.x1 = p1.x >> 2; w.y1 = p1.y;
     w.x2 = p2.x >> 2; w.y2 = p2.y;
     w.tri = t;
+    const double *viz = R.viz + (size_t)b * R.max_verts - v_off;
+#pragma unroll
+    for (int i = 0; i < 3; ++i) w.iz[i] = viz[w.vi[i]];
     if (edge_fn(w.x0, w.y0, w.x1, w.y1, w.x2, w.y2) < 0) {  // make_record's orientation
       int q = w.x1; w.x1 = w.x2; w.x2 = q;
       q = w.y1; w.y1 = w.y2; w.y2 = q;
@@ -742,6 +752,7 @@ __device__ __forceinline__ void load_winner(const Renderer &R, int b, int mesh, 
     w.x0 = q0.x; w.y0 = q0.y; w.x1 = q0.z; w.y1 = q0.w;
     w.x2 = q1.x; w.y2 = q1.y;
     w.tri = q1.z;
+    w.iz[0] = w.iz[1] = w.iz[2] = 0.0;
   }
 }
 
@@ -754,20 +765,21 @@ template <bool LIT>
 __device__ __forceinline__ Shaded shade_pixel(const Renderer &R, const RasterOut &O, const Cam &cam,
                                               int mesh, const WinTri &w,
                                               const float *__restrict__ pose, int b, int x, int y) {
-  double Pc[3][3];
+  double Pc[3][3] = {{0, 0, 0}, {0, 0, 0}, {0, 0, 0}};
   const bool clipped = (w.tri & RT_FLAG_CLIPPED) != 0;
+  // camera-space vertices: only the lit renderers and near-clipped pieces need them; a textured
+  // pixel gets by with the vertex pass's 1/z (w.iz: the same double 1.0 / Pc[i][2] would give)
+  if (LIT || clipped) {
 #pragma unroll
-  for (int i = 0; i < 3; ++i) {
-    const double px = (double)__ldg(R.verts + (size_t)w.vi[i] * 3 + 0);
-    const double py = (double)__ldg(R.verts + (size_t)w.vi[i] * 3 + 1);
-    const double pz = (double)__ldg(R.verts + (size_t)w.vi[i] * 3 + 2);
+    for (int i = 0; i < 3; ++i) {
+      const double px = (double)__ldg(R.verts + (size_t)w.vi[i] * 3 + 0);
+      const double py = (double)__ldg(R.verts + (size_t)w.vi[i] * 3 + 1);
+      const double pz = (double)__ldg(R.verts + (size_t)w.vi[i] * 3 + 2);
 #pragma unroll
-    for (int r = 0; r < 3; ++r)
-      if (LIT || r == 2 || clipped)
+      for (int r = 0; r < 3; ++r)
         Pc[i][r] = (double)pose[r * 4 + 0] * px + (double)pose[r * 4 + 1] * py +
                    (double)pose[r * 4 + 2] * pz + (double)pose[r * 4 + 3];
-      else
-        Pc[i][r] = 0.0;
+    }
   }
   double b1 = 1.0 / 3.0, b2 = 1.0 / 3.0;
   if (!clipped) {
@@ -778,11 +790,10 @@ __device__ __forceinline__ Shaded shade_pixel(const Renderer &R, const RasterOut
     const long long w1 = edge_fn(w.x2, w.y2, w.x0, w.y0, px, py);
     const long long w2 = edge_fn(w.x0, w.y0, w.x1, w.y1, px, py);
     const bool sw = (w.tri & RT_FLAG_SWAPPED) != 0;
-    const double zb = sw ? Pc[2][2] : Pc[1][2], zc = sw ? Pc[1][2] : Pc[2][2];
     // q_i = l_i / z_i up to the common factor 1 / area, which cancels in q_i / sum(q)
-    const double q0 = (double)w0 * (1.0 / Pc[0][2]);
-    const double qb = (double)w1 * (1.0 / zb);
-    const double qc = (double)w2 * (1.0 / zc);
+    const double q0 = (double)w0 * w.iz[0];
+    const double qb = (double)w1 * (sw ? w.iz[2] : w.iz[1]);
+    const double qc = (double)w2 * (sw ? w.iz[1] : w.iz[2]);
     const double iqs = 1.0 / (q0 + qb + qc);
     const double lb = qb * iqs, lc = qc * iqs;
     b1 = sw ? lc : lb;
@@ -1145,7 +1156,7 @@ static int dev_alloc(T **p, size_t n) {
 
 static void renderer_free(Renderer *r) {
   if (!r) return;
-  void *ptrs[] = {r->verts, r->uv, r->normals, r->tris, r->mesh_tri_off, r->mesh_vert_off, r->vtx,
+  void *ptrs[] = {r->verts, r->uv, r->normals, r->tris, r->mesh_tri_off, r->mesh_vert_off, r->vtx, r->viz,
                   r->mesh_has, r->tex,
                   r->tex_off, r->tex_hw, r->recs, r->tbox, r->clip_list, r->clip_box, r->zwin, r->work_count, r->tile_start, r->tile_fill,
                   r->tile_list, r->work_list_b[0], r->work_list_b[1], r->heavy_count, r->bin_list, r->bin_tri, r->bin_n};
@@ -1244,6 +1255,7 @@ int rc_renderer_create(const rc_mesh_desc *meshes, int n_meshes, int height, int
   RC_TRY(rc::dev_alloc(&r->mesh_tri_off, (size_t)n_meshes + 1));
   RC_TRY(rc::dev_alloc(&r->mesh_vert_off, (size_t)n_meshes + 1));
   RC_TRY(rc::dev_alloc(&r->vtx, (size_t)max_batch * max_verts));
+  RC_TRY(rc::dev_alloc(&r->viz, (size_t)max_batch * max_verts));
   RC_TRY(rc::dev_alloc(&r->mesh_has, (size_t)n_meshes));
   RC_TRY(rc::dev_alloc(&r->tex, TX));
   RC_TRY(rc::dev_alloc(&r->tex_off, (size_t)n_meshes));
