@@ -95,7 +95,8 @@ def config_dict(config, n_gpus):
         d.update({"pairs_total": total, "batch_per_gpu": total // max(n_gpus, 1),
                   "iterations_per_loop": ITERS, "meshes": cfg["meshes"],
                   "triangles_per_mesh": 20 * 4 ** cfg["level"], "backward": cfg["backward"],
-                  "occlusion": cfg["occlusion"]})
+                  "occlusion": cfg["occlusion"],
+                  "mask_observed": "TRAIN.INIT_MASK box_gt (bounding rectangle of the label mask)"})
     else:
         d.update({"pairs_total": cfg["batch"] * n_gpus, "batch_per_gpu": cfg["batch"]})
     return d
