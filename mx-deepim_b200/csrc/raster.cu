@@ -1089,7 +1089,7 @@ raster_cover_kernel(Renderer R, int n_tiles) {
 // the blocks are all-empty again when the render ends (no clearing pass, no per-frame memset of
 // 2 KB per tile).
 template <bool LIT>
-__global__ void __launch_bounds__(RT_THREADS, 3)
+__global__ void __launch_bounds__(RT_THREADS, LIT ? 3 : 4)
 raster_resolve_kernel(Renderer R, const int32_t *__restrict__ cls_idx,
                       const float *__restrict__ poses, Cam cam, RasterOut O) {
   const int W = R.W, H = R.H;
@@ -1365,17 +1365,22 @@ int rc_render_dev(void *handle, const rc_render_args *a) {
   };
   int st;
   const int sm_count = rc::device_sm_count(R.device);
-  static int cover_per_sm = 0, resolve_per_sm = 0;  // per kernel, not per device
+  static int cover_per_sm = 0, resolve_per_sm[2] = {0, 0};  // per kernel, not per device
   if (cover_per_sm == 0) {
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&cover_per_sm, rc::raster_cover_kernel,
                                                       rc::RT_CV_THREADS, 0) != cudaSuccess ||
         cover_per_sm < 1)
       cover_per_sm = 4;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resolve_per_sm,
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resolve_per_sm[0],
+                                                      rc::raster_resolve_kernel<false>,
+                                                      rc::RT_THREADS, 0) != cudaSuccess ||
+        resolve_per_sm[0] < 1)
+      resolve_per_sm[0] = 2;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resolve_per_sm[1],
                                                       rc::raster_resolve_kernel<true>,
                                                       rc::RT_THREADS, 0) != cudaSuccess ||
-        resolve_per_sm < 1)
-      resolve_per_sm = 2;
+        resolve_per_sm[1] < 1)
+      resolve_per_sm[1] = 2;
   }
   const long long n_total = (long long)n_tiles * B;
   // With event marks every launch is a normal one (clean per-kernel times); without, setup ...
@@ -1432,7 +1437,7 @@ int rc_render_dev(void *handle, const rc_render_args *a) {
   }
   // 4c resolve: a normal launch, waits for everything before it, the background included
   {
-    long long g = (long long)sm_count * resolve_per_sm * 2;
+    long long g = (long long)sm_count * resolve_per_sm[a->mode == RC_RENDER_TEXTURED ? 0 : 1] * 2;
     if (g > n_total) g = n_total;
     if (a->mode == RC_RENDER_TEXTURED)
       rc::raster_resolve_kernel<false><<<(int)g, rc::RT_THREADS, 0, s>>>(R, a->cls_idx, a->poses, cam, O);

@@ -19,10 +19,14 @@ PTXAS = os.path.join(ROOT, "mx-deepim_b200", "build", "ptxas.log")
 COLS = [
     ("LDG.128", r"\bLDG\.E\.(?:\w+\.)*128"), ("STG.128", r"\bSTG\.E\.(?:\w+\.)*128"),
     ("LDG", r"\bLDG\."), ("STG", r"\bSTG\."), ("LDGSTS", r"\bLDGSTS"), ("LDS", r"\bLDS"),
-    ("STS", r"\bSTS"), ("ATOMS", r"\bATOMS"), ("ATOMG/RED", r"\b(?:ATOMG|RED)\."),
+    ("STS", r"\bSTS"), ("ATOMS", r"\bATOMS"), ("ATOMG/RED", r"\b(?:ATOMG|REDG?)\."),
     ("SHFL", r"\bSHFL"), ("MATCH/VOTE", r"\b(?:MATCH|VOTE)"), ("REDUX", r"\bREDUX"),
     ("cluster", r"\b(?:UCGABAR|CGABAR|MAPA|ST\.E\.\w*CLUSTER|LD\.E\.\w*CLUSTER|MEMBAR\.\w*\.CTA)|ACQBULK"),
     ("FP64", r"\bD(?:FMA|MUL|ADD|SETP|MNMX)\b"), ("MUFU.RCP64", r"MUFU\.RCP64"),
+    # sm_100 packed fp32 pipe (fma.rn.f32x2 and friends)
+    ("F32x2", r"\b(?:FFMA2|FMUL2|FADD2)\b"),
+    # 64-bit min reductions / atomics in global memory (the rasteriser's z-winner blocks)
+    ("REDG/ATOMG.MIN.64", r"\b(?:REDG?|ATOMG)\.E\.MIN\.64"),
 ]
 
 
