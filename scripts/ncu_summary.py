@@ -27,6 +27,8 @@ PROF = os.path.join(ROOT, "profiles")
 METRICS = [
     "gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
     "dram__throughput.avg.pct_of_peak_sustained_elapsed",
+    "dram__bytes_read.sum.pct_of_peak_sustained_elapsed",
+    "dram__bytes_write.sum.pct_of_peak_sustained_elapsed",
     "sm__throughput.avg.pct_of_peak_sustained_elapsed",
     "sm__warps_active.avg.pct_of_peak_sustained_active", "launch__registers_per_thread",
     "launch__shared_mem_per_block_dynamic", "launch__shared_mem_per_block_static",
@@ -80,12 +82,20 @@ def full(tag):
                          text=True).stdout
     rows = list(csv.reader(txt.splitlines()))
     hdr, units = rows[0], rows[1]
-    cols = [m for m in METRICS if m in hdr]
+    # this ncu prefixes some columns with their section ("FBSP.TriageCompute.dram__throughput..."):
+    # match on the metric name itself
+    where = {}
+    for m in METRICS:
+        for i, h in enumerate(hdr):
+            if h == m or h.endswith("." + m):
+                where[m] = i
+                break
+    cols = [m for m in METRICS if m in where]
     out = []
     for r in rows[2:]:
         d = {"kernel": short(r[hdr.index("Kernel Name")])}
         for m in cols:
-            i = hdr.index(m)
+            i = where[m]
             try:
                 v = float(r[i].replace(",", ""))
             except ValueError:
@@ -157,7 +167,10 @@ def main():
             md.append("| `%s` | %.1f | %.1f | %.1f | %.1f | %.1f | %.1f | %d | %.1f | %.3g | %.3g |" % (
                 d["kernel"], g(d, "gpu__time_duration.sum"), g(d, "dram__bytes_read.sum") / 1e6,
                 g(d, "dram__bytes_write.sum") / 1e6,
-                g(d, "dram__throughput.avg.pct_of_peak_sustained_elapsed"),
+                # (this ncu leaves dram__throughput empty: read % + write % of the DRAM peak)
+                g(d, "dram__throughput.avg.pct_of_peak_sustained_elapsed")
+                if g(d, "dram__throughput.avg.pct_of_peak_sustained_elapsed") == g(d, "dram__throughput.avg.pct_of_peak_sustained_elapsed")
+                else g(d, "dram__bytes_read.sum.pct_of_peak_sustained_elapsed") + g(d, "dram__bytes_write.sum.pct_of_peak_sustained_elapsed"),
                 g(d, "sm__throughput.avg.pct_of_peak_sustained_elapsed"),
                 g(d, "sm__warps_active.avg.pct_of_peak_sustained_active"),
                 g(d, "launch__registers_per_thread"), g(d, "lts__t_sector_hit_rate.pct"),
