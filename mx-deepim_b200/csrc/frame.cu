@@ -31,7 +31,7 @@ constexpr int FT_ITEMS_PER_BLOCK = 4;  // 64 threads (two warps) per tile
 // grid-stride over the items of the last frame (compute) followed by the items of the frame
 // before (zero if stale); block = 256.
 template <bool DO_FLOW>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 4)
 frame_tiles_kernel(FrameItems F, const float *__restrict__ depth_src,
                    const float *__restrict__ depth_tgt, const float *__restrict__ KT,
                    const float *__restrict__ Kinv, float *__restrict__ flow,

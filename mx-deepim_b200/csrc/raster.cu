@@ -1096,15 +1096,37 @@ raster_resolve_kernel(Renderer R, const int32_t *__restrict__ cls_idx,
   const int n_heavy = *R.heavy;
   const int n_tiles = R.tiles_x * R.tiles_y;
   const size_t plane = (size_t)H * W;
-  for (int unit = blockIdx.x; unit < n_heavy; unit += gridDim.x) {
-    const int work = __ldg(R.work_list + unit);
-    const int b = work >> 16;
-    const int tile = ((work >> 8) & 0xff) * R.tiles_x + (work & 0xff);
+  // A pixel's loads form a chain (item -> winning key -> vertex ids -> projected vertices, 1/z,
+  // uv -> texel) and a warp has nothing else to do meanwhile: the item and the key of the NEXT
+  // trip are fetched while this one shades.
+  auto fetch = [&](int unit, int &work, unsigned long long *&zp, unsigned long long &key) {
+    work = -1;
+    zp = nullptr;
+    key = ~0ull;
+    if (unit >= n_heavy) return;
+    work = __ldg(R.work_list + unit);
     const int x = (work & 0xff) * RT_TW + (threadIdx.x & (RT_TW - 1));
     const int y = ((work >> 8) & 0xff) * RT_TH + (threadIdx.x >> RT_TW_SHIFT);
-    if (x >= W || y >= H) continue;
-    unsigned long long *zp = R.zwin + ((size_t)b * n_tiles + tile) * RT_PIX + threadIdx.x;
-    const unsigned long long key = *zp;
+    if (x >= W || y >= H) {
+      work = -1;
+      return;
+    }
+    const int tile = ((work >> 8) & 0xff) * R.tiles_x + (work & 0xff);
+    zp = R.zwin + ((size_t)(work >> 16) * n_tiles + tile) * RT_PIX + threadIdx.x;
+    key = *zp;
+  };
+  int work_n;
+  unsigned long long *zp_n, key_n;
+  fetch(blockIdx.x, work_n, zp_n, key_n);
+  for (int unit = blockIdx.x; unit < n_heavy; unit += gridDim.x) {
+    const int work = work_n;
+    unsigned long long *zp = zp_n;
+    const unsigned long long key = key_n;
+    fetch(unit + gridDim.x, work_n, zp_n, key_n);
+    if (work < 0) continue;  // pixel outside the frame (partial tile)
+    const int b = work >> 16;
+    const int x = (work & 0xff) * RT_TW + (threadIdx.x & (RT_TW - 1));
+    const int y = ((work >> 8) & 0xff) * RT_TH + (threadIdx.x >> RT_TW_SHIFT);
     float dz = 0.f, cr = 0.f, cg = 0.f, cb = 0.f;
     int tid = -1;
     if (key != ~0ull) {
