@@ -478,16 +478,26 @@ int rc_standin_predict_dev(const float *rot_gt, const float *trans_gt, const flo
                            const float *noise_t, float damping, float *rot_est, float *trans_est,
                            int batch_size, void *stream);
 
-/* The same stand-in at the head of rc_pose_update_dev's kernel (one launch instead of two on the
- * refine loop's chain of dependent launches): rot_est / trans_est are WRITTEN (the loss and the
- * caller read them) and then used as the update.  rot_gt / trans_gt may alias rot_res /
- * trans_res (labels in, new labels out).  Not a reference interface. */
+/* rc_pose_update_dev for refine loops: optionally with the stand-in at the head of the same kernel
+ * (one launch instead of two on the loop's chain of dependent launches), and optionally in two
+ * parts, so that a caller can run the expensive half beside the rasteriser:
+ *   parts = RC_POSE_PART_POSE    refined_pose only -- all the render waits for;
+ *           RC_POSE_PART_LABELS  rot_res / trans_res / KT only (the float64 eigen-solve of
+ *                                mat2quat is most of the kernel's latency);
+ *           both                 everything, as rc_pose_update_dev.
+ * rot_gt != NULL: the stand-in's prediction is made from (rot_gt, trans_gt, noise) first, WRITTEN
+ * to rot_est / trans_est (the loss and the caller read them) and used as the update; rot_gt /
+ * trans_gt may alias rot_res / trans_res (labels in, new labels out).  rot_gt == NULL: rot_est /
+ * trans_est are the update as given.  Not a reference interface. */
+#define RC_POSE_PART_POSE 1
+#define RC_POSE_PART_LABELS 2
 int rc_pose_update_standin_dev(const float *src_pose, const float *rot_gt, const float *trans_gt,
                                const float *noise_q, const float *noise_t, float damping,
                                float *rot_est, float *trans_est, const float *tgt_pose,
                                const float *K, const float *T_means, const float *T_stds,
                                int rot_coord, float *refined_pose, float *rot_res,
-                               float *trans_res, float *KT, int batch_size, void *stream);
+                               float *trans_res, float *KT, int parts, int batch_size,
+                               void *stream);
 
 /* ------------------------------------------------ test-time mask policies (8(f) rank 1)
  * The "box_rendered" / "box_observed" branches of update_data_batch,

@@ -51,6 +51,7 @@ class rc_zoom_group(ctypes.Structure):
 
 
 RC_STEP_MARKS = 6
+RC_POSE_PART_POSE, RC_POSE_PART_LABELS = 1, 2
 RC_STEP_PHASE_LOSS, RC_STEP_PHASE_FRAME, RC_STEP_PHASE_SAMPLE, RC_STEP_PHASE_ZT_BWD = 1, 2, 4, 8
 _STEP_IN = ("image_observed", "image_rendered", "depth_gt_observed", "depth_rendered",
             "mask_observed", "mask_gt_observed", "src_pose", "KT", "Kinv", "K",
@@ -157,7 +158,7 @@ SIGNATURES = {
     "rc_standin_predict_dev": (c_int, [_P, _P, _P, _P, c_float, _P, _P, c_int, _P]),
     "rc_pose_update_standin_dev": (c_int, [_P, _P, _P, _P, _P, c_float, _P, _P, _P, _P,
                                            POINTER(c_float), POINTER(c_float), c_int, _P, _P, _P,
-                                           _P, c_int, _P]),
+                                           _P, c_int, c_int, _P]),
     "rc_pm_loss_bwd_dev": (c_int, [_P, _P, _P, _P, _P, _P, POINTER(c_float), POINTER(c_float),
                                    c_int, c_int, c_float, c_float, c_float, _P, _P, c_int, c_int,
                                    _P]),

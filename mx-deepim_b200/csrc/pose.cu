@@ -162,7 +162,7 @@ __global__ void pose_update_kernel(const float *__restrict__ src_pose, const flo
                                    const float *__restrict__ tgt_pose, const float *__restrict__ K,
                                    PoseUpdateParams pp, Standin sp, float *__restrict__ refined_pose,
                                    float *rot_res, float *trans_res,
-                                   float *__restrict__ KT, int B) {
+                                   float *__restrict__ KT, int B, int parts) {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= B) return;
   // ---- RT_transform (RT_transform.py:135-161): quat = r / ||r|| in float32, quat2mat float64
@@ -226,7 +226,12 @@ __global__ void pose_update_kernel(const float *__restrict__ src_pose, const flo
     for (int j = 0; j < 3; ++j) Pf[i * 4 + j] = (float)Rn[i * 3 + j];
     Pf[i * 4 + 3] = Tn[i];
   }
-  for (int i = 0; i < 12; ++i) refined_pose[b * 12 + i] = Pf[i];
+  // parts: RC_POSE_PART_POSE = the refined pose (all the rasteriser waits for),
+  // RC_POSE_PART_LABELS = the new regression labels and KT (the float64 eigen-solve of mat2quat
+  // is most of this kernel's latency; a caller may run it beside the render)
+  if (parts & RC_POSE_PART_POSE)
+    for (int i = 0; i < 12; ++i) refined_pose[b * 12 + i] = Pf[i];
+  if (!(parts & RC_POSE_PART_LABELS)) return;
 
   // ---- calc_RT_delta(refined_pose (float64), tgt_pose) -> new regression labels (:288-295)
   double Rt[9], Tt[3];
@@ -361,7 +366,7 @@ int rc_pose_update_dev(const float *src_pose, const float *rot_est, const float 
   rc::Standin none = {};
   rc::pose_update_kernel<<<(batch_size + 63) / 64, 64, 0, static_cast<cudaStream_t>(stream)>>>(
       src_pose, rot_est, trans_est, tgt_pose, K, pp, none, refined_pose, rot_res, trans_res, KT,
-      batch_size);
+      batch_size, RC_POSE_PART_POSE | RC_POSE_PART_LABELS);
   return rc::note_status(rc::check_launch());
 }
 
@@ -370,14 +375,18 @@ int rc_pose_update_standin_dev(const float *src_pose, const float *rot_gt, const
                                float *rot_est, float *trans_est, const float *tgt_pose,
                                const float *K, const float *T_means, const float *T_stds,
                                int rot_coord, float *refined_pose, float *rot_res,
-                               float *trans_res, float *KT, int batch_size, void *stream) {
+                               float *trans_res, float *KT, int parts, int batch_size,
+                               void *stream) {
   RC_REQUIRE(batch_size >= 0, RC_ERR_INVALID_ARG);
   RC_REQUIRE(rot_coord == RC_ROT_MODEL || rot_coord == RC_ROT_CAMERA || rot_coord == RC_ROT_CAMERA_NEW,
              RC_ERR_INVALID_ARG);
+  RC_REQUIRE(parts >= 1 && parts <= 3, RC_ERR_INVALID_ARG);
   if (batch_size == 0) return rc::note_status(RC_OK);
-  RC_REQUIRE(src_pose && rot_gt && trans_gt && noise_q && noise_t && rot_est && trans_est &&
-                 tgt_pose && K && refined_pose && rot_res && trans_res && KT,
-             RC_ERR_INVALID_ARG);
+  // rot_gt == NULL: no stand-in, rot_est / trans_est are the update as given
+  RC_REQUIRE(src_pose && rot_est && trans_est && tgt_pose && K, RC_ERR_INVALID_ARG);
+  RC_REQUIRE(rot_gt == nullptr || (trans_gt && noise_q && noise_t), RC_ERR_INVALID_ARG);
+  RC_REQUIRE(!(parts & RC_POSE_PART_POSE) || refined_pose, RC_ERR_INVALID_ARG);
+  RC_REQUIRE(!(parts & RC_POSE_PART_LABELS) || (rot_res && trans_res && KT), RC_ERR_INVALID_ARG);
   rc::PoseUpdateParams pp;
   for (int i = 0; i < 3; ++i) {
     pp.means[i] = T_means ? T_means[i] : 0.f;
@@ -387,7 +396,7 @@ int rc_pose_update_standin_dev(const float *src_pose, const float *rot_gt, const
   rc::Standin sp = {rot_gt, trans_gt, noise_q, noise_t, rot_est, trans_est, damping};
   rc::pose_update_kernel<<<(batch_size + 63) / 64, 64, 0, static_cast<cudaStream_t>(stream)>>>(
       src_pose, rot_est, trans_est, tgt_pose, K, pp, sp, refined_pose, rot_res, trans_res, KT,
-      batch_size);
+      batch_size, parts);
   return rc::note_status(rc::check_launch());
 }
 

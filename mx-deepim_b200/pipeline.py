@@ -478,7 +478,7 @@ class RefineLoop(object):
         self.damping = float(damping)
         self.predict = predict  # None: the damped-GT stand-in, fused into the pose update's launch
         self.side = torch.cuda.Stream(device=self.device) if side_stream else None
-        self._ev_fork, self._ev_zf, self._ev_join = (torch.cuda.Event() for _ in range(3))
+        self._ev_fork, self._ev_zf, self._ev_join, self._ev_labels = (torch.cuda.Event() for _ in range(4))
         g = torch.Generator(device="cpu").manual_seed(int(seed))
         self.noise_q = (0.01 * torch.randn((8, B, 4), generator=g)).to(self.device)
         self.noise_t = (0.005 * torch.randn((8, B, 3), generator=g)).to(self.device)
@@ -499,7 +499,9 @@ class RefineLoop(object):
             self._bind_frame(self.bound[par])
         # pose update (+ fused stand-in) + 7 render kernels (clear, vertex, setup, scan, fill,
         # cover, resolve) + step
-        self.launches_per_iteration = (1 if predict is None else 2) + 7 + self.step.launches_per_step
+        # (with the side stream the pose update is two launches: pose | labels + KT)
+        self.launches_per_iteration = (2 if (side_stream or predict is not None) else 1) + 7 + \
+            self.step.launches_per_step
 
     def set_batch(self, host):
         """Observed side of the batch + initial poses.  `host`: numpy dict with image_observed,
@@ -546,24 +548,29 @@ class RefineLoop(object):
         self.trans_gt.copy_(self.trans0)
         self.cur = 0
 
-    def _pose_update(self, it, nxt):
-        """pose[cur] (+ prediction) -> pose[nxt], new labels, KT; with the default stand-in the
-        prediction is made at the head of the same launch."""
+    def _pose_update(self, it, nxt, parts=3, stream=None):
+        """pose[cur] (+ prediction) -> pose[nxt] (parts & 1), new labels + KT (parts & 2).  With
+        the default stand-in the prediction is made at the head of the pose part's launch; the
+        labels part reads the prediction back from rot_est / trans_est."""
         out = (self.pose[nxt], self.rot_gt, self.trans_gt, self.KT)
         if self.predict is not None:
             self.predict(it, self.rot_gt, self.trans_gt)
             pose_update(self.pose[self.cur], self.rot_est, self.trans_est, self.obs["tgt_pose"],
                         self.K, out=out)
             return
+        standin = bool(parts & _lib.RC_POSE_PART_POSE)
         with torch.cuda.device(self.device):
             st = _lib.load().rc_pose_update_standin_dev(
-                self.pose[self.cur].data_ptr(), self.rot_gt.data_ptr(), self.trans_gt.data_ptr(),
-                self.noise_q[it % 8].data_ptr(), self.noise_t[it % 8].data_ptr(), self.damping,
+                self.pose[self.cur].data_ptr(),
+                self.rot_gt.data_ptr() if standin else None,
+                self.trans_gt.data_ptr() if standin else None,
+                self.noise_q[it % 8].data_ptr() if standin else None,
+                self.noise_t[it % 8].data_ptr() if standin else None, self.damping,
                 self.rot_est.data_ptr(), self.trans_est.data_ptr(), self.obs["tgt_pose"].data_ptr(),
                 C.device_const(self.K, self.device).data_ptr(), _lib.f3((0, 0, 0)),
                 _lib.f3((1, 1, 1)), _lib.ROT_COORD["camera"], out[0].data_ptr(),
-                out[1].data_ptr(), out[2].data_ptr(), out[3].data_ptr(), self.B,
-                _lib.stream_ptr(None))
+                out[1].data_ptr(), out[2].data_ptr(), out[3].data_ptr(), int(parts), self.B,
+                _lib.stream_ptr(stream))
         _lib.check(st, "rc_pose_update_standin_dev")
 
     def iterate(self, it, marks=None, render_marks=None):
@@ -573,16 +580,22 @@ class RefineLoop(object):
             # somebody else rendered through this renderer since our last frame: its item lists no
             # longer describe what the flow planes / zoomed outputs hold -> one dense step
             self._flow_tracks = False
-        self._pose_update(it, nxt)
         a = self.bound[nxt]
         # the flow / bbox / loss marks serialise the step (clean per-kernel times): one call, one
         # stream; the resampler's marks (2, 3) do not and go with the SAMPLE phase
         serial = marks is not None and any(marks[i] is not None for i in (0, 1, 4, 5))
         split = self.side is not None and not serial and bool(a.loss_sum or a.grad_rot)
+        # the rasteriser waits for the refined pose only: the new labels and KT (mat2quat's
+        # float64 eigen-solve, most of the pose kernel's latency) go to the side stream as well
+        split_pose = split and self.predict is None
+        self._pose_update(it, nxt, parts=_lib.RC_POSE_PART_POSE if split_pose else 3)
         if split:
             main = torch.cuda.current_stream(self.device)
             self._ev_fork.record(main)
             self.side.wait_event(self._ev_fork)
+            if split_pose:
+                self._pose_update(it, nxt, parts=_lib.RC_POSE_PART_LABELS, stream=self.side)
+                self._ev_labels.record(self.side)
             a.phases = _lib.RC_STEP_PHASE_LOSS
             self.step.run(None, args=a, stream=self.side)
         self.renderer.render_batch(self.cls, self.pose[nxt], pixel_means=self.render_means,
@@ -595,6 +608,8 @@ class RefineLoop(object):
         if self.sparse:
             a.outputs_track_frames = 1 if self._flow_tracks else 0
         if split:
+            if split_pose:
+                main.wait_event(self._ev_labels)  # KT (GT flow) and trans_gt (ZoomTrans)
             a.phases = _lib.RC_STEP_PHASE_FRAME
             self.step.run(None, args=a)
             self._ev_zf.record(main)
