@@ -58,10 +58,20 @@ int renderer_frame_items(void *handle, FrameItems *out);
 
 // frame.cu: rendered crop box (into workspace entries 4..7) and, with flow != NULL, GT flow on
 // the frame's tiles (+ zeros on the previous frame's stale tiles when zero_prev).
+// `final` (or NULL): what the pass's last block needs to turn the boxes into zoom factors
+// (+ ZoomTrans forward) itself instead of leaving that to launch_zoom_factor_boxes.
+struct FrameFinal {
+  const int32_t *observed_box;
+  const float *src_pose, *K;
+  float *zoom_factor;
+  int32_t *bbox;
+  const float *trans_in;
+  float *trans_out;
+};
 int launch_frame_tiles(const FrameItems &F, const float *depth_src, const float *depth_tgt,
                        const float *KT, const float *Kinv, float *flow, float *valid,
                        int32_t *workspace, int batch_size, int height, int width, bool zero_prev,
-                       void *stream);
+                       const FrameFinal *final, void *stream);
 
 // zoom.cu: rc_zoom_sample_dev with the compare step's sparse-frame information (or NULL).
 // One state byte per warp of an output tile (128 x 8 pixels, 4 warps of 32 columns):

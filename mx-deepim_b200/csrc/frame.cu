@@ -22,6 +22,7 @@
 
 #include "common.cuh"
 #include "flow_device.cuh"
+#include "zoom_finalize.cuh"
 
 namespace rc {
 
@@ -36,7 +37,7 @@ frame_tiles_kernel(FrameItems F, const float *__restrict__ depth_src,
                    const float *__restrict__ depth_tgt, const float *__restrict__ KT,
                    const float *__restrict__ Kinv, float *__restrict__ flow,
                    float *__restrict__ valid, int32_t *__restrict__ ws, int B, int H, int W,
-                   int zero_prev) {
+                   int zero_prev, FrameFinal fin) {
   pdl_launch_dependents();  // the zoom-factor kernel behind this one waits for the grid's end
   const int n_cur = *F.cur_count;
   const int n_prev = (DO_FLOW && zero_prev) ? *F.prev_count : 0;
@@ -107,12 +108,27 @@ frame_tiles_kernel(FrameItems F, const float *__restrict__ depth_src,
     }
   }
   pdl_wait();  // completion of this grid implies completion of the grid it was launched behind
+  if (fin.zoom_factor == nullptr) return;
+  // ---- the LAST block to finish turns the boxes into zoom factors (+ ZoomTrans) for every pair:
+  // one launch less on the iteration's chain of dependent kernels (was zoom_factor_boxes_kernel
+  // behind this one).  Ticket in the unused workspace entry 9 of pair 0; re-armed here.
+  __shared__ int s_last;
+  __threadfence();  // this block's box merges before its ticket
+  __syncthreads();
+  if (threadIdx.x == 0) s_last = atomicAdd(ws + 9, 1) == (int)gridDim.x - 1;
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  if (threadIdx.x == 0) ws[9] = 0;
+  for (int b = threadIdx.x; b < B; b += blockDim.x)
+    zoom_factor_from_boxes(b, fin.observed_box, ws, fin.src_pose, fin.K, fin.zoom_factor, fin.bbox,
+                           fin.trans_in, fin.trans_out, H, W);
 }
 
 int launch_frame_tiles(const FrameItems &F, const float *depth_src, const float *depth_tgt,
                        const float *KT, const float *Kinv, float *flow, float *valid,
                        int32_t *workspace, int batch_size, int height, int width, bool zero_prev,
-                       void *stream) {
+                       const FrameFinal *final, void *stream) {
   RC_REQUIRE(depth_src && workspace && F.cur_list && F.cur_count && F.tile_count,
              RC_ERR_INVALID_ARG);
   RC_REQUIRE(F.H == height && F.W == width && batch_size <= F.max_batch, RC_ERR_INVALID_ARG);
@@ -131,14 +147,20 @@ int launch_frame_tiles(const FrameItems &F, const float *depth_src, const float 
   if (blocks < 1) blocks = 1;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const int zp = zero_prev ? 1 : 0;
+  FrameFinal fin = {};
+  if (final) {
+    fin = *final;
+    RC_REQUIRE(fin.observed_box && fin.src_pose && fin.K && fin.zoom_factor, RC_ERR_INVALID_ARG);
+    RC_REQUIRE((fin.trans_in == nullptr) == (fin.trans_out == nullptr), RC_ERR_INVALID_ARG);
+  }
   if (do_flow)
     RC_CUDA_TRY(launch_maybe_pdl(frame_tiles_kernel<true>, dim3((unsigned)blocks), dim3(256), 0, s,
                                  tl_pdl, F, depth_src, depth_tgt, KT, Kinv, flow, valid,
-                                 workspace, batch_size, height, width, zp));
+                                 workspace, batch_size, height, width, zp, fin));
   else
     RC_CUDA_TRY(launch_maybe_pdl(frame_tiles_kernel<false>, dim3((unsigned)blocks), dim3(256), 0, s,
                                  tl_pdl, F, depth_src, depth_tgt, KT, Kinv, flow, valid,
-                                 workspace, batch_size, height, width, zp));
+                                 workspace, batch_size, height, width, zp, fin));
   return note_status(check_launch());
 }
 

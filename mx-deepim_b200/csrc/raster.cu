@@ -654,7 +654,6 @@ raster_fill_kernel(Renderer R, const int32_t *__restrict__ cls_idx, int n_tiles)
   int32_t *list = R.tile_list + (size_t)b * R.list_cap;
   const int n_bin = R.bin_n[b];
   const int32_t *bin = R.bin_tri + (size_t)b * R.max_tris;
-  // whole warps run every trip (for_each_tile / tile_atomic use full-mask warp primitives)
   for (int base = blockIdx.x * blockDim.x; base < n_bin; base += gridDim.x * blockDim.x) {
     const int i = base + threadIdx.x;
     int t = 0;
@@ -663,13 +662,30 @@ raster_fill_kernel(Renderer R, const int32_t *__restrict__ cls_idx, int n_tiles)
       t = bin[i];
       tb = R.tbox[(size_t)b * R.max_tris + t];
     }
-    for_each_tile(tb, R.tiles_x, [&](int key) {
-      const int slot = tile_atomic(fill, key, true);
-      if (key >= 0) {
-        const int pos = start[key] + slot;
-        if (pos < R.list_cap) list[pos] = 2 * t;
+    // Each lane walks its own tile box, four tiles per round: the four slot atomics (and the
+    // four loads of the tiles' starts) are in flight together.  The warp-aggregated variant
+    // (tile_atomic) needs each atomic's result for a shuffle before the next tile can be
+    // started -- with ~360 listed triangles per pair there is no contention to aggregate away,
+    // only a chain of L2 round trips (17 us at 128 pairs for a few microseconds of work).
+    const int tx0 = tb & 255, ty0 = (tb >> 8) & 255, tx1 = (tb >> 16) & 255, ty1 = tb >> 24;
+    const int nx = tx1 - tx0 + 1;  // <= 0 for RT_TBOX_NONE
+    const int n_mine = nx > 0 ? nx * (ty1 - ty0 + 1) : 0;
+    for (int i0 = 0; i0 < n_mine; i0 += 4) {
+      int key[4], slot[4], first[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int i = i0 + j;
+        key[j] = i < n_mine ? (ty0 + i / nx) * R.tiles_x + tx0 + i % nx : -1;
       }
-    });
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        slot[j] = key[j] >= 0 ? atomicAdd(fill + key[j], 1) : 0;
+        first[j] = key[j] >= 0 ? start[key[j]] : 0;
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (key[j] >= 0 && first[j] + slot[j] < R.list_cap) list[first[j] + slot[j]] = 2 * t;
+    }
   }
   const int n_clip = R.work_count[RT_WC_CLIP];
   const int gid = (blockIdx.y * gridDim.x + blockIdx.x) * blockDim.x + threadIdx.x;

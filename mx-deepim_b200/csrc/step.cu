@@ -87,10 +87,13 @@ int rc_compare_step_dev(const rc_compare_step_args *a) {
     return rc_flow_dev(a->depth_rendered, a->depth_gt_observed, a->KT, a->Kinv, a->flow, a->valid,
                        B, H, W, a->stream);
   };
-  auto tiles = [&]() -> int {  // rendered box (+ flow) over the frame's tiles
+  auto tiles = [&](bool with_boxes) -> int {  // rendered box (+ flow) over the frame's tiles
+    rc::FrameFinal fin = {a->observed_box, a->src_pose, a->K, a->zoom_factor, a->bbox,
+                          zt ? a->trans_gt : nullptr, zt ? a->zoom_trans_gt : nullptr};
     return rc::launch_frame_tiles(F, a->depth_rendered, a->depth_gt_observed, a->KT, a->Kinv,
                                   flow_tiles ? a->flow : nullptr, flow_tiles ? a->valid : nullptr,
-                                  a->workspace, B, H, W, flow_tiles, a->stream);
+                                  a->workspace, B, H, W, flow_tiles, with_boxes ? &fin : nullptr,
+                                  a->stream);
   };
   auto boxes = [&]() -> int {  // zoom factor (+ ZoomTrans) from the two boxes
     return rc::launch_zoom_factor_boxes(a->observed_box, a->src_pose, a->K, a->zoom_factor,
@@ -132,11 +135,16 @@ int rc_compare_step_dev(const rc_compare_step_args *a) {
         if ((st = dense_flow()) != RC_OK) return st;
         first = false;
       }
+      // small batches: the tile pass's last block also turns the boxes into zoom factors
+      // (+ ZoomTrans) -- one launch less on a chain that is pure latency there (32 pairs: 200 ->
+      // 195 us per iteration).  Larger batches keep the separate one-thread-per-pair kernel: a
+      // single block working through 1024 pairs costs more (15 us) than that launch (5 us).
+      const bool fused_boxes = B <= 64;
       {
         PdlScope scope(!first);
-        if ((st = tiles()) != RC_OK) return st;
+        if ((st = tiles(fused_boxes)) != RC_OK) return st;
       }
-      {
+      if (!fused_boxes) {
         PdlScope scope(true);
         if ((st = boxes()) != RC_OK) return st;
       }
@@ -144,7 +152,7 @@ int rc_compare_step_dev(const rc_compare_step_args *a) {
   } else {
     if ((st = rc::mark(a->marks, 0, s)) != RC_OK) return st;
     if (ph_frame && do_flow && !flow_tiles && (st = dense_flow()) != RC_OK) return st;
-    if (ph_frame && sparse && (st = tiles()) != RC_OK) return st;
+    if (ph_frame && sparse && (st = tiles(false)) != RC_OK) return st;
     if ((st = rc::mark(a->marks, 1, s)) != RC_OK) return st;
     if (ph_frame && (st = sparse ? boxes() : bbox()) != RC_OK) return st;
   }

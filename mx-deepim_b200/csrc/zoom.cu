@@ -25,6 +25,7 @@
 #include <stdlib.h>
 
 #include "common.cuh"
+#include "zoom_finalize.cuh"
 
 namespace rc {
 
@@ -49,62 +50,7 @@ __device__ __forceinline__ float comp(const float4 &v, int k) {
   return k == 0 ? v.x : (k == 1 ? v.y : (k == 2 ? v.z : v.w));
 }
 
-// workspace layout per sample (int32 x 10):
-//   [0..3] obs x0,x1,y0,y1   [4..7] rend x0,x1,y0,y1   [8] ticket  [9] unused
-// Entries are kept in an all-zero-when-idle encoding so that no init launch is needed:
-// minima are stored as INT_MAX - x and maxima as x + 1, both merged with atomicMax
-// (0 = empty set); the finalising block reads them with atomicExch(.., 0), which leaves
-// the workspace zeroed for the next call.
-#define RC_ZF_WS_STRIDE RC_ZF_WS_INTS
-
-// Zoom factor from the two boxes; float64 scalar arithmetic as numpy 1.x
-// evaluates zoom_mask.py:63-105 (np.float32 scalar op Python/int64 scalar ->
-// float64), stored as float32 (:116-119).
-__device__ void zoom_factor_finalize(const int32_t *w, const float *__restrict__ src_pose,
-                                     const float *__restrict__ K, float *__restrict__ zf,
-                                     int32_t *__restrict__ bbox, int H, int W) {
-  const int ox0 = w[0], ox1 = w[1], oy0 = w[2], oy1 = w[3];
-  int rx0 = w[4], rx1 = w[5], ry0 = w[6], ry1 = w[7];
-  if (bbox) {
-#pragma unroll
-    for (int k = 0; k < 8; ++k) bbox[k] = w[k];
-  }
-  if (ox1 < 0) {  // observed set empty: the reference raises (np.min of empty), zoom_mask.py:59
-    const float nanv = __int_as_float(0x7fc00000);
-    zf[0] = zf[1] = zf[2] = zf[3] = nanv;
-    return;
-  }
-  // np.dot(K, src_pose[:, 3]) in float32 (zoom_mask.py:72)
-  const float t0 = src_pose[3], t1 = src_pose[7], t2 = src_pose[11];
-  const float c0 = __fadd_rn(__fadd_rn(__fmul_rn(K[0], t0), __fmul_rn(K[1], t1)), __fmul_rn(K[2], t2));
-  const float c1 = __fadd_rn(__fadd_rn(__fmul_rn(K[3], t0), __fmul_rn(K[4], t1)), __fmul_rn(K[5], t2));
-  const float c2 = __fadd_rn(__fadd_rn(__fmul_rn(K[6], t0), __fmul_rn(K[7], t1)), __fmul_rn(K[8], t2));
-  double zcx, zcy;
-  if (rx1 < 0) {  // "NO POINT VALID IN MASK rendered" fallback, zoom_mask.py:74-81
-    rx0 = ox0;
-    rx1 = ox1;
-    ry0 = oy0;
-    ry1 = oy1;
-    zcx = (double)(ox0 + ox1) * 0.5;
-    zcy = (double)(oy0 + oy1) * 0.5;
-  } else {
-    zcx = (double)__fdiv_rn(c0, c2);  // :73
-    zcy = (double)__fdiv_rn(c1, c2);
-  }
-  const double left = fmax(zcx - rx0, zcx - ox0);
-  const double right = fmax(rx1 - zcx, ox1 - zcx);
-  const double up = fmax(zcy - ry0, zcy - oy0);
-  const double down = fmax(oy1 - zcy, ry1 - zcy);
-  const double m = fmax(fmax(__dmul_rn(0.75, right), __dmul_rn(0.75, left)), fmax(up, down));
-  const double crop_h = __dmul_rn(__dmul_rn(m, 1.4), 2.0);  // :96-100
-  const double wx = crop_h / (double)H;                     // :102-103 (both / height)
-  const double tx = __dadd_rn(__dmul_rn(zcx / (double)W, 2.0), -1.0);  // :104
-  const double ty = __dadd_rn(__dmul_rn(zcy / (double)H, 2.0), -1.0);  // :105
-  zf[0] = (float)wx;
-  zf[1] = (float)wx;
-  zf[2] = (float)tx;
-  zf[3] = (float)ty;
-}
+// (workspace layout and zoom_factor_finalize: zoom_finalize.cuh, shared with frame.cu)
 
 // grid = (blocks_per_sample, B), block = 256.
 // ONE: single-channel inputs (the mask configuration): no per-pixel channel sums to carry.
@@ -1333,23 +1279,8 @@ zoom_factor_boxes_kernel(const int32_t *__restrict__ observed_box, int32_t *__re
   pdl_launch_dependents();
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= B) return;
-  int32_t *w = ws + b * RC_ZF_WS_STRIDE;
-  int32_t fin[8];
-#pragma unroll
-  for (int k = 0; k < 4; ++k) fin[k] = observed_box[b * 4 + k];
-#pragma unroll
-  for (int k = 4; k < 8; ++k) {
-    const int e = atomicExch(w + k, 0);
-    fin[k] = (k & 1) ? e - 1 : INT_MAX - e;
-  }
-  zoom_factor_finalize(fin, src_pose + b * 12, K, zoom_factor + b * 4,
-                       bbox ? bbox + b * 8 : nullptr, H, W);
-  if (trans_out) {  // fused ZoomTrans forward (zoom_trans.py:30-44)
-    const float wx = zoom_factor[b * 4];
-    trans_out[b * 3 + 0] = __fdiv_rn(trans_in[b * 3 + 0], wx);
-    trans_out[b * 3 + 1] = __fdiv_rn(trans_in[b * 3 + 1], wx);
-    trans_out[b * 3 + 2] = trans_in[b * 3 + 2];
-  }
+  zoom_factor_from_boxes(b, observed_box, ws, src_pose, K, zoom_factor, bbox, trans_in, trans_out, H,
+                         W);
 }
 
 int launch_zoom_factor_boxes(const int32_t *observed_box, const float *src_pose, const float *K,

@@ -500,8 +500,10 @@ class RefineLoop(object):
         # pose update (+ fused stand-in) + 7 render kernels (clear, vertex, setup, scan, fill,
         # cover, resolve) + step
         # (with the side stream the pose update is two launches: pose | labels + KT)
+        # (sparse, small batches: the frame pass's last block computes the zoom factors -- one
+        # launch less than CompareStep counts)
         self.launches_per_iteration = (2 if (side_stream or predict is not None) else 1) + 7 + \
-            self.step.launches_per_step
+            self.step.launches_per_step - (1 if (sparse and batch <= 64) else 0)
 
     def set_batch(self, host):
         """Observed side of the batch + initial poses.  `host`: numpy dict with image_observed,
