@@ -562,8 +562,11 @@ def run_loop(args, rank, world, local_rank):
         torch.cuda.synchronize()
         t1 = time.time()
         barrier()
-        return shard.reduce_max(e0.elapsed_ms(e1), dev), (t0, t1)
+        own = e0.elapsed_ms(e1)
+        per_rank[:] = shard.gather_scalar(own, dev)
+        return shard.reduce_max(own, dev), (t0, t1)
 
+    per_rank = []                               # each rank's own device time of the last block
     ms_block, _ = block(1)                      # one K-step block: the burst figure
     repeats = max(1, int(math.ceil(args.min_seconds * 1e3 / max(ms_block, 1e-3))))
     if world > 1:  # every rank must agree on the repeat count
@@ -673,6 +676,7 @@ def run_loop(args, rank, world, local_rank):
             "warmup": Wm, "ms_per_step": ms_per_step, "higher_is_better": True,
             "scaling": cfg["scaling"], "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "repeats": repeats, "timed_ms": ms_total,
+            "per_rank_ms_per_step": [t / steps_timed for t in per_rank],
             "burst": {"value": burst, "ms_per_step": ms_block / K, "steps": K},
             "config": config_dict(args.config, world),
             "run": {"issue": issue, "batch_per_gpu": B,

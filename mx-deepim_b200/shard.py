@@ -34,6 +34,17 @@ def reduce_max(value: float, device=None) -> float:
     return float(t.item())
 
 
+def gather_scalar(value: float, device=None):
+    """The host scalar of every rank, in rank order (e.g. each rank's own device time, so that
+    the spread behind a max-over-ranks figure is visible)."""
+    if not _is_dist():
+        return [float(value)]
+    t = torch.tensor([float(value)], dtype=torch.float64, device=device)
+    out = [torch.empty_like(t) for _ in range(dist.get_world_size())]
+    dist.all_gather(out, t)
+    return [float(o.item()) for o in out]
+
+
 def allreduce_metric(loss_sum: torch.Tensor, count: int):
     """Sum over ranks of (sum of the per-pair loss sums, number of samples): the
     PointMatchingLossMetric numerator / denominator.  8-16 bytes, latency bound."""

@@ -16,6 +16,8 @@ def _worker(rank, world, port, q):
     lo, hi = shard.partition(257, world, rank)
     mx = shard.reduce_max(10.0 + rank)
     s, n = shard.allreduce_metric(torch.tensor([1.0 + rank, 2.0]), hi - lo)
+    every = shard.gather_scalar(2.5 * (rank + 1))
+    assert every == [2.5, 5.0], every  # each rank's own value, in rank order
     q.put((rank, lo, hi, mx, s, n, shard.rank_seed(100, rank, 2)))
     dist.barrier()
     dist.destroy_process_group()
@@ -32,6 +34,7 @@ def test_partition_covers_batch():
             sizes = [hi - lo for lo, hi in spans]
             assert max(sizes) - min(sizes) <= 1
     assert shard.reduce_max(3.5) == 3.5  # no process group: identity
+    assert shard.gather_scalar(3.5) == [3.5]
 
 
 def test_gloo_world_size_2():
